@@ -1,0 +1,205 @@
+/*
+ * flowcuda.h — C ABI of libflowcuda.so: the B200 (sm_100a) implementation of the
+ * normalizing-flow density-evaluation / sampling / training hot path of
+ * kaijennissen/Normalizing_Flows.
+ *
+ * This is the drop-in boundary.  The reference has no FFI of its own
+ * (it is pure Python on JAX); each entry point below replaces the XLA computation that
+ * the cited reference function compiles to, and is what a `jax.ffi` / ctypes binding
+ * on the reference side would bind.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the parameter name ends in `_host`;
+ *   - `stream` is a `cudaStream_t` passed as `void*`; all work is enqueued on it, the
+ *     library never synchronises, allocates, frees or retains pointers
+ *     (exception: the `*_host` convenience entry points, which own their staging buffers);
+ *   - arrays are dense row-major float32 unless stated; sample index is the slowest axis;
+ *   - return value: 0 on success, negative `FLOWCUDA_E*` on error; the message is
+ *     available (thread-local) from `flowcuda_last_error()`; no C++ exception crosses;
+ *   - citations `file:line` are into the reference repository.
+ */
+#ifndef FLOWCUDA_H_
+#define FLOWCUDA_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FLOWCUDA_VERSION 100 /* 0.1.0 */
+
+#define FLOWCUDA_OK 0
+#define FLOWCUDA_EINVAL (-1)    /* bad argument (shape, enum, alignment, NULL) */
+#define FLOWCUDA_ECUDA (-2)     /* a CUDA runtime call failed */
+#define FLOWCUDA_EWORKSPACE (-3)/* workspace too small */
+#define FLOWCUDA_EUNSUPPORTED (-4)
+
+int flowcuda_version(void);
+const char* flowcuda_last_error(void);
+/* Number of SMs of the current device (grid sizing is done in multiples of it). */
+int flowcuda_sm_count(void);
+
+/* ------------------------------------------------------------------------------------
+ * Row #1 — hand-rolled Real NVP (src/real_nvp.py), event dim D = 2, split d = 1.
+ *
+ * `params`: n_layers * (4*hidden + 2) floats; per layer W1[1,hidden], b1[hidden],
+ * W2[hidden,2] (row-major; column 0 = shift, column 1 = log_scale), b2[2]
+ * — the reference's params[layer] = [[W1,b1],[W2,b2]] flattened (real_nvp.py:188-195).
+ * `flip_mask`: bit l set <=> layer l is built with flip=True (real_nvp.py:209-218).
+ * Conditioner: leaky_relu(0.01) MLP on the pass-through half (real_nvp.py:161-171).
+ * n_layers <= 64, 1 <= hidden <= 32.
+ * ---------------------------------------------------------------------------------- */
+
+/* log_prob_nvp_chains(params, fns_config, log_prob_N01, y) (real_nvp.py:268-283):
+ * the LAST layer's inverse is applied to the data first; base = N(0, I_2)
+ * (real_nvp.py:57-68).  y[N,2] -> log_prob[N].
+ * Optional outputs (may be NULL): z[N,2] = the base-space point. */
+int flowcuda_realnvp_log_prob(const float* params, int n_layers, int hidden, uint64_t flip_mask,
+                              const float* y, float* log_prob, float* z, int64_t n, void* stream);
+
+/* sample_nvp_chain with the base noise given (real_nvp.py:228-248): layer 0's
+ * forward_nvp first ... layer L-1 last.  z[N,2] -> x[N,2]. */
+int flowcuda_realnvp_sample(const float* params, int n_layers, int hidden, uint64_t flip_mask,
+                            const float* z, float* x, int64_t n, void* stream);
+
+/* forward_nvp (real_nvp.py:71-101): one layer, x[N,2] -> y[N,2]. `layer_params` = that
+ * layer's 4*hidden+2 floats. */
+int flowcuda_realnvp_forward(const float* layer_params, int hidden, int flip,
+                             const float* x, float* y, int64_t n, void* stream);
+
+/* inverse_nvp (real_nvp.py:104-134): one layer, y[N,2] -> x[N,2], log_scale[N] (the
+ * reference returns log_scale as [N,1]; same memory). */
+int flowcuda_realnvp_inverse(const float* layer_params, int hidden, int flip,
+                             const float* y, float* x, float* log_scale, int64_t n, void* stream);
+
+/* value_and_grad of loss = -mean(log_prob_nvp_chains(...)) (real_nvp.py:292-297).
+ * Deterministic two-stage reduction: per-block partials are written to `workspace`
+ * (size from flowcuda_realnvp_nll_grad_workspace_bytes) and summed in a fixed order in
+ * double precision.  loss[1], grad[n_layers*(4*hidden+2)] (same layout as params).
+ * If lr != 0 the SGD update p <- p - lr*g (real_nvp.py:298) is fused into the second
+ * stage and written to `params_out` (may alias params). */
+size_t flowcuda_realnvp_nll_grad_workspace_bytes(int n_layers, int hidden, int64_t n);
+int flowcuda_realnvp_nll_grad(const float* params, int n_layers, int hidden, uint64_t flip_mask,
+                              const float* y, int64_t n, float* loss, float* grad,
+                              float lr, float* params_out,
+                              void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Row #5 — BernsteinBijector (src/BernsteinBijector.py).  2 <= order M <= 64.
+ * ---------------------------------------------------------------------------------- */
+
+/* constrain_thetas (BernsteinBijector.py:60-71): theta_raw[rows,M] -> theta[rows,M]:
+ * theta_0 = raw_0, theta_k = theta_{k-1} + softplus(raw_k) + 1e-4. */
+int flowcuda_bernstein_constrain_thetas(const float* theta_raw, float* theta, int64_t rows, int order,
+                                        void* stream);
+
+/* forward_and_log_det (BernsteinBijector.py:81-93,113-117) on CONSTRAINED thetas:
+ *   xc = clip(x, 1e-7, 1-1e-7);  y = mean_k Beta(k, M-k+1).pdf(xc) * theta_k;
+ *   log_det = log(sum_k Beta(k, M-k).pdf(xc) * (theta_{k+1}-theta_k)).
+ * theta_stride = 0: one theta[M] shared by every element (bflow.py:24);
+ * theta_stride = M: theta[n,M], one row per element (maf_mwe.py:103-107).
+ * y or log_det may be NULL (forward / forward_log_det_jacobian alone). */
+int flowcuda_bernstein_forward_and_log_det(const float* theta, int order, int64_t theta_stride,
+                                           const float* x, float* y, float* log_det, int64_t n,
+                                           void* stream);
+
+/* inverse (BernsteinBijector.py:95-111): 200-point grid of forward() on
+ * linspace(1e-7, 1-1e-7) per event column e, then linear interpolation (jnp.interp,
+ * clamped).  theta[E,M] constrained, y[N,E] row-major -> x[E,N] (vmap(in_axes=-1)
+ * stacks on axis 0: the reference's transposed output).  The log-det the reference
+ * returns for this direction is the constant 0 (BernsteinBijector.py:119-123).
+ * workspace: E*n_points floats (n_points = 200 in the reference). */
+int flowcuda_bernstein_inverse(const float* theta, int order, int64_t n_events, int n_points,
+                               const float* y, float* x, int64_t n, float* workspace, void* stream);
+
+/* Transformed(Normal(0,1), Inverse(Chain([T4,T3,T2,T1]))).log_prob(x) of the Bernstein
+ * flow demo (bflow.py:28-34,82-88), fused in one pass:
+ *   T1: v = softplus(a)*(x+b);  T2: tfb.SoftClip(0,1,hinge_softness=1.5);
+ *   T3: BernsteinBijector(theta) (theta as passed: already constrained as the caller
+ *       wants it — the demo double-constrains);
+ *   T4: v = softplus(alpha)*(v+beta);  base Normal(0,1).
+ * scal[4] = {a, b, alpha, beta} (device). x[n] -> log_prob[n]. */
+int flowcuda_bernstein_flow_log_prob(const float* theta, int order, const float* scal,
+                                     const float* x, float* log_prob, int64_t n, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Rows #2, #3, #4, #6 — distrax MaskedCoupling flows
+ * (src/real_nvp_toy_densities.py:56-110, src/maf_toy_densities.py:55-111,
+ *  src/maf_mnist.py:34-89).
+ * ---------------------------------------------------------------------------------- */
+
+#define FLOWCUDA_TRANSFORM_AFFINE_SCALAR 0 /* ScalarAffine, (shift,log_scale)[N,1] broadcast over D
+                                              (real_nvp_toy_densities.py:84-86) */
+#define FLOWCUDA_TRANSFORM_AFFINE 1        /* per-dimension (shift,log_scale): cond out [N,D,2] */
+#define FLOWCUDA_TRANSFORM_RQS 2           /* RationalQuadraticSpline, cond out [N,D,3K+1]
+                                              (maf_toy_densities.py:84-87, maf_mnist.py:63-66) */
+#define FLOWCUDA_BASE_NORMAL 0             /* Independent(Normal(0,1)) */
+#define FLOWCUDA_BASE_UNIFORM01 1          /* Independent(Uniform(0,1)) (maf_mnist.py:85-88) */
+#define FLOWCUDA_MAX_HIDDEN_LAYERS 4
+
+#define FLOWCUDA_PRECISION_FP32 0   /* CUDA-core FP32 FMA conditioner */
+#define FLOWCUDA_PRECISION_3XTF32 1 /* tcgen05 kind::tf32, error-compensated 3-pass split */
+#define FLOWCUDA_PRECISION_TF32 2   /* tcgen05 kind::tf32 single pass */
+
+typedef struct flowcuda_coupling_spec {
+  int32_t event_dim;   /* D: flattened event size (2, or 784 for [28,28,1]) */
+  int32_t num_layers;  /* flow layers L */
+  int32_t num_hidden;  /* hidden Linear layers of the conditioner MLP (relu, activate_final) */
+  int32_t hidden[FLOWCUDA_MAX_HIDDEN_LAYERS];
+  int32_t transform;   /* FLOWCUDA_TRANSFORM_* */
+  int32_t num_bins;    /* K (RQS only) */
+  float range_min;     /* RQS only */
+  float range_max;
+  int32_t base;        /* FLOWCUDA_BASE_* */
+  int32_t precision;   /* FLOWCUDA_PRECISION_* */
+} flowcuda_coupling_spec;
+
+/* Parameter layout (`params`): for each flow layer l = 0..L-1, for each Linear of the
+ * conditioner in order (hidden..., final): W[in,out] row-major then b[out] — haiku's
+ * `w`,`b` of mlp/~/linear_i and linear.  Layer l's mask is
+ * (arange(D) % 2 == 1) for even l and its negation for odd l
+ * (real_nvp_toy_densities.py:80-82,102); mask True = passed through and visible. */
+int64_t flowcuda_coupling_param_count(const flowcuda_coupling_spec* spec);
+size_t flowcuda_coupling_workspace_bytes(const flowcuda_coupling_spec* spec, int64_t n);
+
+/* distrax.Transformed.log_prob: x[N,D] -> log_prob[N]; applies layer L-1's forward first
+ * ... layer 0 last (Inverse(Chain(layers)), real_nvp_toy_densities.py:104), adds the base
+ * log-density.  z (optional) receives the base-space point, log_det (optional) the
+ * summed log-det. `layer_begin/layer_end` select a sub-chain (0, L for the full flow). */
+int flowcuda_coupling_log_prob(const flowcuda_coupling_spec* spec, const float* params,
+                               const float* x, float* log_prob, float* z, float* log_det, int64_t n,
+                               int layer_begin, int layer_end, int with_base,
+                               void* workspace, size_t workspace_bytes, void* stream);
+
+/* distrax.Transformed.sample with the base noise given: z[N,D] -> x[N,D]; layer 0's
+ * inverse first ... layer L-1 last (real_nvp_toy_densities.py:126-136).  log_det
+ * (optional) receives the summed inverse log-det. */
+int flowcuda_coupling_sample(const flowcuda_coupling_spec* spec, const float* params,
+                             const float* z, float* x, float* log_det, int64_t n,
+                             int layer_begin, int layer_end,
+                             void* workspace, size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------------------
+ * Rows #7, #9 — loss reduction and optimiser steps.
+ * ---------------------------------------------------------------------------------- */
+
+/* out[0] = -mean(log_prob[0..n)) scaled: out = scale * sum(log_prob), deterministic
+ * (fixed-order two-stage, double accumulation). workspace: 1024 doubles. */
+int flowcuda_sum_scaled(const float* v, int64_t n, double scale, float* out, void* workspace,
+                        void* stream);
+
+/* p <- p - lr*g (real_nvp.py:298). */
+int flowcuda_sgd_step(float* p, const float* g, int64_t count, float lr, float grad_scale, void* stream);
+
+/* optax.adam(lr) + apply_updates (real_nvp_toy_densities.py:162,171-172): b1,b2,eps as
+ * given; step is 1-based; grad_scale multiplies g first (1/world_size after a sum
+ * all-reduce). */
+int flowcuda_adam_step(float* p, const float* g, float* m, float* v, int64_t count, int64_t step,
+                       float lr, float b1, float b2, float eps, float grad_scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FLOWCUDA_H_ */

@@ -1,0 +1,300 @@
+// bernstein.cu — row #5: BernsteinBijector (src/BernsteinBijector.py) and the fused Bernstein
+// flow density of src/bflow.py.
+//
+// The reference evaluates  y = mean_k Beta(k, M-k+1).pdf(x)·θ_k  and
+// J = Σ_k Beta(k, M-k).pdf(x)·(θ_{k+1}-θ_k)  by materialising [N, M] Beta-pdf temporaries.
+// With integer Beta parameters these are Bernstein forms of degree n=M-1 and n-1
+// (SURVEY §4 K5):   y = Σ_j θ_j C(n,j) u^j v^(n-j),   J = n Σ_j Δθ_j C(n-1,j) u^j v^(n-1-j),
+// u = clip(x), v = 1-u.  Both are evaluated in one pass with the uniform-coefficient
+// recurrence  r <- r·v + c_j·u^j  (stable on the whole of [0,1]; all lanes read the same
+// coefficient), on the packed fp32x2 pipe: 5 packed ops per coefficient per two elements.
+// HBM traffic: x in, (y, log_det) out — nothing else.
+#include "common.cuh"
+
+namespace flowcuda {
+
+constexpr int kBernThreads = 256;
+constexpr int kBernMaxOrder = 64;
+
+__device__ __forceinline__ float bern_clip(float x) {
+  // jnp.clip(x, 1e-7, 1 - 1e-7) in float32: the upper bound rounds to 1 - 2^-23
+  return fminf(fmaxf(x, 1e-7f), 0.99999988079071044921875f);
+}
+
+// Coefficient tables for a shared theta: tab[j] = {a_j, a_j, d_j, d_j},
+// a_j = θ_j C(n,j) (j<=n), d_j = n (θ_{j+1}-θ_j) C(n-1,j) (j<=n-1; d_n = 0).
+__device__ void bern_build_table(float4* tab, const float* __restrict__ theta, int M) {
+  if (threadIdx.x == 0) {
+    const int n = M - 1;
+    double ca = 1.0, cd = 1.0;  // C(n,j), C(n-1,j)
+    for (int j = 0; j <= n; ++j) {
+      float a = (float)((double)theta[j] * ca);
+      float d = 0.f;
+      if (j < n) d = (float)((double)n * ((double)theta[j + 1] - (double)theta[j]) * cd);
+      tab[j] = make_float4(a, a, d, d);
+      ca = ca * (double)(n - j) / (double)(j + 1);
+      if (j < n - 1) cd = cd * (double)(n - 1 - j) / (double)(j + 1);
+    }
+  }
+  __syncthreads();
+}
+
+// Evaluate (y, J) for two clipped elements u = {uA, uB}.
+__device__ __forceinline__ void bern_eval_pair(const float4* __restrict__ tab, int n, float2 u, float2& y, float2& J) {
+  float2 v = make_float2(1.f - u.x, 1.f - u.y);
+  float4 c0 = tab[0];
+  y = make_float2(c0.x, c0.y);
+  J = make_float2(c0.z, c0.w);
+  float2 pw = u;
+#pragma unroll 4
+  for (int j = 1; j < n; ++j) {
+    float4 c = tab[j];
+    y = ffma2(y, v, fmul2(make_float2(c.x, c.y), pw));
+    J = ffma2(J, v, fmul2(make_float2(c.z, c.w), pw));
+    pw = fmul2(pw, u);
+  }
+  // last coefficient: only y has a degree-n term
+  float4 c = tab[n];
+  y = ffma2(y, v, fmul2(make_float2(c.x, c.y), pw));
+}
+
+// tfb.SoftClip(0, 1, hinge_softness=c) forward and log-det (bflow.py:29).
+__device__ __forceinline__ void softclip01(float x, float c, float k, float logk, float& y, float& ld) {
+  float inv_c = 1.f / c;
+  float spx = c * softplus_f(x * inv_c);
+  float u = 1.f - spx;
+  y = 1.f - k * (c * softplus_f(u * inv_c));
+  ld = logk - softplus_f(-u * inv_c) - softplus_f(-x * inv_c);
+}
+
+// MODE 0: forward_and_log_det (y, ld);  MODE 1: fused bflow log_prob.
+template <int MODE>
+__global__ void __launch_bounds__(kBernThreads)
+bern_shared_kernel(const float* __restrict__ theta, int M, const float* __restrict__ scal,
+                   const float* __restrict__ x, float* __restrict__ out_y, float* __restrict__ out_ld, int64_t n) {
+  __shared__ float4 tab[kBernMaxOrder];
+  bern_build_table(tab, theta, M);
+  const int deg = M - 1;
+  float s1 = 1.f, b1 = 0.f, s4 = 1.f, b4 = 0.f, lconst = 0.f, kk = 1.f, logk = 0.f;
+  if (MODE == 1) {
+    // T1 = Chain([Scale(softplus(a)), Shift(b)]): v = softplus(a)·(x + b)  (bflow.py:28)
+    s1 = softplus_f(scal[0]);
+    b1 = scal[1];
+    s4 = softplus_f(scal[2]);
+    b4 = scal[3];
+    kk = 1.f / (1.5f * softplus_f(1.f / 1.5f));
+    logk = logf(kk);
+    lconst = logf(s1) + logf(s4) - kHalfLog2Pi;
+  }
+  const int64_t nquads = n >> 2;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < nquads; q += stride) {
+    float4 xv = ld_stream_f4(reinterpret_cast<const float4*>(x) + q);
+    float xs[4] = {xv.x, xv.y, xv.z, xv.w};
+    float pre_ld[4] = {0.f, 0.f, 0.f, 0.f};
+    if (MODE == 1) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        float t = s1 * (xs[i] + b1);
+        softclip01(t, 1.5f, kk, logk, xs[i], pre_ld[i]);
+      }
+    }
+    float2 y01, J01, y23, J23;
+    bern_eval_pair(tab, deg, make_float2(bern_clip(xs[0]), bern_clip(xs[1])), y01, J01);
+    bern_eval_pair(tab, deg, make_float2(bern_clip(xs[2]), bern_clip(xs[3])), y23, J23);
+    float ys[4] = {y01.x, y01.y, y23.x, y23.y};
+    float ld[4] = {logf(J01.x), logf(J01.y), logf(J23.x), logf(J23.y)};
+    if (MODE == 0) {
+      if (out_y) st_stream_f4(reinterpret_cast<float4*>(out_y) + q, make_float4(ys[0], ys[1], ys[2], ys[3]));
+      if (out_ld) st_stream_f4(reinterpret_cast<float4*>(out_ld) + q, make_float4(ld[0], ld[1], ld[2], ld[3]));
+    } else {
+      float lp[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        float z = s4 * (ys[i] + b4);  // T4 (bflow.py:31-32)
+        lp[i] = fmaf(-0.5f * z, z, lconst + pre_ld[i] + ld[i]);
+      }
+      st_stream_f4(reinterpret_cast<float4*>(out_ld) + q, make_float4(lp[0], lp[1], lp[2], lp[3]));
+    }
+  }
+  // tail (n % 4 elements)
+  int64_t t = (nquads << 2) + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n) {
+    float xi = x[t], pl = 0.f;
+    if (MODE == 1) softclip01(s1 * (xi + b1), 1.5f, kk, logk, xi, pl);
+    float2 y, J;
+    bern_eval_pair(tab, deg, splat2(bern_clip(xi)), y, J);
+    if (MODE == 0) {
+      if (out_y) out_y[t] = y.x;
+      if (out_ld) out_ld[t] = logf(J.x);
+    } else {
+      float z = s4 * (y.x + b4);
+      out_ld[t] = fmaf(-0.5f * z, z, lconst + pl + logf(J.x));
+    }
+  }
+}
+
+// Per-element theta rows (maf_mwe.py:103-107): theta[n, M], x[n].  Binomials are uniform.
+__global__ void __launch_bounds__(kBernThreads)
+bern_rows_kernel(const float* __restrict__ theta, int M, int64_t theta_stride, const float* __restrict__ x,
+                 float* __restrict__ out_y, float* __restrict__ out_ld, int64_t n) {
+  __shared__ float binA[kBernMaxOrder], binD[kBernMaxOrder];
+  const int deg = M - 1;
+  if (threadIdx.x == 0) {
+    double ca = 1.0, cd = 1.0;
+    for (int j = 0; j <= deg; ++j) {
+      binA[j] = (float)ca;
+      binD[j] = j < deg ? (float)((double)deg * cd) : 0.f;
+      ca = ca * (double)(deg - j) / (double)(j + 1);
+      if (j < deg - 1) cd = cd * (double)(deg - 1 - j) / (double)(j + 1);
+    }
+  }
+  __syncthreads();
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const float* th = theta + i * theta_stride;
+    float u = bern_clip(x[i]), v = 1.f - u;
+    float t0 = th[0], t1 = th[1];
+    float y = t0 * binA[0], J = (t1 - t0) * binD[0], pw = u;
+    for (int j = 1; j < deg; ++j) {
+      t0 = t1;
+      t1 = th[j + 1];
+      y = fmaf(y, v, t0 * binA[j] * pw);
+      J = fmaf(J, v, (t1 - t0) * binD[j] * pw);
+      pw *= u;
+    }
+    y = fmaf(y, v, t1 * binA[deg] * pw);
+    if (out_y) out_y[i] = y;
+    if (out_ld) out_ld[i] = logf(J);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+bern_constrain_kernel(const float* __restrict__ raw, float* __restrict__ out, int64_t rows, int M) {
+  int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= rows) return;
+  const float* p = raw + r * M;
+  float* o = out + r * M;
+  float acc = p[0];  // cumsum of [θ0, softplus(θ_k)+1e-4 ...] (BernsteinBijector.py:60-71)
+  o[0] = acc;
+  for (int k = 1; k < M; ++k) {
+    acc += softplus_f(p[k]) + 1e-4f;
+    o[k] = acc;
+  }
+}
+
+// inverse, step 1: y_fit[e][p] = forward(theta_e, x_fit[p]), x_fit = linspace(1e-7, 1-1e-7, P)
+__global__ void __launch_bounds__(256)
+bern_grid_kernel(const float* __restrict__ theta, int M, int64_t E, int P, float* __restrict__ yfit) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= E * P) return;
+  int64_t e = i / P;
+  int p = (int)(i - e * P);
+  const float* th = theta + e * M;
+  const double lo = 1e-7, hi = 1.0 - 1e-7;
+  float xf = (float)(lo + (hi - lo) * (double)p / (double)(P - 1));
+  float u = bern_clip(xf), v = 1.f - u;
+  const int deg = M - 1;
+  double c = 1.0;
+  float y = th[0], pw = u;
+  for (int j = 1; j <= deg; ++j) {
+    c = c * (double)(deg - j + 1) / (double)j;
+    y = fmaf(y, v, th[j] * (float)c * pw);
+    pw *= u;
+  }
+  yfit[i] = y;
+}
+
+// inverse, step 2: x[e][n] = interp(y[n][e], y_fit[e], x_fit)   (BernsteinBijector.py:104-110)
+__global__ void __launch_bounds__(256)
+bern_interp_kernel(const float* __restrict__ yfit, int64_t E, int P, const float* __restrict__ y,
+                   float* __restrict__ x, int64_t n) {
+  const double lo = 1e-7, hi = 1.0 - 1e-7;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    for (int64_t e = 0; e < E; ++e) {
+      const float* f = yfit + e * P;
+      float yq = y[i * E + e];
+      // np.interp: idx = searchsorted(xp, xq, side='right'); clamp outside
+      int a = 0, b = P;  // first index with f[idx] > yq
+      while (a < b) {
+        int m = (a + b) >> 1;
+        if (__ldg(f + m) <= yq) a = m + 1; else b = m;
+      }
+      float r;
+      if (a == 0) r = (float)lo;
+      else if (a >= P) r = (float)hi;
+      else {
+        float f0 = __ldg(f + a - 1), f1 = __ldg(f + a);
+        float x0 = (float)(lo + (hi - lo) * (double)(a - 1) / (double)(P - 1));
+        float x1 = (float)(lo + (hi - lo) * (double)a / (double)(P - 1));
+        float df = f1 - f0;
+        r = df > 0.f ? x0 + (yq - f0) / df * (x1 - x0) : x0;
+      }
+      x[e * n + i] = r;
+    }
+  }
+}
+
+}  // namespace flowcuda
+
+using namespace flowcuda;
+
+extern "C" {
+
+int flowcuda_bernstein_constrain_thetas(const float* theta_raw, float* theta, int64_t rows, int order, void* stream) {
+  FC_REQUIRE(theta_raw && theta && rows >= 0 && order >= 1, "constrain_thetas: bad arguments");
+  if (rows == 0) return FLOWCUDA_OK;
+  bern_constrain_kernel<<<(int)((rows + 255) / 256), 256, 0, (cudaStream_t)stream>>>(theta_raw, theta, rows, order);
+  FC_LAUNCH_CHECK("bern_constrain_kernel");
+  return FLOWCUDA_OK;
+}
+
+int flowcuda_bernstein_forward_and_log_det(const float* theta, int order, int64_t theta_stride, const float* x,
+                                           float* y, float* log_det, int64_t n, void* stream) {
+  FC_REQUIRE(theta && x && (y || log_det), "bernstein_forward: NULL pointer");
+  FC_REQUIRE(order >= 2 && order <= kBernMaxOrder, "bernstein_forward: order=%d outside [2,%d]", order, kBernMaxOrder);
+  FC_REQUIRE(theta_stride == 0 || theta_stride >= order, "bernstein_forward: theta_stride must be 0 or >= order");
+  FC_REQUIRE(n >= 0, "bernstein_forward: negative n");
+  if (n == 0) return FLOWCUDA_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  if (theta_stride == 0) {
+    FC_REQUIRE((((uintptr_t)x | (uintptr_t)y | (uintptr_t)log_det) & 15) == 0, "bernstein_forward: buffers must be 16-byte aligned");
+    int grid = grid_for((n + 3) / 4, kBernThreads, 8);
+    bern_shared_kernel<0><<<grid, kBernThreads, 0, s>>>(theta, order, nullptr, x, y, log_det, n);
+  } else {
+    bern_rows_kernel<<<grid_for(n, kBernThreads, 8), kBernThreads, 0, s>>>(theta, order, theta_stride, x, y, log_det, n);
+  }
+  FC_LAUNCH_CHECK("bernstein forward kernel");
+  return FLOWCUDA_OK;
+}
+
+int flowcuda_bernstein_flow_log_prob(const float* theta, int order, const float* scal, const float* x, float* log_prob,
+                                     int64_t n, void* stream) {
+  FC_REQUIRE(theta && scal && x && log_prob, "bernstein_flow_log_prob: NULL pointer");
+  FC_REQUIRE(order >= 2 && order <= kBernMaxOrder, "bernstein_flow_log_prob: order=%d outside [2,%d]", order, kBernMaxOrder);
+  FC_REQUIRE((((uintptr_t)x | (uintptr_t)log_prob) & 15) == 0, "bernstein_flow_log_prob: buffers must be 16-byte aligned");
+  FC_REQUIRE(n >= 0, "bernstein_flow_log_prob: negative n");
+  if (n == 0) return FLOWCUDA_OK;
+  int grid = grid_for((n + 3) / 4, kBernThreads, 8);
+  bern_shared_kernel<1><<<grid, kBernThreads, 0, (cudaStream_t)stream>>>(theta, order, scal, x, nullptr, log_prob, n);
+  FC_LAUNCH_CHECK("bern_shared_kernel<1>");
+  return FLOWCUDA_OK;
+}
+
+int flowcuda_bernstein_inverse(const float* theta, int order, int64_t n_events, int n_points, const float* y, float* x,
+                               int64_t n, float* workspace, void* stream) {
+  FC_REQUIRE(theta && y && x && workspace, "bernstein_inverse: NULL pointer");
+  FC_REQUIRE(order >= 2 && order <= kBernMaxOrder, "bernstein_inverse: order=%d outside [2,%d]", order, kBernMaxOrder);
+  FC_REQUIRE(n_events >= 1 && n_points >= 2 && n >= 0, "bernstein_inverse: bad sizes");
+  if (n == 0) return FLOWCUDA_OK;
+  cudaStream_t s = (cudaStream_t)stream;
+  int64_t tot = n_events * n_points;
+  bern_grid_kernel<<<(int)((tot + 255) / 256), 256, 0, s>>>(theta, order, n_events, n_points, workspace);
+  FC_LAUNCH_CHECK("bern_grid_kernel");
+  bern_interp_kernel<<<grid_for(n, 256, 8), 256, 0, s>>>(workspace, n_events, n_points, y, x, n);
+  FC_LAUNCH_CHECK("bern_interp_kernel");
+  return FLOWCUDA_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,144 @@
+// core.cu — error plumbing, device queries, loss reduction and optimiser steps (rows #7, #9).
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace flowcuda {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+  set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
+  return FLOWCUDA_ECUDA;
+}
+
+int sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+// ---- deterministic scaled sum: out = scale * sum(v) -------------------------------------
+constexpr int kSumBlocks = 1024;  // == workspace doubles
+constexpr int kSumThreads = 256;
+
+__global__ void __launch_bounds__(kSumThreads) sum_stage1(const float* __restrict__ v, int64_t n,
+                                                         double* __restrict__ partial) {
+  __shared__ double sm[kSumThreads / 32];
+  // fixed assignment: block b owns the contiguous chunk [b*chunk, (b+1)*chunk)
+  int64_t chunk = (n + gridDim.x - 1) / gridDim.x;
+  int64_t lo = (int64_t)blockIdx.x * chunk;
+  int64_t hi = lo + chunk < n ? lo + chunk : n;
+  double acc = 0.0;
+  for (int64_t i = lo + threadIdx.x; i < hi; i += kSumThreads) acc += (double)v[i];
+  acc = warp_sum_d(acc);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+#pragma unroll
+    for (int w = 0; w < kSumThreads / 32; ++w) t += sm[w];
+    partial[blockIdx.x] = t;
+  }
+}
+
+__global__ void __launch_bounds__(kSumThreads) sum_stage2(const double* __restrict__ partial, int nb,
+                                                         double scale, float* __restrict__ out) {
+  __shared__ double sm[kSumThreads / 32];
+  double acc = 0.0;
+  for (int i = threadIdx.x; i < nb; i += kSumThreads) acc += partial[i];
+  acc = warp_sum_d(acc);
+  if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+#pragma unroll
+    for (int w = 0; w < kSumThreads / 32; ++w) t += sm[w];
+    out[0] = (float)(t * scale);
+  }
+}
+
+// ---- optimiser steps ---------------------------------------------------------------------
+__global__ void __launch_bounds__(256) sgd_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                  int64_t n, float lr, float gs) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) p[i] = p[i] - lr * (g[i] * gs);
+}
+
+__global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const float* __restrict__ g,
+                                                   float* __restrict__ m, float* __restrict__ v, int64_t n,
+                                                   float lr, float b1, float b2, float eps, float gs,
+                                                   float inv_bc1, float inv_bc2) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    float gi = g[i] * gs;
+    float mi = b1 * m[i] + (1.f - b1) * gi;
+    float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    float mh = mi * inv_bc1;
+    float vh = vi * inv_bc2;
+    p[i] = p[i] - lr * mh / (sqrtf(vh) + eps);
+  }
+}
+
+}  // namespace flowcuda
+
+using namespace flowcuda;
+
+extern "C" {
+
+int flowcuda_version(void) { return FLOWCUDA_VERSION; }
+const char* flowcuda_last_error(void) { return g_err; }
+int flowcuda_sm_count(void) { return sm_count(); }
+
+int flowcuda_sum_scaled(const float* v, int64_t n, double scale, float* out, void* workspace, void* stream) {
+  FC_REQUIRE(v && out && workspace && n >= 0, "sum_scaled: NULL pointer or negative n");
+  cudaStream_t s = (cudaStream_t)stream;
+  int nb = (int)((n + 4095) / 4096);
+  if (nb < 1) nb = 1;
+  if (nb > kSumBlocks) nb = kSumBlocks;
+  sum_stage1<<<nb, kSumThreads, 0, s>>>(v, n, (double*)workspace);
+  FC_LAUNCH_CHECK("sum_stage1");
+  sum_stage2<<<1, kSumThreads, 0, s>>>((const double*)workspace, nb, scale, out);
+  FC_LAUNCH_CHECK("sum_stage2");
+  return FLOWCUDA_OK;
+}
+
+int flowcuda_sgd_step(float* p, const float* g, int64_t count, float lr, float grad_scale, void* stream) {
+  FC_REQUIRE(p && g && count >= 0, "sgd_step: NULL pointer or negative count");
+  if (count == 0) return FLOWCUDA_OK;
+  sgd_kernel<<<grid_for(count, 256), 256, 0, (cudaStream_t)stream>>>(p, g, count, lr, grad_scale);
+  FC_LAUNCH_CHECK("sgd_kernel");
+  return FLOWCUDA_OK;
+}
+
+int flowcuda_adam_step(float* p, const float* g, float* m, float* v, int64_t count, int64_t step, float lr,
+                       float b1, float b2, float eps, float grad_scale, void* stream) {
+  FC_REQUIRE(p && g && m && v && count >= 0 && step >= 1, "adam_step: bad arguments");
+  if (count == 0) return FLOWCUDA_OK;
+  float inv_bc1 = (float)(1.0 / (1.0 - pow((double)b1, (double)step)));
+  float inv_bc2 = (float)(1.0 / (1.0 - pow((double)b2, (double)step)));
+  adam_kernel<<<grid_for(count, 256), 256, 0, (cudaStream_t)stream>>>(p, g, m, v, count, lr, b1, b2, eps,
+                                                                      grad_scale, inv_bc1, inv_bc2);
+  FC_LAUNCH_CHECK("adam_kernel");
+  return FLOWCUDA_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,250 @@
+"""Tensor-level entry points: torch CUDA tensors in, torch CUDA tensors out, every op a call
+into libflowcuda.so on torch's current stream.  torch is used for device memory and streams
+only; no torch kernel computes flow math here."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import CouplingSpec, check
+
+
+def _dev_check(*ts):
+    for t in ts:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise _lib.FlowCudaError("flowcuda ops need CUDA tensors (there is no CPU path)")
+        if t.dtype != torch.float32:
+            raise _lib.FlowCudaError(f"flowcuda ops are float32; got {t.dtype}")
+        if not t.is_contiguous():
+            raise _lib.FlowCudaError("flowcuda ops need contiguous tensors")
+
+
+def _f32(t: torch.Tensor) -> torch.Tensor:
+    return t.detach().to(dtype=torch.float32).contiguous()
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return C.c_void_p(0 if t is None else t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def flip_mask_of(flips: Sequence[bool]) -> int:
+    m = 0
+    for i, f in enumerate(flips):
+        if f:
+            m |= 1 << i
+    return m
+
+
+# ---------------------------------------------------------------------------- row #1
+def realnvp_log_prob(params: torch.Tensor, n_layers: int, hidden: int, flip_mask: int, y: torch.Tensor,
+                     want_z: bool = False):
+    y = _f32(y)
+    _dev_check(params, y)
+    n = y.shape[0]
+    lp = torch.empty(n, device=y.device, dtype=torch.float32)
+    z = torch.empty_like(y) if want_z else None
+    check(_lib.load().flowcuda_realnvp_log_prob(_ptr(params), n_layers, hidden, flip_mask, _ptr(y), _ptr(lp), _ptr(z),
+                                                n, _stream()), "realnvp_log_prob")
+    return (lp, z) if want_z else lp
+
+
+def realnvp_sample(params: torch.Tensor, n_layers: int, hidden: int, flip_mask: int, z: torch.Tensor) -> torch.Tensor:
+    z = _f32(z)
+    _dev_check(params, z)
+    x = torch.empty_like(z)
+    check(_lib.load().flowcuda_realnvp_sample(_ptr(params), n_layers, hidden, flip_mask, _ptr(z), _ptr(x), z.shape[0],
+                                              _stream()), "realnvp_sample")
+    return x
+
+
+def realnvp_forward(layer_params: torch.Tensor, hidden: int, flip: bool, x: torch.Tensor) -> torch.Tensor:
+    x = _f32(x)
+    _dev_check(layer_params, x)
+    y = torch.empty_like(x)
+    check(_lib.load().flowcuda_realnvp_forward(_ptr(layer_params), hidden, int(flip), _ptr(x), _ptr(y), x.shape[0],
+                                               _stream()), "realnvp_forward")
+    return y
+
+
+def realnvp_inverse(layer_params: torch.Tensor, hidden: int, flip: bool, y: torch.Tensor):
+    y = _f32(y)
+    _dev_check(layer_params, y)
+    x = torch.empty_like(y)
+    ls = torch.empty(y.shape[0], 1, device=y.device, dtype=torch.float32)
+    check(_lib.load().flowcuda_realnvp_inverse(_ptr(layer_params), hidden, int(flip), _ptr(y), _ptr(x), _ptr(ls),
+                                               y.shape[0], _stream()), "realnvp_inverse")
+    return x, ls
+
+
+def realnvp_nll_grad(params: torch.Tensor, n_layers: int, hidden: int, flip_mask: int, y: torch.Tensor,
+                     lr: float = 0.0, params_out: Optional[torch.Tensor] = None,
+                     workspace: Optional[torch.Tensor] = None):
+    """(loss[1], grad[L*(4H+2)]); with lr != 0 also writes p - lr*g into params_out."""
+    y = _f32(y)
+    _dev_check(params, y, params_out)
+    lib = _lib.load()
+    n = y.shape[0]
+    need = lib.flowcuda_realnvp_nll_grad_workspace_bytes(n_layers, hidden, n)
+    if workspace is None or workspace.numel() * workspace.element_size() < need:
+        workspace = torch.empty((need + 3) // 4, device=y.device, dtype=torch.float32)
+    loss = torch.empty(1, device=y.device, dtype=torch.float32)
+    grad = torch.empty_like(params)
+    check(lib.flowcuda_realnvp_nll_grad(_ptr(params), n_layers, hidden, flip_mask, _ptr(y), n, _ptr(loss), _ptr(grad),
+                                        float(lr), _ptr(params_out), _ptr(workspace),
+                                        workspace.numel() * workspace.element_size(), _stream()), "realnvp_nll_grad")
+    return loss, grad
+
+
+# ---------------------------------------------------------------------------- row #5
+def bernstein_constrain_thetas(theta_raw: torch.Tensor) -> torch.Tensor:
+    t = _f32(theta_raw)
+    _dev_check(t)
+    order = t.shape[-1]
+    out = torch.empty_like(t)
+    check(_lib.load().flowcuda_bernstein_constrain_thetas(_ptr(t), _ptr(out), t.numel() // order, order, _stream()),
+          "bernstein_constrain_thetas")
+    return out
+
+
+def bernstein_forward_and_log_det(theta: torch.Tensor, x: torch.Tensor, want_y: bool = True, want_ld: bool = True):
+    """theta [M] (shared) or [*x.shape, M] (one row per element); x any shape."""
+    theta, x = _f32(theta), _f32(x)
+    _dev_check(theta, x)
+    order = theta.shape[-1]
+    if theta.dim() == 1:
+        stride = 0
+    else:
+        if tuple(theta.shape[:-1]) != tuple(x.shape):
+            theta = theta.expand(*x.shape, order).contiguous()
+        stride = order
+    y = torch.empty_like(x) if want_y else None
+    ld = torch.empty_like(x) if want_ld else None
+    check(_lib.load().flowcuda_bernstein_forward_and_log_det(_ptr(theta), order, stride, _ptr(x), _ptr(y), _ptr(ld),
+                                                             x.numel(), _stream()), "bernstein_forward_and_log_det")
+    return y, ld
+
+
+def bernstein_inverse(theta: torch.Tensor, y: torch.Tensor, n_points: int = 200) -> torch.Tensor:
+    """theta [E,M] (or [M] with E=1), y [N,E] -> x [E,N] (the reference's vmap output layout)."""
+    theta, y = _f32(theta), _f32(y)
+    _dev_check(theta, y)
+    if theta.dim() == 1:
+        theta = theta[None, :].contiguous()
+    E, order = theta.shape
+    if y.dim() != 2 or y.shape[1] != E:
+        raise ValueError("vmap got inconsistent sizes for array axes to be mapped: y must be [N, %d]" % E)
+    n = y.shape[0]
+    x = torch.empty(E, n, device=y.device, dtype=torch.float32)
+    ws = torch.empty(E * n_points, device=y.device, dtype=torch.float32)
+    check(_lib.load().flowcuda_bernstein_inverse(_ptr(theta), order, E, n_points, _ptr(y), _ptr(x), n, _ptr(ws),
+                                                 _stream()), "bernstein_inverse")
+    return x
+
+
+def bernstein_flow_log_prob(theta: torch.Tensor, scal: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
+    theta, scal, x = _f32(theta), _f32(scal), _f32(x)
+    _dev_check(theta, scal, x)
+    lp = torch.empty_like(x)
+    check(_lib.load().flowcuda_bernstein_flow_log_prob(_ptr(theta), theta.shape[-1], _ptr(scal), _ptr(x), _ptr(lp),
+                                                       x.numel(), _stream()), "bernstein_flow_log_prob")
+    return lp
+
+
+# ---------------------------------------------------------------------------- rows #2-#4
+def make_spec(event_dim: int, num_layers: int, hidden: Sequence[int], transform: int, num_bins: int = 0,
+              range_min: float = 0.0, range_max: float = 1.0, base: int = _lib.BASE_NORMAL,
+              precision: int = _lib.PRECISION_FP32) -> CouplingSpec:
+    if len(hidden) > _lib.MAX_HIDDEN_LAYERS:
+        raise ValueError("at most %d hidden layers" % _lib.MAX_HIDDEN_LAYERS)
+    sp = CouplingSpec()
+    sp.event_dim, sp.num_layers, sp.num_hidden = event_dim, num_layers, len(hidden)
+    for i, h in enumerate(hidden):
+        sp.hidden[i] = h
+    sp.transform, sp.num_bins = transform, num_bins
+    sp.range_min, sp.range_max = range_min, range_max
+    sp.base, sp.precision = base, precision
+    return sp
+
+
+def coupling_param_count(spec: CouplingSpec) -> int:
+    n = _lib.load().flowcuda_coupling_param_count(C.byref(spec))
+    if n < 0:
+        check(-1, "coupling_param_count")
+    return n
+
+
+def _workspace(spec: CouplingSpec, n: int, device) -> Tuple[Optional[torch.Tensor], int]:
+    need = _lib.load().flowcuda_coupling_workspace_bytes(C.byref(spec), n)
+    if need == 0:
+        return None, 0
+    ws = torch.empty((need + 3) // 4, device=device, dtype=torch.float32)
+    return ws, ws.numel() * 4
+
+
+def coupling_log_prob(spec: CouplingSpec, params: torch.Tensor, x: torch.Tensor, want_z: bool = False,
+                      want_log_det: bool = False, want_log_prob: bool = True, layers: Optional[Tuple[int, int]] = None,
+                      with_base: bool = True):
+    """Data -> base direction (Transformed.log_prob).  Returns (log_prob, z, log_det) with None
+    for outputs that were not requested."""
+    x = _f32(x).reshape(x.shape[0], -1)
+    _dev_check(params, x)
+    n = x.shape[0]
+    lb, le = layers if layers is not None else (0, spec.num_layers)
+    lp = torch.empty(n, device=x.device, dtype=torch.float32) if want_log_prob else None
+    z = torch.empty_like(x) if want_z else None
+    ld = torch.empty(n, device=x.device, dtype=torch.float32) if want_log_det else None
+    ws, wsb = _workspace(spec, n, x.device)
+    check(_lib.load().flowcuda_coupling_log_prob(C.byref(spec), _ptr(params), _ptr(x), _ptr(lp), _ptr(z), _ptr(ld), n,
+                                                 lb, le, int(with_base), _ptr(ws), wsb, _stream()), "coupling_log_prob")
+    return lp, z, ld
+
+
+def coupling_sample(spec: CouplingSpec, params: torch.Tensor, z: torch.Tensor, want_log_det: bool = False,
+                    layers: Optional[Tuple[int, int]] = None):
+    """Base -> data direction (Transformed.sample with the noise given).  Returns (x, log_det)."""
+    z = _f32(z).reshape(z.shape[0], -1)
+    _dev_check(params, z)
+    n = z.shape[0]
+    lb, le = layers if layers is not None else (0, spec.num_layers)
+    x = torch.empty_like(z)
+    ld = torch.empty(n, device=z.device, dtype=torch.float32) if want_log_det else None
+    ws, wsb = _workspace(spec, n, z.device)
+    check(_lib.load().flowcuda_coupling_sample(C.byref(spec), _ptr(params), _ptr(z), _ptr(x), _ptr(ld), n, lb, le,
+                                               _ptr(ws), wsb, _stream()), "coupling_sample")
+    return x, ld
+
+
+# ---------------------------------------------------------------------------- rows #7, #9
+def sum_scaled(v: torch.Tensor, scale: float) -> torch.Tensor:
+    v = _f32(v).reshape(-1)
+    _dev_check(v)
+    out = torch.empty(1, device=v.device, dtype=torch.float32)
+    ws = torch.empty(1024, device=v.device, dtype=torch.float64)
+    check(_lib.load().flowcuda_sum_scaled(_ptr(v), v.numel(), float(scale), _ptr(out), _ptr(ws), _stream()), "sum_scaled")
+    return out
+
+
+def nll(log_prob: torch.Tensor) -> torch.Tensor:
+    """-jnp.mean(log_prob) (real_nvp.py:293)."""
+    return sum_scaled(log_prob, -1.0 / max(1, log_prob.numel()))
+
+
+def sgd_step(p: torch.Tensor, g: torch.Tensor, lr: float, grad_scale: float = 1.0) -> None:
+    _dev_check(p, g)
+    check(_lib.load().flowcuda_sgd_step(_ptr(p), _ptr(g), p.numel(), float(lr), float(grad_scale), _stream()), "sgd_step")
+
+
+def adam_step(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, step: int, lr: float,
+              b1: float = 0.9, b2: float = 0.999, eps: float = 1e-8, grad_scale: float = 1.0) -> None:
+    _dev_check(p, g, m, v)
+    check(_lib.load().flowcuda_adam_step(_ptr(p), _ptr(g), _ptr(m), _ptr(v), p.numel(), int(step), float(lr), float(b1),
+                                         float(b2), float(eps), float(grad_scale), _stream()), "adam_step")

@@ -1,0 +1,281 @@
+"""GPU parity tests proper: every call goes through the C ABI of libflowcuda.so (via
+normalizing_flows_b200.ops) and is compared with the float64 CPU oracle on the same inputs,
+or with the committed golden vectors produced by the reference's own source.
+
+Tolerance (BASELINE.json north_star): |Δ| <= 1e-5 · max(1, |ref|) for the FP32 paths
+("per-sample log_prob relative error <= 1e-5"; max(1,·) because log_prob crosses zero)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import flows_oracle as O
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+DEV = "cuda"
+T64 = lambda a: torch.as_tensor(np.asarray(a), dtype=torch.float64)
+
+
+def G(a):
+    return torch.as_tensor(np.asarray(a), dtype=torch.float32).to(DEV).contiguous()
+
+
+def close(got, ref, tol=1e-5, what=""):
+    got = got.detach().double().cpu().numpy()
+    ref = np.asarray(ref, dtype=np.float64)
+    assert got.shape == ref.shape, (what, got.shape, ref.shape)
+    fin = np.isfinite(ref)
+    assert np.array_equal(np.isfinite(got), fin), what
+    err = np.abs(got[fin] - ref[fin]) / np.maximum(1.0, np.abs(ref[fin]))
+    assert err.size == 0 or err.max() <= tol, f"{what}: max scaled err {err.max():.3e} > {tol}"
+    assert np.array_equal(got[~fin], ref[~fin]), what
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from normalizing_flows_b200 import ops as _ops
+
+    return _ops
+
+
+# ------------------------------------------------------------------ row #1: real_nvp.py
+def test_realnvp_golden(ops):
+    g = np.load(os.path.join(GOLDEN, "real_nvp_golden.npz"))
+    L, H = int(g["n_layers"]), int(g["hidden"])
+    P = 4 * H + 2
+    params = G(g["params_flat"])
+    fm = ops.flip_mask_of([bool(f) for f in g["flips"]])
+    y, z = G(g["y"]), G(g["z"])
+    lp, zb = ops.realnvp_log_prob(params, L, H, fm, y, want_z=True)
+    close(lp, g["log_prob"], what="log_prob_nvp_chains")
+    close(ops.realnvp_sample(params, L, H, fm, z), g["sample"], what="sample_nvp_chain")
+    close(ops.realnvp_forward(params[0:P], H, False, z), g["fwd0"], what="forward_nvp l0")
+    close(ops.realnvp_forward(params[P : 2 * P].contiguous(), H, True, z), g["fwd1"], what="forward_nvp l1 flip")
+    x0, ls0 = ops.realnvp_inverse(params[0:P], H, False, y)
+    close(x0, g["inv0"]); close(ls0, g["ls0"])
+    x1, ls1 = ops.realnvp_inverse(params[P : 2 * P].contiguous(), H, True, y)
+    close(x1, g["inv1"]); close(ls1, g["ls1"])
+    # round trip: sample(z) pushed back to the base recovers z
+    xs = ops.realnvp_sample(params, L, H, fm, z)
+    _, zr = ops.realnvp_log_prob(params, L, H, fm, xs, want_z=True)
+    close(zr, g["z"], tol=2e-5, what="round trip")
+
+
+@pytest.mark.parametrize("n", [0, 1, 2, 3, 127, 128, 1025])
+@pytest.mark.parametrize("L,H", [(8, 4), (3, 7), (1, 32), (64, 4)])
+def test_realnvp_shapes(ops, n, L, H):
+    params64, flips = O.init_nvp_chain_like(L, hidden=H, seed=L * 100 + H, scale=0.3)
+    flat = O.flatten_layers(params64)
+    g = torch.Generator().manual_seed(n + 1)
+    y64 = torch.randn(n, 2, generator=g, dtype=torch.float64) * 1.5
+    y = y64.float().to(DEV)
+    y64 = y.double().cpu()
+    fm = ops.flip_mask_of(flips)
+    lp = ops.realnvp_log_prob(G(flat), L, H, fm, y)
+    close(lp, O.log_prob_nvp_chains(params64, flips, y64).numpy(), what="log_prob")
+    close(ops.realnvp_sample(G(flat), L, H, fm, y), O.sample_nvp_chain(params64, flips, y64).numpy(), tol=3e-5, what="sample")
+
+
+@pytest.mark.parametrize("n", [1, 128, 1000, 5000])
+@pytest.mark.parametrize("L,H", [(8, 4), (2, 6)])
+def test_realnvp_nll_grad(ops, n, L, H):
+    params64, flips = O.init_nvp_chain_like(L, hidden=H, seed=7, scale=0.4)
+    flat = O.flatten_layers(params64)
+    y = (torch.randn(n, 2, generator=torch.Generator().manual_seed(3), dtype=torch.float64) * 1.3).float()
+    y64 = y.double()
+
+    def lp_fn(leaves):
+        ps, o = [], 0
+        for _ in range(L):
+            W1 = leaves[0][o : o + H].reshape(1, H); o += H
+            b1 = leaves[0][o : o + H]; o += H
+            W2 = leaves[0][o : o + 2 * H].reshape(H, 2); o += 2 * H
+            b2 = leaves[0][o : o + 2]; o += 2
+            ps.append([[W1, b1], [W2, b2]])
+        return O.log_prob_nvp_chains(ps, flips, y64)
+
+    loss_ref, (grad_ref,) = O.nll_and_grads(lp_fn, [flat])
+    fm = ops.flip_mask_of(flips)
+    p = G(flat)
+    loss, grad = ops.realnvp_nll_grad(p, L, H, fm, y.to(DEV))
+    close(loss, loss_ref.reshape(1).numpy(), what="loss")
+    gr = grad_ref.numpy()
+    err = np.abs(grad.double().cpu().numpy() - gr).max() / max(1.0, np.abs(gr).max())
+    assert err < 2e-5, err
+    # determinism + fused SGD step (real_nvp.py:298)
+    pout = torch.empty_like(p)
+    loss2, grad2 = ops.realnvp_nll_grad(p, L, H, fm, y.to(DEV), lr=1e-2, params_out=pout)
+    assert torch.equal(grad, grad2) and torch.equal(loss, loss2)
+    close(pout, (p - 1e-2 * grad).cpu().numpy(), tol=1e-7)
+
+
+# ------------------------------------------------------------------ row #5: BernsteinBijector.py
+def test_bernstein_golden(ops):
+    g = np.load(os.path.join(GOLDEN, "bernstein_golden.npz"))
+    x = G(g["x"])
+    for name in ("demo", "tf", "m32", "m64", "m2", "m8"):
+        th = ops.bernstein_constrain_thetas(G(g[f"{name}_theta_raw"]))
+        close(th, g[f"{name}_theta_constrained"], what=f"constrain {name}")
+        # feed the float64-constrained thetas so the comparison isolates the polynomial
+        y, ld = ops.bernstein_forward_and_log_det(G(g[f"{name}_theta_constrained"]), x)
+        # the golden x has out-of-range values (clip) and fp32 rounding of x moves y by up to J*ulp
+        xr = x.double().cpu()
+        yref, ldref = O.bernstein_forward_and_log_det(T64(G(g[f"{name}_theta_constrained"]).cpu().double()), xr)
+        tol = 1e-5 if name != "m64" else 3e-5
+        close(y, yref.numpy(), tol=tol, what=f"y {name}")
+        close(ld, ldref.numpy(), tol=tol, what=f"ld {name}")
+    close(ops.bernstein_constrain_thetas(G(g["batch_theta_raw"])), g["batch_theta_constrained"])
+    # per-sample thetas (maf_mwe.py:103-107)
+    thc = G(g["ps_theta_raw"])
+    thc = ops.bernstein_constrain_thetas(thc)
+    y, ld = ops.bernstein_forward_and_log_det(thc, G(g["ps_x"]))
+    yref, ldref = O.bernstein_forward_and_log_det(thc.double().cpu(), G(g["ps_x"]).double().cpu())
+    close(y, yref.numpy()); close(ld, ldref.numpy())
+    close(y, g["ps_y"], tol=1e-4); close(ld, g["ps_ld"], tol=1e-4)
+
+
+def test_bernstein_inverse_golden(ops):
+    g = np.load(os.path.join(GOLDEN, "bernstein_golden.npz"))
+    th = G(g["inv_theta_raw"])
+    thc = ops.bernstein_constrain_thetas(th)
+    xi = ops.bernstein_inverse(thc, G(g["inv_y"]))
+    assert tuple(xi.shape) == g["inv_x"].shape  # [E, N]
+    # interpolation on an fp32 grid: absolute tolerance on x in [0,1]
+    np.testing.assert_allclose(xi.cpu().numpy(), g["inv_x"], atol=2e-5)
+    th1 = ops.bernstein_constrain_thetas(G(g["tf_theta_raw"]))
+    np.testing.assert_allclose(ops.bernstein_inverse(th1, G(g["inv1_y"])).cpu().numpy(), g["inv1_x"], atol=2e-5)
+
+
+@pytest.mark.parametrize("n", [0, 1, 3, 4, 5, 1023, 4096 + 2])
+@pytest.mark.parametrize("M", [2, 3, 9, 32, 64])
+def test_bernstein_shapes(ops, n, M):
+    gen = torch.Generator().manual_seed(M * 7 + n)
+    raw = torch.randn(M, generator=gen, dtype=torch.float64)
+    th = O.constrain_thetas(raw).float()
+    x = torch.rand(n, generator=gen, dtype=torch.float64).float()
+    y, ld = ops.bernstein_forward_and_log_det(th.to(DEV), x.to(DEV))
+    yref, ldref = O.bernstein_forward_and_log_det(th.double(), x.double())
+    tol = 1e-5 if M <= 32 else 3e-5
+    close(y, yref.numpy(), tol=tol); close(ld, ldref.numpy(), tol=tol)
+    y2, _ = ops.bernstein_forward_and_log_det(th.to(DEV), x.to(DEV), want_ld=False)
+    assert torch.equal(y, y2)
+
+
+def test_bernstein_flow_log_prob(ops):
+    """bflow.py:22-34,82-88 with its literal parameters."""
+    theta = torch.tensor([-2.5, 2, 3, -7, -7, -7, -7, -7, 7], dtype=torch.float64)
+    a, b, alpha, beta = 2.0, -0.1, 0.2, -2.5
+    x = torch.cat([torch.linspace(-4, 4, 2001, dtype=torch.float64), torch.randn(4099, dtype=torch.float64) * 2]).float()
+    ref = O.bernstein_flow_log_prob(a, b, theta, alpha, beta, x.double())
+    thc = ops.bernstein_constrain_thetas(ops.bernstein_constrain_thetas(G(theta)))  # double constrain (bflow.py:30)
+    lp = ops.bernstein_flow_log_prob(thc, G([a, b, alpha, beta]), x.to(DEV))
+    close(lp, ref.numpy(), tol=3e-5, what="bflow log_prob")
+
+
+# ------------------------------------------------------------------ rows #2-#4, #6: MaskedCoupling flows
+def _spec_pair(ops, ospec, precision=0):
+    from normalizing_flows_b200 import _lib
+
+    tr = {"affine_scalar": 0, "affine": 1, "rqs": 2}[ospec.transform]
+    base = {"normal": 0, "uniform": 1}[ospec.base]
+    return ops.make_spec(ospec.event_dim, ospec.num_layers, ospec.hidden, tr, ospec.num_bins, ospec.range_min,
+                         ospec.range_max, base, precision)
+
+
+COUPLING_CASES = {
+    "realnvp_toy": (O.REAL_NVP_TOY, 0.5, 2.0),
+    "rqs_toy": (O.RQS_TOY, 0.5, 3.0),
+    "rqs_toy_k8": (O.CouplingSpec(2, 3, [32, 48], "rqs", 8, -3.0, 3.0), 0.5, 2.0),
+    "affine_toy": (O.CouplingSpec(2, 4, [64, 64], "affine"), 0.5, 2.0),
+    "affine_d6": (O.CouplingSpec(6, 3, [16], "affine"), 0.5, 1.5),
+    "scalar_d5": (O.CouplingSpec(5, 3, [16, 8], "affine_scalar"), 0.5, 1.5),
+    "rqs_d7": (O.CouplingSpec(7, 3, [24, 24], "rqs", 5, -3.0, 3.0), 0.5, 2.0),
+    "rqs_d40_uniform": (O.CouplingSpec(40, 2, [32, 32, 32], "rqs", 8, 0.0, 1.0, "uniform"), 0.3, None),
+}
+
+
+@pytest.mark.parametrize("case", sorted(COUPLING_CASES))
+@pytest.mark.parametrize("n", [1, 77, 1024 + 3])
+def test_coupling_parity(ops, case, n):
+    ospec, scale, xs = COUPLING_CASES[case]
+    params = O.init_coupling_params(ospec, seed=11, scale=scale)
+    flat = O.flatten_layers(params)
+    spec = _spec_pair(ops, ospec)
+    assert ops.coupling_param_count(spec) == flat.numel()
+    gen = torch.Generator().manual_seed(n)
+    if xs is None:
+        x = torch.rand(n, ospec.event_dim, generator=gen, dtype=torch.float64).float()
+        if n > 3:
+            x[3, 1] = 1.5  # outside the Uniform support -> -inf
+    else:
+        x = (torch.randn(n, ospec.event_dim, generator=gen, dtype=torch.float64) * xs).float()
+    x64 = x.double()
+    lp, z, ld = ops.coupling_log_prob(spec, G(flat), x.to(DEV), want_z=True, want_log_det=True)
+    zref, ldref = O.coupling_flow_to_base(ospec, params, x64)
+    close(lp, O.coupling_flow_log_prob(ospec, params, x64).numpy(), tol=2e-5, what="log_prob")
+    close(z, zref.numpy(), tol=2e-5, what="z")
+    close(ld, ldref.numpy(), tol=2e-5, what="log_det")
+    xsamp, _ = ops.coupling_sample(spec, G(flat), x.to(DEV))
+    close(xsamp, O.coupling_flow_sample(ospec, params, x64).numpy(), tol=5e-5, what="sample")
+    # single layer == MaskedCoupling.forward_and_log_det of that layer
+    _, z1, ld1 = ops.coupling_log_prob(spec, G(flat), x.to(DEV), want_z=True, want_log_det=True, want_log_prob=False,
+                                       layers=(1, 2), with_base=False)
+    zr1, lr1 = O.masked_coupling(ospec, params[1], 1, x64, inverse=False)
+    close(z1, zr1.numpy(), tol=2e-5); close(ld1, lr1.numpy(), tol=2e-5)
+
+
+def test_coupling_identity_at_init_K1_K2(ops):
+    """zero-initialised final Linear => identity flow."""
+    for ospec in (O.REAL_NVP_TOY, O.RQS_TOY):
+        params = O.init_coupling_params(ospec, seed=1, final_scale=0.0)
+        x = torch.randn(513, 2) * 2
+        lp, z, _ = ops.coupling_log_prob(_spec_pair(ops, ospec), G(O.flatten_layers(params)), x.to(DEV), want_z=True)
+        close(lp, O.log_prob_N01(x.double()).numpy(), tol=2e-6)
+        close(z, x.double().numpy(), tol=2e-6)
+
+
+def test_coupling_mnist_shape(ops):
+    """maf_mnist.py:28-31 full conditioner 784->512->512->512->19600, 8 bins, Uniform base (2 layers to bound CPU time)."""
+    ospec = O.CouplingSpec(784, 2, [512, 512, 512], "rqs", 8, 0.0, 1.0, "uniform")
+    params = O.init_coupling_params(ospec, seed=5, scale=0.1)
+    gen = torch.Generator().manual_seed(0)
+    x = ((torch.randint(0, 256, (48, 28, 28, 1), generator=gen).double() + torch.rand(48, 28, 28, 1, generator=gen, dtype=torch.float64)) / 256).float()
+    lp, _, _ = ops.coupling_log_prob(_spec_pair(ops, ospec), G(O.flatten_layers(params)), x.to(DEV))
+    ref = O.coupling_flow_log_prob(ospec, params, x.double())
+    got = lp.double().cpu().numpy()
+    # north_star: <= 1e-3 absolute on the MNIST path
+    assert np.abs(got - ref.numpy()).max() <= 1e-3, np.abs(got - ref.numpy()).max()
+
+
+# ------------------------------------------------------------------ rows #7, #9
+def test_sum_sgd_adam(ops):
+    v = torch.randn(1_000_003, dtype=torch.float64)
+    out = ops.nll(v.float().to(DEV))
+    np.testing.assert_allclose(out.item(), -v.float().double().mean().item(), rtol=1e-6)
+    out2 = ops.nll(v.float().to(DEV))
+    assert torch.equal(out, out2)
+    p = torch.randn(10_001, dtype=torch.float64); g = torch.randn(10_001, dtype=torch.float64)
+    pd = p.float().to(DEV); gd = g.float().to(DEV)
+    ops.sgd_step(pd, gd, 1e-2)
+    close(pd, O.sgd_step(p.float().double(), g.float().double(), 1e-2).numpy(), tol=1e-6)
+    m = torch.zeros_like(p); vv = torch.zeros_like(p)
+    md, vd = m.float().to(DEV), vv.float().to(DEV)
+    pr = pd.double().cpu()
+    for step in (1, 2, 3):
+        ops.adam_step(pd, gd, md, vd, step, 1e-3)
+        pr, m, vv = O.adam_step(pr, g.float().double(), m, vv, step, 1e-3)
+    close(pd, pr.numpy(), tol=1e-6); close(md, m.numpy(), tol=1e-6); close(vd, vv.numpy(), tol=1e-6)
+
+
+def test_error_paths(ops):
+    from normalizing_flows_b200._lib import FlowCudaError
+
+    y = torch.zeros(4, 2, device=DEV)
+    with pytest.raises(FlowCudaError):
+        ops.realnvp_log_prob(torch.zeros(18, device=DEV), 65, 4, 0, y)
+    with pytest.raises(FlowCudaError):
+        ops.realnvp_log_prob(torch.zeros(18), 1, 4, 0, y)  # CPU tensor: no CPU path
+    with pytest.raises(FlowCudaError):
+        ops.bernstein_forward_and_log_det(torch.zeros(65, device=DEV), torch.zeros(4, device=DEV))
