@@ -1,0 +1,73 @@
+"""Mirror of the reference's src/BernsteinBijector.py on libflowcuda kernels: same names
+(`constrain_thetas`, `get_bernstein_poly`, `get_bernstein_poly_jac`, `BernsteinBijector`),
+same argument meaning, same quirks (the inverse returns [E, N] and log-det 0)."""
+from __future__ import annotations
+
+import torch
+
+from . import ops
+from .distrax_api import Bijector
+
+
+def constrain_thetas(theta_unconstrained, range_min=None, range_max=None, fn=None):
+    """BernsteinBijector.py:60-71 (range_min/range_max/fn are unused there too)."""
+    return ops.bernstein_constrain_thetas(torch.as_tensor(theta_unconstrained, dtype=torch.float32, device="cuda"))
+
+
+def get_bernstein_poly(theta):
+    """BernsteinBijector.py:23-36: returns x -> mean_k Beta(k, M-k+1).pdf(x) * theta_k (no clip)."""
+    theta = torch.as_tensor(theta, dtype=torch.float32, device="cuda")
+
+    def bernstein_poly(x):
+        return ops.bernstein_forward_and_log_det(theta, _cuda(x), want_ld=False)[0]
+
+    return bernstein_poly
+
+
+def get_bernstein_poly_jac(theta):
+    """BernsteinBijector.py:45-57: returns y -> sum_k Beta(k, M-k).pdf(y) * (theta_{k+1}-theta_k)."""
+    theta = torch.as_tensor(theta, dtype=torch.float32, device="cuda")
+
+    def bernstein_poly_jac(y):
+        return torch.exp(ops.bernstein_forward_and_log_det(theta, _cuda(y), want_y=False)[1])
+
+    return bernstein_poly_jac
+
+
+def _cuda(x):
+    return torch.as_tensor(x, dtype=torch.float32).to("cuda")
+
+
+class BernsteinBijector(Bijector):
+    """BernsteinBijector.py:74-123.  `thetas` are UNCONSTRAINED; __init__ constrains them."""
+
+    def __init__(self, thetas):
+        super().__init__(event_ndims_in=0)
+        self.thetas = constrain_thetas(thetas)
+
+    def forward(self, x):
+        return ops.bernstein_forward_and_log_det(self.thetas, _cuda(x), want_ld=False)[0]
+
+    def forward_log_det_jacobian(self, x):
+        return ops.bernstein_forward_and_log_det(self.thetas, _cuda(x), want_y=False)[1]
+
+    def forward_and_log_det(self, x):
+        return ops.bernstein_forward_and_log_det(self.thetas, _cuda(x))
+
+    def inverse(self, y):
+        return ops.bernstein_inverse(self.thetas, _cuda(y))
+
+    def inverse_and_log_det(self, y):
+        return self.inverse(y), 0  # reference behaviour (BernsteinBijector.py:119-123)
+
+
+def bernstein_flow_log_prob(a, b, theta, alpha, beta, x, double_constrain: bool = True):
+    """Transformed(Normal(0,1), Inverse(Chain([T4,T3,T2,T1]))).log_prob(x) of bflow.py:28-34,82-88
+    in one fused kernel.  `theta` is unconstrained; bflow.py:30 constrains it before
+    BernsteinBijector.__init__ constrains it again (`double_constrain`)."""
+    th = constrain_thetas(theta)
+    if double_constrain:
+        th = ops.bernstein_constrain_thetas(th)
+    scal = torch.tensor([float(a), float(b), float(alpha), float(beta)], dtype=torch.float32, device="cuda")
+    x = _cuda(x)
+    return ops.bernstein_flow_log_prob(th, scal, x.reshape(-1)).reshape(x.shape)

@@ -252,6 +252,7 @@ int flowcuda_bernstein_constrain_thetas(const float* theta_raw, float* theta, in
 
 int flowcuda_bernstein_forward_and_log_det(const float* theta, int order, int64_t theta_stride, const float* x,
                                            float* y, float* log_det, int64_t n, void* stream) {
+  if (n == 0) return FLOWCUDA_OK;
   FC_REQUIRE(theta && x && (y || log_det), "bernstein_forward: NULL pointer");
   FC_REQUIRE(order >= 2 && order <= kBernMaxOrder, "bernstein_forward: order=%d outside [2,%d]", order, kBernMaxOrder);
   FC_REQUIRE(theta_stride == 0 || theta_stride >= order, "bernstein_forward: theta_stride must be 0 or >= order");
@@ -271,6 +272,7 @@ int flowcuda_bernstein_forward_and_log_det(const float* theta, int order, int64_
 
 int flowcuda_bernstein_flow_log_prob(const float* theta, int order, const float* scal, const float* x, float* log_prob,
                                      int64_t n, void* stream) {
+  if (n == 0) return FLOWCUDA_OK;
   FC_REQUIRE(theta && scal && x && log_prob, "bernstein_flow_log_prob: NULL pointer");
   FC_REQUIRE(order >= 2 && order <= kBernMaxOrder, "bernstein_flow_log_prob: order=%d outside [2,%d]", order, kBernMaxOrder);
   FC_REQUIRE((((uintptr_t)x | (uintptr_t)log_prob) & 15) == 0, "bernstein_flow_log_prob: buffers must be 16-byte aligned");
@@ -284,6 +286,7 @@ int flowcuda_bernstein_flow_log_prob(const float* theta, int order, const float*
 
 int flowcuda_bernstein_inverse(const float* theta, int order, int64_t n_events, int n_points, const float* y, float* x,
                                int64_t n, float* workspace, void* stream) {
+  if (n == 0) return FLOWCUDA_OK;
   FC_REQUIRE(theta && y && x && workspace, "bernstein_inverse: NULL pointer");
   FC_REQUIRE(order >= 2 && order <= kBernMaxOrder, "bernstein_inverse: order=%d outside [2,%d]", order, kBernMaxOrder);
   FC_REQUIRE(n_events >= 1 && n_points >= 2 && n >= 0, "bernstein_inverse: bad sizes");

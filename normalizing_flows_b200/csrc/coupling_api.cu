@@ -39,8 +39,9 @@ static int run(const flowcuda_coupling_spec* sp, const float* params, const floa
                cudaStream_t s) {
   int rc = check_spec(sp);
   if (rc) return rc;
-  FC_REQUIRE(params && in, "coupling: NULL params or input");
   FC_REQUIRE(n >= 0, "coupling: negative n");
+  if (n == 0) return FLOWCUDA_OK;
+  FC_REQUIRE(params && in, "coupling: NULL params or input");
   FC_REQUIRE(lb >= 0 && le <= sp->num_layers && lb <= le, "coupling: layer range [%d,%d) outside [0,%d]", lb, le, sp->num_layers);
   FC_REQUIRE(sp->precision == FLOWCUDA_PRECISION_FP32, "coupling: tensor-core precisions are not built into this library version");
   if (n == 0) return FLOWCUDA_OK;
@@ -78,6 +79,7 @@ size_t flowcuda_coupling_workspace_bytes(const flowcuda_coupling_spec* spec, int
 int flowcuda_coupling_log_prob(const flowcuda_coupling_spec* spec, const float* params, const float* x, float* log_prob,
                                float* z, float* log_det, int64_t n, int layer_begin, int layer_end, int with_base,
                                void* workspace, size_t workspace_bytes, void* stream) {
+  if (n == 0) return FLOWCUDA_OK;
   FC_REQUIRE(log_prob || z || log_det, "coupling_log_prob: no output requested");
   return run(spec, params, x, z, log_prob, log_det, n, layer_begin, layer_end, with_base, false, workspace,
              workspace_bytes, (cudaStream_t)stream);
@@ -86,6 +88,7 @@ int flowcuda_coupling_log_prob(const flowcuda_coupling_spec* spec, const float* 
 int flowcuda_coupling_sample(const flowcuda_coupling_spec* spec, const float* params, const float* z, float* x,
                              float* log_det, int64_t n, int layer_begin, int layer_end, void* workspace,
                              size_t workspace_bytes, void* stream) {
+  if (n == 0) return FLOWCUDA_OK;
   FC_REQUIRE(x || log_det, "coupling_sample: no output requested");
   return run(spec, params, z, x, nullptr, log_det, n, layer_begin, layer_end, 0, true, workspace, workspace_bytes,
              (cudaStream_t)stream);

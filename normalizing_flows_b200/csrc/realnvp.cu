@@ -126,6 +126,8 @@ realnvp_chain_kernel(const float* __restrict__ params, int L, int Hrt, uint64_t 
 template <int MODE>
 static int launch_chain(const float* params, int L, int H, uint64_t flip_mask, const float* in, float* out_v,
                         float* out_lp, float* out_ls, int64_t n, cudaStream_t s) {
+  FC_REQUIRE(n >= 0, "realnvp: negative n");
+  if (n == 0) return FLOWCUDA_OK;
   FC_REQUIRE(params && in, "realnvp: NULL params or input");
   FC_REQUIRE(L >= 1 && L <= kNvpMaxLayers, "realnvp: n_layers=%d outside [1,%d]", L, kNvpMaxLayers);
   FC_REQUIRE(H >= 1 && H <= kNvpMaxHidden, "realnvp: hidden=%d outside [1,%d]", H, kNvpMaxHidden);
@@ -158,24 +160,28 @@ extern "C" {
 
 int flowcuda_realnvp_log_prob(const float* params, int n_layers, int hidden, uint64_t flip_mask, const float* y,
                               float* log_prob, float* z, int64_t n, void* stream) {
+  if (n == 0) return FLOWCUDA_OK;
   FC_REQUIRE(log_prob || z, "realnvp_log_prob: no output requested");
   return launch_chain<0>(params, n_layers, hidden, flip_mask, y, z, log_prob, nullptr, n, (cudaStream_t)stream);
 }
 
 int flowcuda_realnvp_sample(const float* params, int n_layers, int hidden, uint64_t flip_mask, const float* z,
                             float* x, int64_t n, void* stream) {
+  if (n == 0) return FLOWCUDA_OK;
   FC_REQUIRE(x, "realnvp_sample: NULL output");
   return launch_chain<1>(params, n_layers, hidden, flip_mask, z, x, nullptr, nullptr, n, (cudaStream_t)stream);
 }
 
 int flowcuda_realnvp_forward(const float* layer_params, int hidden, int flip, const float* x, float* y, int64_t n,
                              void* stream) {
+  if (n == 0) return FLOWCUDA_OK;
   FC_REQUIRE(y, "realnvp_forward: NULL output");
   return launch_chain<1>(layer_params, 1, hidden, flip ? 1ull : 0ull, x, y, nullptr, nullptr, n, (cudaStream_t)stream);
 }
 
 int flowcuda_realnvp_inverse(const float* layer_params, int hidden, int flip, const float* y, float* x,
                              float* log_scale, int64_t n, void* stream) {
+  if (n == 0) return FLOWCUDA_OK;
   FC_REQUIRE(x || log_scale, "realnvp_inverse: no output requested");
   return launch_chain<0>(layer_params, 1, hidden, flip ? 1ull : 0ull, y, x, nullptr, log_scale, n, (cudaStream_t)stream);
 }
