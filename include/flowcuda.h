@@ -199,6 +199,18 @@ int flowcuda_sgd_step(float* p, const float* g, int64_t count, float lr, float g
 int flowcuda_adam_step(float* p, const float* g, float* m, float* v, int64_t count, int64_t step,
                        float lr, float b1, float b2, float eps, float grad_scale, void* stream);
 
+/* ------------------------------------------------------------------------------------
+ * Diagnostics — one 128-row tile through every tensor-core primitive the flow kernels use
+ * (tile-image staging, TMA bulk copy, tcgen05.mma kind::tf32 / kind::f16 in 1- and 3-pass
+ * form, tcgen05.commit, tcgen05.ld at aligned and unaligned columns).
+ *   d[128,n] = a[128,k] @ w[k,n];  mode 0 tf32x3, 1 bf16x3, 2 tf32, 3 bf16.
+ * d_unaligned (optional, [128,n]) receives columns [0, 25*(n/25)) re-read in 25-column
+ * groups at unaligned TMEM offsets.
+ * ---------------------------------------------------------------------------------- */
+size_t flowcuda_selftest_umma_workspace_bytes(int n, int k);
+int flowcuda_selftest_umma(const float* a, const float* w, float* d, float* d_unaligned, int n, int k,
+                           int mode, void* workspace, size_t workspace_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -69,6 +69,8 @@ SIGNATURES = {
     "flowcuda_sum_scaled": (_i, [_p, _i64, _d, _p, _p, _p]),
     "flowcuda_sgd_step": (_i, [_p, _p, _i64, _f, _f, _p]),
     "flowcuda_adam_step": (_i, [_p, _p, _p, _p, _i64, _i64, _f, _f, _f, _f, _f, _p]),
+    "flowcuda_selftest_umma_workspace_bytes": (_sz, [_i, _i]),
+    "flowcuda_selftest_umma": (_i, [_p, _p, _p, _p, _i, _i, _i, _p, _sz, _p]),
 }
 
 _lib = None

@@ -1,0 +1,203 @@
+// tc.cuh — hand-written Blackwell (sm_100a) tensor-core primitives used by the flow kernels:
+// mbarrier, TMA bulk copy (cp.async.bulk -> UBLKCP), TMEM allocation, tcgen05.mma
+// (kind::tf32 / kind::f16) with shared-memory operand descriptors, tcgen05.commit and
+// tcgen05.ld.  No CUTLASS/CuTe: the encodings below follow the PTX ISA tcgen05 tables.
+//
+// Operand layout used everywhere in this library ("tile image"): K-major, no swizzle.
+// A tile of R rows (R % 8 == 0) by K elements is stored as 16-byte chunks (CH = 16/sizeof(T)
+// elements along K); 8 rows x 16 B form one contiguous 128-byte core matrix:
+//     byte(r, k) = ((k / CH) * (R / 8) + r / 8) * 128 + (r % 8) * 16 + (k % CH) * sizeof(T)
+// so the leading-dimension byte offset (between the two K chunks one MMA consumes) is
+// LBO = R/8 * 128 and the stride byte offset (between 8-row groups) is SBO = 128.
+// One tcgen05.mma consumes 32 bytes of K (8 tf32 / 16 bf16) = 2 chunks: K step s starts at
+// base + s * 2 * LBO.  A warp of 32 consecutive rows writing one chunk each touches 512
+// contiguous bytes (conflict-free), and a whole tile is one contiguous block, i.e. one
+// cp.async.bulk when the same image is kept in global memory.
+#pragma once
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace flowcuda {
+namespace tc {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// ---- tile image addressing --------------------------------------------------------------
+// byte offset of chunk (r, kc) in an R-row tile image
+__host__ __device__ __forceinline__ uint32_t img_off(int R, int r, int kc) {
+  return (uint32_t)((kc * (R >> 3) + (r >> 3)) * 128 + (r & 7) * 16);
+}
+
+// ---- mbarrier -----------------------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+
+// ---- TMA bulk copy global -> shared, completion on an mbarrier ------------------------------
+__device__ __forceinline__ void tma_bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+// ---- proxy / tcgen05 fences --------------------------------------------------------------------
+// generic-proxy st.shared must be made visible to the async proxy (tensor core reads) first
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// ---- TMEM allocation (one full warp executes these) -----------------------------------------
+__device__ __forceinline__ void tmem_alloc(uint32_t* result_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(result_smem)),
+               "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+
+// ---- descriptors ------------------------------------------------------------------------------
+// shared-memory matrix descriptor: start>>4 [0,14), LBO>>4 [16,30), SBO>>4 [32,46),
+// version=1 [46,48), base_offset=0, layout_type [61,64) = 0 (no swizzle)
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = (uint64_t)((saddr >> 4) & 0x3FFFu);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFFu) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFFu) << 32;
+  d |= (uint64_t)1 << 46;
+  return d;
+}
+constexpr uint32_t kFmtBF16 = 1, kFmtTF32 = 2;
+// instruction descriptor: D=f32 [4,6)=1, A fmt [7,10), B fmt [10,13), A/B K-major (bits 15,16 = 0),
+// N>>3 [17,23), M>>4 [24,29)
+__host__ __device__ constexpr uint32_t make_idesc(uint32_t fmt, int M, int N) {
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// ---- MMA issue (ONE thread) -----------------------------------------------------------------------
+template <uint32_t FMT>
+__device__ __forceinline__ void mma_ss(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  if (FMT == kFmtTF32) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  }
+}
+// all MMAs issued so far by this thread arrive on `bar` when they complete
+// (implies tcgen05.fence::before_thread_sync)
+__device__ __forceinline__ void mma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+
+// Error-compensated 3-pass product D (+)= A·B with A = Ah + Al, B = Bh + Bl given as separate
+// tile images: Ah·Bh + Ah·Bl + Al·Bh (the Al·Bl term is below the split's own rounding).
+// a_rows / b_rows: rows of the A / B tile image; ksteps: number of 32-byte K steps.
+template <uint32_t FMT>
+__device__ __forceinline__ void mma_3pass(uint32_t d_tmem, uint32_t a_hi, uint32_t a_lo, int a_rows, uint32_t b_hi,
+                                          uint32_t b_lo, int b_rows, int ksteps, uint32_t idesc, bool accumulate_first) {
+  const uint32_t lbo_a = (uint32_t)(a_rows >> 3) * 128u, lbo_b = (uint32_t)(b_rows >> 3) * 128u;
+  uint32_t acc = accumulate_first ? 1u : 0u;
+#pragma unroll 1
+  for (int pass = 0; pass < 3; ++pass) {
+    const uint32_t a = pass == 2 ? a_lo : a_hi;
+    const uint32_t b = pass == 1 ? b_lo : b_hi;
+    for (int s = 0; s < ksteps; ++s) {
+      mma_ss<FMT>(d_tmem, make_smem_desc(a + (uint32_t)s * 2u * lbo_a, lbo_a, 128u),
+                  make_smem_desc(b + (uint32_t)s * 2u * lbo_b, lbo_b, 128u), idesc, acc);
+      acc = 1u;
+    }
+  }
+}
+
+// ---- TMEM -> registers: warp w reads lanes 32*(w%4)..+31; thread t gets lane base+t, N consecutive columns
+#define FC_TMEM_LD_DECL(N)                                                        \
+  __device__ __forceinline__ void tmem_ld_x##N(uint32_t taddr, uint32_t* v)
+
+FC_TMEM_LD_DECL(1) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(v[0]) : "r"(taddr));
+}
+FC_TMEM_LD_DECL(2) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x2.b32 {%0,%1}, [%2];" : "=r"(v[0]), "=r"(v[1]) : "r"(taddr));
+}
+FC_TMEM_LD_DECL(4) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3])
+               : "r"(taddr));
+}
+FC_TMEM_LD_DECL(8) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+               : "r"(taddr));
+}
+FC_TMEM_LD_DECL(16) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr));
+}
+FC_TMEM_LD_DECL(32) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,"
+      "%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr));
+}
+#undef FC_TMEM_LD_DECL
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// ---- precision splits ---------------------------------------------------------------------------
+// tf32: the tensor core reads the top 19 bits of an fp32 word; hi = x with the low 13 bits
+// cleared (exactly what the hardware would see), lo = x - hi (exact in fp32).
+__device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
+  hi = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);
+  lo = x - hi;
+}
+// bf16: hi = rn(x), lo = rn(x - hi); packs two elements per 32-bit word (element 0 in the low half)
+__device__ __forceinline__ void split_bf16x2(float x0, float x1, uint32_t& hi, uint32_t& lo) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(x0, x1);
+  float r0 = x0 - __low2float(h), r1 = x1 - __high2float(h);
+  __nv_bfloat162 l = __floats2bfloat162_rn(r0, r1);
+  hi = *reinterpret_cast<uint32_t*>(&h);
+  lo = *reinterpret_cast<uint32_t*>(&l);
+}
+
+}  // namespace tc
+}  // namespace flowcuda

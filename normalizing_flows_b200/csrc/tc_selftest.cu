@@ -1,0 +1,174 @@
+// tc_selftest.cu — diagnostic entry point that exercises every tensor-core primitive of tc.cuh
+// on one 128-row tile: tile-image staging by st.shared (A) and by pack kernel + TMA bulk copy
+// (B), tcgen05.mma kind::tf32 / kind::f16 in 1-pass and 3-pass form, tcgen05.commit ->
+// mbarrier, tcgen05.ld at aligned and unaligned column offsets.  tests/test_gpu_tc.py compares
+// the result with a float64 matmul.
+#include "tc.cuh"
+
+namespace flowcuda {
+
+// W[K,N] row-major fp32 (y = x @ W) -> B-operand tile images (rows = n, K-major), hi and lo.
+// BF16 = false: tf32 words (4 per chunk); true: bf16 (8 per chunk).
+template <bool BF16>
+__global__ void __launch_bounds__(256) pack_b_image_kernel(const float* __restrict__ W, int K, int N, int ldw,
+                                                           uint8_t* __restrict__ hi, uint8_t* __restrict__ lo) {
+  constexpr int CH = BF16 ? 8 : 4;
+  const int chunks = K / CH;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N * chunks; i += gridDim.x * blockDim.x) {
+    const int n = i % N, kc = i / N;
+    const uint32_t off = tc::img_off(N, n, kc);
+    float v[CH];
+#pragma unroll
+    for (int e = 0; e < CH; ++e) v[e] = W[(size_t)(kc * CH + e) * ldw + n];
+    if (BF16) {
+      uint32_t h[4], l[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) tc::split_bf16x2(v[2 * e], v[2 * e + 1], h[e], l[e]);
+      *reinterpret_cast<uint4*>(hi + off) = make_uint4(h[0], h[1], h[2], h[3]);
+      *reinterpret_cast<uint4*>(lo + off) = make_uint4(l[0], l[1], l[2], l[3]);
+    } else {
+      float h[4], l[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) tc::split_tf32(v[e], h[e], l[e]);
+      *reinterpret_cast<float4*>(hi + off) = make_float4(h[0], h[1], h[2], h[3]);
+      *reinterpret_cast<float4*>(lo + off) = make_float4(l[0], l[1], l[2], l[3]);
+    }
+  }
+}
+
+template <bool BF16>
+__global__ void __launch_bounds__(128) tc_selftest_kernel(const float* __restrict__ A, const uint8_t* __restrict__ Bhi,
+                                                          const uint8_t* __restrict__ Blo, float* __restrict__ D,
+                                                          float* __restrict__ D2, int N, int K, int three_pass,
+                                                          uint32_t tmem_cols) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  constexpr int CH = BF16 ? 8 : 4;
+  constexpr int ES = BF16 ? 2 : 4;
+  constexpr uint32_t FMT = BF16 ? tc::kFmtBF16 : tc::kFmtTF32;
+  const uint32_t a_bytes = 128u * K * ES, b_bytes = (uint32_t)N * K * ES;
+  uint8_t* a_hi = smem;
+  uint8_t* a_lo = a_hi + a_bytes;
+  uint8_t* b_hi = a_lo + a_bytes;
+  uint8_t* b_lo = b_hi + b_bytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(b_lo + b_bytes);  // [0] B landed, [1] D ready
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+  const int tid = threadIdx.x, warp = tid >> 5;
+
+  if (warp == 0) tc::tmem_alloc(tmem_slot, tmem_cols);
+  if (tid == 0) {
+    tc::mbar_init(&bars[0], 1);
+    tc::mbar_init(&bars[1], 1);
+    tc::fence_mbar_init();
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (tid == 0) {
+    tc::mbar_arrive_expect_tx(&bars[0], 2 * b_bytes);
+    tc::tma_bulk_g2s(b_hi, Bhi, b_bytes, &bars[0]);
+    tc::tma_bulk_g2s(b_lo, Blo, b_bytes, &bars[0]);
+  }
+  // A: thread = row
+  for (int kc = 0; kc < K / CH; ++kc) {
+    const float* src = A + (size_t)tid * K + kc * CH;
+    const uint32_t off = tc::img_off(128, tid, kc);
+    if (BF16) {
+      uint32_t h[4], l[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) tc::split_bf16x2(src[2 * e], src[2 * e + 1], h[e], l[e]);
+      *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(h[0], h[1], h[2], h[3]);
+      *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(l[0], l[1], l[2], l[3]);
+    } else {
+      float h[4], l[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) tc::split_tf32(src[e], h[e], l[e]);
+      *reinterpret_cast<float4*>(a_hi + off) = make_float4(h[0], h[1], h[2], h[3]);
+      *reinterpret_cast<float4*>(a_lo + off) = make_float4(l[0], l[1], l[2], l[3]);
+    }
+  }
+  tc::fence_async_smem();
+  __syncthreads();
+
+  if (tid == 0) {
+    tc::mbar_wait(&bars[0], 0);
+    tc::tc_fence_after();
+    const uint32_t idesc = tc::make_idesc(FMT, 128, N);
+    const int ksteps = K / (2 * CH);
+    if (three_pass) {
+      tc::mma_3pass<FMT>(tmem, tc::smem_u32(a_hi), tc::smem_u32(a_lo), 128, tc::smem_u32(b_hi), tc::smem_u32(b_lo), N,
+                         ksteps, idesc, false);
+    } else {
+      const uint32_t lbo_a = 16u * 128u, lbo_b = (uint32_t)(N >> 3) * 128u;
+      for (int s = 0; s < ksteps; ++s)
+        tc::mma_ss<FMT>(tmem, tc::make_smem_desc(tc::smem_u32(a_hi) + s * 2u * lbo_a, lbo_a, 128u),
+                        tc::make_smem_desc(tc::smem_u32(b_hi) + s * 2u * lbo_b, lbo_b, 128u), idesc, s > 0);
+    }
+    tc::mma_commit(&bars[1]);
+  }
+  tc::mbar_wait(&bars[1], 0);
+  tc::tc_fence_after();
+  const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+  for (int c = 0; c < N; c += 8) {
+    uint32_t v[8];
+    tc::tmem_ld_x8(lane_base + (uint32_t)c, v);
+    tc::tmem_ld_wait();
+#pragma unroll
+    for (int e = 0; e < 8; ++e) D[(size_t)tid * N + c + e] = __uint_as_float(v[e]);
+  }
+  if (D2) {  // 25-column groups at unaligned offsets: x16 @25d, x8 @25d+16, x1 @25d+24
+    for (int d = 0; d < N / 25; ++d) {
+      uint32_t v[25];
+      tc::tmem_ld_x16(lane_base + (uint32_t)(25 * d), v);
+      tc::tmem_ld_x8(lane_base + (uint32_t)(25 * d + 16), v + 16);
+      tc::tmem_ld_x1(lane_base + (uint32_t)(25 * d + 24), v + 24);
+      tc::tmem_ld_wait();
+#pragma unroll
+      for (int e = 0; e < 25; ++e) D2[(size_t)tid * N + 25 * d + e] = __uint_as_float(v[e]);
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, tmem_cols);
+}
+
+}  // namespace flowcuda
+
+using namespace flowcuda;
+
+extern "C" {
+
+size_t flowcuda_selftest_umma_workspace_bytes(int n, int k) { return (size_t)2 * n * k * 4 + 512; }
+
+int flowcuda_selftest_umma(const float* a, const float* w, float* d, float* d_unaligned, int n, int k, int mode,
+                           void* workspace, size_t workspace_bytes, void* stream) {
+  FC_REQUIRE(a && w && d && workspace, "selftest_umma: NULL pointer");
+  FC_REQUIRE(mode >= 0 && mode <= 3, "selftest_umma: mode must be 0 (tf32x3), 1 (bf16x3), 2 (tf32), 3 (bf16)");
+  const bool bf16 = (mode & 1) != 0;
+  FC_REQUIRE(n >= 16 && n <= 256 && n % 16 == 0, "selftest_umma: n=%d must be a multiple of 16 in [16,256]", n);
+  FC_REQUIRE(k >= 16 && k % 16 == 0 && k <= 128, "selftest_umma: k=%d must be a multiple of 16 in [16,128]", k);
+  FC_REQUIRE(workspace_bytes >= flowcuda_selftest_umma_workspace_bytes(n, k), "selftest_umma: workspace too small");
+  cudaStream_t s = (cudaStream_t)stream;
+  const int es = bf16 ? 2 : 4;
+  uint8_t* hi = (uint8_t*)(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
+  uint8_t* lo = hi + (size_t)n * k * es;
+  uint32_t cols = 32;
+  while (cols < (uint32_t)n) cols <<= 1;
+  size_t smem = (size_t)2 * 128 * k * es + (size_t)2 * n * k * es + 64;
+  if (bf16) {
+    pack_b_image_kernel<true><<<8, 256, 0, s>>>(w, k, n, n, hi, lo);
+    FC_LAUNCH_CHECK("pack_b_image_kernel");
+    FC_CUDA(cudaFuncSetAttribute(tc_selftest_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    tc_selftest_kernel<true><<<1, 128, smem, s>>>(a, hi, lo, d, d_unaligned, n, k, mode < 2, cols);
+  } else {
+    pack_b_image_kernel<false><<<8, 256, 0, s>>>(w, k, n, n, hi, lo);
+    FC_LAUNCH_CHECK("pack_b_image_kernel");
+    FC_CUDA(cudaFuncSetAttribute(tc_selftest_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    tc_selftest_kernel<false><<<1, 128, smem, s>>>(a, hi, lo, d, d_unaligned, n, k, mode < 2, cols);
+  }
+  FC_LAUNCH_CHECK("tc_selftest_kernel");
+  return FLOWCUDA_OK;
+}
+
+}  // extern "C"

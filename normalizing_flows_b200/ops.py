@@ -248,3 +248,19 @@ def adam_step(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor
     _dev_check(p, g, m, v)
     check(_lib.load().flowcuda_adam_step(_ptr(p), _ptr(g), _ptr(m), _ptr(v), p.numel(), int(step), float(lr), float(b1),
                                          float(b2), float(eps), float(grad_scale), _stream()), "adam_step")
+
+
+# ---------------------------------------------------------------------------- diagnostics
+def selftest_umma(a: torch.Tensor, w: torch.Tensor, mode: int, want_unaligned: bool = False):
+    """d[128,n] = a[128,k] @ w[k,n] through the tcgen05 primitives (mode 0 tf32x3, 1 bf16x3, 2 tf32, 3 bf16)."""
+    a, w = _f32(a), _f32(w)
+    _dev_check(a, w)
+    k, n = w.shape
+    lib = _lib.load()
+    need = lib.flowcuda_selftest_umma_workspace_bytes(n, k)
+    ws = torch.empty((need + 3) // 4, device=a.device, dtype=torch.float32)
+    d = torch.zeros(128, n, device=a.device, dtype=torch.float32)
+    d2 = torch.zeros(128, n, device=a.device, dtype=torch.float32) if want_unaligned else None
+    check(lib.flowcuda_selftest_umma(_ptr(a), _ptr(w), _ptr(d), _ptr(d2), n, k, mode, _ptr(ws), ws.numel() * 4,
+                                     _stream()), "selftest_umma")
+    return (d, d2) if want_unaligned else d
