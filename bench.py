@@ -74,6 +74,8 @@ class Workload:
     bound = "hbm"
     dtype = "f32"
     launches_per_step = 1
+    tc_launches = 2      # weight pack + fused stack kernel
+    tc_dtype = "tf32x3 (fp32 accumulate)"
     cpu_sample = 1 << 16
 
     def make_inputs(self, gen, n):
@@ -94,6 +96,8 @@ class CouplingWorkload(Workload):
     ospec_name = "RQS_TOY"
     data = staticmethod(gaussian_blobs)
     transform = "rqs"
+    precision = "tc"   # "tc": tensor-core path (3xTF32 at event_dim 2); "fp32": CUDA-core FP32 path
+    tc_precision = 1   # FLOWCUDA_PRECISION_3XTF32
 
     def _ospec(self):
         from oracle import flows_oracle as O
@@ -118,7 +122,11 @@ class CouplingWorkload(Workload):
         flat = O.flatten_layers(self._p).float()
         self.model = flows.make_flow_model((sp.event_dim,), sp.num_layers, sp.hidden, transform=self.transform,
                                            num_bins=sp.num_bins, range_min=sp.range_min, range_max=sp.range_max,
-                                           base=sp.base, params=flat.to(dev))
+                                           base=sp.base, params=flat.to(dev),
+                                           precision=self.tc_precision if self.precision == "tc" else 0)
+        if self.precision == "tc":
+            self.launches_per_step = self.tc_launches
+            self.dtype = self.tc_dtype
 
     def run(self, x):
         return self.model.log_prob(x)
@@ -160,6 +168,7 @@ class MafMnist(CouplingWorkload):
     flops_per_sample = 95_100_000
     bound = "tensor"
     launches_per_step = 8 * 5 + 1
+    precision = "fp32"
     cpu_sample = 256
 
 
@@ -356,9 +365,13 @@ def main():
     ap.add_argument("--impl", default="flowcuda", choices=["flowcuda", "reference"])
     ap.add_argument("--workload", default="maf_toy", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--precision", default=None, choices=["tc", "fp32"],
+                    help="coupling workloads: tensor-core path (default where built) or the FP32 CUDA-core path")
     ap.add_argument("--others", action="store_true", help="also time the other workloads (kernel-only) into 'others'")
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
+    if args.precision is not None and issubclass(wl, CouplingWorkload):
+        wl.precision = args.precision
     if args.impl == "reference":
         run_reference(args, wl)
         return
@@ -397,6 +410,7 @@ def main():
             "warmup": W, "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": w.dtype, "data": "synthetic",
             "config": {"workload": w.name, "desc": w.desc, "samples_per_step_per_gpu": w.n, "parallelism": f"dp{world}",
+                       "precision": getattr(w, "precision", "fp32"),
                        "l2": f"inputs rotate over {res['nbuf']} distinct batches ({res['nbuf'] * w.n * w.bytes_per_sample / 1e6:.0f} MB > 126 MB L2)"},
             "roofline": roofline(w, res, peaks),
             "e2e": res["e2e"],

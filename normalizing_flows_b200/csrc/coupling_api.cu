@@ -6,6 +6,10 @@ namespace flowcuda {
 int coupling_toy_dispatch(const flowcuda_coupling_spec* sp, const float* params, const float* in, float* out_v,
                           float* out_lp, int64_t n, int layer_begin, int layer_end, int with_base, bool inverse,
                           cudaStream_t s);
+int coupling_toy_tc_dispatch(const flowcuda_coupling_spec* sp, const float* params, const float* in, float* out_v,
+                             float* out_lp, int64_t n, int layer_begin, int layer_end, int with_base, bool inverse,
+                             void* ws, size_t wsb, cudaStream_t s);
+size_t coupling_toy_tc_workspace_bytes(const flowcuda_coupling_spec* sp);
 int64_t coupling_param_count(const flowcuda_coupling_spec* sp);
 size_t coupling_dense_workspace_bytes(const flowcuda_coupling_spec* sp, int64_t n);
 int coupling_dense_run(const flowcuda_coupling_spec* sp, const float* params, const float* in, float* out_v,
@@ -43,8 +47,19 @@ static int run(const flowcuda_coupling_spec* sp, const float* params, const floa
   if (n == 0) return FLOWCUDA_OK;
   FC_REQUIRE(params && in, "coupling: NULL params or input");
   FC_REQUIRE(lb >= 0 && le <= sp->num_layers && lb <= le, "coupling: layer range [%d,%d) outside [0,%d]", lb, le, sp->num_layers);
-  FC_REQUIRE(sp->precision == FLOWCUDA_PRECISION_FP32, "coupling: tensor-core precisions are not built into this library version");
-  if (n == 0) return FLOWCUDA_OK;
+  if (sp->precision != FLOWCUDA_PRECISION_FP32) {
+    FC_REQUIRE(sp->precision == FLOWCUDA_PRECISION_3XTF32 && toy_eligible(sp) && le > lb,
+               "coupling: precision %d is not available for this flow shape (3xTF32 needs event_dim 2, two hidden layers <= 64)",
+               sp->precision);
+    FC_REQUIRE((((uintptr_t)in | (uintptr_t)out_v) & 7) == 0, "coupling: [N,2] buffers must be 8-byte aligned");
+    if (out_lp && out_ld) {
+      rc = coupling_toy_tc_dispatch(sp, params, in, nullptr, out_ld, n, lb, le, 0, inverse, ws, wsb, s);
+      if (rc) return rc;
+      return coupling_toy_tc_dispatch(sp, params, in, out_v, out_lp, n, lb, le, with_base, inverse, ws, wsb, s);
+    }
+    if (out_ld) return coupling_toy_tc_dispatch(sp, params, in, out_v, out_ld, n, lb, le, 0, inverse, ws, wsb, s);
+    return coupling_toy_tc_dispatch(sp, params, in, out_v, out_lp, n, lb, le, with_base, inverse, ws, wsb, s);
+  }
   if (toy_eligible(sp)) {
     FC_REQUIRE((((uintptr_t)in | (uintptr_t)out_v) & 7) == 0, "coupling: [N,2] buffers must be 8-byte aligned");
     if (out_lp && out_ld) {
@@ -73,6 +88,7 @@ int64_t flowcuda_coupling_param_count(const flowcuda_coupling_spec* spec) {
 size_t flowcuda_coupling_workspace_bytes(const flowcuda_coupling_spec* spec, int64_t n) {
   if (check_spec(spec) || n < 0) return 0;
   if (toy_eligible(spec) && spec->precision == FLOWCUDA_PRECISION_FP32) return 0;
+  if (toy_eligible(spec) && spec->precision == FLOWCUDA_PRECISION_3XTF32) return coupling_toy_tc_workspace_bytes(spec);
   return coupling_dense_workspace_bytes(spec, n);
 }
 

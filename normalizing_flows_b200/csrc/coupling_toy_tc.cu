@@ -1,0 +1,420 @@
+// coupling_toy_tc.cu — rows #2/#3/#6 at event_dim = 2 on the 5th-gen tensor cores
+// (FLOWCUDA_PRECISION_3XTF32): the whole distrax MaskedCoupling stack of
+// src/real_nvp_toy_densities.py:74-110 / src/maf_toy_densities.py:73-111 in ONE persistent
+// kernel, the two hidden Linears of every conditioner as tcgen05.mma kind::tf32 in
+// error-compensated 3-pass form (hi·hi + hi·lo + lo·hi, fp32 accumulate in TMEM).
+//
+// CTA = 2 sample warpgroups + 1 MMA-issuer warp + 1 weight-loader warp, one CTA per SM.
+// A warpgroup owns a 128-sample tile: thread = sample = TMEM lane.  Per flow layer
+//   L1  (2->64, only the visible coordinate contributes): CUDA cores, result split into tf32
+//       hi/lo and written straight into TMEM as the A operand (tcgen05.st) — activations never
+//       touch shared or global memory;
+//   L2  (64->64): 24 MMAs M128 N64 K8, A from TMEM, W2 (hi/lo tile images) from shared memory;
+//   epilogue 2: tcgen05.ld, +bias, relu, split, tcgen05.st back as the next A operand;
+//   L3  (64->needed columns only, padded to N3): 24 MMAs M128 N{48,32,16};
+//   epilogue 3: tcgen05.ld of the 3K+1 spline (or 2 affine) parameters of the transformed
+//       coordinate, inner bijector, log-det accumulation.
+// The two warpgroups' tiles interleave on the tensor pipe (one computes its epilogue while the
+// other's MMAs run).  Weights of a layer are one contiguous pre-packed image fetched by a single
+// cp.async.bulk (TMA) into a double-buffered slot and shared by T tile pairs whose per-sample
+// state (x0, x1, log-det) waits in shared memory, so a chunk of T*256 samples reads each layer's
+// weights once.  HBM traffic: x in, log_prob (and/or z) out.
+#include "tc.cuh"
+#include "transforms.cuh"
+
+namespace flowcuda {
+
+constexpr int kTcThreads = 320;  // warps 0-3: WG0, 4-7: WG1, 8: MMA issuer, 9: loader
+constexpr int kTcMaxT = 8;       // tile pairs per chunk
+
+template <int N3>
+struct ToyTcImg {  // per-layer packed image (bytes)
+  static constexpr int w2 = 64 * 64 * 4;                  // one of hi / lo
+  static constexpr int w3 = N3 * 64 * 4;
+  static constexpr int off_w2hi = 0, off_w2lo = w2, off_w3hi = 2 * w2, off_w3lo = 2 * w2 + w3;
+  static constexpr int wbytes = 2 * w2 + 2 * w3;          // the TMA-fetched part
+  static constexpr int small_floats = 192 + N3;           // w1(visible row)[64] b1[64] b2[64] b3[N3]
+  static constexpr int bytes = (wbytes + small_floats * 4 + 127) & ~127;
+};
+
+__host__ __device__ constexpr int toy_need(int TR, int KT) { return TR == FLOWCUDA_TRANSFORM_RQS ? 3 * KT + 1 : 2; }
+__host__ __device__ constexpr int toy_n3(int TR, int KT) { return (toy_need(TR, KT) + 15) & ~15; }
+
+struct ToyTcArgs {
+  const uint8_t* img;  // [num_layers][Img::bytes]
+  const float* in;     // [N,2]
+  float* out_v;        // [N,2] or NULL
+  float* out_lp;       // [N] or NULL
+  int64_t n;
+  int layer_begin, layer_end;
+  int with_base, base;
+  float lo, hi;
+  int T;               // tile pairs per chunk
+};
+
+// params (haiku order) -> per-layer image.  One CTA per flow layer.
+template <int TR, int KT>
+__global__ void __launch_bounds__(256) toy_tc_pack_kernel(const float* __restrict__ params, int h1, int h2, int of,
+                                                          uint8_t* __restrict__ img) {
+  constexpr int NEED = toy_need(TR, KT), N3 = toy_n3(TR, KT);
+  using I = ToyTcImg<N3>;
+  const int l = blockIdx.x;
+  const size_t per_layer = (size_t)2 * h1 + h1 + (size_t)h1 * h2 + h2 + (size_t)h2 * of + of;
+  const float* p = params + per_layer * l;
+  const float* pW1 = p;
+  const float* pb1 = pW1 + 2 * h1;
+  const float* pW2 = pb1 + h1;
+  const float* pb2 = pW2 + (size_t)h1 * h2;
+  const float* pW3 = pb2 + h2;
+  const float* pb3 = pW3 + (size_t)h2 * of;
+  uint8_t* out = img + (size_t)l * I::bytes;
+  const int t = l & 1;  // transformed coordinate; the visible one is 1 - t
+  const int col0 = TR == FLOWCUDA_TRANSFORM_AFFINE_SCALAR ? 0 : t * NEED;
+  for (int i = threadIdx.x; i < 64 * 16; i += blockDim.x) {  // W2: rows n (out), 16 K chunks
+    const int n = i & 63, kc = i >> 6;
+    float h[4], lo[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int k = kc * 4 + e;
+      tc::split_tf32_rn((k < h1 && n < h2) ? pW2[(size_t)k * h2 + n] : 0.f, h[e], lo[e]);
+    }
+    const uint32_t off = tc::img_off(64, n, kc);
+    *reinterpret_cast<float4*>(out + I::off_w2hi + off) = make_float4(h[0], h[1], h[2], h[3]);
+    *reinterpret_cast<float4*>(out + I::off_w2lo + off) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+  }
+  for (int i = threadIdx.x; i < N3 * 16; i += blockDim.x) {  // W3: needed columns only
+    const int n = i % N3, kc = i / N3;
+    float h[4], lo[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int k = kc * 4 + e;
+      tc::split_tf32_rn((k < h2 && n < NEED) ? pW3[(size_t)k * of + col0 + n] : 0.f, h[e], lo[e]);
+    }
+    const uint32_t off = tc::img_off(N3, n, kc);
+    *reinterpret_cast<float4*>(out + I::off_w3hi + off) = make_float4(h[0], h[1], h[2], h[3]);
+    *reinterpret_cast<float4*>(out + I::off_w3lo + off) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+  }
+  float* sm = reinterpret_cast<float*>(out + I::wbytes);
+  for (int i = threadIdx.x; i < I::small_floats; i += blockDim.x) {
+    float v = 0.f;
+    if (i < 64) v = i < h1 ? pW1[(1 - t) * h1 + i] : 0.f;
+    else if (i < 128) v = (i - 64) < h1 ? pb1[i - 64] : 0.f;
+    else if (i < 192) v = (i - 128) < h2 ? pb2[i - 128] : 0.f;
+    else v = (i - 192) < NEED ? pb3[col0 + i - 192] : 0.f;
+    sm[i] = v;
+  }
+}
+
+// load NEED consecutive TMEM columns of this thread's lane into o[]
+template <int NEED>
+__device__ __forceinline__ void tmem_load_cols(uint32_t taddr, uint32_t* o) {
+  constexpr int c32 = NEED >= 32 ? 32 : 0;
+  constexpr int c16 = (NEED - c32) >= 16 ? 16 : 0;
+  constexpr int c8 = (NEED - c32 - c16) >= 8 ? 8 : 0;
+  constexpr int c4 = (NEED - c32 - c16 - c8) >= 4 ? 4 : 0;
+  constexpr int c2 = (NEED - c32 - c16 - c8 - c4) >= 2 ? 2 : 0;
+  constexpr int c1 = NEED - c32 - c16 - c8 - c4 - c2;
+  static_assert(NEED < 64 && c1 <= 1, "unsupported column count");
+  if (c32) tc::tmem_ld_x32(taddr, o);
+  if (c16) tc::tmem_ld_x16(taddr + c32, o + c32);
+  if (c8) tc::tmem_ld_x8(taddr + c32 + c16, o + c32 + c16);
+  if (c4) tc::tmem_ld_x4(taddr + c32 + c16 + c8, o + c32 + c16 + c8);
+  if (c2) tc::tmem_ld_x2(taddr + c32 + c16 + c8 + c4, o + c32 + c16 + c8 + c4);
+  if (c1) tc::tmem_ld_x1(taddr + c32 + c16 + c8 + c4 + c2, o + c32 + c16 + c8 + c4 + c2);
+  tc::tmem_ld_wait();
+}
+
+template <int TR, int KT, bool INV>
+__global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArgs a) {
+  constexpr int NEED = toy_need(TR, KT), N3 = toy_n3(TR, KT);
+  using I = ToyTcImg<N3>;
+  constexpr int SF = I::small_floats;
+  extern __shared__ __align__(128) uint8_t smem[];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int nl = a.layer_end - a.layer_begin;
+  const int T = a.T;
+  // ---- shared memory carve-up
+  uint8_t* wbuf = smem;                                             // [2][I::wbytes]
+  float* smalls = reinterpret_cast<float*>(wbuf + 2 * I::wbytes);   // [nl][SF]
+  float* sx0 = smalls + ((nl * SF + 3) & ~3);                       // [T*256] x 3
+  float* sx1 = sx0 + T * 256;
+  float* sld = sx1 + T * 256;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sld + T * 256);
+  uint64_t* a_ready = bars;       // [2] count 128: a warpgroup's A operand is in TMEM
+  uint64_t* d_full = bars + 2;    // [2] count 1: the MMAs of a warpgroup's request completed
+  uint64_t* w_full = bars + 4;    // [2] count 1 + tx: weight image landed
+  uint64_t* w_free = bars + 6;    // [2] count 1: every MMA reading the slot completed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+
+  if (warp == 8) tc::tmem_alloc(tmem_slot, 512);
+  if (tid == 0) {
+    for (int g = 0; g < 2; ++g) {
+      tc::mbar_init(&a_ready[g], 128);
+      tc::mbar_init(&d_full[g], 1);
+      tc::mbar_init(&w_full[g], 1);
+      tc::mbar_init(&w_free[g], 1);
+    }
+    tc::fence_mbar_init();
+  }
+  for (int i = tid; i < nl * SF; i += kTcThreads) {
+    const int it = i / SF;
+    const int l = INV ? a.layer_begin + it : a.layer_end - 1 - it;
+    smalls[i] = reinterpret_cast<const float*>(a.img + (size_t)l * I::bytes + I::wbytes)[i - it * SF];
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  const int64_t chunk_samples = (int64_t)T * 256;
+  const int64_t nchunks = (a.n + chunk_samples - 1) / chunk_samples;
+  const int my_chunks = blockIdx.x < nchunks ? (int)((nchunks - 1 - blockIdx.x) / gridDim.x + 1) : 0;
+  const int Q = my_chunks * nl;  // layer steps this CTA runs
+
+  if (warp == 9) {
+    // ===== weight loader: one cp.async.bulk per layer step into slot q&1 =====
+    if (lane == 0) {
+      for (int q = 0; q < Q; ++q) {
+        const int it = q % nl, b = q & 1;
+        const int l = INV ? a.layer_begin + it : a.layer_end - 1 - it;
+        if (q >= 2) tc::mbar_wait(&w_free[b], (uint32_t)(((q >> 1) - 1) & 1));
+        tc::mbar_arrive_expect_tx(&w_full[b], I::wbytes);
+        tc::tma_bulk_g2s(wbuf + b * I::wbytes, a.img + (size_t)l * I::bytes, I::wbytes, &w_full[b]);
+      }
+    }
+  } else if (warp == 8) {
+    // ===== MMA issuer: serves the two warpgroups' requests in arrival order =====
+    if (lane == 0) {
+      constexpr uint32_t idesc2 = tc::make_idesc(tc::kFmtTF32, 128, 64);
+      constexpr uint32_t idesc3 = tc::make_idesc(tc::kFmtTF32, 128, N3);
+      const int R = Q * T * 2;  // requests per warpgroup: (step, tile, {L2, L3})
+      int c[2] = {0, 0};
+      int done3[2] = {0, 0};    // L3 requests served per weight slot
+      while (c[0] < R || c[1] < R) {
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {
+          if (c[g] >= R) continue;
+          const int r = c[g];
+          const int q = r / (2 * T), p = r & 1, b = q & 1;
+          if (!tc::mbar_try_wait(&a_ready[g], (uint32_t)(r & 1))) continue;
+          if (!tc::mbar_try_wait(&w_full[b], (uint32_t)((q >> 1) & 1))) continue;
+          tc::tc_fence_after();
+          const uint32_t tb = tmem + (uint32_t)g * 192u;  // A hi [0,64) A lo [64,128) D [128,192)
+          const uint32_t wb = tc::smem_u32(wbuf + b * I::wbytes);
+          const uint32_t bh = wb + (p ? I::off_w3hi : I::off_w2hi), bl = wb + (p ? I::off_w3lo : I::off_w2lo);
+          const uint32_t lbo = (uint32_t)((p ? N3 : 64) >> 3) * 128u;
+          const uint32_t idesc = p ? idesc3 : idesc2;
+          uint32_t acc = 0;
+#pragma unroll 1
+          for (int pass = 0; pass < 3; ++pass) {
+            const uint32_t at = tb + (pass == 2 ? 64u : 0u);
+            const uint32_t bb = pass == 1 ? bl : bh;
+#pragma unroll
+            for (int s = 0; s < 8; ++s) {
+              tc::mma_ts<tc::kFmtTF32>(tb + 128u, at + 8u * s, tc::make_smem_desc(bb + (uint32_t)s * 2u * lbo, lbo, 128u),
+                                       idesc, acc);
+              acc = 1;
+            }
+          }
+          tc::mma_commit(&d_full[g]);
+          c[g] = r + 1;
+          if (p && ++done3[b] == 2 * T) {
+            done3[b] = 0;
+            tc::mma_commit(&w_free[b]);
+          }
+        }
+      }
+    }
+  } else {
+    // ===== sample warpgroups =====
+    const int g = warp >> 2, row = tid & 127;
+    const uint32_t tb = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)g * 192u;
+    uint32_t r = 0;  // request counter (parity of a_ready / d_full)
+    for (int ci = 0; ci < my_chunks; ++ci) {
+      const int64_t base = ((int64_t)blockIdx.x + (int64_t)ci * gridDim.x) * chunk_samples;
+      for (int t = 0; t < T; ++t) {
+        const int slot = t * 256 + g * 128 + row;
+        const int64_t idx = base + slot;
+        float2 v = idx < a.n ? ld_stream_f2(reinterpret_cast<const float2*>(a.in) + idx) : make_float2(0.f, 0.f);
+        sx0[slot] = v.x;
+        sx1[slot] = v.y;
+        sld[slot] = 0.f;
+      }
+      for (int it = 0; it < nl; ++it) {
+        const int l = INV ? a.layer_begin + it : a.layer_end - 1 - it;
+        const int td = l & 1;  // transformed coordinate (mask = arange(2)%2 on even layers, negated on odd)
+        const float* sm = smalls + it * SF;
+#pragma unroll 1
+        for (int t = 0; t < T; ++t) {
+          const int slot = t * 256 + g * 128 + row;
+          const float x0 = sx0[slot], x1 = sx1[slot];
+          const float xm = td ? x0 : x1;  // visible value
+          const float xt = td ? x1 : x0;  // value to transform
+          // ---- L1: Linear(2->64)+relu on where(mask, x, 0); split; A operand -> TMEM
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t hi[16], lo[16];
+#pragma unroll
+            for (int e4 = 0; e4 < 4; ++e4) {
+              const float4 w = *reinterpret_cast<const float4*>(sm + 16 * c + 4 * e4);
+              const float4 b = *reinterpret_cast<const float4*>(sm + 64 + 16 * c + 4 * e4);
+              const float h[4] = {fmaxf(fmaf(xm, w.x, b.x), 0.f), fmaxf(fmaf(xm, w.y, b.y), 0.f),
+                                  fmaxf(fmaf(xm, w.z, b.z), 0.f), fmaxf(fmaf(xm, w.w, b.w), 0.f)};
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                float fh, fl;
+                tc::split_tf32(h[e], fh, fl);
+                hi[4 * e4 + e] = __float_as_uint(fh);
+                lo[4 * e4 + e] = __float_as_uint(fl);
+              }
+            }
+            tc::tmem_st_x16(tb + 16u * c, hi);
+            tc::tmem_st_x16(tb + 64u + 16u * c, lo);
+          }
+          tc::tmem_st_wait();
+          tc::tc_fence_before();
+          tc::mbar_arrive(&a_ready[g]);
+          tc::mbar_wait(&d_full[g], r & 1);
+          ++r;
+          tc::tc_fence_after();
+          // ---- epilogue 2: +b2, relu, split, next A operand -> TMEM
+          {
+            uint32_t v[64];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) tc::tmem_ld_x16(tb + 128u + 16u * c, v + 16 * c);
+            tc::tmem_ld_wait();
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              uint32_t hi[16], lo[16];
+#pragma unroll
+              for (int e = 0; e < 16; ++e) {
+                float fh, fl;
+                tc::split_tf32(fmaxf(__uint_as_float(v[16 * c + e]) + sm[128 + 16 * c + e], 0.f), fh, fl);
+                hi[e] = __float_as_uint(fh);
+                lo[e] = __float_as_uint(fl);
+              }
+              tc::tmem_st_x16(tb + 16u * c, hi);
+              tc::tmem_st_x16(tb + 64u + 16u * c, lo);
+            }
+          }
+          tc::tmem_st_wait();
+          tc::tc_fence_before();
+          tc::mbar_arrive(&a_ready[g]);
+          tc::mbar_wait(&d_full[g], r & 1);
+          ++r;
+          tc::tc_fence_after();
+          // ---- epilogue 3: inner bijector on the transformed coordinate
+          float o[NEED];
+          {
+            uint32_t v[NEED];
+            tmem_load_cols<NEED>(tb + 128u, v);
+#pragma unroll
+            for (int i = 0; i < NEED; ++i) o[i] = __uint_as_float(v[i]) + sm[192 + i];
+          }
+          float nv, l1;
+          if (TR == FLOWCUDA_TRANSFORM_RQS) {
+            rqs_apply<INV, KT>([&](int i) { return o[i]; }, KT, a.lo, a.hi, xt, nv, l1);
+          } else {
+            affine_apply<INV>(o[0], o[1], xt, nv, l1);
+          }
+          if (td) sx1[slot] = nv; else sx0[slot] = nv;
+          sld[slot] += l1;
+        }
+      }
+      for (int t = 0; t < T; ++t) {
+        const int slot = t * 256 + g * 128 + row;
+        const int64_t idx = base + slot;
+        if (idx < a.n) {
+          const float x0 = sx0[slot], x1 = sx1[slot];
+          if (a.out_v) st_stream_f2(reinterpret_cast<float2*>(a.out_v) + idx, make_float2(x0, x1));
+          if (a.out_lp) {
+            float lp = sld[slot];
+            if (a.with_base) lp += base_term(a.base, x0) + base_term(a.base, x1);
+            a.out_lp[idx] = lp;
+          }
+        }
+      }
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 8) {
+    __syncwarp();
+    tc::tmem_dealloc(tmem, 512);
+  }
+}
+
+template <int TR, int KT>
+static size_t toy_tc_smem(int nl, int T) {
+  using I = ToyTcImg<toy_n3(TR, KT)>;
+  return (size_t)2 * I::wbytes + (size_t)((nl * I::small_floats + 3) & ~3) * 4 + (size_t)3 * T * 256 * 4 + 8 * 8 + 16;
+}
+
+template <int TR, int KT, bool INV>
+static int toy_tc_launch(const flowcuda_coupling_spec* sp, const float* params, ToyTcArgs a, void* ws, size_t wsb,
+                         cudaStream_t s) {
+  using I = ToyTcImg<toy_n3(TR, KT)>;
+  const size_t need = (size_t)sp->num_layers * I::bytes + 256;
+  if (!ws || wsb < need) {
+    set_error("coupling(3xTF32): workspace %zu < %zu bytes", wsb, need);
+    return FLOWCUDA_EWORKSPACE;
+  }
+  uint8_t* img = (uint8_t*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
+  const int of = TR == FLOWCUDA_TRANSFORM_AFFINE_SCALAR ? 2 : 2 * toy_need(TR, KT);
+  toy_tc_pack_kernel<TR, KT><<<sp->num_layers, 256, 0, s>>>(params, sp->hidden[0], sp->hidden[1], of, img);
+  FC_LAUNCH_CHECK("toy_tc_pack_kernel");
+  a.img = img;
+  const int nl = a.layer_end - a.layer_begin;
+  const int sms = sm_count();
+  int T = (int)((a.n + (int64_t)256 * sms - 1) / ((int64_t)256 * sms));
+  T = T < 1 ? 1 : (T > kTcMaxT ? kTcMaxT : T);
+  while (T > 1 && toy_tc_smem<TR, KT>(nl, T) > 227 * 1024) --T;
+  const size_t smem = toy_tc_smem<TR, KT>(nl, T);
+  if (smem > 227 * 1024) {
+    set_error("coupling(3xTF32): %d layers do not fit in shared memory", nl);
+    return FLOWCUDA_EUNSUPPORTED;
+  }
+  a.T = T;
+  auto kern = coupling_toy_tc_kernel<TR, KT, INV>;
+  FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int64_t nchunks = (a.n + (int64_t)T * 256 - 1) / ((int64_t)T * 256);
+  const int grid = (int)(nchunks < sms ? nchunks : sms);
+  kern<<<grid, kTcThreads, smem, s>>>(a);
+  FC_LAUNCH_CHECK("coupling_toy_tc_kernel");
+  return FLOWCUDA_OK;
+}
+
+size_t coupling_toy_tc_workspace_bytes(const flowcuda_coupling_spec* sp) {
+  // the largest image (RQS, 12 bins) bounds every variant
+  return (size_t)sp->num_layers * ToyTcImg<48>::bytes + 256;
+}
+
+int coupling_toy_tc_dispatch(const flowcuda_coupling_spec* sp, const float* params, const float* in, float* out_v,
+                             float* out_lp, int64_t n, int layer_begin, int layer_end, int with_base, bool inverse,
+                             void* ws, size_t wsb, cudaStream_t s) {
+  if (sp->event_dim != 2 || sp->num_hidden != 2 || sp->hidden[0] > 64 || sp->hidden[1] > 64) return FLOWCUDA_EUNSUPPORTED;
+  if (layer_end <= layer_begin) return FLOWCUDA_EUNSUPPORTED;
+  ToyTcArgs a;
+  a.img = nullptr; a.in = in; a.out_v = out_v; a.out_lp = out_lp; a.n = n;
+  a.layer_begin = layer_begin; a.layer_end = layer_end; a.with_base = with_base; a.base = sp->base;
+  a.lo = sp->range_min; a.hi = sp->range_max; a.T = 1;
+  switch (sp->transform) {
+    case FLOWCUDA_TRANSFORM_AFFINE_SCALAR:
+      return inverse ? toy_tc_launch<FLOWCUDA_TRANSFORM_AFFINE_SCALAR, 0, true>(sp, params, a, ws, wsb, s)
+                     : toy_tc_launch<FLOWCUDA_TRANSFORM_AFFINE_SCALAR, 0, false>(sp, params, a, ws, wsb, s);
+    case FLOWCUDA_TRANSFORM_AFFINE:
+      return inverse ? toy_tc_launch<FLOWCUDA_TRANSFORM_AFFINE, 0, true>(sp, params, a, ws, wsb, s)
+                     : toy_tc_launch<FLOWCUDA_TRANSFORM_AFFINE, 0, false>(sp, params, a, ws, wsb, s);
+    case FLOWCUDA_TRANSFORM_RQS:
+      if (sp->num_bins == 12)
+        return inverse ? toy_tc_launch<FLOWCUDA_TRANSFORM_RQS, 12, true>(sp, params, a, ws, wsb, s)
+                       : toy_tc_launch<FLOWCUDA_TRANSFORM_RQS, 12, false>(sp, params, a, ws, wsb, s);
+      if (sp->num_bins == 8)
+        return inverse ? toy_tc_launch<FLOWCUDA_TRANSFORM_RQS, 8, true>(sp, params, a, ws, wsb, s)
+                       : toy_tc_launch<FLOWCUDA_TRANSFORM_RQS, 8, false>(sp, params, a, ws, wsb, s);
+      return FLOWCUDA_EUNSUPPORTED;
+  }
+  return FLOWCUDA_EUNSUPPORTED;
+}
+
+}  // namespace flowcuda

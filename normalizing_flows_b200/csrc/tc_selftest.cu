@@ -40,7 +40,7 @@ template <bool BF16>
 __global__ void __launch_bounds__(128) tc_selftest_kernel(const float* __restrict__ A, const uint8_t* __restrict__ Bhi,
                                                           const uint8_t* __restrict__ Blo, float* __restrict__ D,
                                                           float* __restrict__ D2, int N, int K, int three_pass,
-                                                          uint32_t tmem_cols) {
+                                                          int a_in_tmem, uint32_t tmem_cols) {
   extern __shared__ __align__(128) uint8_t smem[];
   constexpr int CH = BF16 ? 8 : 4;
   constexpr int ES = BF16 ? 2 : 4;
@@ -70,7 +70,10 @@ __global__ void __launch_bounds__(128) tc_selftest_kernel(const float* __restric
     tc::tma_bulk_g2s(b_hi, Bhi, b_bytes, &bars[0]);
     tc::tma_bulk_g2s(b_lo, Blo, b_bytes, &bars[0]);
   }
-  // A: thread = row
+  // A: thread = row.  a_in_tmem: operand A goes to TMEM columns [256, 256+Kc) (hi) and
+  // [256+Kc, 256+2Kc) (lo), lane = row, one 32-bit column per tf32 element / bf16 pair.
+  const uint32_t Kc = (uint32_t)(K * ES / 4);
+  const uint32_t my_lanes = tmem + ((uint32_t)(warp * 32) << 16);
   for (int kc = 0; kc < K / CH; ++kc) {
     const float* src = A + (size_t)tid * K + kc * CH;
     const uint32_t off = tc::img_off(128, tid, kc);
@@ -78,17 +81,29 @@ __global__ void __launch_bounds__(128) tc_selftest_kernel(const float* __restric
       uint32_t h[4], l[4];
 #pragma unroll
       for (int e = 0; e < 4; ++e) tc::split_bf16x2(src[2 * e], src[2 * e + 1], h[e], l[e]);
-      *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(h[0], h[1], h[2], h[3]);
-      *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(l[0], l[1], l[2], l[3]);
+      if (a_in_tmem) {
+        tc::tmem_st_x4(my_lanes + 256u + 4u * kc, h);
+        tc::tmem_st_x4(my_lanes + 256u + Kc + 4u * kc, l);
+      } else {
+        *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(h[0], h[1], h[2], h[3]);
+        *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(l[0], l[1], l[2], l[3]);
+      }
     } else {
       float h[4], l[4];
 #pragma unroll
       for (int e = 0; e < 4; ++e) tc::split_tf32(src[e], h[e], l[e]);
-      *reinterpret_cast<float4*>(a_hi + off) = make_float4(h[0], h[1], h[2], h[3]);
-      *reinterpret_cast<float4*>(a_lo + off) = make_float4(l[0], l[1], l[2], l[3]);
+      if (a_in_tmem) {
+        tc::tmem_st_x4(my_lanes + 256u + 4u * kc, reinterpret_cast<uint32_t*>(h));
+        tc::tmem_st_x4(my_lanes + 256u + Kc + 4u * kc, reinterpret_cast<uint32_t*>(l));
+      } else {
+        *reinterpret_cast<float4*>(a_hi + off) = make_float4(h[0], h[1], h[2], h[3]);
+        *reinterpret_cast<float4*>(a_lo + off) = make_float4(l[0], l[1], l[2], l[3]);
+      }
     }
   }
+  if (a_in_tmem) tc::tmem_st_wait();
   tc::fence_async_smem();
+  tc::tc_fence_before();
   __syncthreads();
 
   if (tid == 0) {
@@ -96,7 +111,18 @@ __global__ void __launch_bounds__(128) tc_selftest_kernel(const float* __restric
     tc::tc_fence_after();
     const uint32_t idesc = tc::make_idesc(FMT, 128, N);
     const int ksteps = K / (2 * CH);
-    if (three_pass) {
+    if (a_in_tmem) {
+      const uint32_t lbo_b = (uint32_t)(N >> 3) * 128u;
+      uint32_t acc = 0;
+      for (int pass = 0; pass < 3; ++pass) {
+        const uint32_t at = tmem + 256u + (pass == 2 ? Kc : 0u);
+        const uint32_t b = tc::smem_u32(pass == 1 ? b_lo : b_hi);
+        for (int s = 0; s < ksteps; ++s) {
+          tc::mma_ts<FMT>(tmem, at + 8u * s, tc::make_smem_desc(b + s * 2u * lbo_b, lbo_b, 128u), idesc, acc);
+          acc = 1;
+        }
+      }
+    } else if (three_pass) {
       tc::mma_3pass<FMT>(tmem, tc::smem_u32(a_hi), tc::smem_u32(a_lo), 128, tc::smem_u32(b_hi), tc::smem_u32(b_lo), N,
                          ksteps, idesc, false);
     } else {
@@ -144,7 +170,7 @@ size_t flowcuda_selftest_umma_workspace_bytes(int n, int k) { return (size_t)2 *
 int flowcuda_selftest_umma(const float* a, const float* w, float* d, float* d_unaligned, int n, int k, int mode,
                            void* workspace, size_t workspace_bytes, void* stream) {
   FC_REQUIRE(a && w && d && workspace, "selftest_umma: NULL pointer");
-  FC_REQUIRE(mode >= 0 && mode <= 3, "selftest_umma: mode must be 0 (tf32x3), 1 (bf16x3), 2 (tf32), 3 (bf16)");
+  FC_REQUIRE(mode >= 0 && mode <= 5, "selftest_umma: mode must be 0 (tf32x3), 1 (bf16x3), 2 (tf32), 3 (bf16), 4/5 (tf32x3/bf16x3, A in TMEM)");
   const bool bf16 = (mode & 1) != 0;
   FC_REQUIRE(n >= 16 && n <= 256 && n % 16 == 0, "selftest_umma: n=%d must be a multiple of 16 in [16,256]", n);
   FC_REQUIRE(k >= 16 && k % 16 == 0 && k <= 128, "selftest_umma: k=%d must be a multiple of 16 in [16,128]", k);
@@ -155,17 +181,19 @@ int flowcuda_selftest_umma(const float* a, const float* w, float* d, float* d_un
   uint8_t* lo = hi + (size_t)n * k * es;
   uint32_t cols = 32;
   while (cols < (uint32_t)n) cols <<= 1;
+  const int a_tmem = mode >= 4;
+  if (a_tmem) cols = 512;
   size_t smem = (size_t)2 * 128 * k * es + (size_t)2 * n * k * es + 64;
   if (bf16) {
     pack_b_image_kernel<true><<<8, 256, 0, s>>>(w, k, n, n, hi, lo);
     FC_LAUNCH_CHECK("pack_b_image_kernel");
     FC_CUDA(cudaFuncSetAttribute(tc_selftest_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    tc_selftest_kernel<true><<<1, 128, smem, s>>>(a, hi, lo, d, d_unaligned, n, k, mode < 2, cols);
+    tc_selftest_kernel<true><<<1, 128, smem, s>>>(a, hi, lo, d, d_unaligned, n, k, mode < 2 || a_tmem, a_tmem, cols);
   } else {
     pack_b_image_kernel<false><<<8, 256, 0, s>>>(w, k, n, n, hi, lo);
     FC_LAUNCH_CHECK("pack_b_image_kernel");
     FC_CUDA(cudaFuncSetAttribute(tc_selftest_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    tc_selftest_kernel<false><<<1, 128, smem, s>>>(a, hi, lo, d, d_unaligned, n, k, mode < 2, cols);
+    tc_selftest_kernel<false><<<1, 128, smem, s>>>(a, hi, lo, d, d_unaligned, n, k, mode < 2 || a_tmem, a_tmem, cols);
   }
   FC_LAUNCH_CHECK("tc_selftest_kernel");
   return FLOWCUDA_OK;
