@@ -211,6 +211,12 @@ size_t flowcuda_selftest_umma_workspace_bytes(int n, int k);
 int flowcuda_selftest_umma(const float* a, const float* w, float* d, float* d_unaligned, int n, int k,
                            int mode, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Microbenchmark: device cycles of chains of small tcgen05.mma (M128, K8, tf32) for several N,
+ * 1-3 independent accumulators, A from TMEM or shared memory.  out_device: int64 records
+ * {N, nacc*1000 + n_mma (+100000: A from smem), issue cycles, cycles until the commit arrives},
+ * terminated by -1. */
+int flowcuda_selftest_mma_timing(long long* out_device, int capacity, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -70,6 +70,7 @@ SIGNATURES = {
     "flowcuda_sgd_step": (_i, [_p, _p, _i64, _f, _f, _p]),
     "flowcuda_adam_step": (_i, [_p, _p, _p, _p, _i64, _i64, _f, _f, _f, _f, _f, _p]),
     "flowcuda_selftest_umma_workspace_bytes": (_sz, [_i, _i]),
+    "flowcuda_selftest_mma_timing": (_i, [_p, _i, _p]),
     "flowcuda_selftest_umma": (_i, [_p, _p, _p, _p, _i, _i, _i, _p, _sz, _p]),
 }
 

@@ -4,7 +4,7 @@
 // kernel, the two hidden Linears of every conditioner as tcgen05.mma kind::tf32 in
 // error-compensated 3-pass form (hi·hi + hi·lo + lo·hi, fp32 accumulate in TMEM).
 //
-// CTA = 2 sample warpgroups + 1 MMA-issuer warp + 1 weight-loader warp, one CTA per SM.
+// CTA = 2 sample warpgroups + 2 MMA-issuer warps (one per warpgroup) + 1 weight-loader warp, one CTA per SM.
 // A warpgroup owns a 128-sample tile: thread = sample = TMEM lane.  Per flow layer
 //   L1  (2->64, only the visible coordinate contributes): CUDA cores, result split into tf32
 //       hi/lo and written straight into TMEM as the A operand (tcgen05.st) — activations never
@@ -24,7 +24,7 @@
 
 namespace flowcuda {
 
-constexpr int kTcThreads = 320;  // warps 0-3: WG0, 4-7: WG1, 8: MMA issuer, 9: loader
+constexpr int kTcThreads = 352;  // warps 0-3: WG0, 4-7: WG1, 8/9: MMA issuers of WG0/WG1, 10: loader
 constexpr int kTcMaxT = 8;       // tile pairs per chunk
 
 template <int N3>
@@ -152,7 +152,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
       tc::mbar_init(&a_ready[g], 128);
       tc::mbar_init(&d_full[g], 1);
       tc::mbar_init(&w_full[g], 1);
-      tc::mbar_init(&w_free[g], 1);
+      tc::mbar_init(&w_free[g], 2);
     }
     tc::fence_mbar_init();
   }
@@ -171,7 +171,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
   const int my_chunks = blockIdx.x < nchunks ? (int)((nchunks - 1 - blockIdx.x) / gridDim.x + 1) : 0;
   const int Q = my_chunks * nl;  // layer steps this CTA runs
 
-  if (warp == 9) {
+  if (warp == 10) {
     // ===== weight loader: one cp.async.bulk per layer step into slot q&1 =====
     if (lane == 0) {
       for (int q = 0; q < Q; ++q) {
@@ -182,47 +182,42 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
         tc::tma_bulk_g2s(wbuf + b * I::wbytes, a.img + (size_t)l * I::bytes, I::wbytes, &w_full[b]);
       }
     }
-  } else if (warp == 8) {
-    // ===== MMA issuer: serves the two warpgroups' requests in arrival order =====
+  } else if (warp >= 8) {
+    // ===== MMA issuers: warp 8 serves warpgroup 0, warp 9 warpgroup 1 (blocking waits, no polling) =====
     if (lane == 0) {
       constexpr uint32_t idesc2 = tc::make_idesc(tc::kFmtTF32, 128, 64);
       constexpr uint32_t idesc3 = tc::make_idesc(tc::kFmtTF32, 128, N3);
-      const int R = Q * T * 2;  // requests per warpgroup: (step, tile, {L2, L3})
-      int c[2] = {0, 0};
-      int done3[2] = {0, 0};    // L3 requests served per weight slot
-      while (c[0] < R || c[1] < R) {
-#pragma unroll
-        for (int g = 0; g < 2; ++g) {
-          if (c[g] >= R) continue;
-          const int r = c[g];
-          const int q = r / (2 * T), p = r & 1, b = q & 1;
-          if (!tc::mbar_try_wait(&a_ready[g], (uint32_t)(r & 1))) continue;
-          if (!tc::mbar_try_wait(&w_full[b], (uint32_t)((q >> 1) & 1))) continue;
-          tc::tc_fence_after();
-          const uint32_t tb = tmem + (uint32_t)g * 192u;  // A hi [0,64) A lo [64,128) D [128,192)
-          const uint32_t wb = tc::smem_u32(wbuf + b * I::wbytes);
-          const uint32_t bh = wb + (p ? I::off_w3hi : I::off_w2hi), bl = wb + (p ? I::off_w3lo : I::off_w2lo);
-          const uint32_t lbo = (uint32_t)((p ? N3 : 64) >> 3) * 128u;
-          const uint32_t idesc = p ? idesc3 : idesc2;
-          uint32_t acc = 0;
+      const int g = warp - 8;
+      const uint32_t tb = tmem + (uint32_t)g * 192u;  // A hi [0,64) A lo [64,128) D [128,192)
+      uint32_t r = 0;
+      for (int q = 0; q < Q; ++q) {
+        const int b = q & 1;
+        const uint32_t wb = tc::smem_u32(wbuf + b * I::wbytes);
+        for (int t = 0; t < T; ++t) {
 #pragma unroll 1
-          for (int pass = 0; pass < 3; ++pass) {
-            const uint32_t at = tb + (pass == 2 ? 64u : 0u);
-            const uint32_t bb = pass == 1 ? bl : bh;
+          for (int p = 0; p < 2; ++p, ++r) {
+            tc::mbar_wait(&a_ready[g], r & 1);
+            if (t == 0 && p == 0) tc::mbar_wait(&w_full[b], (uint32_t)((q >> 1) & 1));
+            tc::tc_fence_after();
+            const uint32_t bh = wb + (p ? I::off_w3hi : I::off_w2hi), bl = wb + (p ? I::off_w3lo : I::off_w2lo);
+            const uint32_t lbo = (uint32_t)((p ? N3 : 64) >> 3) * 128u;
+            const uint32_t idesc = p ? idesc3 : idesc2;
+            uint32_t acc = 0;
+#pragma unroll 1
+            for (int pass = 0; pass < 3; ++pass) {
+              const uint32_t at = tb + (pass == 2 ? 64u : 0u);
+              const uint32_t bb = pass == 1 ? bl : bh;
 #pragma unroll
-            for (int s = 0; s < 8; ++s) {
-              tc::mma_ts<tc::kFmtTF32>(tb + 128u, at + 8u * s, tc::make_smem_desc(bb + (uint32_t)s * 2u * lbo, lbo, 128u),
-                                       idesc, acc);
-              acc = 1;
+              for (int s = 0; s < 8; ++s) {
+                tc::mma_ts<tc::kFmtTF32>(tb + 128u, at + 8u * s, tc::make_smem_desc(bb + (uint32_t)s * 2u * lbo, lbo, 128u),
+                                         idesc, acc);
+                acc = 1;
+              }
             }
-          }
-          tc::mma_commit(&d_full[g]);
-          c[g] = r + 1;
-          if (p && ++done3[b] == 2 * T) {
-            done3[b] = 0;
-            tc::mma_commit(&w_free[b]);
+            tc::mma_commit(&d_full[g]);
           }
         }
+        tc::mma_commit(&w_free[b]);  // this issuer's MMAs on slot b are done (count 2: both issuers)
       }
     }
   } else {

@@ -200,3 +200,140 @@ int flowcuda_selftest_umma(const float* a, const float* w, float* d, float* d_un
 }
 
 }  // extern "C"
+
+// ---- MMA timing microbenchmark: chains of small tcgen05.mma kind::tf32 (M128, K8) ------------------
+namespace flowcuda {
+// out[4*i + {0,1,2,3}] = {N, nacc*1000 + n_mma (+100000 if A from smem), issue cycles, total cycles to commit arrival}
+__global__ void __launch_bounds__(128) tc_mma_timing_kernel(volatile long long* out) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint64_t* bar = reinterpret_cast<uint64_t*>(smem + 160 * 1024);
+  uint32_t* slot = reinterpret_cast<uint32_t*>(bar + 1);
+  const int tid = threadIdx.x, warp = tid >> 5;
+  for (int i = tid; i < 160 * 1024 / 4; i += 128) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+  if (warp == 0) tc::tmem_alloc(slot, 512);
+  if (tid == 0) {
+    tc::mbar_init(bar, 1);
+    tc::fence_mbar_init();
+  }
+  tc::fence_async_smem();
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = *slot;
+  if (tid == 0) {
+    const int Ns[4] = {48, 64, 128, 256};
+    int rec = 0;
+    uint32_t phase = 0;
+    for (int a_smem = 0; a_smem < 2; ++a_smem)
+      for (int ni = 0; ni < 4; ++ni)
+        for (int nacc = 1; nacc <= 3; ++nacc)
+          for (int nm = 24; nm <= 96; nm += 72) {
+            const int N = Ns[ni];
+            if (nacc * N > 384) continue;
+            const uint32_t idesc = tc::make_idesc(tc::kFmtTF32, 128, N);
+            const uint32_t lbo_b = (uint32_t)(N >> 3) * 128u, lbo_a = 16u * 128u;
+            const uint32_t bbase = tc::smem_u32(smem), abase = tc::smem_u32(smem + 96 * 1024);
+            long long t0 = clock64();
+            for (int m = 0; m < nm; ++m) {
+              const uint32_t d = tmem + 128u + (uint32_t)((m % nacc) * N);
+              const uint32_t s = (uint32_t)(m & 7);
+              if (a_smem)
+                tc::mma_ss<tc::kFmtTF32>(d, tc::make_smem_desc(abase + s * 2u * lbo_a, lbo_a, 128u),
+                                         tc::make_smem_desc(bbase + s * 2u * lbo_b, lbo_b, 128u), idesc, 1u);
+              else
+                tc::mma_ts<tc::kFmtTF32>(d, tmem + 8u * s, tc::make_smem_desc(bbase + s * 2u * lbo_b, lbo_b, 128u), idesc, 1u);
+            }
+            long long t1 = clock64();
+            tc::mma_commit(bar);
+            tc::mbar_wait(bar, phase);
+            phase ^= 1;
+            long long t2 = clock64();
+            out[4 * rec + 0] = N;
+            out[4 * rec + 1] = nacc * 1000 + nm + (a_smem ? 100000 : 0);
+            out[4 * rec + 2] = t1 - t0;
+            out[4 * rec + 3] = t2 - t0;
+            ++rec;
+          }
+    // tight variant: descriptors prebuilt, 8-way unrolled, A from TMEM, one accumulator
+    for (int ni = 0; ni < 5; ++ni) {
+      const int Nt[5] = {16, 48, 64, 128, 256};
+      const int N = Nt[ni];
+      const uint32_t idesc = tc::make_idesc(tc::kFmtTF32, 128, N);
+      const uint32_t lbo_b = (uint32_t)(N >> 3) * 128u;
+      uint64_t bd[8];
+#pragma unroll
+      for (int k = 0; k < 8; ++k) bd[k] = tc::make_smem_desc(tc::smem_u32(smem) + k * 2u * lbo_b, lbo_b, 128u);
+      for (int nm = 24; nm <= 96; nm += 72) {
+        long long t0 = clock64();
+        for (int m = 0; m < nm; m += 8) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) tc::mma_ts<tc::kFmtTF32>(tmem + 128u, tmem + 8u * k, bd[k], idesc, 1u);
+        }
+        long long t1 = clock64();
+        tc::mma_commit(bar);
+        tc::mbar_wait(bar, phase);
+        phase ^= 1;
+        long long t2 = clock64();
+        out[4 * rec + 0] = N;
+        out[4 * rec + 1] = 9000 + nm;
+        out[4 * rec + 2] = t1 - t0;
+        out[4 * rec + 3] = t2 - t0;
+        ++rec;
+      }
+    }
+    out[4 * rec] = -1;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    // warp-convergent variant (code 8000 + n): every lane runs the loop, one elected lane issues
+    int rec = 0;
+    while (out[4 * rec] != -1) ++rec;
+    __syncwarp();
+    uint32_t phase = 0;
+    {  // bar was used `rec` times by tid 0 above
+      phase = (uint32_t)(rec & 1);
+    }
+    for (int ni = 0; ni < 5; ++ni) {
+      const int Nt[5] = {16, 48, 64, 128, 256};
+      const int N = Nt[ni];
+      const uint32_t idesc = tc::make_idesc(tc::kFmtTF32, 128, N);
+      const uint32_t lbo_b = (uint32_t)(N >> 3) * 128u;
+      const uint32_t bbase = tc::smem_u32(smem);
+      for (int nm = 24; nm <= 96; nm += 72) {
+        long long t0 = clock64();
+        for (int m = 0; m < nm; m += 8) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k)
+            tc::mma_ts_warp<tc::kFmtTF32>(tmem + 128u, tmem + 8u * k, tc::make_smem_desc(bbase + k * 2u * lbo_b, lbo_b, 128u),
+                                          idesc, 1u);
+        }
+        long long t1 = clock64();
+        tc::mma_commit_warp(bar);
+        tc::mbar_wait(bar, phase);
+        phase ^= 1;
+        long long t2 = clock64();
+        if ((tid & 31) == 0) {
+          out[4 * rec + 0] = N;
+          out[4 * rec + 1] = 8000 + nm;
+          out[4 * rec + 2] = t1 - t0;
+          out[4 * rec + 3] = t2 - t0;
+        }
+        ++rec;
+      }
+    }
+    if ((tid & 31) == 0) out[4 * rec] = -1;
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tc::tmem_dealloc(tmem, 512);
+}
+}  // namespace flowcuda
+
+extern "C" int flowcuda_selftest_mma_timing(long long* out_device, int capacity, void* stream) {
+  FC_REQUIRE(out_device && capacity >= 4 * 64, "selftest_mma_timing: need room for 64 records");
+  const size_t smem = 160 * 1024 + 64;
+  FC_CUDA(cudaFuncSetAttribute(flowcuda::tc_mma_timing_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  flowcuda::tc_mma_timing_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(out_device);
+  FC_LAUNCH_CHECK("tc_mma_timing_kernel");
+  return FLOWCUDA_OK;
+}

@@ -1,0 +1,18 @@
+"""Print the tcgen05.mma chain timing table (flowcuda_selftest_mma_timing)."""
+import os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import ctypes as C, torch
+from normalizing_flows_b200 import _lib
+lib = _lib.load()
+out = torch.zeros(4 * 80, dtype=torch.int64, device="cuda")
+for rep in range(2):
+    _lib.check(lib.flowcuda_selftest_mma_timing(C.c_void_p(out.data_ptr()), out.numel(), None))
+    torch.cuda.synchronize()
+o = out.cpu().tolist()
+print("A_src  N  nacc  n_mma  issue_cyc  total_cyc  cyc/mma")
+i = 0
+while o[4 * i] != -1:
+    N, code, ti, tt = o[4 * i:4 * i + 4]
+    a = "smem" if code >= 100000 else "tmem"; code %= 100000
+    print(f"{a}  {N:4d}  {code // 1000}  {code % 1000:4d}  {ti:7d}  {tt:7d}  {tt / (code % 1000):7.1f}")
+    i += 1
