@@ -24,7 +24,7 @@
 
 namespace flowcuda {
 
-constexpr int kTcThreads = 352;  // warps 0-3: WG0, 4-7: WG1, 8/9: MMA issuers of WG0/WG1, 10: loader
+constexpr int kTcThreads = 4 * 128 + 96;  // warps 0-15: WG0-3 (WG g works in TMEM slot g&1), 16/17: MMA issuers of slot 0/1, 18: loader
 constexpr int kTcMaxT = 8;       // tile pairs per chunk
 
 template <int N3>
@@ -137,22 +137,24 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
   uint8_t* wbuf = smem;                                             // [2][I::wbytes]
   float* smalls = reinterpret_cast<float*>(wbuf + 2 * I::wbytes);   // [nl][SF]
   float* sx0 = smalls + ((nl * SF + 3) & ~3);                       // [T*256] x 3
-  float* sx1 = sx0 + T * 256;
-  float* sld = sx1 + T * 256;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sld + T * 256);
+  float* sx1 = sx0 + T * 512;
+  float* sld = sx1 + T * 512;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sld + T * 512);
   uint64_t* a_ready = bars;       // [2] count 128: a warpgroup's A operand is in TMEM
   uint64_t* d_full = bars + 2;    // [2] count 1: the MMAs of a warpgroup's request completed
   uint64_t* w_full = bars + 4;    // [2] count 1 + tx: weight image landed
   uint64_t* w_free = bars + 6;    // [2] count 1: every MMA reading the slot completed
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  uint64_t* slot_free = bars + 8; // [2] count 128: the slot's current warpgroup has drained its accumulator
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
 
-  if (warp == 8) tc::tmem_alloc(tmem_slot, 512);
+  if (warp == 16) tc::tmem_alloc(tmem_slot, 512);
   if (tid == 0) {
     for (int g = 0; g < 2; ++g) {
       tc::mbar_init(&a_ready[g], 128);
       tc::mbar_init(&d_full[g], 1);
       tc::mbar_init(&w_full[g], 1);
       tc::mbar_init(&w_free[g], 2);
+      tc::mbar_init(&slot_free[g], 128);
     }
     tc::fence_mbar_init();
   }
@@ -166,12 +168,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
   tc::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
-  const int64_t chunk_samples = (int64_t)T * 256;
+  const int64_t chunk_samples = (int64_t)T * 512;
   const int64_t nchunks = (a.n + chunk_samples - 1) / chunk_samples;
   const int my_chunks = blockIdx.x < nchunks ? (int)((nchunks - 1 - blockIdx.x) / gridDim.x + 1) : 0;
   const int Q = my_chunks * nl;  // layer steps this CTA runs
 
-  if (warp == 10) {
+  if (warp == 18) {
     // ===== weight loader: one cp.async.bulk per layer step into slot q&1 =====
     if (lane == 0) {
       for (int q = 0; q < Q; ++q) {
@@ -182,18 +184,18 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
         tc::tma_bulk_g2s(wbuf + b * I::wbytes, a.img + (size_t)l * I::bytes, I::wbytes, &w_full[b]);
       }
     }
-  } else if (warp >= 8) {
+  } else if (warp >= 16) {
     // ===== MMA issuers: warp 8 serves warpgroup 0, warp 9 warpgroup 1 (blocking waits, no polling) =====
     if (lane == 0) {
       constexpr uint32_t idesc2 = tc::make_idesc(tc::kFmtTF32, 128, 64);
       constexpr uint32_t idesc3 = tc::make_idesc(tc::kFmtTF32, 128, N3);
-      const int g = warp - 8;
+      const int g = warp - 16;  // TMEM slot served
       const uint32_t tb = tmem + (uint32_t)g * 192u;  // A hi [0,64) A lo [64,128) D [128,192)
       uint32_t r = 0;
       for (int q = 0; q < Q; ++q) {
         const int b = q & 1;
         const uint32_t wb = tc::smem_u32(wbuf + b * I::wbytes);
-        for (int t = 0; t < T; ++t) {
+        for (int t = 0; t < 2 * T; ++t) {  // the slot's two warpgroups alternate, T tiles each
 #pragma unroll 1
           for (int p = 0; p < 2; ++p, ++r) {
             tc::mbar_wait(&a_ready[g], r & 1);
@@ -206,11 +208,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
 #pragma unroll 1
             for (int pass = 0; pass < 3; ++pass) {
               const uint32_t at = tb + (pass == 2 ? 64u : 0u);
-              const uint32_t bb = pass == 1 ? bl : bh;
+              // descriptor of K step s = descriptor of step 0 + (s * 2 * LBO) >> 4 in the address field
+              const uint64_t d0 = tc::make_smem_desc(pass == 1 ? bl : bh, lbo, 128u);
+              const uint64_t dstep = (uint64_t)((2u * lbo) >> 4);
 #pragma unroll
               for (int s = 0; s < 8; ++s) {
-                tc::mma_ts<tc::kFmtTF32>(tb + 128u, at + 8u * s, tc::make_smem_desc(bb + (uint32_t)s * 2u * lbo, lbo, 128u),
-                                         idesc, acc);
+                tc::mma_ts<tc::kFmtTF32>(tb + 128u, at + 8u * s, d0 + dstep * (uint64_t)s, idesc, acc);
                 acc = 1;
               }
             }
@@ -222,13 +225,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
     }
   } else {
     // ===== sample warpgroups =====
-    const int g = warp >> 2, row = tid & 127;
-    const uint32_t tb = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)g * 192u;
-    uint32_t r = 0;  // request counter (parity of a_ready / d_full)
+    const int g = warp >> 2, sl = g & 1, row = tid & 127;
+    const uint32_t tb = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)sl * 192u;
+    uint32_t use = (uint32_t)(g >> 1);  // this warpgroup's next turn in its slot (turns alternate g, g^2)
     for (int ci = 0; ci < my_chunks; ++ci) {
       const int64_t base = ((int64_t)blockIdx.x + (int64_t)ci * gridDim.x) * chunk_samples;
       for (int t = 0; t < T; ++t) {
-        const int slot = t * 256 + g * 128 + row;
+        const int slot = t * 512 + g * 128 + row;
         const int64_t idx = base + slot;
         float2 v = idx < a.n ? ld_stream_f2(reinterpret_cast<const float2*>(a.in) + idx) : make_float2(0.f, 0.f);
         sx0[slot] = v.x;
@@ -241,10 +244,12 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
         const float* sm = smalls + it * SF;
 #pragma unroll 1
         for (int t = 0; t < T; ++t) {
-          const int slot = t * 256 + g * 128 + row;
+          const int slot = t * 512 + g * 128 + row;
           const float x0 = sx0[slot], x1 = sx1[slot];
           const float xm = td ? x0 : x1;  // visible value
           const float xt = td ? x1 : x0;  // value to transform
+          if (use > 0) tc::mbar_wait(&slot_free[sl], (use - 1) & 1);  // previous user drained the slot
+          tc::tc_fence_after();
           // ---- L1: Linear(2->64)+relu on where(mask, x, 0); split; A operand -> TMEM
 #pragma unroll
           for (int c = 0; c < 4; ++c) {
@@ -268,9 +273,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
           }
           tc::tmem_st_wait();
           tc::tc_fence_before();
-          tc::mbar_arrive(&a_ready[g]);
-          tc::mbar_wait(&d_full[g], r & 1);
-          ++r;
+          tc::mbar_arrive(&a_ready[sl]);
+          tc::mbar_wait(&d_full[sl], 0);
           tc::tc_fence_after();
           // ---- epilogue 2: +b2, relu, split, next A operand -> TMEM
           {
@@ -294,9 +298,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
           }
           tc::tmem_st_wait();
           tc::tc_fence_before();
-          tc::mbar_arrive(&a_ready[g]);
-          tc::mbar_wait(&d_full[g], r & 1);
-          ++r;
+          tc::mbar_arrive(&a_ready[sl]);
+          tc::mbar_wait(&d_full[sl], 1);
           tc::tc_fence_after();
           // ---- epilogue 3: inner bijector on the transformed coordinate
           float o[NEED];
@@ -306,6 +309,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
 #pragma unroll
             for (int i = 0; i < NEED; ++i) o[i] = __uint_as_float(v[i]) + sm[192 + i];
           }
+          tc::tc_fence_before();
+          tc::mbar_arrive(&slot_free[sl]);  // hand the slot to the partner warpgroup
+          use += 2;
           float nv, l1;
           if (TR == FLOWCUDA_TRANSFORM_RQS) {
             rqs_apply<INV, KT>([&](int i) { return o[i]; }, KT, a.lo, a.hi, xt, nv, l1);
@@ -317,7 +323,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
         }
       }
       for (int t = 0; t < T; ++t) {
-        const int slot = t * 256 + g * 128 + row;
+        const int slot = t * 512 + g * 128 + row;
         const int64_t idx = base + slot;
         if (idx < a.n) {
           const float x0 = sx0[slot], x1 = sx1[slot];
@@ -333,7 +339,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
   }
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 8) {
+  if (warp == 16) {
     __syncwarp();
     tc::tmem_dealloc(tmem, 512);
   }
@@ -342,7 +348,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
 template <int TR, int KT>
 static size_t toy_tc_smem(int nl, int T) {
   using I = ToyTcImg<toy_n3(TR, KT)>;
-  return (size_t)2 * I::wbytes + (size_t)((nl * I::small_floats + 3) & ~3) * 4 + (size_t)3 * T * 256 * 4 + 8 * 8 + 16;
+  return (size_t)2 * I::wbytes + (size_t)((nl * I::small_floats + 3) & ~3) * 4 + (size_t)3 * T * 512 * 4 + 10 * 8 + 16;
 }
 
 template <int TR, int KT, bool INV>
@@ -361,7 +367,7 @@ static int toy_tc_launch(const flowcuda_coupling_spec* sp, const float* params, 
   a.img = img;
   const int nl = a.layer_end - a.layer_begin;
   const int sms = sm_count();
-  int T = (int)((a.n + (int64_t)256 * sms - 1) / ((int64_t)256 * sms));
+  int T = (int)((a.n + (int64_t)512 * sms - 1) / ((int64_t)512 * sms));
   T = T < 1 ? 1 : (T > kTcMaxT ? kTcMaxT : T);
   while (T > 1 && toy_tc_smem<TR, KT>(nl, T) > 227 * 1024) --T;
   const size_t smem = toy_tc_smem<TR, KT>(nl, T);
@@ -372,7 +378,7 @@ static int toy_tc_launch(const flowcuda_coupling_spec* sp, const float* params, 
   a.T = T;
   auto kern = coupling_toy_tc_kernel<TR, KT, INV>;
   FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int64_t nchunks = (a.n + (int64_t)T * 256 - 1) / ((int64_t)T * 256);
+  const int64_t nchunks = (a.n + (int64_t)T * 512 - 1) / ((int64_t)T * 512);
   const int grid = (int)(nchunks < sms ? nchunks : sms);
   kern<<<grid, kTcThreads, smem, s>>>(a);
   FC_LAUNCH_CHECK("coupling_toy_tc_kernel");
