@@ -168,7 +168,9 @@ class MafMnist(CouplingWorkload):
     flops_per_sample = 95_100_000
     bound = "tensor"
     launches_per_step = 8 * 5 + 1
-    precision = "fp32"
+    tc_precision = 3          # FLOWCUDA_PRECISION_BF16X3
+    tc_launches = 4 + 8 * 6 + 1  # weight packs + per layer (pack_x, 4 GEMMs, log-det accumulate) + finish
+    tc_dtype = "bf16x3 (fp32 accumulate)"
     cpu_sample = 256
 
 

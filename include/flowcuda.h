@@ -141,7 +141,8 @@ int flowcuda_bernstein_flow_log_prob(const float* theta, int order, const float*
 
 #define FLOWCUDA_PRECISION_FP32 0   /* CUDA-core FP32 FMA conditioner */
 #define FLOWCUDA_PRECISION_3XTF32 1 /* tcgen05 kind::tf32, error-compensated 3-pass split */
-#define FLOWCUDA_PRECISION_TF32 2   /* tcgen05 kind::tf32 single pass */
+#define FLOWCUDA_PRECISION_TF32 2   /* tcgen05 kind::tf32 single pass (reserved) */
+#define FLOWCUDA_PRECISION_BF16X3 3 /* tcgen05 kind::f16 bf16, error-compensated 3-pass split (wide conditioners) */
 
 typedef struct flowcuda_coupling_spec {
   int32_t event_dim;   /* D: flattened event size (2, or 784 for [28,28,1]) */

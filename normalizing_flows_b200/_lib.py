@@ -13,7 +13,7 @@ LIB_PATH = os.path.join(PKG, "libflowcuda.so")
 
 TRANSFORM_AFFINE_SCALAR, TRANSFORM_AFFINE, TRANSFORM_RQS = 0, 1, 2
 BASE_NORMAL, BASE_UNIFORM01 = 0, 1
-PRECISION_FP32, PRECISION_3XTF32, PRECISION_TF32 = 0, 1, 2
+PRECISION_FP32, PRECISION_3XTF32, PRECISION_TF32, PRECISION_BF16X3 = 0, 1, 2, 3
 MAX_HIDDEN_LAYERS = 4
 
 

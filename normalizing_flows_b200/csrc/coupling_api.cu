@@ -10,6 +10,11 @@ int coupling_toy_tc_dispatch(const flowcuda_coupling_spec* sp, const float* para
                              float* out_lp, int64_t n, int layer_begin, int layer_end, int with_base, bool inverse,
                              void* ws, size_t wsb, cudaStream_t s);
 size_t coupling_toy_tc_workspace_bytes(const flowcuda_coupling_spec* sp);
+bool coupling_dense_tc_supported(const flowcuda_coupling_spec* sp);
+size_t coupling_dense_tc_workspace_bytes(const flowcuda_coupling_spec* sp, int64_t n);
+int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params, const float* in, float* out_v,
+                          float* out_lp, float* out_ld, int64_t n, int layer_begin, int layer_end, int with_base,
+                          bool inverse, void* workspace, size_t workspace_bytes, cudaStream_t s);
 int64_t coupling_param_count(const flowcuda_coupling_spec* sp);
 size_t coupling_dense_workspace_bytes(const flowcuda_coupling_spec* sp, int64_t n);
 int coupling_dense_run(const flowcuda_coupling_spec* sp, const float* params, const float* in, float* out_v,
@@ -29,7 +34,7 @@ static int check_spec(const flowcuda_coupling_spec* sp) {
     FC_REQUIRE(sp->range_max > sp->range_min, "coupling: empty spline range");
   }
   FC_REQUIRE(sp->base == FLOWCUDA_BASE_NORMAL || sp->base == FLOWCUDA_BASE_UNIFORM01, "coupling: unknown base %d", sp->base);
-  FC_REQUIRE(sp->precision >= 0 && sp->precision <= 2, "coupling: unknown precision %d", sp->precision);
+  FC_REQUIRE(sp->precision >= 0 && sp->precision <= 3 && sp->precision != FLOWCUDA_PRECISION_TF32, "coupling: unknown precision %d", sp->precision);
   return FLOWCUDA_OK;
 }
 
@@ -47,6 +52,8 @@ static int run(const flowcuda_coupling_spec* sp, const float* params, const floa
   if (n == 0) return FLOWCUDA_OK;
   FC_REQUIRE(params && in, "coupling: NULL params or input");
   FC_REQUIRE(lb >= 0 && le <= sp->num_layers && lb <= le, "coupling: layer range [%d,%d) outside [0,%d]", lb, le, sp->num_layers);
+  if (sp->precision == FLOWCUDA_PRECISION_BF16X3)
+    return coupling_dense_tc_run(sp, params, in, out_v, out_lp, out_ld, n, lb, le, with_base, inverse, ws, wsb, s);
   if (sp->precision != FLOWCUDA_PRECISION_FP32) {
     FC_REQUIRE(sp->precision == FLOWCUDA_PRECISION_3XTF32 && toy_eligible(sp) && le > lb,
                "coupling: precision %d is not available for this flow shape (3xTF32 needs event_dim 2, two hidden layers <= 64)",
@@ -89,6 +96,7 @@ size_t flowcuda_coupling_workspace_bytes(const flowcuda_coupling_spec* spec, int
   if (check_spec(spec) || n < 0) return 0;
   if (toy_eligible(spec) && spec->precision == FLOWCUDA_PRECISION_FP32) return 0;
   if (toy_eligible(spec) && spec->precision == FLOWCUDA_PRECISION_3XTF32) return coupling_toy_tc_workspace_bytes(spec);
+  if (spec->precision == FLOWCUDA_PRECISION_BF16X3) return coupling_dense_tc_workspace_bytes(spec, n);
   return coupling_dense_workspace_bytes(spec, n);
 }
 

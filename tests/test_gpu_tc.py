@@ -101,3 +101,57 @@ def test_toy_coupling_3xtf32_matches_fp32_kernel_at_scale():
     lptc, _, _ = ops.coupling_log_prob(_spec_pair(ops, ospec, precision=_lib.PRECISION_3XTF32), flat, x)
     err = ((lptc - lp32).abs() / lp32.abs().clamp(min=1)).max().item()
     assert err <= 2e-5, err
+
+
+# ------------------------------------------------------------------ bf16x3 dense coupling stacks (row #4, C5)
+DENSE_TC = {
+    "rqs_d40_uniform": (O.CouplingSpec(40, 2, [32, 32, 32], "rqs", 8, 0.0, 1.0, "uniform"), 0.3, None),
+    "rqs_d7_k8": (O.CouplingSpec(7, 3, [24, 24], "rqs", 8, -3.0, 3.0), 0.3, 2.0),
+    "affine_d6": (O.CouplingSpec(6, 3, [16], "affine"), 0.3, 1.5),
+    "affine_d300": (O.CouplingSpec(300, 2, [320, 64], "affine"), 0.2, 1.0),
+    "rqs_d50_wide": (O.CouplingSpec(50, 2, [300], "rqs", 8, -4.0, 4.0), 0.3, 2.0),
+}
+
+
+@pytest.mark.parametrize("case", sorted(DENSE_TC))
+@pytest.mark.parametrize("n", [1, 77, 300])
+def test_dense_coupling_bf16x3_parity(case, n):
+    """Tensor-core path of the wide-conditioner flows; north_star tolerance for this path is 1e-3
+    absolute on log_prob — held here at 2e-4·max(1,|ref|) on every output."""
+    from normalizing_flows_b200 import _lib, ops
+
+    ospec, scale, xs = DENSE_TC[case]
+    params = O.init_coupling_params(ospec, seed=11, scale=scale)
+    flat = O.flatten_layers(params)
+    spec = _spec_pair(ops, ospec, precision=_lib.PRECISION_BF16X3)
+    gen = torch.Generator().manual_seed(n)
+    if xs is None:
+        x = torch.rand(n, ospec.event_dim, generator=gen, dtype=torch.float64).float()
+        if n > 3:
+            x[3, 1] = 1.5  # outside the Uniform support -> -inf
+    else:
+        x = (torch.randn(n, ospec.event_dim, generator=gen, dtype=torch.float64) * xs).float()
+    x64 = x.double()
+    lp, z, ld = ops.coupling_log_prob(spec, G(flat), x.cuda(), want_z=True, want_log_det=True)
+    zref, ldref = O.coupling_flow_to_base(ospec, params, x64)
+    lpref = O.coupling_flow_log_prob(ospec, params, x64)
+    close(lp, lpref.numpy(), tol=2e-4, what="log_prob", nonfinite="equal")
+    close(z, zref.numpy(), tol=2e-4, what="z")
+    close(ld, ldref.numpy(), tol=2e-4, what="log_det")
+    xsamp, _ = ops.coupling_sample(spec, G(flat), x.cuda())
+    close(xsamp, O.coupling_flow_sample(ospec, params, x64).numpy(), tol=2e-4, what="sample")
+
+
+def test_dense_coupling_bf16x3_mnist_shape():
+    """maf_mnist.py:28-31 conditioner 784->512->512->512->19600, 8 bins, Uniform base (2 flow layers to
+    bound the CPU oracle's time): |log_prob - float64 oracle| <= 1e-3 absolute (north_star)."""
+    from normalizing_flows_b200 import _lib, ops
+
+    ospec = O.CouplingSpec(784, 2, [512, 512, 512], "rqs", 8, 0.0, 1.0, "uniform")
+    params = O.init_coupling_params(ospec, seed=5, scale=0.1)
+    gen = torch.Generator().manual_seed(0)
+    x = ((torch.randint(0, 256, (200, 784), generator=gen).double() + torch.rand(200, 784, generator=gen, dtype=torch.float64)) / 256).float()
+    lp, _, _ = ops.coupling_log_prob(_spec_pair(ops, ospec, precision=_lib.PRECISION_BF16X3), G(O.flatten_layers(params)), x.cuda())
+    ref = O.coupling_flow_log_prob(ospec, params, x.double()).numpy()
+    err = np.abs(lp.double().cpu().numpy() - ref).max()
+    assert err <= 1e-3, err
