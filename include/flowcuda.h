@@ -182,6 +182,16 @@ int flowcuda_coupling_sample(const flowcuda_coupling_spec* spec, const float* pa
                              int layer_begin, int layer_end,
                              void* workspace, size_t workspace_bytes, void* stream);
 
+/* value_and_grad of loss = -mean(Transformed.log_prob(x)) w.r.t. the flow parameters
+ * (real_nvp_toy_densities.py:139-151,170; maf_toy_densities.py:140-152,171): hand-written
+ * reverse mode, deterministic two-stage reduction.  loss[1], grad[param_count] (layout of
+ * `params`).  Available for event_dim 2 with two hidden layers <= 64 (the toy flows);
+ * FLOWCUDA_EUNSUPPORTED otherwise. */
+size_t flowcuda_coupling_nll_grad_workspace_bytes(const flowcuda_coupling_spec* spec, int64_t n);
+int flowcuda_coupling_nll_grad(const flowcuda_coupling_spec* spec, const float* params, const float* x,
+                               int64_t n, float* loss, float* grad, void* workspace,
+                               size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------
  * Rows #7, #9 — loss reduction and optimiser steps.
  * ---------------------------------------------------------------------------------- */

@@ -66,6 +66,8 @@ SIGNATURES = {
     "flowcuda_coupling_workspace_bytes": (_sz, [_spec, _i64]),
     "flowcuda_coupling_log_prob": (_i, [_spec, _p, _p, _p, _p, _p, _i64, _i, _i, _i, _p, _sz, _p]),
     "flowcuda_coupling_sample": (_i, [_spec, _p, _p, _p, _p, _i64, _i, _i, _p, _sz, _p]),
+    "flowcuda_coupling_nll_grad_workspace_bytes": (_sz, [_spec, _i64]),
+    "flowcuda_coupling_nll_grad": (_i, [_spec, _p, _p, _i64, _p, _p, _p, _sz, _p]),
     "flowcuda_sum_scaled": (_i, [_p, _i64, _d, _p, _p, _p]),
     "flowcuda_sgd_step": (_i, [_p, _p, _i64, _f, _f, _p]),
     "flowcuda_adam_step": (_i, [_p, _p, _p, _p, _i64, _i64, _f, _f, _f, _f, _f, _p]),

@@ -223,6 +223,21 @@ def coupling_sample(spec: CouplingSpec, params: torch.Tensor, z: torch.Tensor, w
     return x, ld
 
 
+def coupling_nll_grad(spec: CouplingSpec, params: torch.Tensor, x: torch.Tensor):
+    """(loss[1], grad[param_count]) of -mean(log_prob(x)) — jax.value_and_grad(loss_fn) of the toy scripts."""
+    x = _f32(x).reshape(x.shape[0], -1)
+    _dev_check(params, x)
+    lib = _lib.load()
+    n = x.shape[0]
+    need = lib.flowcuda_coupling_nll_grad_workspace_bytes(C.byref(spec), n)
+    ws = torch.empty(max(1, (need + 3) // 4), device=x.device, dtype=torch.float32)
+    loss = torch.empty(1, device=x.device, dtype=torch.float32)
+    grad = torch.empty_like(params)
+    check(lib.flowcuda_coupling_nll_grad(C.byref(spec), _ptr(params), _ptr(x), n, _ptr(loss), _ptr(grad), _ptr(ws),
+                                         ws.numel() * 4, _stream()), "coupling_nll_grad")
+    return loss, grad
+
+
 # ---------------------------------------------------------------------------- rows #7, #9
 def sum_scaled(v: torch.Tensor, scale: float) -> torch.Tensor:
     v = _f32(v).reshape(-1)
