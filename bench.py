@@ -418,6 +418,7 @@ def main():
             "e2e": res["e2e"],
             "gpu_launches": res["launches"],
             "clocks": res["clocks"],
+            "train": res.get("train"),
         }
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(w)
@@ -499,7 +500,52 @@ def time_workload(w, dev, rank, world, dist, W, K, ops, e2e, clocks):
            "nbuf": nbuf, "clocks": clk, "launches": K * (w.launches_per_step + (2 if dist is not None else 0))}
     if e2e:
         out["e2e"] = time_e2e(w, dev, host, dist, world, max(3, K // 2))
+        out["train"] = time_train(w, dev, rank, world, dist, ops)
     return out
+
+
+def time_train(w, dev, rank, world, dist, ops, K=5, batch=1 << 18):
+    """train samples/s: one step = value_and_grad of -mean(log_prob) over a batch (hand-written
+    reverse mode), the gradient all-reduce across ranks (NCCL sum, only exchange of the step) and the
+    fused Adam update (optax.adam, real_nvp_toy_densities.py:162-173).  Batch per GPU is fixed (weak)."""
+    if not isinstance(w, CouplingWorkload) or w._ospec().event_dim != 2:
+        return None
+    from normalizing_flows_b200 import _lib
+
+    sp = w._ospec()
+    tr = {"affine_scalar": 0, "affine": 1, "rqs": 2}[sp.transform]
+    spec = ops.make_spec(2, sp.num_layers, sp.hidden, tr, sp.num_bins, sp.range_min, sp.range_max, _lib.BASE_NORMAL, 0)
+    p = w.model.params.clone()
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    gen = torch.Generator().manual_seed(77 + rank)
+    xs = [w.make_inputs(gen, batch).to(dev) for _ in range(4)]
+
+    def step(i):
+        loss, grad = ops.coupling_nll_grad(spec, p, xs[i % len(xs)])
+        if dist is not None:
+            dist.all_reduce(grad)
+        ops.adam_step(p, grad, m, v, i + 1, 1e-4, grad_scale=1.0 / world)
+        return loss
+
+    for i in range(2):
+        step(i)
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(K):
+        loss = step(2 + i)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if dist is not None:
+        t = torch.tensor([ms], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = t.item()
+    return {"value": batch * world * K / (ms * 1e-3), "unit": "samples/s", "batch_per_gpu": batch, "steps": K,
+            "ms_per_step": ms / K, "final_loss": float(loss.item()), "optimizer": "adam(1e-4)",
+            "grad_allreduce_bytes": int(p.numel() * 4) if dist is not None else 0, "precision": "fp32"}
 
 
 def time_e2e(w, dev, host, dist, world, K):
