@@ -468,13 +468,17 @@ def time_workload(w, dev, rank, world, dist, W, K, ops, e2e, clocks):
     for i in range(W):
         step(i)
     torch.cuda.synchronize()
-    if dist is not None:
-        dist.barrier()
-    torch.cuda.synchronize()
+    # rank 0 starts its clock sampler BEFORE the barrier, so no rank enters the timed region early
+    # and then waits in the first all-reduce for rank 0 to wake up
     sampler = ClockSampler(dev.index) if clocks and rank == 0 else None
     if sampler:
         sampler.start()
-        time.sleep(0.25)
+        t_wait = time.time()
+        while not sampler.rows and time.time() - t_wait < 5.0:  # nvidia-smi takes a while to print its first row
+            time.sleep(0.05)
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
     t0 = time.time()
     start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
