@@ -174,6 +174,65 @@ class MafMnist(CouplingWorkload):
     cpu_sample = 256
 
 
+class MafMade(Workload):
+    """Row #8: the MADE-conditioned MAF north_star names for the MNIST-shaped configs."""
+    name = "maf_made"
+    desc = ("configs[3]/north_star(b): 8x MADE-affine MAF, masked MLP 784->512->512->1568, reversal between layers, Normal base "
+            "(SURVEY A.7; the reference has no MADE code); synthetic dequantised 28x28, 16384 samples/GPU, log_prob")
+    n = 16384
+    bytes_per_sample = 3140
+    bound = "tensor"
+    dtype = "bf16x3 (fp32 accumulate)"
+    launches_per_step = 3 + 8 * 5 + 1  # weight packs + per layer (pack_x, 3 GEMMs, log-det accumulate) + finish
+    cpu_sample = 1024
+
+    def _ospec(self):
+        from oracle import flows_oracle as O
+
+        return O.MadeSpec(784, 8, [512, 512])
+
+    @property
+    def flops_per_sample(self):
+        # needed-only: 2 FLOP per UNMASKED weight (SURVEY §8d counts 23.5 M for the dense shapes)
+        sp = self._ospec()
+        return int(2 * sp.num_layers * sum(float(m.sum()) for m in sp.masks()))
+
+    def make_inputs(self, gen, n):
+        return mnist_like(n, gen)
+
+    def setup(self, dev):
+        from normalizing_flows_b200 import flows
+        from oracle import flows_oracle as O
+
+        sp = self._ospec()
+        self._p = O.init_made_params(sp, seed=1234, dtype=torch.float32, scale=0.1)
+        self.model = flows.make_maf_model((784,), sp.num_layers, sp.hidden, params=O.flatten_layers(self._p).float().to(dev))
+
+    def run(self, x):
+        return self.model.log_prob(x)
+
+    def cpu_run(self, x):
+        from oracle import flows_oracle as O
+
+        return O.maf_log_prob(self._ospec(), self._p, x)
+
+    def sampling(self, dev, K=3):
+        """Sequential sampling (persistent kernel over the D positions), base noise resident in HBM."""
+        n = 148 * 8 * 4
+        z = torch.randn(n, 784, device=dev, generator=torch.Generator(device=dev).manual_seed(5))
+        for _ in range(2):
+            self.model.sample_from_noise(z)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(K):
+            x = self.model.sample_from_noise(z)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / K
+        return {"value": n / (ms * 1e-3), "unit": "samples/s", "samples_per_step_per_gpu": n, "ms_per_step": ms,
+                "finite": bool(torch.isfinite(x).all().item())}
+
+
 class RealNvpHand(Workload):
     name = "realnvp_hand"
     desc = "hand-rolled Real NVP chain, 8 layers [1,4,2] leaky_relu (src/real_nvp.py); banana, 2^22 samples/GPU, log_prob"
@@ -234,7 +293,7 @@ class Bernstein(Workload):
         return O.bernstein_forward_and_log_det(O.constrain_thetas(self.raw), x)[1]
 
 
-WORKLOADS = {w.name: w for w in (MafToy, RealNvpToy, MafMnist, RealNvpHand, Bernstein)}
+WORKLOADS = {w.name: w for w in (MafToy, RealNvpToy, MafMnist, MafMade, RealNvpHand, Bernstein)}
 
 
 # ----------------------------------------------------------------------------- clocks
@@ -332,6 +391,8 @@ def _cpu_setup(w):
 
     if isinstance(w, CouplingWorkload):
         w._p = w._params()
+    elif isinstance(w, MafMade):
+        w._p = O.init_made_params(w._ospec(), seed=1234, dtype=torch.float32, scale=0.1)
     elif isinstance(w, RealNvpHand):
         w._p, w._flips = O.init_nvp_chain_like(8, hidden=4, seed=534, dtype=torch.float32, scale=0.1)
     elif isinstance(w, Bernstein):
@@ -419,6 +480,7 @@ def main():
             "gpu_launches": res["launches"],
             "clocks": res["clocks"],
             "train": res.get("train"),
+            "sampling": res.get("sampling"),
         }
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(w)
@@ -505,6 +567,8 @@ def time_workload(w, dev, rank, world, dist, W, K, ops, e2e, clocks):
     if e2e:
         out["e2e"] = time_e2e(w, dev, host, dist, world, max(3, K // 2))
         out["train"] = time_train(w, dev, rank, world, dist, ops)
+        if hasattr(w, "sampling"):
+            out["sampling"] = w.sampling(dev)
     return out
 
 

@@ -193,6 +193,45 @@ int flowcuda_coupling_nll_grad(const flowcuda_coupling_spec* spec, const float* 
                                size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------
+ * Row #8 — MADE-conditioned masked autoregressive affine flow (MAF), named by
+ * BASELINE.json's north_star for the D=784 configs.  The reference has NO code for it
+ * (src/maf_mwe.py:36-88 is commented out and is not MADE; the scripts import `tfb`,
+ * whose MaskedAutoregressiveFlow/AutoregressiveNetwork this follows — SURVEY App. A.7):
+ *   per flow layer a masked MLP [D -> hidden... -> 2D], relu; input degrees 1..D, hidden
+ *   degrees max(1, ceil(k (D-1)/(H+1))) (k = 1..H), hidden mask deg_in <= deg_out, output
+ *   mask deg_in < deg_out; output columns [shift_0..shift_{D-1}, log_scale_0..log_scale_{D-1}];
+ *   odd layers see the dimensions in reversed order.
+ * Parameter layout: per layer, per Linear: W[in,out] row-major then b[out] (UNMASKED
+ * weights; the masks are applied by the library when it packs them).
+ * ---------------------------------------------------------------------------------- */
+typedef struct flowcuda_made_spec {
+  int32_t event_dim;   /* D */
+  int32_t num_layers;  /* flow layers L */
+  int32_t num_hidden;  /* hidden Linears of each MADE */
+  int32_t hidden[FLOWCUDA_MAX_HIDDEN_LAYERS];
+  int32_t base;        /* FLOWCUDA_BASE_* */
+  int32_t reserved;
+} flowcuda_made_spec;
+
+int64_t flowcuda_made_param_count(const flowcuda_made_spec* spec);
+size_t flowcuda_made_workspace_bytes(const flowcuda_made_spec* spec, int64_t n);
+
+/* Density pass x[N,D] -> log_prob[N]: layer L-1 first ... layer 0 last, per layer ONE
+ * conditioner evaluation, u = (x - shift)·exp(-log_scale), log-det = -sum(log_scale); the
+ * conditioner runs as tcgen05 bf16x3 GEMMs with fp32 accumulation (|d log_prob| <= 1e-3).
+ * Optional outputs (may be NULL): u[N,D] the base-space point, log_det[N]. */
+int flowcuda_made_log_prob(const flowcuda_made_spec* spec, const float* params, const float* x,
+                           float* log_prob, float* u, float* log_det, int64_t n, int with_base,
+                           void* workspace, size_t workspace_bytes, void* stream);
+
+/* Sampling with the base noise given, z[N,D] -> x[N,D]: layer 0 first ... layer L-1 last,
+ * within a layer x_i = z_i·exp(log_scale_i(x_<i)) + shift_i(x_<i) sequentially over the D
+ * positions — one persistent FP32 kernel with incrementally updated pre-activations.
+ * Needs num_hidden == 2, hidden <= 512, event_dim <= 1024 (FLOWCUDA_EUNSUPPORTED otherwise). */
+int flowcuda_made_sample(const flowcuda_made_spec* spec, const float* params, const float* z,
+                         float* x, int64_t n, void* stream);
+
+/* ------------------------------------------------------------------------------------
  * Rows #7, #9 — loss reduction and optimiser steps.
  * ---------------------------------------------------------------------------------- */
 

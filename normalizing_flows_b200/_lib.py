@@ -38,6 +38,19 @@ class CouplingSpec(C.Structure):
     ]
 
 
+class MadeSpec(C.Structure):
+    """Mirror of `flowcuda_made_spec`."""
+
+    _fields_ = [
+        ("event_dim", C.c_int32),
+        ("num_layers", C.c_int32),
+        ("num_hidden", C.c_int32),
+        ("hidden", C.c_int32 * MAX_HIDDEN_LAYERS),
+        ("base", C.c_int32),
+        ("reserved", C.c_int32),
+    ]
+
+
 _p = C.c_void_p
 _i = C.c_int
 _i64 = C.c_int64
@@ -46,6 +59,7 @@ _f = C.c_float
 _d = C.c_double
 _sz = C.c_size_t
 _spec = C.POINTER(CouplingSpec)
+_mspec = C.POINTER(MadeSpec)
 
 # name -> (restype, argtypes); every symbol include/flowcuda.h declares
 SIGNATURES = {
@@ -68,6 +82,10 @@ SIGNATURES = {
     "flowcuda_coupling_sample": (_i, [_spec, _p, _p, _p, _p, _i64, _i, _i, _p, _sz, _p]),
     "flowcuda_coupling_nll_grad_workspace_bytes": (_sz, [_spec, _i64]),
     "flowcuda_coupling_nll_grad": (_i, [_spec, _p, _p, _i64, _p, _p, _p, _sz, _p]),
+    "flowcuda_made_param_count": (_i64, [_mspec]),
+    "flowcuda_made_workspace_bytes": (_sz, [_mspec, _i64]),
+    "flowcuda_made_log_prob": (_i, [_mspec, _p, _p, _p, _p, _p, _i64, _i, _p, _sz, _p]),
+    "flowcuda_made_sample": (_i, [_mspec, _p, _p, _p, _i64, _p]),
     "flowcuda_sum_scaled": (_i, [_p, _i64, _d, _p, _p, _p]),
     "flowcuda_sgd_step": (_i, [_p, _p, _i64, _f, _f, _p]),
     "flowcuda_adam_step": (_i, [_p, _p, _p, _p, _i64, _i64, _f, _f, _f, _f, _f, _p]),

@@ -1,0 +1,296 @@
+// dense_tc.cuh — the tcgen05 bf16x3 GEMM shared by the wide-conditioner flows
+// (coupling_dense_tc.cu: distrax.MaskedCoupling stacks, src/maf_mnist.py:34-89;
+//  made.cu: MADE-affine MAF).
+//
+// Every Linear is C[128 x 256 tile] = A · W with bf16 operands in error-compensated 3-pass form
+// (hi·hi + hi·lo + lo·hi, fp32 accumulate in TMEM; single-pass bf16 misses the 1e-3 log_prob
+// budget by 7x — profiles/r01/precision_study.txt).  Operands live in HBM as ready-made
+// shared-memory tile images (tc.cuh), so a pipeline stage is two cp.async.bulk (TMA) copies:
+//   A image  [m_tile][k_stage][hi|lo][4 chunks][128 rows][16 B]   (activations, 32 K per stage)
+//   B image  [n_tile][k_stage][hi|lo][4 chunks][256 rows][16 B]   (weights, masks folded in)
+// CTA = loader warp + MMA warp + 4 epilogue warps, 2 CTAs per SM so that one CTA's epilogue
+// overlaps the other's MMAs.  Epilogues (thread = sample row = TMEM lane):
+//   hidden: +bias, relu, bf16 hi/lo split, written straight into the next Linear's A image;
+//   last:   the inner bijector (RQS / affine) on the tile's dims, state updated in place,
+//           log-det partial per (row, tile) — the [N, D*params] conditioner output never exists.
+// A masked (MADE) Linear is block lower-triangular once its units are sorted by degree, so an
+// n tile only walks the first ks_tile[nt] K stages: the all-zero weight blocks are never loaded.
+#pragma once
+#include "tc.cuh"
+#include "transforms.cuh"
+
+namespace flowcuda {
+
+constexpr int kDtBN = 256, kDtBK = 32, kDtStages = 2, kDtThreads = 192;
+constexpr int kDtABytes = 128 * kDtBK * 2;   // one of hi/lo of an A stage (8 KB)
+constexpr int kDtBBytes = kDtBN * kDtBK * 2; // one of hi/lo of a B stage (16 KB)
+constexpr int kDtStageBytes = 2 * kDtABytes + 2 * kDtBBytes;  // 48 KB
+constexpr int kDtMaxKsTiles = 48;
+
+// ---- activation packing -------------------------------------------------------------------
+// v[N, D] fp32 (flow state) -> A image whose K index j reads dim d = off + stride*j (j < nk),
+// K padded to KS*32.  Coupling layers: off = visible parity, stride 2.  MADE: (0, 1) or, for the
+// layers that see the reversed ordering, (D-1, -1).
+static __global__ void __launch_bounds__(256) dense_tc_pack_x_kernel(const float* __restrict__ v, int64_t N, int D,
+                                                                    int off, int stride, int nk, int KS,
+                                                                    uint8_t* __restrict__ img) {
+  const int64_t rows = (N + 127) / 128 * 128;
+  const int64_t total = rows * (KS * 4);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = i % rows;
+    const int ck = (int)(i / rows);  // global chunk index along K (8 elements each)
+    float f[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int j = ck * 8 + e;
+      f[e] = (row < N && j < nk) ? v[row * D + off + stride * j] : 0.f;
+    }
+    uint32_t h[4], l[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) tc::split_bf16x2(f[2 * e], f[2 * e + 1], h[e], l[e]);
+    const int64_t mt = row >> 7;
+    const int ks = ck >> 2, c = ck & 3;
+    uint8_t* st = img + ((mt * KS + ks) * 2) * (int64_t)kDtABytes + tc::img_off(128, (int)(row & 127), c);
+    *reinterpret_cast<uint4*>(st) = make_uint4(h[0], h[1], h[2], h[3]);
+    *reinterpret_cast<uint4*>(st + kDtABytes) = make_uint4(l[0], l[1], l[2], l[3]);
+  }
+}
+
+// ---- the GEMM ---------------------------------------------------------------------------------
+struct DtGemm {
+  const uint8_t* a_img;  // [m_tiles][KS][hi|lo][8 KB]
+  const uint8_t* b_img;  // [n_tiles][KS][hi|lo][16 KB]
+  const float* bias;     // this Linear's bias (inside the flow parameters)
+  int KS;                // K stages of the images (the image strides)
+  int n_out;             // valid output columns (hidden epilogue) / conditioner width (transform epilogue)
+  uint8_t* out_img;      // hidden epilogue: next Linear's A image, out_KS stages
+  int out_KS;
+  float* v;              // transform epilogue: state [N, D], updated in place
+  float* ldp;            // [N, tiles] log-det partials
+  int64_t N;
+  int D, tp, dstride;    // tile dim index `dim` -> state dim d = tp + dstride*dim
+  int ndims, dpt, ppd, tiles;
+  int made, rev;         // made: bias columns are [shift_0..shift_{D-1}, log_scale_0..]; rev: this layer sees dims reversed
+  float lo, hi;
+  unsigned char ks_tile[kDtMaxKsTiles];  // K stages n tile nt really needs (0 = all KS)
+};
+
+constexpr int kEpiHidden = 0, kEpiRqs8 = 1, kEpiAffine = 2;
+
+// bias index of tile column n (transform epilogues)
+__device__ __forceinline__ float dt_tile_bias(const DtGemm& a, int nt, int n) {
+  const int di = n / a.ppd, pp = n - di * a.ppd, dim = nt * a.dpt + di;
+  if (di >= a.dpt || dim >= a.ndims) return 0.f;
+  if (a.made) {
+    const int q = a.rev ? a.D - 1 - dim : dim;
+    return a.bias[pp * a.D + q];
+  }
+  return a.bias[(a.tp + a.dstride * dim) * a.ppd + pp];
+}
+
+template <int EPI, bool INV>
+__global__ void __launch_bounds__(kDtThreads, 2) dense_tc_gemm_kernel(DtGemm a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* stages = smem;                                                     // [stages][48 KB]
+  float* sbias = reinterpret_cast<float*>(smem + kDtStages * kDtStageBytes);  // [256]
+  uint64_t* full = reinterpret_cast<uint64_t*>(sbias + kDtBN);               // [stages]
+  uint64_t* empty = full + kDtStages;                                         // [stages]
+  uint64_t* dfull = empty + kDtStages;                                        // [1]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(dfull + 1);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int mt = blockIdx.x, nt = blockIdx.y;
+  int KS = a.KS;
+  if (nt < kDtMaxKsTiles && a.ks_tile[nt] != 0) KS = a.ks_tile[nt];
+
+  if (warp == 1) tc::tmem_alloc(tmem_slot, kDtBN);
+  if (tid == 0) {
+    for (int s = 0; s < kDtStages; ++s) {
+      tc::mbar_init(&full[s], 1);
+      tc::mbar_init(&empty[s], 1);
+    }
+    tc::mbar_init(dfull, 1);
+    tc::fence_mbar_init();
+  }
+  if (warp >= 2) {  // bias of this tile's columns
+    const int c = tid - 64;
+    for (int n = c; n < kDtBN; n += 128) {
+      float b = 0.f;
+      if (EPI == kEpiHidden) {
+        const int col = nt * kDtBN + n;
+        if (col < a.n_out) b = a.bias[col];
+      } else {
+        b = dt_tile_bias(a, nt, n);
+      }
+      sbias[n] = b;
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {  // ===== TMA loader
+      const uint8_t* ag = a.a_img + (int64_t)mt * a.KS * 2 * kDtABytes;
+      const uint8_t* bg = a.b_img + (int64_t)nt * a.KS * 2 * kDtBBytes;
+      for (int ks = 0; ks < KS; ++ks) {
+        const int st = ks % kDtStages, use = ks / kDtStages;
+        if (use > 0) tc::mbar_wait(&empty[st], (uint32_t)((use - 1) & 1));
+        uint8_t* dst = stages + st * kDtStageBytes;
+        tc::mbar_arrive_expect_tx(&full[st], kDtStageBytes);
+        tc::tma_bulk_g2s(dst, ag + (int64_t)ks * 2 * kDtABytes, 2 * kDtABytes, &full[st]);
+        tc::tma_bulk_g2s(dst + 2 * kDtABytes, bg + (int64_t)ks * 2 * kDtBBytes, 2 * kDtBBytes, &full[st]);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {  // ===== MMA issuer: 3 passes x 2 K steps per stage
+      constexpr uint32_t idesc = tc::make_idesc(tc::kFmtBF16, 128, kDtBN);
+      constexpr uint32_t lbo_a = 16u * 128u, lbo_b = (uint32_t)(kDtBN >> 3) * 128u;
+      uint32_t acc = 0;
+      for (int ks = 0; ks < KS; ++ks) {
+        const int st = ks % kDtStages, use = ks / kDtStages;
+        tc::mbar_wait(&full[st], (uint32_t)(use & 1));
+        tc::tc_fence_after();
+        const uint32_t sa = tc::smem_u32(stages + st * kDtStageBytes), sb = sa + 2 * kDtABytes;
+#pragma unroll
+        for (int pass = 0; pass < 3; ++pass) {
+          const uint32_t ab = sa + (pass == 2 ? kDtABytes : 0), bb = sb + (pass == 1 ? kDtBBytes : 0);
+#pragma unroll
+          for (int s = 0; s < kDtBK / 16; ++s) {
+            tc::mma_ss<tc::kFmtBF16>(tmem, tc::make_smem_desc(ab + s * 2u * lbo_a, lbo_a, 128u),
+                                     tc::make_smem_desc(bb + s * 2u * lbo_b, lbo_b, 128u), idesc, acc);
+            acc = 1;
+          }
+        }
+        tc::mma_commit(&empty[st]);
+      }
+      tc::mma_commit(dfull);
+    }
+  } else {
+    // ===== epilogue warps: thread = row = TMEM lane
+    const int row = (warp & 3) * 32 + lane;
+    const int64_t grow = (int64_t)mt * 128 + row;
+    const uint32_t tb = tmem + ((uint32_t)((warp & 3) * 32) << 16);
+    tc::mbar_wait(dfull, 0);
+    tc::tc_fence_after();
+    if (EPI == kEpiHidden) {
+      uint8_t* og = a.out_img + (int64_t)mt * a.out_KS * 2 * kDtABytes;
+#pragma unroll 1
+      for (int c = 0; c < kDtBN; c += 16) {
+        uint32_t vv[16];
+        tc::tmem_ld_x16(tb + (uint32_t)c, vv);
+        tc::tmem_ld_wait();
+        uint32_t h[8], l[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float f0 = fmaxf(__uint_as_float(vv[2 * e]) + sbias[c + 2 * e], 0.f);
+          const float f1 = fmaxf(__uint_as_float(vv[2 * e + 1]) + sbias[c + 2 * e + 1], 0.f);
+          tc::split_bf16x2(f0, f1, h[e], l[e]);
+        }
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+          const int ck = (nt * kDtBN + c) / 8 + q;  // chunk index along the next Linear's K
+          if (ck < a.out_KS * 4) {
+            uint8_t* st = og + (int64_t)(ck >> 2) * 2 * kDtABytes + tc::img_off(128, row, ck & 3);
+            *reinterpret_cast<uint4*>(st) = make_uint4(h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]);
+            *reinterpret_cast<uint4*>(st + kDtABytes) = make_uint4(l[4 * q], l[4 * q + 1], l[4 * q + 2], l[4 * q + 3]);
+          }
+        }
+      }
+    } else if (EPI == kEpiRqs8) {
+      float ldsum = 0.f;
+#pragma unroll 1
+      for (int di = 0; di < 10; ++di) {
+        const int dim = nt * 10 + di;
+        if (dim >= a.ndims) break;  // uniform across the CTA
+        uint32_t vv[25];
+        tc::tmem_ld_x16(tb + (uint32_t)(25 * di), vv);
+        tc::tmem_ld_x8(tb + (uint32_t)(25 * di + 16), vv + 16);
+        tc::tmem_ld_x1(tb + (uint32_t)(25 * di + 24), vv + 24);
+        tc::tmem_ld_wait();
+        if (grow < a.N) {
+          float o[25];
+#pragma unroll
+          for (int i = 0; i < 25; ++i) o[i] = __uint_as_float(vv[i]) + sbias[25 * di + i];
+          const int d = a.tp + a.dstride * dim;
+          const float xin = a.v[grow * a.D + d];
+          float nv, l1;
+          rqs_apply<INV, 8>([&](int i) { return o[i]; }, 8, a.lo, a.hi, xin, nv, l1);
+          a.v[grow * a.D + d] = nv;
+          ldsum += l1;
+        }
+      }
+      if (grow < a.N) a.ldp[grow * a.tiles + nt] = ldsum;
+    } else {
+      float ldsum = 0.f;
+#pragma unroll 1
+      for (int c = 0; c < kDtBN; c += 32) {
+        if (nt * 128 + c / 2 >= a.ndims) break;
+        uint32_t vv[32];
+        tc::tmem_ld_x32(tb + (uint32_t)c, vv);
+        tc::tmem_ld_wait();
+        if (grow < a.N) {
+#pragma unroll
+          for (int e = 0; e < 16; ++e) {
+            const int dim = nt * 128 + c / 2 + e;
+            if (dim < a.ndims) {
+              const int d = a.tp + a.dstride * dim;
+              float nv, l1;
+              affine_apply<INV>(__uint_as_float(vv[2 * e]) + sbias[c + 2 * e],
+                                __uint_as_float(vv[2 * e + 1]) + sbias[c + 2 * e + 1], a.v[grow * a.D + d], nv, l1);
+              a.v[grow * a.D + d] = nv;
+              ldsum += l1;
+            }
+          }
+        }
+      }
+      if (grow < a.N) a.ldp[grow * a.tiles + nt] = ldsum;
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    tc::tmem_dealloc(tmem, kDtBN);
+  }
+}
+
+template <int EPI, bool INV>
+static int dt_launch_gemm(const DtGemm& g, int64_t MT, int NT, cudaStream_t s) {
+  const size_t smem = (size_t)kDtStages * kDtStageBytes + kDtBN * 4 + (2 * kDtStages + 1) * 8 + 16;
+  auto kern = dense_tc_gemm_kernel<EPI, INV>;
+  FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  kern<<<dim3((unsigned)MT, (unsigned)NT), kDtThreads, smem, s>>>(g);
+  FC_LAUNCH_CHECK("dense_tc_gemm_kernel");
+  return FLOWCUDA_OK;
+}
+
+// ---- log-det bookkeeping (fixed summation order: deterministic) ----------------------------------
+static __global__ void __launch_bounds__(256) dense_tc_ld_accum_kernel(const float* __restrict__ ldp, int tiles, int used,
+                                                                      float* __restrict__ ld, int64_t N, int first) {
+  int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= N) return;
+  float s = first ? 0.f : ld[r];
+  for (int t = 0; t < used; ++t) s += ldp[r * tiles + t];
+  ld[r] = s;
+}
+
+static __global__ void __launch_bounds__(256) dense_tc_finish_kernel(const float* __restrict__ v, const float* __restrict__ ld,
+                                                                    int64_t N, int D, int with_base, int base,
+                                                                    float* __restrict__ out_lp, float* __restrict__ out_ld) {
+  int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;  // one warp per row
+  int lane = threadIdx.x & 31;
+  if (r >= N) return;
+  float s = 0.f;
+  if (with_base)
+    for (int d = lane; d < D; d += 32) s += base_term(base, v[r * D + d]);
+  s = warp_sum(s);
+  if (lane == 0) {
+    if (out_ld) out_ld[r] = ld[r];
+    if (out_lp) out_lp[r] = ld[r] + s;
+  }
+}
+
+static inline size_t dt_al256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+}  // namespace flowcuda

@@ -300,6 +300,51 @@ def _try_fuse(bijectors) -> Optional[_FusedCouplingStack]:
     return _FusedCouplingStack(bijectors, flat)
 
 
+class MaskedAutoregressiveFlow(Bijector):
+    """A stack of MADE-conditioned masked autoregressive affine layers (tfb.MaskedAutoregressiveFlow
+    over tfb.AutoregressiveNetwork(params=2, hidden_units=hidden, activation="relu"), with a reversal
+    between layers — the `tfb` component north_star names; the reference has no code for it,
+    SURVEY App. A.7).  As in TFP, `forward` is the sequential sampling direction (base -> data) and
+    `inverse` the one-pass density direction.  `params`: flat fp32 buffer, per layer per Linear
+    W[in,out] then b[out], unmasked (csrc/made.cu folds the masks in)."""
+
+    def __init__(self, event_dim: int, num_layers: int, hidden_sizes: Sequence[int], params: Optional[Array] = None,
+                 seed: int = 0):
+        super().__init__(event_ndims_in=1)
+        self.event_dim, self.num_layers, self.hidden_sizes = int(event_dim), int(num_layers), [int(h) for h in hidden_sizes]
+        self._mspec = ops.make_made_spec(self.event_dim, self.num_layers, self.hidden_sizes)
+        count = ops.made_param_count(self._mspec)
+        if params is None:
+            gen = torch.Generator().manual_seed(seed)
+            sizes = [self.event_dim] + self.hidden_sizes + [2 * self.event_dim]
+            chunks = []
+            for _ in range(self.num_layers):
+                for i, (m, n) in enumerate(zip(sizes[:-1], sizes[1:])):
+                    last = i == len(sizes) - 2  # zeros-initialised output Linear: the flow starts as the identity
+                    w = torch.zeros(m, n) if last else torch.nn.init.trunc_normal_(torch.empty(m, n), std=1.0 / math.sqrt(m), generator=gen)
+                    chunks += [w.reshape(-1), torch.zeros(n)]
+            params = torch.cat(chunks)
+        params = params.to("cuda", torch.float32).contiguous()
+        if params.numel() != count:
+            raise ValueError(f"expected {count} parameters, got {params.numel()}")
+        self.params = params
+
+    def spec(self, base: int = _lib.BASE_NORMAL):
+        return ops.make_made_spec(self.event_dim, self.num_layers, self.hidden_sizes, base)
+
+    def inverse_and_log_det(self, y):
+        batch = y.shape[:-1]
+        _, u, ld = ops.made_log_prob(self._mspec, self.params, y.reshape(-1, self.event_dim), want_u=True,
+                                     want_log_det=True, want_log_prob=False)
+        return u.reshape(y.shape), ld.reshape(batch)
+
+    def forward_and_log_det(self, x):
+        batch = x.shape[:-1]
+        y = ops.made_sample(self._mspec, self.params, x.reshape(-1, self.event_dim))
+        _, _, ld = ops.made_log_prob(self._mspec, self.params, y, want_log_det=True, want_log_prob=False)
+        return y.reshape(x.shape), (-ld).reshape(batch)
+
+
 # ------------------------------------------------------------------------------ distributions
 class Distribution:
     event_shape: Tuple[int, ...] = ()
@@ -377,11 +422,19 @@ class Transformed(Distribution):
         self.precision = precision
         self._stack = None
         inner = bijector.bijector if isinstance(bijector, Inverse) else None
+        self._maf = bijector if isinstance(bijector, MaskedAutoregressiveFlow) and isinstance(distribution, Independent) else None
+        if self._maf is not None:
+            self._base = distribution._base_code()
         if isinstance(inner, Chain) and inner._fused is not None and isinstance(distribution, Independent):
             self._stack = inner._fused
             self._base = distribution._base_code()
 
     def log_prob(self, value: Array) -> Array:
+        if self._maf is not None:
+            D = self._maf.event_dim
+            batch = value.shape[:-1] if value.shape[-1] == D else (value.numel() // D,)
+            lp, _, _ = ops.made_log_prob(self._maf.spec(self._base), self._maf.params, value.reshape(-1, self._maf.event_dim))
+            return lp.reshape(batch)
         if self._stack is None:
             raise NotImplementedError("Transformed.log_prob is implemented for Inverse(Chain([MaskedCoupling...])) flows; "
                                       "see BernsteinBijector.bernstein_flow_log_prob for the bflow chain")
@@ -393,6 +446,8 @@ class Transformed(Distribution):
 
     def sample_from_noise(self, z: Array) -> Array:
         """Transformed.sample with the base noise given: bijector.forward(z)."""
+        if self._maf is not None:
+            return ops.made_sample(self._maf._mspec, self._maf.params, z.reshape(-1, self._maf.event_dim)).reshape(z.shape)
         if self._stack is None:
             return self.bijector.forward(z)
         D = self._stack.first.conditioner.event_dim

@@ -64,3 +64,22 @@ def make_flow_model(event_shape: Sequence[int], num_layers: int, hidden_sizes: S
     model = distrax.Transformed(base_dist, flow, precision=precision)
     model.params = params
     return model
+
+
+def make_maf_model(event_shape: Sequence[int], num_layers: int, hidden_sizes: Sequence[int], *, base: str = "normal",
+                   params: Optional[torch.Tensor] = None, seed: int = 42) -> distrax.Transformed:
+    """MADE-conditioned masked autoregressive flow (the `tfb.MaskedAutoregressiveFlow` stack north_star
+    names for the D=784 configs) over a flattened event, with the reference scripts'
+    base distributions (maf_mnist.py:84-89)."""
+    event_shape = tuple(int(s) for s in event_shape)
+    D = int(math.prod(event_shape))
+    flow = distrax.MaskedAutoregressiveFlow(D, num_layers, hidden_sizes, params=params, seed=seed)
+    if base == "normal":
+        base_dist = distrax.Independent(distrax.Normal(torch.zeros(D), torch.ones(D)), 1)
+    elif base == "uniform":
+        base_dist = distrax.Independent(distrax.Uniform(torch.zeros(D), torch.ones(D)), 1)
+    else:
+        raise ValueError(base)
+    model = distrax.Transformed(base_dist, flow)
+    model.params = flow.params
+    return model

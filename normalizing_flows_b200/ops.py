@@ -238,6 +238,55 @@ def coupling_nll_grad(spec: CouplingSpec, params: torch.Tensor, x: torch.Tensor)
     return loss, grad
 
 
+# ---------------------------------------------------------------------------- row #8
+def make_made_spec(event_dim: int, num_layers: int, hidden: Sequence[int], base: int = _lib.BASE_NORMAL) -> _lib.MadeSpec:
+    if len(hidden) > _lib.MAX_HIDDEN_LAYERS:
+        raise ValueError("at most %d hidden layers" % _lib.MAX_HIDDEN_LAYERS)
+    sp = _lib.MadeSpec()
+    sp.event_dim, sp.num_layers, sp.num_hidden = event_dim, num_layers, len(hidden)
+    for i, h in enumerate(hidden):
+        sp.hidden[i] = h
+    sp.base = base
+    return sp
+
+
+def made_param_count(spec: _lib.MadeSpec) -> int:
+    n = _lib.load().flowcuda_made_param_count(C.byref(spec))
+    if n < 0:
+        check(-1, "made_param_count")
+    return n
+
+
+def made_log_prob(spec: _lib.MadeSpec, params: torch.Tensor, x: torch.Tensor, want_u: bool = False,
+                  want_log_det: bool = False, want_log_prob: bool = True, with_base: bool = True,
+                  workspace: Optional[torch.Tensor] = None):
+    """MAF density pass (data -> base).  Returns (log_prob, u, log_det), None where not requested."""
+    x = _f32(x).reshape(x.shape[0], spec.event_dim)
+    _dev_check(params, x)
+    lib = _lib.load()
+    n = x.shape[0]
+    lp = torch.empty(n, device=x.device, dtype=torch.float32) if want_log_prob else None
+    u = torch.empty_like(x) if want_u else None
+    ld = torch.empty(n, device=x.device, dtype=torch.float32) if want_log_det else None
+    need = lib.flowcuda_made_workspace_bytes(C.byref(spec), n)
+    if workspace is None or workspace.numel() * workspace.element_size() < need:
+        workspace = torch.empty((need + 3) // 4, device=x.device, dtype=torch.float32)
+    check(lib.flowcuda_made_log_prob(C.byref(spec), _ptr(params), _ptr(x), _ptr(lp), _ptr(u), _ptr(ld), n,
+                                     int(with_base), _ptr(workspace), workspace.numel() * workspace.element_size(),
+                                     _stream()), "made_log_prob")
+    return lp, u, ld
+
+
+def made_sample(spec: _lib.MadeSpec, params: torch.Tensor, z: torch.Tensor) -> torch.Tensor:
+    """MAF sampling with the base noise given (base -> data), sequential over dimensions."""
+    z = _f32(z).reshape(z.shape[0], spec.event_dim)
+    _dev_check(params, z)
+    x = torch.empty_like(z)
+    check(_lib.load().flowcuda_made_sample(C.byref(spec), _ptr(params), _ptr(z), _ptr(x), z.shape[0], _stream()),
+          "made_sample")
+    return x
+
+
 # ---------------------------------------------------------------------------- rows #7, #9
 def sum_scaled(v: torch.Tensor, scale: float) -> torch.Tensor:
     v = _f32(v).reshape(-1)

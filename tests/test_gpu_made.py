@@ -1,0 +1,131 @@
+"""GPU: row #8 — the MADE-conditioned masked autoregressive affine flow (csrc/made.cu) against the
+float64 oracle (oracle/flows_oracle.py:510-606; PARITY UNPINNED — the reference has no MADE code,
+SURVEY App. A.7).  The density pass runs on the tensor cores (bf16x3): north_star tolerance 1e-3
+absolute on log_prob, held here at 2e-4·max(1,|ref|); the sequential sampler is FP32."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import flows_oracle as O
+from test_gpu_parity import G, close
+
+pytestmark = pytest.mark.gpu
+
+CASES = {
+    "d6": (O.MadeSpec(6, 2, [16, 16]), 0.5),
+    "toy_d2": (O.MadeSpec(2, 8, [64, 64]), 0.3),
+    "d50_ragged": (O.MadeSpec(50, 3, [40, 70]), 0.4),
+    "d300_wide": (O.MadeSpec(300, 2, [512, 300]), 0.3),
+    "d1": (O.MadeSpec(1, 2, [8, 8]), 0.5),
+}
+
+
+def _spec(ops, ospec):
+    return ops.make_made_spec(ospec.event_dim, ospec.num_layers, ospec.hidden)
+
+
+@pytest.mark.parametrize("case", sorted(CASES))
+@pytest.mark.parametrize("n", [1, 77, 300])
+def test_made_log_prob_parity(case, n):
+    from normalizing_flows_b200 import ops
+
+    ospec, scale = CASES[case]
+    params = O.init_made_params(ospec, seed=3, scale=scale)
+    flat = O.flatten_layers(params)
+    spec = _spec(ops, ospec)
+    assert ops.made_param_count(spec) == flat.numel()
+    x = torch.randn(n, ospec.event_dim, generator=torch.Generator().manual_seed(n), dtype=torch.float64).float()
+    lp, u, ld = ops.made_log_prob(spec, G(flat), x.cuda(), want_u=True, want_log_det=True)
+    lpref = O.maf_log_prob(ospec, params, x.double())
+    close(lp, lpref.numpy(), tol=2e-4, what="log_prob")
+    # u and log_det from the oracle: log_prob = base(u) + log_det
+    uref = _oracle_u(ospec, params, x.double())
+    close(u, uref.numpy(), tol=2e-4, what="u")
+    ldref = lpref - (-0.5 * uref * uref - 0.5 * O.LOG_2PI).sum(-1)
+    close(ld, ldref.numpy(), tol=2e-4, what="log_det")
+
+
+def _oracle_u(ospec, params, x):
+    v = x
+    for l in reversed(range(ospec.num_layers)):
+        vp = O._maf_perm(l, v)
+        mu, alpha = O.made_conditioner(ospec, params[l], vp)
+        v = O._maf_perm(l, (vp - mu) * torch.exp(-alpha))
+    return v
+
+
+@pytest.mark.parametrize("case", ["d6", "toy_d2", "d50_ragged", "d300_wide"])
+@pytest.mark.parametrize("n", [1, 13, 40])
+def test_made_sample_parity(case, n):
+    """Sequential sampler (FP32, incremental pre-activations) vs the oracle's D-pass loop."""
+    from normalizing_flows_b200 import ops
+
+    ospec, scale = CASES[case]
+    params = O.init_made_params(ospec, seed=4, scale=scale)
+    flat = O.flatten_layers(params)
+    z = torch.randn(n, ospec.event_dim, generator=torch.Generator().manual_seed(7 + n), dtype=torch.float64).float()
+    x = ops.made_sample(_spec(ops, ospec), G(flat), z.cuda())
+    xref = O.maf_sample(ospec, params, z.double())
+    close(x, xref.numpy(), tol=2e-5, what="sample")
+
+
+def test_made_mnist_shape_log_prob_and_round_trip():
+    """D=784, H=512 (the north_star MAF-MNIST shape; 2 flow layers to bound the CPU oracle):
+    |log_prob - float64 oracle| <= 1e-3 absolute, and log_prob's u inverts the sampler."""
+    from normalizing_flows_b200 import ops
+
+    ospec = O.MadeSpec(784, 2, [512, 512])
+    params = O.init_made_params(ospec, seed=5, scale=0.3)
+    flat = G(O.flatten_layers(params))
+    spec = _spec(ops, ospec)
+    gen = torch.Generator().manual_seed(0)
+    x = torch.randn(200, 784, generator=gen, dtype=torch.float64).float()
+    lp, _, _ = ops.made_log_prob(spec, flat, x.cuda())
+    ref = O.maf_log_prob(ospec, params, x.double()).numpy()
+    err = np.abs(lp.double().cpu().numpy() - ref).max()
+    assert err <= 1e-3, err
+    z = torch.randn(24, 784, generator=gen, dtype=torch.float64).float()
+    xs = ops.made_sample(spec, flat, z.cuda())
+    xref = O.maf_sample(ospec, params, z.double())
+    close(xs, xref.numpy(), tol=5e-5, what="sample d784")
+    _, u, _ = ops.made_log_prob(spec, flat, xs, want_u=True)
+    assert (u.cpu() - z).abs().max().item() <= 2e-3
+
+
+def test_made_full_size_round_trip_and_autoregressive_property():
+    """Size-independent properties at the bench shape (8 layers, D=784, batch 4096): sample then
+    density pass returns the noise; perturbing x_j changes u_i only for i >= j in the layer's ordering."""
+    from normalizing_flows_b200 import ops
+
+    ospec = O.MadeSpec(784, 8, [512, 512])
+    params = O.init_made_params(ospec, seed=6, dtype=torch.float32, scale=0.2)
+    flat = O.flatten_layers(params).float().cuda()
+    spec = _spec(ops, ospec)
+    z = torch.randn(4096, 784, generator=torch.Generator().manual_seed(1)).cuda()
+    x = ops.made_sample(spec, flat, z)
+    assert torch.isfinite(x).all()
+    lp, u, ld = ops.made_log_prob(spec, flat, x, want_u=True, want_log_det=True)
+    assert (u - z).abs().max().item() <= 5e-3
+    base = (-0.5 * u.double() ** 2 - 0.5 * O.LOG_2PI).sum(-1)
+    assert ((lp.double() - base - ld.double()).abs() <= 1e-3 * base.abs().clamp(min=1)).all()
+    # single layer: u_i must not depend on x_j for j > i (even layer = natural ordering)
+    one = ops.make_made_spec(784, 1, [512, 512])
+    xa = x[:64].clone()
+    xb = xa.clone()
+    xb[:, 400:] += 1.0
+    _, ua, _ = ops.made_log_prob(one, flat, xa, want_u=True)
+    _, ub, _ = ops.made_log_prob(one, flat, xb, want_u=True)
+    assert torch.equal(ua[:, :400], ub[:, :400])
+    assert (ua[:, 400:] - ub[:, 400:]).abs().min().item() > 0
+
+
+def test_made_rejects_bad_arguments():
+    from normalizing_flows_b200 import _lib, ops
+
+    spec = ops.make_made_spec(6, 2, [16])
+    flat = torch.zeros(ops.made_param_count(spec), device="cuda")
+    with pytest.raises(_lib.FlowCudaError):
+        ops.made_sample(spec, flat, torch.zeros(4, 6, device="cuda"))  # sampler needs two hidden layers
+    with pytest.raises(_lib.FlowCudaError):
+        ops.made_log_prob(spec, flat, torch.zeros(4, 6))  # CPU tensor: no CPU path
+    assert ops.made_log_prob(spec, flat, torch.zeros(0, 6, device="cuda"))[0].numel() == 0
