@@ -70,6 +70,7 @@ struct DtGemm {
   int64_t N;
   int D, tp, dstride;    // tile dim index `dim` -> state dim d = tp + dstride*dim
   int ndims, dpt, ppd, tiles;
+  int next_rev;          // affine epilogue with out_img: the next layer reads the dims reversed
   int made, rev;         // made: bias columns are [shift_0..shift_{D-1}, log_scale_0..]; rev: this layer sees dims reversed
   float lo, hi;
   unsigned char ks_tile[kDtMaxKsTiles];  // K stages n tile nt really needs (0 = all KS)
@@ -222,27 +223,92 @@ __global__ void __launch_bounds__(kDtThreads, 2) dense_tc_gemm_kernel(DtGemm a) 
       }
       if (grow < a.N) a.ldp[grow * a.tiles + nt] = ldsum;
     } else {
+      // Affine epilogue.  The accumulator comes out of TMEM as thread = sample row, but the state v[N, D]
+      // is row-major: a thread-per-row access touches 32 cache lines per request.  Each warp therefore
+      // transposes its 32 rows x 32 columns through shared memory (the pipeline stages are idle by now)
+      // and applies the bijector as lane = dimension, so the state is read and written in 64-byte runs;
+      // a third phase (thread = row again) sums the log-det and, for MADE stacks, writes the NEXT
+      // layer's activation image directly (bf16 hi/lo), so no separate packing pass re-reads v.
+      constexpr int TS = 36;  // row stride of the transposition tile in floats (16-byte aligned rows)
+      float* T = reinterpret_cast<float*>(stages) + (warp & 3) * 32 * TS;
+      const int r0 = (warp & 3) * 32;
+      const int k = lane & 15, hp = lane >> 4;
+      uint8_t* og = a.out_img ? a.out_img + (int64_t)mt * a.out_KS * 2 * kDtABytes : nullptr;
       float ldsum = 0.f;
 #pragma unroll 1
       for (int c = 0; c < kDtBN; c += 32) {
-        if (nt * 128 + c / 2 >= a.ndims) break;
+        const int dim0 = nt * 128 + c / 2;
+        if (dim0 >= a.ndims) break;  // uniform across the CTA
         uint32_t vv[32];
         tc::tmem_ld_x32(tb + (uint32_t)c, vv);
         tc::tmem_ld_wait();
-        if (grow < a.N) {
 #pragma unroll
-          for (int e = 0; e < 16; ++e) {
-            const int dim = nt * 128 + c / 2 + e;
-            if (dim < a.ndims) {
-              const int d = a.tp + a.dstride * dim;
-              float nv, l1;
-              affine_apply<INV>(__uint_as_float(vv[2 * e]) + sbias[c + 2 * e],
-                                __uint_as_float(vv[2 * e + 1]) + sbias[c + 2 * e + 1], a.v[grow * a.D + d], nv, l1);
-              a.v[grow * a.D + d] = nv;
-              ldsum += l1;
+        for (int e = 0; e < 8; ++e) {
+          float4 t4;
+          t4.x = __uint_as_float(vv[4 * e]) + sbias[c + 4 * e];
+          t4.y = __uint_as_float(vv[4 * e + 1]) + sbias[c + 4 * e + 1];
+          t4.z = __uint_as_float(vv[4 * e + 2]) + sbias[c + 4 * e + 2];
+          t4.w = __uint_as_float(vv[4 * e + 3]) + sbias[c + 4 * e + 3];
+          *reinterpret_cast<float4*>(T + lane * TS + 4 * e) = t4;
+        }
+        __syncwarp();
+        {  // lane = (dimension k, row parity hp)
+          const int dim = dim0 + k;
+          const bool dvalid = dim < a.ndims;
+          const int d = a.tp + a.dstride * dim;
+          float xv[16];
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int64_t gr = (int64_t)mt * 128 + r0 + 2 * i + hp;
+            xv[i] = (dvalid && gr < a.N) ? a.v[gr * a.D + d] : 0.f;
+          }
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {
+            const int r = 2 * i + hp;
+            const int64_t gr = (int64_t)mt * 128 + r0 + r;
+            const float2 p = *reinterpret_cast<const float2*>(T + r * TS + 2 * k);
+            float nv, l1;
+            affine_apply<INV>(p.x, p.y, xv[i], nv, l1);
+            if (dvalid && gr < a.N) {
+              a.v[gr * a.D + d] = nv;
+            } else {
+              nv = 0.f;
+              l1 = 0.f;
+            }
+            *reinterpret_cast<float2*>(T + r * TS + 2 * k) = make_float2(nv, l1);
+          }
+        }
+        __syncwarp();
+        {  // thread = row again: log-det partial, next layer's activation image
+          float u[16];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const float4 t4 = *reinterpret_cast<const float4*>(T + lane * TS + 4 * e);
+            u[2 * e] = t4.x;
+            u[2 * e + 1] = t4.z;
+            ldsum += t4.y + t4.w;
+          }
+          if (og != nullptr) {
+            uint32_t h[8], l[8];
+            int ck;
+            if (a.next_rev) {
+#pragma unroll
+              for (int e = 0; e < 8; ++e) tc::split_bf16x2(u[15 - 2 * e], u[14 - 2 * e], h[e], l[e]);
+              ck = (a.D - 16 - dim0) >> 3;
+            } else {
+#pragma unroll
+              for (int e = 0; e < 8; ++e) tc::split_bf16x2(u[2 * e], u[2 * e + 1], h[e], l[e]);
+              ck = dim0 >> 3;
+            }
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+              uint8_t* st = og + (int64_t)((ck + q) >> 2) * 2 * kDtABytes + tc::img_off(128, row, (ck + q) & 3);
+              *reinterpret_cast<uint4*>(st) = make_uint4(h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]);
+              *reinterpret_cast<uint4*>(st + kDtABytes) = make_uint4(l[4 * q], l[4 * q + 1], l[4 * q + 2], l[4 * q + 3]);
             }
           }
         }
+        __syncwarp();
       }
       if (grow < a.N) a.ldp[grow * a.tiles + nt] = ldsum;
     }

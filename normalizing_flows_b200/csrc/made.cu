@@ -200,7 +200,9 @@ static int made_log_prob_run(const flowcuda_made_spec* sp, const float* params, 
     const int l = sp->num_layers - 1 - it;  // data -> base: last layer first
     const bool rev = (l & 1) != 0;
     const float* lp = params + L.per_layer * l;
-    {
+    // the previous layer's epilogue has already written this layer's activation image when it can
+    const bool fuse_x = (D % 16) == 0;
+    if (it == 0 || !fuse_x) {
       int64_t total = L.MT * 128 * L.KS[0] * 4;
       int blocks = (int)((total + 255) / 256);
       dense_tc_pack_x_kernel<<<blocks, 256, 0, s>>>(v, n, D, rev ? D - 1 : 0, rev ? -1 : 1, D, L.KS[0], ws + L.off_x);
@@ -224,6 +226,11 @@ static int made_log_prob_run(const flowcuda_made_spec* sp, const float* params, 
         rc = dt_launch_gemm<kEpiHidden, false>(g, L.MT, L.NT[i], s);
         aimg = g.out_img;
       } else {
+        if (fuse_x && it + 1 < sp->num_layers) {
+          g.out_img = ws + L.off_x;
+          g.out_KS = L.KS[0];
+          g.next_rev = ((l - 1) & 1) != 0;
+        }
         rc = dt_launch_gemm<kEpiAffine, true>(g, L.MT, L.tiles, s);
         if (rc) return rc;
         dense_tc_ld_accum_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(ldp, L.tiles, L.tiles, ld, n, it == 0);
@@ -250,15 +257,29 @@ struct MadeSample {
   int D, H1, H2, L;
 };
 
+__device__ __forceinline__ void cp_async4(float* dst_smem, const float* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(tc::smem_u32(dst_smem)), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
 // S samples per CTA, T threads; thread t owns hidden columns t + T*c (c < CH) of both hidden layers and
 // the (shift, log_scale) accumulators of ordering positions t + T*c (c < CD).
+// Step q needs row q of W1 and the W2 / W3 rows of the hidden units whose degree completes at q; which
+// rows is known in advance, so every thread streams ITS elements of those rows into a private
+// shared-memory ring kMsPF steps ahead (cp.async), hiding the L2 latency behind the previous steps.
+constexpr int kMsRing = 4, kMsPF = 3;
+
 template <int S, int T, int CH, int CD>
 __global__ void __launch_bounds__(T, 1) made_sample_kernel(MadeSample a) {
   extern __shared__ __align__(16) float sm[];
   const int D = a.D, H1 = a.H1, H2 = a.H2;
+  constexpr int NC = 2 * CH + 2 * CD;  // ring components per thread and step
   float* zbuf = sm;            // [D][S] state, indexed by STATE dim
   float* hb1 = zbuf + D * S;   // [H1][S] finished hidden-1 activations
   float* hb2 = hb1 + H1 * S;   // [H2][S]
+  float* ring = hb2 + H2 * S;  // [kMsRing][NC][T]
   const int tid = threadIdx.x;
   const int64_t n0 = (int64_t)blockIdx.x * S;
   for (int i = tid; i < D * S; i += T) {
@@ -281,6 +302,37 @@ __global__ void __launch_bounds__(T, 1) made_sample_kernel(MadeSample a) {
     const float* __restrict__ W2 = P + a.w_off[1];
     const float* __restrict__ W3 = P + a.w_off[2];
     const bool rev = (l & 1) != 0;
+    // this thread's weights for step qq -> ring slot qq % kMsRing (always commits a group, possibly empty)
+    auto issue = [&](int qq) {
+      if (qq < D - 1) {
+        float* rb = ring + (qq % kMsRing) * (NC * T) + tid;
+        const int m = qq + 1;
+#pragma unroll
+        for (int c = 0; c < CH; ++c)
+          if (tid + T * c < H1 && deg1[c] >= m) cp_async4(rb + c * T, W1 + (int64_t)qq * H1 + tid + T * c);
+        const int k1 = made_kmin(m, H1, D);
+        if (made_kmin(m + 1, H1, D) > k1) {
+#pragma unroll
+          for (int c = 0; c < CH; ++c)
+            if (deg2[c] >= m) cp_async4(rb + (CH + c) * T, W2 + (int64_t)k1 * H2 + tid + T * c);
+        }
+        const int k2 = made_kmin(m, H2, D);
+        if (made_kmin(m + 1, H2, D) > k2) {
+#pragma unroll
+          for (int c = 0; c < CD; ++c) {
+            const int qd = tid + T * c;
+            if (qd > qq && qd < D) {
+              cp_async4(rb + (2 * CH + 2 * c) * T, W3 + (int64_t)k2 * 2 * D + qd);
+              cp_async4(rb + (2 * CH + 2 * c + 1) * T, W3 + (int64_t)k2 * 2 * D + D + qd);
+            }
+          }
+        }
+      }
+      cp_async_commit();
+    };
+#pragma unroll
+    for (int i = 0; i < kMsPF; ++i) issue(i);
+
     float a1[CH][S], a2[CH][S], om[CD][S], oa[CD][S];
 #pragma unroll
     for (int c = 0; c < CH; ++c) {
@@ -296,13 +348,11 @@ __global__ void __launch_bounds__(T, 1) made_sample_kernel(MadeSample a) {
 #pragma unroll
       for (int s = 0; s < S; ++s) { om[c][s] = bm; oa[c][s] = ba; }
     }
-    float w1n[CH];
-#pragma unroll
-    for (int c = 0; c < CH; ++c) w1n[c] = (tid + T * c) < H1 ? W1[tid + T * c] : 0.f;  // row 0
 
     for (int q = 0; q < D; ++q) {
       const int m = q + 1;  // the degree that completes at this step
       const int pos = rev ? D - 1 - q : q;
+      issue(q + kMsPF);
       // x_q = u_q * exp(log_scale_q) + shift_q  (owner of position q)
 #pragma unroll
       for (int c = 0; c < CD; ++c) {
@@ -311,8 +361,10 @@ __global__ void __launch_bounds__(T, 1) made_sample_kernel(MadeSample a) {
           for (int s = 0; s < S; ++s) zbuf[pos * S + s] = fmaf(zbuf[pos * S + s], expf(oa[c][s]), om[c][s]);
         }
       }
+      cp_async_wait<kMsPF>();  // this thread's ring entries of step q have landed
       __syncthreads();
       if (q == D - 1) break;  // nothing downstream of the last position
+      const float* rb = ring + (q % kMsRing) * (NC * T) + tid;
       float xs[S];
 #pragma unroll
       for (int s = 0; s < S; s += 4) {
@@ -323,7 +375,7 @@ __global__ void __launch_bounds__(T, 1) made_sample_kernel(MadeSample a) {
 #pragma unroll
       for (int c = 0; c < CH; ++c) {
         if (deg1[c] >= m) {
-          const float w = w1n[c];
+          const float w = rb[c * T];
 #pragma unroll
           for (int s = 0; s < S; ++s) a1[c][s] = fmaf(xs[s], w, a1[c][s]);
           if (deg1[c] == m) {
@@ -332,8 +384,6 @@ __global__ void __launch_bounds__(T, 1) made_sample_kernel(MadeSample a) {
           }
         }
       }
-#pragma unroll
-      for (int c = 0; c < CH; ++c) w1n[c] = (tid + T * c) < H1 ? W1[(int64_t)(q + 1) * H1 + tid + T * c] : 0.f;
       // hidden 2: the hidden-1 units of degree m are final now
       const int k1lo = made_kmin(m, H1, D), k1hi = made_kmin(m + 1, H1, D);
       if (k1hi > k1lo) {
@@ -348,7 +398,7 @@ __global__ void __launch_bounds__(T, 1) made_sample_kernel(MadeSample a) {
 #pragma unroll
           for (int c = 0; c < CH; ++c) {
             if (deg2[c] >= m) {
-              const float w = W2[(int64_t)ks * H2 + tid + T * c];
+              const float w = ks == k1lo ? rb[(CH + c) * T] : W2[(int64_t)ks * H2 + tid + T * c];
 #pragma unroll
               for (int s = 0; s < S; ++s) a2[c][s] = fmaf(hs[s], w, a2[c][s]);
             }
@@ -377,7 +427,14 @@ __global__ void __launch_bounds__(T, 1) made_sample_kernel(MadeSample a) {
           for (int c = 0; c < CD; ++c) {
             const int qq = tid + T * c;
             if (qq > q && qq < D) {
-              const float wm = W3[(int64_t)js * 2 * D + qq], wa = W3[(int64_t)js * 2 * D + D + qq];
+              float wm, wa;
+              if (js == k2lo) {
+                wm = rb[(2 * CH + 2 * c) * T];
+                wa = rb[(2 * CH + 2 * c + 1) * T];
+              } else {
+                wm = W3[(int64_t)js * 2 * D + qq];
+                wa = W3[(int64_t)js * 2 * D + D + qq];
+              }
 #pragma unroll
               for (int s = 0; s < S; ++s) {
                 om[c][s] = fmaf(gs[s], wm, om[c][s]);
@@ -388,6 +445,7 @@ __global__ void __launch_bounds__(T, 1) made_sample_kernel(MadeSample a) {
         }
       }
     }
+    cp_async_wait<0>();
     __syncthreads();
   }
   for (int i = tid; i < D * S; i += T) {
@@ -416,7 +474,7 @@ static int made_sample_run(const flowcuda_made_spec* sp, const float* params, co
   a.params = params; a.z = z; a.x = x; a.N = n; a.per_layer = L.per_layer;
   for (int i = 0; i < 3; ++i) { a.w_off[i] = L.w_off[i]; a.b_off[i] = L.b_off[i]; }
   a.D = D; a.H1 = H1; a.H2 = H2; a.L = sp->num_layers;
-  const size_t smem = (size_t)(D + H1 + H2) * kMsS * sizeof(float);
+  const size_t smem = ((size_t)(D + H1 + H2) * kMsS + (size_t)kMsRing * (2 * 1 + 2 * 2) * kMsT) * sizeof(float);
   auto kern = made_sample_kernel<kMsS, kMsT, 1, 2>;
   FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int64_t blocks = (n + kMsS - 1) / kMsS;

@@ -17,6 +17,8 @@ CASES = {
     "d50_ragged": (O.MadeSpec(50, 3, [40, 70]), 0.4),
     "d300_wide": (O.MadeSpec(300, 2, [512, 300]), 0.3),
     "d1": (O.MadeSpec(1, 2, [8, 8]), 0.5),
+    "d32_fused": (O.MadeSpec(32, 4, [40, 40]), 0.4),   # D % 16 == 0: the epilogue writes the next layer's image
+    "d160_fused": (O.MadeSpec(160, 3, [96, 200]), 0.3),
 }
 
 
@@ -54,7 +56,7 @@ def _oracle_u(ospec, params, x):
     return v
 
 
-@pytest.mark.parametrize("case", ["d6", "toy_d2", "d50_ragged", "d300_wide"])
+@pytest.mark.parametrize("case", ["d6", "toy_d2", "d50_ragged", "d300_wide", "d32_fused"])
 @pytest.mark.parametrize("n", [1, 13, 40])
 def test_made_sample_parity(case, n):
     """Sequential sampler (FP32, incremental pre-activations) vs the oracle's D-pass loop."""
