@@ -105,6 +105,35 @@ __device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
 }
 __device__ __forceinline__ float2 splat2(float a) { return make_float2(a, a); }
 
+// The same instructions on values that STAY packed: f2_t is one 64-bit register pair holding two fp32.
+// Keeping operands in this form end to end lets ptxas allocate aligned pairs once; the float2 helpers
+// above re-pack on every call, which costs one MOV per operand in hot loops.
+typedef unsigned long long f2_t;
+__device__ __forceinline__ f2_t f2_pack(float lo, float hi) {
+  f2_t r;
+  asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ f2_t f2_splat(float a) { return f2_pack(a, a); }
+__device__ __forceinline__ void f2_unpack(f2_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f2_t f2_fma(f2_t a, f2_t b, f2_t c) {
+  f2_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ f2_t f2_mul(f2_t a, f2_t b) {
+  f2_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f2_t f2_add(f2_t a, f2_t b) {
+  f2_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+
 // ---- scalar math with controlled accuracy -----------------------------------------
 // exp via MUFU.EX2 (abs err ~2 ulp on the scaled argument; rel err ~1e-7·|x| — inside the
 // 1e-5 parity budget for |x| <~ 30, which log-scales of a trained flow satisfy).
@@ -124,6 +153,18 @@ __device__ __forceinline__ double warp_sum_d(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
+}
+
+// Persistent grid for a grid-stride kernel: exactly the CTAs that are resident at once (SMs x occupancy),
+// so there is no partial last wave; fewer when the work does not fill them.
+template <typename K>
+inline int grid_resident(K kernel, int threads, size_t smem, int64_t work_items, int per_block) {
+  int occ = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, threads, smem) != cudaSuccess || occ < 1) occ = 1;
+  int64_t need = (work_items + per_block - 1) / per_block;
+  int64_t cap = (int64_t)sm_count() * occ;
+  if (need < 1) need = 1;
+  return (int)(need < cap ? need : cap);
 }
 
 inline int grid_for(int64_t work_items, int per_block, int waves_cap = 8) {

@@ -280,7 +280,15 @@ __global__ void __launch_bounds__(T, 1) made_sample_kernel(MadeSample a) {
   float* hb1 = zbuf + D * S;   // [H1][S] finished hidden-1 activations
   float* hb2 = hb1 + H1 * S;   // [H2][S]
   float* ring = hb2 + H2 * S;  // [kMsRing][NC][T]
+  // km1[m] / km2[m]: first hidden unit whose degree is >= m (the 64-bit division of made_kmin is far too
+  // slow for the per-step path)
+  int* km1 = reinterpret_cast<int*>(ring + kMsRing * NC * T);  // [D + 2]
+  int* km2 = km1 + D + 2;
   const int tid = threadIdx.x;
+  for (int m = tid; m < D + 2; m += T) {
+    km1[m] = made_kmin(m, H1, D);
+    km2[m] = made_kmin(m, H2, D);
+  }
   const int64_t n0 = (int64_t)blockIdx.x * S;
   for (int i = tid; i < D * S; i += T) {
     const int s = i / D, d = i - s * D;
@@ -310,14 +318,14 @@ __global__ void __launch_bounds__(T, 1) made_sample_kernel(MadeSample a) {
 #pragma unroll
         for (int c = 0; c < CH; ++c)
           if (tid + T * c < H1 && deg1[c] >= m) cp_async4(rb + c * T, W1 + (int64_t)qq * H1 + tid + T * c);
-        const int k1 = made_kmin(m, H1, D);
-        if (made_kmin(m + 1, H1, D) > k1) {
+        const int k1 = km1[m];
+        if (km1[m + 1] > k1) {
 #pragma unroll
           for (int c = 0; c < CH; ++c)
             if (deg2[c] >= m) cp_async4(rb + (CH + c) * T, W2 + (int64_t)k1 * H2 + tid + T * c);
         }
-        const int k2 = made_kmin(m, H2, D);
-        if (made_kmin(m + 1, H2, D) > k2) {
+        const int k2 = km2[m];
+        if (km2[m + 1] > k2) {
 #pragma unroll
           for (int c = 0; c < CD; ++c) {
             const int qd = tid + T * c;
@@ -385,7 +393,7 @@ __global__ void __launch_bounds__(T, 1) made_sample_kernel(MadeSample a) {
         }
       }
       // hidden 2: the hidden-1 units of degree m are final now
-      const int k1lo = made_kmin(m, H1, D), k1hi = made_kmin(m + 1, H1, D);
+      const int k1lo = km1[m], k1hi = km1[m + 1];
       if (k1hi > k1lo) {
         __syncthreads();
         for (int ks = k1lo; ks < k1hi; ++ks) {
@@ -405,7 +413,7 @@ __global__ void __launch_bounds__(T, 1) made_sample_kernel(MadeSample a) {
           }
         }
       }
-      const int k2lo = made_kmin(m, H2, D), k2hi = made_kmin(m + 1, H2, D);
+      const int k2lo = km2[m], k2hi = km2[m + 1];
       if (k2hi > k2lo) {
 #pragma unroll
         for (int c = 0; c < CH; ++c) {
@@ -474,7 +482,7 @@ static int made_sample_run(const flowcuda_made_spec* sp, const float* params, co
   a.params = params; a.z = z; a.x = x; a.N = n; a.per_layer = L.per_layer;
   for (int i = 0; i < 3; ++i) { a.w_off[i] = L.w_off[i]; a.b_off[i] = L.b_off[i]; }
   a.D = D; a.H1 = H1; a.H2 = H2; a.L = sp->num_layers;
-  const size_t smem = ((size_t)(D + H1 + H2) * kMsS + (size_t)kMsRing * (2 * 1 + 2 * 2) * kMsT) * sizeof(float);
+  const size_t smem = ((size_t)(D + H1 + H2) * kMsS + (size_t)kMsRing * (2 * 1 + 2 * 2) * kMsT + 2 * (size_t)(D + 2)) * sizeof(float);
   auto kern = made_sample_kernel<kMsS, kMsT, 1, 2>;
   FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int64_t blocks = (n + kMsS - 1) / kMsS;
