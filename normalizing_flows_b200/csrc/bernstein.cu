@@ -21,56 +21,106 @@ __device__ __forceinline__ float bern_clip(float x) {
   return fminf(fmaxf(x, 1e-7f), 0.99999988079071044921875f);
 }
 
-// Coefficient tables for a shared theta: tab[j] = {a_j, a_j, d_j, d_j},
-// a_j = θ_j C(n,j) (j<=n), d_j = n (θ_{j+1}-θ_j) C(n-1,j) (j<=n-1; d_n = 0).
-__device__ void bern_build_table(float4* tab, const float* __restrict__ theta, int M) {
+// Coefficient tables for a shared theta (plain floats, 16-byte aligned, zero padded):
+//   ta[j] = θ_j C(n,j) (j <= n),   td[j] = n (θ_{j+1}-θ_j) C(n-1,j) (j <= n-1), td[n] = 0.
+struct BernTab {
+  float a[kBernMaxOrder + 8];
+  float d[kBernMaxOrder + 8];
+};
+
+__device__ void bern_build_table(BernTab* tab, const float* __restrict__ theta, int M) {
   if (threadIdx.x == 0) {
     const int n = M - 1;
     double ca = 1.0, cd = 1.0;  // C(n,j), C(n-1,j)
     for (int j = 0; j <= n; ++j) {
-      float a = (float)((double)theta[j] * ca);
-      float d = 0.f;
-      if (j < n) d = (float)((double)n * ((double)theta[j + 1] - (double)theta[j]) * cd);
-      tab[j] = make_float4(a, a, d, d);
+      tab->a[j] = (float)((double)theta[j] * ca);
+      tab->d[j] = j < n ? (float)((double)n * ((double)theta[j + 1] - (double)theta[j]) * cd) : 0.f;
       ca = ca * (double)(n - j) / (double)(j + 1);
       if (j < n - 1) cd = cd * (double)(n - 1 - j) / (double)(j + 1);
     }
+    for (int j = M; j < kBernMaxOrder + 8; ++j) tab->a[j] = tab->d[j] = 0.f;
   }
   __syncthreads();
 }
 
-// Evaluate (y, J) for FOUR clipped elements, two packed pairs u0 = {uA, uB}, u1 = {uC, uD}: one 128-bit
-// broadcast load of {a_j, a_j, d_j, d_j} feeds ten packed ops (2.75 instructions per element and
-// coefficient).  All operands stay in 64-bit register pairs (f2_t).
-__device__ __forceinline__ void bern_eval_quad(const float4* __restrict__ tab, int n, f2_t u0, f2_t u1, f2_t& y0,
+// Evaluate y = Σ_j a_j u^j v^(n-j) and vJ = Σ_j d_j u^j v^(n-j) (= v·J: the J form has degree n-1, its
+// padding coefficient d_n = 0 costs one factor v that the caller divides out) for FOUR clipped elements,
+// two packed pairs.  The plain recurrence r <- r·v + c_j·u^j costs 2.5 FP32 ops per coefficient and
+// polynomial and is FMA-pipe bound well below the HBM roof; here eight coefficients are folded per
+// step against the precomputed monomials m_i = u^i v^(7-i):
+//     r <- r·v^8 + u^(8b) · Σ_{i<8} c_{8b+i} m_i            (1.3 ops per coefficient and polynomial)
+// which is the same sum of non-negative Bernstein terms, only associated differently (stable on [0,1]).
+__device__ __forceinline__ void bern_eval_quad(const BernTab* __restrict__ tab, int M, f2_t u0, f2_t u1, f2_t& y0,
                                                f2_t& J0, f2_t& y1, f2_t& J1) {
-  const ulonglong2* t2 = reinterpret_cast<const ulonglong2*>(tab);
   const f2_t one = f2_splat(1.f), neg1 = f2_splat(-1.f);
   const f2_t v0 = f2_fma(u0, neg1, one), v1 = f2_fma(u1, neg1, one);
-  ulonglong2 c = t2[0];
-  y0 = c.x; y1 = c.x;
-  J0 = c.y; J1 = c.y;
-  f2_t pw0 = u0, pw1 = u1;
-#pragma unroll 4
-  for (int j = 1; j < n; ++j) {
-    c = t2[j];
-    y0 = f2_fma(y0, v0, f2_mul(c.x, pw0));
-    y1 = f2_fma(y1, v1, f2_mul(c.x, pw1));
-    J0 = f2_fma(J0, v0, f2_mul(c.y, pw0));
-    J1 = f2_fma(J1, v1, f2_mul(c.y, pw1));
+  f2_t ry0 = f2_splat(0.f), ry1 = ry0, rj0 = ry0, rj1 = ry0, pw0 = one, pw1 = one;
+  const int nb = M >> 3;
+  if (nb > 0) {
+    f2_t m0[8], m1[8];
+    {
+      // powers u^k, v^k (k <= 7), then m[i] = u^i v^(7-i)
+      f2_t up0[8], vp0[8], up1[8], vp1[8];
+      up0[0] = one; vp0[0] = one; up1[0] = one; vp1[0] = one;
+#pragma unroll
+      for (int k = 1; k < 8; ++k) {
+        up0[k] = f2_mul(up0[k - 1], u0); vp0[k] = f2_mul(vp0[k - 1], v0);
+        up1[k] = f2_mul(up1[k - 1], u1); vp1[k] = f2_mul(vp1[k - 1], v1);
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        m0[i] = f2_mul(up0[i], vp0[7 - i]);
+        m1[i] = f2_mul(up1[i], vp1[7 - i]);
+      }
+    }
+    const f2_t u80 = f2_mul(m0[7], u0), v80 = f2_mul(m0[0], v0), u81 = f2_mul(m1[7], u1), v81 = f2_mul(m1[0], v1);
+#pragma unroll 1
+    for (int b = 0; b < nb; ++b) {
+      const float4 a0 = *reinterpret_cast<const float4*>(tab->a + 8 * b), a1 = *reinterpret_cast<const float4*>(tab->a + 8 * b + 4);
+      const float4 d0 = *reinterpret_cast<const float4*>(tab->d + 8 * b), d1 = *reinterpret_cast<const float4*>(tab->d + 8 * b + 4);
+      const float ca[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      const float cd[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+      f2_t c = f2_splat(ca[0]), e = f2_splat(cd[0]);
+      f2_t iy0 = f2_mul(c, m0[0]), iy1 = f2_mul(c, m1[0]), ij0 = f2_mul(e, m0[0]), ij1 = f2_mul(e, m1[0]);
+#pragma unroll
+      for (int i = 1; i < 8; ++i) {
+        c = f2_splat(ca[i]);
+        e = f2_splat(cd[i]);
+        iy0 = f2_fma(c, m0[i], iy0);
+        iy1 = f2_fma(c, m1[i], iy1);
+        ij0 = f2_fma(e, m0[i], ij0);
+        ij1 = f2_fma(e, m1[i], ij1);
+      }
+      ry0 = f2_fma(ry0, v80, f2_mul(pw0, iy0));
+      ry1 = f2_fma(ry1, v81, f2_mul(pw1, iy1));
+      rj0 = f2_fma(rj0, v80, f2_mul(pw0, ij0));
+      rj1 = f2_fma(rj1, v81, f2_mul(pw1, ij1));
+      pw0 = f2_mul(pw0, u80);
+      pw1 = f2_mul(pw1, u81);
+    }
+  }
+  for (int j = nb << 3; j < M; ++j) {  // remaining coefficients, one at a time
+    const f2_t c = f2_splat(tab->a[j]), e = f2_splat(tab->d[j]);
+    ry0 = f2_fma(ry0, v0, f2_mul(c, pw0));
+    ry1 = f2_fma(ry1, v1, f2_mul(c, pw1));
+    rj0 = f2_fma(rj0, v0, f2_mul(e, pw0));
+    rj1 = f2_fma(rj1, v1, f2_mul(e, pw1));
     pw0 = f2_mul(pw0, u0);
     pw1 = f2_mul(pw1, u1);
   }
-  // last coefficient: only y has a degree-n term
-  c = t2[n];
-  y0 = f2_fma(y0, v0, f2_mul(c.x, pw0));
-  y1 = f2_fma(y1, v1, f2_mul(c.x, pw1));
+  y0 = ry0; y1 = ry1;
+  // divide the padding factor v out of the Jacobian form
+  float a, b, c, d, va, vb, vc, vd;
+  f2_unpack(rj0, a, b); f2_unpack(rj1, c, d);
+  f2_unpack(v0, va, vb); f2_unpack(v1, vc, vd);
+  J0 = f2_pack(a / va, b / vb);
+  J1 = f2_pack(c / vc, d / vd);
 }
 
 // scalar form for the ragged tail
-__device__ __forceinline__ void bern_eval_pair(const float4* __restrict__ tab, int n, float2 u, float2& y, float2& J) {
+__device__ __forceinline__ void bern_eval_pair(const BernTab* __restrict__ tab, int M, float2 u, float2& y, float2& J) {
   f2_t y0, J0, y1, J1;
-  bern_eval_quad(tab, n, f2_pack(u.x, u.y), f2_pack(u.x, u.y), y0, J0, y1, J1);
+  bern_eval_quad(tab, M, f2_pack(u.x, u.y), f2_pack(u.x, u.y), y0, J0, y1, J1);
   f2_unpack(y0, y.x, y.y);
   f2_unpack(J0, J.x, J.y);
 }
@@ -89,9 +139,9 @@ template <int MODE>
 __global__ void __launch_bounds__(kBernThreads)
 bern_shared_kernel(const float* __restrict__ theta, int M, const float* __restrict__ scal,
                    const float* __restrict__ x, float* __restrict__ out_y, float* __restrict__ out_ld, int64_t n) {
-  __shared__ float4 tab[kBernMaxOrder];
-  bern_build_table(tab, theta, M);
-  const int deg = M - 1;
+  __shared__ __align__(16) BernTab tab_s;
+  const BernTab* tab = &tab_s;
+  bern_build_table(&tab_s, theta, M);
   float s1 = 1.f, b1 = 0.f, s4 = 1.f, b4 = 0.f, lconst = 0.f, kk = 1.f, logk = 0.f;
   if (MODE == 1) {
     // T1 = Chain([Scale(softplus(a)), Shift(b)]): v = softplus(a)·(x + b)  (bflow.py:28)
@@ -117,7 +167,7 @@ bern_shared_kernel(const float* __restrict__ theta, int M, const float* __restri
       }
     }
     f2_t y01, J01, y23, J23;
-    bern_eval_quad(tab, deg, f2_pack(bern_clip(xs[0]), bern_clip(xs[1])), f2_pack(bern_clip(xs[2]), bern_clip(xs[3])),
+    bern_eval_quad(tab, M, f2_pack(bern_clip(xs[0]), bern_clip(xs[1])), f2_pack(bern_clip(xs[2]), bern_clip(xs[3])),
                    y01, J01, y23, J23);
     float ys[4], jj[4];
     f2_unpack(y01, ys[0], ys[1]);
@@ -144,7 +194,7 @@ bern_shared_kernel(const float* __restrict__ theta, int M, const float* __restri
     float xi = x[t], pl = 0.f;
     if (MODE == 1) softclip01(s1 * (xi + b1), 1.5f, kk, logk, xi, pl);
     float2 y, J;
-    bern_eval_pair(tab, deg, splat2(bern_clip(xi)), y, J);
+    bern_eval_pair(tab, M, splat2(bern_clip(xi)), y, J);
     if (MODE == 0) {
       if (out_y) out_y[t] = y.x;
       if (out_ld) out_ld[t] = logf(J.x);

@@ -138,6 +138,12 @@ __device__ __forceinline__ f2_t f2_add(f2_t a, f2_t b) {
 // exp via MUFU.EX2 (abs err ~2 ulp on the scaled argument; rel err ~1e-7·|x| — inside the
 // 1e-5 parity budget for |x| <~ 30, which log-scales of a trained flow satisfy).
 __device__ __forceinline__ float fast_exp(float x) { return exp2f(x * kLog2e); }
+// bare MUFU.EX2 (no denormal-range fix-up code around it; results below 2^-126 flush to zero)
+__device__ __forceinline__ float ex2_ftz(float x) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
 __device__ __forceinline__ float softplus_f(float x) {
   // log1p(exp(x)) evaluated as max(x,0) + log1p(exp(-|x|)) (no overflow, full fp32 accuracy)
   return fmaxf(x, 0.f) + log1pf(expf(-fabsf(x)));

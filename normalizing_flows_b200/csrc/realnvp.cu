@@ -2,9 +2,9 @@
 //
 // One kernel runs the whole L-layer chain per sample and fuses the N(0,I) log-density:
 // HBM traffic is y in (8 B) and log_prob out (4 B) per sample.  The 18-float conditioner
-// [1 -> H -> 2] of every layer is staged once per CTA in shared memory, pre-splatted as
-// {w,w} pairs so that the Blackwell packed-fp32 pipe (fma.rn.f32x2 -> FFMA2) processes two
-// samples per issue slot.
+// [1 -> H -> 2] of every layer is staged once per CTA in shared memory; a thread carries eight
+// samples as four packed pairs, so a weight is loaded and splatted once per eight samples and the
+// Blackwell packed-fp32 pipe (fma.rn.f32x2 -> FFMA2) processes two samples per issue slot.
 #include "common.cuh"
 
 namespace flowcuda {
@@ -13,43 +13,80 @@ constexpr int kNvpThreads = 256;
 constexpr int kNvpMaxLayers = 64;
 constexpr int kNvpMaxHidden = 32;
 
-// smem image of one layer (in float2 units, each weight duplicated):
-//   [0,H) W1   [H,2H) b1   [2H,3H) W2[:,0] (shift)   [3H,4H) W2[:,1] (log_scale)   4H: b2s  4H+1: b2l
-__host__ __device__ constexpr int nvp_layer_f2(int H) { return 4 * H + 2; }
+// smem image of one layer, 4H+4 plain floats (16-byte aligned rows):
+//   [0,H) W1   [H,2H) b1   [2H,3H) 0.99·W2[:,0]   [3H,4H) 0.99·W2[:,1]   then As, Bs, Al, Bl
+// with leaky_relu(p) = 0.01·p + 0.99·relu(p) (exact) the conditioner output is
+//   shift(y) = Bs + As·y + Σ_j 0.99·W2[j,0]·relu(W1_j·y + b1_j),
+//   As = 0.01·Σ_j W2[j,0]·W1_j,  Bs = b2_0 + 0.01·Σ_j W2[j,0]·b1_j        (likewise log_scale),
+// i.e. one FMNMX instead of FMUL+FMNMX per hidden unit and sample.
+__host__ __device__ constexpr int nvp_layer_floats(int H) { return (4 * H + 4 + 3) & ~3; }
 
 template <int H>
-__device__ __forceinline__ void stage_params(float2* sp, const float* __restrict__ params, int L, int Hrt) {
+__device__ __forceinline__ void stage_params(float* sp, const float* __restrict__ params, int L, int Hrt) {
   const int Hh = H > 0 ? H : Hrt;
-  const int P = 4 * Hh + 2;
-  for (int i = threadIdx.x; i < L * P; i += blockDim.x) {
-    int l = i / P, r = i - l * P;
+  const int P = 4 * Hh + 2, PS = nvp_layer_floats(Hh);
+  for (int i = threadIdx.x; i < L * PS; i += blockDim.x) {
+    const int l = i / PS, r = i - l * PS;
     const float* p = params + (size_t)l * P;
-    float v;
-    if (r < Hh) v = p[r];                          // W1[0, j]
-    else if (r < 2 * Hh) v = p[r];                 // b1[j]
-    else if (r < 3 * Hh) v = p[2 * Hh + 2 * (r - 2 * Hh)];      // W2[j, 0]
-    else if (r < 4 * Hh) v = p[2 * Hh + 2 * (r - 3 * Hh) + 1];  // W2[j, 1]
-    else v = p[4 * Hh + (r - 4 * Hh)];             // b2
-    sp[i] = make_float2(v, v);
+    float v = 0.f;
+    if (r < 2 * Hh) v = p[r];                                             // W1[0, j], b1[j]
+    else if (r < 3 * Hh) v = 0.99f * p[2 * Hh + 2 * (r - 2 * Hh)];        // W2[j, 0]
+    else if (r < 4 * Hh) v = 0.99f * p[2 * Hh + 2 * (r - 3 * Hh) + 1];    // W2[j, 1]
+    else if (r < 4 * Hh + 4) {
+      const int which = (r - 4 * Hh) >> 1, isB = (r - 4 * Hh) & 1;        // As, Bs, Al, Bl
+      float acc = isB ? p[4 * Hh + which] : 0.f;
+      for (int j = 0; j < Hh; ++j) acc = fmaf(0.01f * p[2 * Hh + 2 * j + which], isB ? p[Hh + j] : p[j], acc);
+      v = acc;
+    }
+    sp[i] = v;
   }
 }
 
-// Conditioner on the pass-through value of two samples at once (src/real_nvp.py:161-171).
-template <int H>
-__device__ __forceinline__ void cond_pair(const float2* __restrict__ w, int Hrt, float2 y1, float2& shift,
-                                          float2& ls) {
+// One coupling layer on NP packed pairs (2·NP samples): `pass` conditions, `tr` is transformed.
+template <int H, int MODE, int NP>
+__device__ __forceinline__ void nvp_layer(const float* __restrict__ w, int Hrt, const f2_t (&pass)[NP], f2_t (&tr)[NP],
+                                          f2_t (&lsum)[NP]) {
   const int Hh = H > 0 ? H : Hrt;
-  shift = w[4 * Hh];
-  ls = w[4 * Hh + 1];
+  f2_t shift[NP], ls[NP];
+  {
+    const float4 k = *reinterpret_cast<const float4*>(w + 4 * Hh);  // As, Bs, Al, Bl
+    const f2_t as = f2_splat(k.x), bs = f2_splat(k.y), al = f2_splat(k.z), bl = f2_splat(k.w);
+#pragma unroll
+    for (int p = 0; p < NP; ++p) {
+      shift[p] = f2_fma(pass[p], as, bs);
+      ls[p] = f2_fma(pass[p], al, bl);
+    }
+  }
 #pragma unroll
   for (int j = 0; j < Hh; ++j) {
-    float2 pre = ffma2(y1, w[j], w[Hh + j]);
-    float2 sm = fmul2(pre, splat2(0.01f));
-    float2 h = make_float2(fmaxf(pre.x, sm.x), fmaxf(pre.y, sm.y));  // jax.nn.leaky_relu
-    shift = ffma2(h, w[2 * Hh + j], shift);
-    ls = ffma2(h, w[3 * Hh + j], ls);
+    const f2_t w1 = f2_splat(w[j]), b1 = f2_splat(w[Hh + j]), ws = f2_splat(w[2 * Hh + j]), wl = f2_splat(w[3 * Hh + j]);
+#pragma unroll
+    for (int p = 0; p < NP; ++p) {
+      float a, b;
+      f2_unpack(f2_fma(pass[p], w1, b1), a, b);
+      const f2_t h = f2_pack(fmaxf(a, 0.f), fmaxf(b, 0.f));
+      shift[p] = f2_fma(h, ws, shift[p]);
+      ls[p] = f2_fma(h, wl, ls[p]);
+    }
+  }
+#pragma unroll
+  for (int p = 0; p < NP; ++p) {
+    float la, lb;
+    f2_unpack(ls[p], la, lb);
+    if (MODE == 0) {
+      // x2 = (y2 - shift) * exp(-log_scale)   (real_nvp.py:129)
+      const f2_t e = f2_pack(ex2_ftz(-kLog2e * la), ex2_ftz(-kLog2e * lb));
+      tr[p] = f2_mul(f2_fma(shift[p], f2_splat(-1.f), tr[p]), e);
+    } else {
+      // y2 = x2 * exp(log_scale) + shift      (real_nvp.py:96)
+      const f2_t e = f2_pack(ex2_ftz(kLog2e * la), ex2_ftz(kLog2e * lb));
+      tr[p] = f2_fma(tr[p], e, shift[p]);
+    }
+    lsum[p] = f2_add(lsum[p], ls[p]);
   }
 }
+
+constexpr int kNvpPairs = 4;  // packed pairs per thread and iteration (8 samples): amortises the weight loads
 
 // MODE 0: data -> base (inverse_nvp chain, layers L-1..0) ; MODE 1: base -> data (forward_nvp, 0..L-1)
 template <int H, int MODE>
@@ -57,69 +94,70 @@ __global__ void __launch_bounds__(kNvpThreads)
 realnvp_chain_kernel(const float* __restrict__ params, int L, int Hrt, uint64_t flip_mask,
                      const float* __restrict__ in, float* __restrict__ out_v, float* __restrict__ out_lp,
                      float* __restrict__ out_ls, int64_t n) {
-  extern __shared__ float2 sp[];
+  extern __shared__ __align__(16) float sp[];
   stage_params<H>(sp, params, L, Hrt);
   __syncthreads();
   const int Hh = H > 0 ? H : Hrt;
-  const int P2 = nvp_layer_f2(Hh);
+  const int PS = nvp_layer_floats(Hh);
+  constexpr int NP = kNvpPairs;
 
-  // one "pair" = samples (2q, 2q+1) = one float4 of the [N,2] input
+  // one "pair" = samples (2q, 2q+1) = one float4 of the [N,2] input; a thread takes NP pairs that are
+  // blockDim apart so that every 128-bit access of a warp is contiguous
   const int64_t npairs = n >> 1;
-  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   const float4* in4 = reinterpret_cast<const float4*>(in);
-  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < npairs; q += stride) {
-    float4 v = ld_stream_f4(in4 + q);
-    float2 c0 = make_float2(v.x, v.z);  // component 0 of samples A,B
-    float2 c1 = make_float2(v.y, v.w);  // component 1
-    float2 lsum = make_float2(0.f, 0.f);
+  const int64_t tile = (int64_t)blockDim.x * NP;
+  for (int64_t base = (int64_t)blockIdx.x * tile; base < npairs; base += (int64_t)gridDim.x * tile) {
+    f2_t c0[NP], c1[NP], lsum[NP];
+#pragma unroll
+    for (int p = 0; p < NP; ++p) {
+      const int64_t q = base + (int64_t)p * blockDim.x + threadIdx.x;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (q < npairs) v = ld_stream_f4(in4 + q);
+      c0[p] = f2_pack(v.x, v.z);  // component 0 of samples A,B
+      c1[p] = f2_pack(v.y, v.w);  // component 1
+      lsum[p] = f2_splat(0.f);
+    }
 #pragma unroll 1
     for (int i = 0; i < L; ++i) {
       const int l = MODE == 0 ? L - 1 - i : i;
-      const float2* w = sp + l * P2;
-      const bool flip = (flip_mask >> l) & 1ull;
-      float2 pass = flip ? c1 : c0;
-      float2 tr = flip ? c0 : c1;
-      float2 shift, ls;
-      cond_pair<H>(w, Hrt, pass, shift, ls);
-      if (MODE == 0) {
-        // x2 = (y2 - shift) * exp(-log_scale)   (real_nvp.py:129)
-        float2 d = fadd2(tr, make_float2(-shift.x, -shift.y));
-        float2 e = make_float2(exp2f(-kLog2e * ls.x), exp2f(-kLog2e * ls.y));
-        tr = fmul2(d, e);
-      } else {
-        // y2 = x2 * exp(log_scale) + shift      (real_nvp.py:96)
-        float2 e = make_float2(exp2f(kLog2e * ls.x), exp2f(kLog2e * ls.y));
-        tr = ffma2(tr, e, shift);
+      const float* w = sp + l * PS;
+      if ((flip_mask >> l) & 1ull) nvp_layer<H, MODE, NP>(w, Hrt, c1, c0, lsum);  // flip: component 1 conditions
+      else nvp_layer<H, MODE, NP>(w, Hrt, c0, c1, lsum);
+    }
+#pragma unroll
+    for (int p = 0; p < NP; ++p) {
+      const int64_t q = base + (int64_t)p * blockDim.x + threadIdx.x;
+      if (q >= npairs) continue;
+      float a0, b0, a1, b1, la, lb;
+      f2_unpack(c0[p], a0, b0);
+      f2_unpack(c1[p], a1, b1);
+      f2_unpack(lsum[p], la, lb);
+      if (out_v) st_stream_f4(reinterpret_cast<float4*>(out_v) + q, make_float4(a0, a1, b0, b1));
+      if (out_lp) {
+        // log N(z;0,I) - sum(log_scale)   (real_nvp.py:57-68,157)
+        const float pa = fmaf(-0.5f, fmaf(a0, a0, a1 * a1), -2.f * kHalfLog2Pi - la);
+        const float pb = fmaf(-0.5f, fmaf(b0, b0, b1 * b1), -2.f * kHalfLog2Pi - lb);
+        st_stream_f2(reinterpret_cast<float2*>(out_lp) + q, make_float2(pa, pb));
       }
-      lsum = fadd2(lsum, ls);
-      if (flip) c0 = tr; else c1 = tr;
+      if (out_ls) st_stream_f2(reinterpret_cast<float2*>(out_ls) + q, make_float2(la, lb));
     }
-    if (out_v) st_stream_f4(reinterpret_cast<float4*>(out_v) + q, make_float4(c0.x, c1.x, c0.y, c1.y));
-    if (out_lp) {
-      // log N(z;0,I) - sum(log_scale)   (real_nvp.py:57-68,157)
-      float2 r2 = ffma2(c0, c0, fmul2(c1, c1));
-      float2 lp = ffma2(r2, splat2(-0.5f), make_float2(-2.f * kHalfLog2Pi - lsum.x, -2.f * kHalfLog2Pi - lsum.y));
-      st_stream_f2(reinterpret_cast<float2*>(out_lp) + q, lp);
-    }
-    if (out_ls) st_stream_f2(reinterpret_cast<float2*>(out_ls) + q, lsum);
   }
   // odd tail sample
   if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
-    int64_t s = n - 1;
-    float2 c0 = splat2(in[2 * s]), c1 = splat2(in[2 * s + 1]), lsum = splat2(0.f);
+    const int64_t s = n - 1;
+    f2_t c0[1] = {f2_splat(in[2 * s])}, c1[1] = {f2_splat(in[2 * s + 1])}, lsum[1] = {f2_splat(0.f)};
     for (int i = 0; i < L; ++i) {
       const int l = MODE == 0 ? L - 1 - i : i;
-      const bool flip = (flip_mask >> l) & 1ull;
-      float2 pass = flip ? c1 : c0, tr = flip ? c0 : c1, shift, ls;
-      cond_pair<H>(sp + l * P2, Hrt, pass, shift, ls);
-      if (MODE == 0) tr = splat2((tr.x - shift.x) * exp2f(-kLog2e * ls.x));
-      else tr = splat2(fmaf(tr.x, exp2f(kLog2e * ls.x), shift.x));
-      lsum.x += ls.x;
-      if (flip) c0 = tr; else c1 = tr;
+      if ((flip_mask >> l) & 1ull) nvp_layer<H, MODE, 1>(sp + l * PS, Hrt, c1, c0, lsum);
+      else nvp_layer<H, MODE, 1>(sp + l * PS, Hrt, c0, c1, lsum);
     }
-    if (out_v) { out_v[2 * s] = c0.x; out_v[2 * s + 1] = c1.x; }
-    if (out_lp) out_lp[s] = -0.5f * (c0.x * c0.x + c1.x * c1.x) - 2.f * kHalfLog2Pi - lsum.x;
-    if (out_ls) out_ls[s] = lsum.x;
+    float a0, a1, la, t;
+    f2_unpack(c0[0], a0, t);
+    f2_unpack(c1[0], a1, t);
+    f2_unpack(lsum[0], la, t);
+    if (out_v) { out_v[2 * s] = a0; out_v[2 * s + 1] = a1; }
+    if (out_lp) out_lp[s] = fmaf(-0.5f, fmaf(a0, a0, a1 * a1), -2.f * kHalfLog2Pi - la);
+    if (out_ls) out_ls[s] = la;
   }
 }
 
@@ -136,16 +174,16 @@ static int launch_chain(const float* params, int L, int H, uint64_t flip_mask, c
                  ((uintptr_t)out_ls & 7) == 0,
              "realnvp: buffers must be 16-byte ([N,2]) / 8-byte ([N]) aligned");
   if (n == 0) return FLOWCUDA_OK;
-  size_t smem = (size_t)L * nvp_layer_f2(H) * sizeof(float2);
-  // grid: a multiple of the SM count; 8 CTAs of 256 threads are resident per SM
-  int64_t need = ((n >> 1) + kNvpThreads - 1) / kNvpThreads;
-  int64_t cap = (int64_t)sm_count() * 8;
-  int grid = (int)(need < 1 ? 1 : (need < cap ? need : cap));
+  size_t smem = (size_t)L * nvp_layer_floats(H) * sizeof(float);
+  // persistent grid: exactly the CTAs resident at once (no partial last wave), grid-stride over tiles
+  const int64_t work = ((n >> 1) + kNvpPairs - 1) / kNvpPairs;
   if (H == 4) {
+    int grid = grid_resident(realnvp_chain_kernel<4, MODE>, kNvpThreads, smem, work, kNvpThreads);
     realnvp_chain_kernel<4, MODE><<<grid, kNvpThreads, smem, s>>>(params, L, H, flip_mask, in, out_v, out_lp, out_ls, n);
   } else {
     if (smem > 48 * 1024)
       FC_CUDA(cudaFuncSetAttribute(realnvp_chain_kernel<0, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int grid = grid_resident(realnvp_chain_kernel<0, MODE>, kNvpThreads, smem, work, kNvpThreads);
     realnvp_chain_kernel<0, MODE><<<grid, kNvpThreads, smem, s>>>(params, L, H, flip_mask, in, out_v, out_lp, out_ls, n);
   }
   FC_LAUNCH_CHECK("realnvp_chain_kernel");
