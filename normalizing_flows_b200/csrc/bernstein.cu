@@ -21,24 +21,37 @@ __device__ __forceinline__ float bern_clip(float x) {
   return fminf(fmaxf(x, 1e-7f), 0.99999988079071044921875f);
 }
 
-// Coefficient tables for a shared theta (plain floats, 16-byte aligned, zero padded):
-//   ta[j] = θ_j C(n,j) (j <= n),   td[j] = n (θ_{j+1}-θ_j) C(n-1,j) (j <= n-1), td[n] = 0.
+// Coefficient tables for a shared theta, every coefficient duplicated ({c, c}: a ready-made packed
+// operand, so the inner loop needs no splat moves), zero padded:
+//   a[j] = θ_j C(n,j) (j <= n),   d[j] = n (θ_{j+1}-θ_j) C(n-1,j) (j <= n-1), d[n] = 0.
 struct BernTab {
-  float a[kBernMaxOrder + 8];
-  float d[kBernMaxOrder + 8];
+  float2 a[kBernMaxOrder + 8];
+  float2 d[kBernMaxOrder + 8];
 };
 
+// C(n, j) in double by the multiplicative formula over min(j, n-j) factors (one division at the end)
+__device__ __forceinline__ double bern_binom(int n, int j) {
+  if (j < 0 || j > n) return 0.0;
+  const int k = j < n - j ? j : n - j;
+  double num = 1.0, den = 1.0;
+  for (int i = 1; i <= k; ++i) {
+    num *= (double)(n - k + i);
+    den *= (double)i;
+  }
+  return num / den;
+}
+
+// one thread per coefficient (a serial build by thread 0 costs ~10 us of FP64 latency per CTA)
 __device__ void bern_build_table(BernTab* tab, const float* __restrict__ theta, int M) {
-  if (threadIdx.x == 0) {
-    const int n = M - 1;
-    double ca = 1.0, cd = 1.0;  // C(n,j), C(n-1,j)
-    for (int j = 0; j <= n; ++j) {
-      tab->a[j] = (float)((double)theta[j] * ca);
-      tab->d[j] = j < n ? (float)((double)n * ((double)theta[j + 1] - (double)theta[j]) * cd) : 0.f;
-      ca = ca * (double)(n - j) / (double)(j + 1);
-      if (j < n - 1) cd = cd * (double)(n - 1 - j) / (double)(j + 1);
+  const int n = M - 1;
+  for (int j = threadIdx.x; j < kBernMaxOrder + 8; j += blockDim.x) {
+    float a = 0.f, d = 0.f;
+    if (j <= n) {
+      a = (float)((double)theta[j] * bern_binom(n, j));
+      if (j < n) d = (float)((double)n * ((double)theta[j + 1] - (double)theta[j]) * bern_binom(n - 1, j));
     }
-    for (int j = M; j < kBernMaxOrder + 8; ++j) tab->a[j] = tab->d[j] = 0.f;
+    tab->a[j] = make_float2(a, a);
+    tab->d[j] = make_float2(d, d);
   }
   __syncthreads();
 }
@@ -76,20 +89,21 @@ __device__ __forceinline__ void bern_eval_quad(const BernTab* __restrict__ tab, 
     const f2_t u80 = f2_mul(m0[7], u0), v80 = f2_mul(m0[0], v0), u81 = f2_mul(m1[7], u1), v81 = f2_mul(m1[0], v1);
 #pragma unroll 1
     for (int b = 0; b < nb; ++b) {
-      const float4 a0 = *reinterpret_cast<const float4*>(tab->a + 8 * b), a1 = *reinterpret_cast<const float4*>(tab->a + 8 * b + 4);
-      const float4 d0 = *reinterpret_cast<const float4*>(tab->d + 8 * b), d1 = *reinterpret_cast<const float4*>(tab->d + 8 * b + 4);
-      const float ca[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-      const float cd[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
-      f2_t c = f2_splat(ca[0]), e = f2_splat(cd[0]);
-      f2_t iy0 = f2_mul(c, m0[0]), iy1 = f2_mul(c, m1[0]), ij0 = f2_mul(e, m0[0]), ij1 = f2_mul(e, m1[0]);
+      const ulonglong2* ta = reinterpret_cast<const ulonglong2*>(tab->a + 8 * b);
+      const ulonglong2* td = reinterpret_cast<const ulonglong2*>(tab->d + 8 * b);
+      f2_t iy0, iy1, ij0, ij1;
 #pragma unroll
-      for (int i = 1; i < 8; ++i) {
-        c = f2_splat(ca[i]);
-        e = f2_splat(cd[i]);
-        iy0 = f2_fma(c, m0[i], iy0);
-        iy1 = f2_fma(c, m1[i], iy1);
-        ij0 = f2_fma(e, m0[i], ij0);
-        ij1 = f2_fma(e, m1[i], ij1);
+      for (int i = 0; i < 4; ++i) {
+        const ulonglong2 c = ta[i], e = td[i];  // {a_{2i}, a_{2i+1}} and {d_{2i}, d_{2i+1}}, each splatted
+        if (i == 0) {
+          iy0 = f2_mul(c.x, m0[0]); iy1 = f2_mul(c.x, m1[0]);
+          ij0 = f2_mul(e.x, m0[0]); ij1 = f2_mul(e.x, m1[0]);
+        } else {
+          iy0 = f2_fma(c.x, m0[2 * i], iy0); iy1 = f2_fma(c.x, m1[2 * i], iy1);
+          ij0 = f2_fma(e.x, m0[2 * i], ij0); ij1 = f2_fma(e.x, m1[2 * i], ij1);
+        }
+        iy0 = f2_fma(c.y, m0[2 * i + 1], iy0); iy1 = f2_fma(c.y, m1[2 * i + 1], iy1);
+        ij0 = f2_fma(e.y, m0[2 * i + 1], ij0); ij1 = f2_fma(e.y, m1[2 * i + 1], ij1);
       }
       ry0 = f2_fma(ry0, v80, f2_mul(pw0, iy0));
       ry1 = f2_fma(ry1, v81, f2_mul(pw1, iy1));
@@ -100,7 +114,7 @@ __device__ __forceinline__ void bern_eval_quad(const BernTab* __restrict__ tab, 
     }
   }
   for (int j = nb << 3; j < M; ++j) {  // remaining coefficients, one at a time
-    const f2_t c = f2_splat(tab->a[j]), e = f2_splat(tab->d[j]);
+    const f2_t c = *reinterpret_cast<const f2_t*>(tab->a + j), e = *reinterpret_cast<const f2_t*>(tab->d + j);
     ry0 = f2_fma(ry0, v0, f2_mul(c, pw0));
     ry1 = f2_fma(ry1, v1, f2_mul(c, pw1));
     rj0 = f2_fma(rj0, v0, f2_mul(e, pw0));
@@ -113,8 +127,8 @@ __device__ __forceinline__ void bern_eval_quad(const BernTab* __restrict__ tab, 
   float a, b, c, d, va, vb, vc, vd;
   f2_unpack(rj0, a, b); f2_unpack(rj1, c, d);
   f2_unpack(v0, va, vb); f2_unpack(v1, vc, vd);
-  J0 = f2_pack(a / va, b / vb);
-  J1 = f2_pack(c / vc, d / vd);
+  J0 = f2_pack(__fdividef(a, va), __fdividef(b, vb));
+  J1 = f2_pack(__fdividef(c, vc), __fdividef(d, vd));
 }
 
 // scalar form for the ragged tail
@@ -136,7 +150,7 @@ __device__ __forceinline__ void softclip01(float x, float c, float k, float logk
 
 // MODE 0: forward_and_log_det (y, ld);  MODE 1: fused bflow log_prob.
 template <int MODE>
-__global__ void __launch_bounds__(kBernThreads)
+__global__ void __launch_bounds__(kBernThreads, 3)
 bern_shared_kernel(const float* __restrict__ theta, int M, const float* __restrict__ scal,
                    const float* __restrict__ x, float* __restrict__ out_y, float* __restrict__ out_ld, int64_t n) {
   __shared__ __align__(16) BernTab tab_s;
@@ -155,8 +169,12 @@ bern_shared_kernel(const float* __restrict__ theta, int M, const float* __restri
   }
   const int64_t nquads = n >> 2;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < nquads; q += stride) {
-    float4 xv = ld_stream_f4(reinterpret_cast<const float4*>(x) + q);
+  int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  float4 xnext = make_float4(0.5f, 0.5f, 0.5f, 0.5f);
+  if (q < nquads) xnext = ld_stream_f4(reinterpret_cast<const float4*>(x) + q);
+  for (; q < nquads; q += stride) {
+    const float4 xv = xnext;
+    if (q + stride < nquads) xnext = ld_stream_f4(reinterpret_cast<const float4*>(x) + q + stride);  // next iteration's load
     float xs[4] = {xv.x, xv.y, xv.z, xv.w};
     float pre_ld[4] = {0.f, 0.f, 0.f, 0.f};
     if (MODE == 1) {
@@ -174,7 +192,8 @@ bern_shared_kernel(const float* __restrict__ theta, int M, const float* __restri
     f2_unpack(y23, ys[2], ys[3]);
     f2_unpack(J01, jj[0], jj[1]);
     f2_unpack(J23, jj[2], jj[3]);
-    float ld[4] = {logf(jj[0]), logf(jj[1]), logf(jj[2]), logf(jj[3])};
+    // MUFU.LG2 based log: relative error 2^-22 away from J = 1, absolute 1e-7 near it (inside the 1e-5 budget)
+    float ld[4] = {__logf(jj[0]), __logf(jj[1]), __logf(jj[2]), __logf(jj[3])};
     if (MODE == 0) {
       if (out_y) st_stream_f4(reinterpret_cast<float4*>(out_y) + q, make_float4(ys[0], ys[1], ys[2], ys[3]));
       if (out_ld) st_stream_f4(reinterpret_cast<float4*>(out_ld) + q, make_float4(ld[0], ld[1], ld[2], ld[3]));

@@ -90,7 +90,7 @@ constexpr int kNvpPairs = 4;  // packed pairs per thread and iteration (8 sample
 
 // MODE 0: data -> base (inverse_nvp chain, layers L-1..0) ; MODE 1: base -> data (forward_nvp, 0..L-1)
 template <int H, int MODE>
-__global__ void __launch_bounds__(kNvpThreads)
+__global__ void __launch_bounds__(kNvpThreads, 4)
 realnvp_chain_kernel(const float* __restrict__ params, int L, int Hrt, uint64_t flip_mask,
                      const float* __restrict__ in, float* __restrict__ out_v, float* __restrict__ out_lp,
                      float* __restrict__ out_ls, int64_t n) {
