@@ -8,8 +8,8 @@
 // shared-memory tile images (tc.cuh), so a pipeline stage is two cp.async.bulk (TMA) copies:
 //   A image  [m_tile][k_stage][hi|lo][4 chunks][128 rows][16 B]   (activations, 32 K per stage)
 //   B image  [n_tile][k_stage][hi|lo][4 chunks][256 rows][16 B]   (weights, masks folded in)
-// CTA = loader warp + MMA warp + 4 epilogue warps, 2 CTAs per SM so that one CTA's epilogue
-// overlaps the other's MMAs.  Epilogues (thread = sample row = TMEM lane):
+// CTA = loader warp + MMA warp + 4 epilogue warps, persistent (one per SM) with two TMEM accumulators so
+// that a tile's epilogue overlaps the next tile's MMAs.  Epilogues (thread = sample row = TMEM lane):
 //   hidden: +bias, relu, bf16 hi/lo split, written straight into the next Linear's A image;
 //   last:   the inner bijector (RQS / affine) on the tile's dims, state updated in place,
 //           log-det partial per (row, tile) — the [N, D*params] conditioner output never exists.
@@ -21,7 +21,7 @@
 
 namespace flowcuda {
 
-constexpr int kDtBN = 256, kDtBK = 32, kDtStages = 2, kDtThreads = 192;
+constexpr int kDtBN = 256, kDtBK = 32, kDtThreads = 320;
 constexpr int kDtABytes = 128 * kDtBK * 2;   // one of hi/lo of an A stage (8 KB)
 constexpr int kDtBBytes = kDtBN * kDtBK * 2; // one of hi/lo of a B stage (16 KB)
 constexpr int kDtStageBytes = 2 * kDtABytes + 2 * kDtBBytes;  // 48 KB
@@ -89,41 +89,191 @@ __device__ __forceinline__ float dt_tile_bias(const DtGemm& a, int nt, int n) {
   return a.bias[(a.tp + a.dstride * dim) * a.ppd + pp];
 }
 
+// One 128 x 256 accumulator tile -> its epilogue (thread = sample row = TMEM lane).  `tb` is the TMEM
+// address of this warp's lane quarter of the accumulator, `Tbase` the CTA's transposition scratch.
 template <int EPI, bool INV>
-__global__ void __launch_bounds__(kDtThreads, 2) dense_tc_gemm_kernel(DtGemm a) {
-  extern __shared__ __align__(128) uint8_t smem[];
-  uint8_t* stages = smem;                                                     // [stages][48 KB]
-  float* sbias = reinterpret_cast<float*>(smem + kDtStages * kDtStageBytes);  // [256]
-  uint64_t* full = reinterpret_cast<uint64_t*>(sbias + kDtBN);               // [stages]
-  uint64_t* empty = full + kDtStages;                                         // [stages]
-  uint64_t* dfull = empty + kDtStages;                                        // [1]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(dfull + 1);
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int mt = blockIdx.x, nt = blockIdx.y;
-  int KS = a.KS;
-  if (nt < kDtMaxKsTiles && a.ks_tile[nt] != 0) KS = a.ks_tile[nt];
+__device__ __forceinline__ void dt_epilogue(const DtGemm& a, int mt, int nt, uint32_t tb, const float* __restrict__ sbias,
+                                            float* Tbase, int warp, int lane) {
+  const int row = (warp & 3) * 32 + lane;
+  const int64_t grow = (int64_t)mt * 128 + row;
+  if (EPI == kEpiHidden) {
+    uint8_t* og = a.out_img + (int64_t)mt * a.out_KS * 2 * kDtABytes;
+#pragma unroll 1
+    for (int c = 0; c < kDtBN; c += 16) {
+      uint32_t vv[16];
+      tc::tmem_ld_x16(tb + (uint32_t)c, vv);
+      tc::tmem_ld_wait();
+      uint32_t h[8], l[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float f0 = fmaxf(__uint_as_float(vv[2 * e]) + sbias[c + 2 * e], 0.f);
+        const float f1 = fmaxf(__uint_as_float(vv[2 * e + 1]) + sbias[c + 2 * e + 1], 0.f);
+        tc::split_bf16x2(f0, f1, h[e], l[e]);
+      }
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int ck = (nt * kDtBN + c) / 8 + q;  // chunk index along the next Linear's K
+        if (ck < a.out_KS * 4) {
+          uint8_t* st = og + (int64_t)(ck >> 2) * 2 * kDtABytes + tc::img_off(128, row, ck & 3);
+          *reinterpret_cast<uint4*>(st) = make_uint4(h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]);
+          *reinterpret_cast<uint4*>(st + kDtABytes) = make_uint4(l[4 * q], l[4 * q + 1], l[4 * q + 2], l[4 * q + 3]);
+        }
+      }
+    }
+  } else if (EPI == kEpiRqs8) {
+    float ldsum = 0.f;
+#pragma unroll 1
+    for (int di = 0; di < 10; ++di) {
+      const int dim = nt * 10 + di;
+      if (dim >= a.ndims) break;  // uniform across the CTA
+      uint32_t vv[25];
+      tc::tmem_ld_x16(tb + (uint32_t)(25 * di), vv);
+      tc::tmem_ld_x8(tb + (uint32_t)(25 * di + 16), vv + 16);
+      tc::tmem_ld_x1(tb + (uint32_t)(25 * di + 24), vv + 24);
+      tc::tmem_ld_wait();
+      if (grow < a.N) {
+        float o[25];
+#pragma unroll
+        for (int i = 0; i < 25; ++i) o[i] = __uint_as_float(vv[i]) + sbias[25 * di + i];
+        const int d = a.tp + a.dstride * dim;
+        const float xin = a.v[grow * a.D + d];
+        float nv, l1;
+        rqs_apply<INV, 8>([&](int i) { return o[i]; }, 8, a.lo, a.hi, xin, nv, l1);
+        a.v[grow * a.D + d] = nv;
+        ldsum += l1;
+      }
+    }
+    if (grow < a.N) a.ldp[grow * a.tiles + nt] = ldsum;
+  } else {
+    // Affine epilogue.  The accumulator comes out of TMEM as thread = sample row, but the state v[N, D]
+    // is row-major: a thread-per-row access touches 32 cache lines per request.  Each warp therefore
+    // transposes its 32 rows x 32 columns through shared memory (the pipeline stages are idle by now)
+    // and applies the bijector as lane = dimension, so the state is read and written in 64-byte runs;
+    // a third phase (thread = row again) sums the log-det and, for MADE stacks, writes the NEXT
+    // layer's activation image directly (bf16 hi/lo), so no separate packing pass re-reads v.
+    constexpr int TS = 36;  // row stride of the transposition tile in floats (16-byte aligned rows)
+    float* T = Tbase + (warp & 3) * 32 * TS;
+    const int r0 = (warp & 3) * 32;
+    const int k = lane & 15, hp = lane >> 4;
+    uint8_t* og = a.out_img ? a.out_img + (int64_t)mt * a.out_KS * 2 * kDtABytes : nullptr;
+    float ldsum = 0.f;
+#pragma unroll 1
+    for (int c = 0; c < kDtBN; c += 32) {
+      const int dim0 = nt * 128 + c / 2;
+      if (dim0 >= a.ndims) break;  // uniform across the CTA
+      uint32_t vv[32];
+      tc::tmem_ld_x32(tb + (uint32_t)c, vv);
+      tc::tmem_ld_wait();
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        float4 t4;
+        t4.x = __uint_as_float(vv[4 * e]) + sbias[c + 4 * e];
+        t4.y = __uint_as_float(vv[4 * e + 1]) + sbias[c + 4 * e + 1];
+        t4.z = __uint_as_float(vv[4 * e + 2]) + sbias[c + 4 * e + 2];
+        t4.w = __uint_as_float(vv[4 * e + 3]) + sbias[c + 4 * e + 3];
+        *reinterpret_cast<float4*>(T + lane * TS + 4 * e) = t4;
+      }
+      __syncwarp();
+      {  // lane = (dimension k, row parity hp)
+        const int dim = dim0 + k;
+        const bool dvalid = dim < a.ndims;
+        const int d = a.tp + a.dstride * dim;
+        float xv[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int64_t gr = (int64_t)mt * 128 + r0 + 2 * i + hp;
+          xv[i] = (dvalid && gr < a.N) ? a.v[gr * a.D + d] : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          const int r = 2 * i + hp;
+          const int64_t gr = (int64_t)mt * 128 + r0 + r;
+          const float2 p = *reinterpret_cast<const float2*>(T + r * TS + 2 * k);
+          float nv, l1;
+          affine_apply<INV>(p.x, p.y, xv[i], nv, l1);
+          if (dvalid && gr < a.N) {
+            a.v[gr * a.D + d] = nv;
+          } else {
+            nv = 0.f;
+            l1 = 0.f;
+          }
+          *reinterpret_cast<float2*>(T + r * TS + 2 * k) = make_float2(nv, l1);
+        }
+      }
+      __syncwarp();
+      {  // thread = row again: log-det partial, next layer's activation image
+        float u[16];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float4 t4 = *reinterpret_cast<const float4*>(T + lane * TS + 4 * e);
+          u[2 * e] = t4.x;
+          u[2 * e + 1] = t4.z;
+          ldsum += t4.y + t4.w;
+        }
+        if (og != nullptr) {
+          uint32_t h[8], l[8];
+          int ck;
+          if (a.next_rev) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) tc::split_bf16x2(u[15 - 2 * e], u[14 - 2 * e], h[e], l[e]);
+            ck = (a.D - 16 - dim0) >> 3;
+          } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) tc::split_bf16x2(u[2 * e], u[2 * e + 1], h[e], l[e]);
+            ck = dim0 >> 3;
+          }
+#pragma unroll
+          for (int q = 0; q < 2; ++q) {
+            uint8_t* st = og + (int64_t)((ck + q) >> 2) * 2 * kDtABytes + tc::img_off(128, row, (ck + q) & 3);
+            *reinterpret_cast<uint4*>(st) = make_uint4(h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]);
+            *reinterpret_cast<uint4*>(st + kDtABytes) = make_uint4(l[4 * q], l[4 * q + 1], l[4 * q + 2], l[4 * q + 3]);
+          }
+        }
+      }
+      __syncwarp();
+    }
+    if (grow < a.N) a.ldp[grow * a.tiles + nt] = ldsum;
+  }
+}
 
-  if (warp == 1) tc::tmem_alloc(tmem_slot, kDtBN);
+constexpr int kDtTileScratchFloats = 4 * 32 * 36;  // per-warp 32 x 36 transposition tiles of the affine epilogue
+// The affine epilogue needs the transposition scratch (two epilogue groups) and runs a 3-stage ring; the
+// other epilogues have the room for 4 stages.
+template <int EPI> struct DtCfg {
+  static constexpr int kStages = EPI == 2 ? 3 : 4;
+  static constexpr int kScratch = EPI == 2 ? 2 * kDtTileScratchFloats : 0;
+  static constexpr size_t kSmem = (size_t)kStages * kDtStageBytes + kScratch * 4 + 2 * kDtBN * 4 + (2 * kStages + 4) * 8 + 16;
+};
+
+// Persistent kernel: one CTA per SM walks the (m tile, n tile) list; a TMA ring feeds the MMA warp across
+// tile boundaries, and the two 256-column TMEM accumulators alternate between two epilogue warpgroups, so
+// an epilogue may take twice the MMA time of a tile before it stalls the tensor pipe.
+template <int EPI, bool INV>
+__global__ void __launch_bounds__(kDtThreads, 1) dense_tc_gemm_kernel(DtGemm a, int MT, int NT) {
+  constexpr int kDtStages = DtCfg<EPI>::kStages;
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* stages = smem;                                                          // [stages][48 KB]
+  float* Tbase = reinterpret_cast<float*>(smem + kDtStages * kDtStageBytes);       // epilogue scratch
+  float* sbias2 = Tbase + DtCfg<EPI>::kScratch;                                    // [2][256]
+  uint64_t* full = reinterpret_cast<uint64_t*>(sbias2 + 2 * kDtBN);                // [stages]
+  uint64_t* empty = full + kDtStages;                                              // [stages]
+  uint64_t* acc_full = empty + kDtStages;                                          // [2]
+  uint64_t* acc_empty = acc_full + 2;                                              // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int ntiles = MT * NT;
+
+  if (warp == 1) tc::tmem_alloc(tmem_slot, 2 * kDtBN);
   if (tid == 0) {
     for (int s = 0; s < kDtStages; ++s) {
       tc::mbar_init(&full[s], 1);
       tc::mbar_init(&empty[s], 1);
     }
-    tc::mbar_init(dfull, 1);
-    tc::fence_mbar_init();
-  }
-  if (warp >= 2) {  // bias of this tile's columns
-    const int c = tid - 64;
-    for (int n = c; n < kDtBN; n += 128) {
-      float b = 0.f;
-      if (EPI == kEpiHidden) {
-        const int col = nt * kDtBN + n;
-        if (col < a.n_out) b = a.bias[col];
-      } else {
-        b = dt_tile_bias(a, nt, n);
-      }
-      sbias[n] = b;
+    for (int s = 0; s < 2; ++s) {
+      tc::mbar_init(&acc_full[s], 1);
+      tc::mbar_init(&acc_empty[s], 4);  // one arrival per epilogue warp
     }
+    tc::fence_mbar_init();
   }
   tc::tc_fence_before();
   __syncthreads();
@@ -132,201 +282,107 @@ __global__ void __launch_bounds__(kDtThreads, 2) dense_tc_gemm_kernel(DtGemm a) 
 
   if (warp == 0) {
     if (lane == 0) {  // ===== TMA loader
-      const uint8_t* ag = a.a_img + (int64_t)mt * a.KS * 2 * kDtABytes;
-      const uint8_t* bg = a.b_img + (int64_t)nt * a.KS * 2 * kDtBBytes;
-      for (int ks = 0; ks < KS; ++ks) {
-        const int st = ks % kDtStages, use = ks / kDtStages;
-        if (use > 0) tc::mbar_wait(&empty[st], (uint32_t)((use - 1) & 1));
-        uint8_t* dst = stages + st * kDtStageBytes;
-        tc::mbar_arrive_expect_tx(&full[st], kDtStageBytes);
-        tc::tma_bulk_g2s(dst, ag + (int64_t)ks * 2 * kDtABytes, 2 * kDtABytes, &full[st]);
-        tc::tma_bulk_g2s(dst + 2 * kDtABytes, bg + (int64_t)ks * 2 * kDtBBytes, 2 * kDtBBytes, &full[st]);
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
+        const int mt = t / NT, nt = t - mt * NT;
+        int KS = a.KS;
+        if (nt < kDtMaxKsTiles && a.ks_tile[nt] != 0) KS = a.ks_tile[nt];
+        const uint8_t* ag = a.a_img + (int64_t)mt * a.KS * 2 * kDtABytes;
+        const uint8_t* bg = a.b_img + (int64_t)nt * a.KS * 2 * kDtBBytes;
+        for (int ks = 0; ks < KS; ++ks, ++it) {
+          const uint32_t st = it % kDtStages, ph = (it / kDtStages) & 1u;
+          tc::mbar_wait(&empty[st], ph ^ 1u);  // passes at once on a fresh barrier
+          uint8_t* dst = stages + st * kDtStageBytes;
+          tc::mbar_arrive_expect_tx(&full[st], kDtStageBytes);
+          tc::tma_bulk_g2s(dst, ag + (int64_t)ks * 2 * kDtABytes, 2 * kDtABytes, &full[st]);
+          tc::tma_bulk_g2s(dst + 2 * kDtABytes, bg + (int64_t)ks * 2 * kDtBBytes, 2 * kDtBBytes, &full[st]);
+        }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {  // ===== MMA issuer: 3 passes x 2 K steps per stage
       constexpr uint32_t idesc = tc::make_idesc(tc::kFmtBF16, 128, kDtBN);
       constexpr uint32_t lbo_a = 16u * 128u, lbo_b = (uint32_t)(kDtBN >> 3) * 128u;
-      uint32_t acc = 0;
-      for (int ks = 0; ks < KS; ++ks) {
-        const int st = ks % kDtStages, use = ks / kDtStages;
-        tc::mbar_wait(&full[st], (uint32_t)(use & 1));
+      uint32_t it = 0, tl = 0;
+      for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tl) {
+        const int nt = t % NT;
+        int KS = a.KS;
+        if (nt < kDtMaxKsTiles && a.ks_tile[nt] != 0) KS = a.ks_tile[nt];
+        const uint32_t slot = tl & 1u, aph = (tl >> 1) & 1u;
+        tc::mbar_wait(&acc_empty[slot], aph ^ 1u);  // the epilogue has drained this accumulator
         tc::tc_fence_after();
-        const uint32_t sa = tc::smem_u32(stages + st * kDtStageBytes), sb = sa + 2 * kDtABytes;
+        const uint32_t dtm = tmem + slot * (uint32_t)kDtBN;
+        uint32_t acc = 0;
+        for (int ks = 0; ks < KS; ++ks, ++it) {
+          const uint32_t st = it % kDtStages, ph = (it / kDtStages) & 1u;
+          tc::mbar_wait(&full[st], ph);
+          tc::tc_fence_after();
+          const uint32_t sa = tc::smem_u32(stages + st * kDtStageBytes), sb = sa + 2 * kDtABytes;
 #pragma unroll
-        for (int pass = 0; pass < 3; ++pass) {
-          const uint32_t ab = sa + (pass == 2 ? kDtABytes : 0), bb = sb + (pass == 1 ? kDtBBytes : 0);
+          for (int pass = 0; pass < 3; ++pass) {
+            const uint32_t ab = sa + (pass == 2 ? kDtABytes : 0), bb = sb + (pass == 1 ? kDtBBytes : 0);
 #pragma unroll
-          for (int s = 0; s < kDtBK / 16; ++s) {
-            tc::mma_ss<tc::kFmtBF16>(tmem, tc::make_smem_desc(ab + s * 2u * lbo_a, lbo_a, 128u),
-                                     tc::make_smem_desc(bb + s * 2u * lbo_b, lbo_b, 128u), idesc, acc);
-            acc = 1;
+            for (int s = 0; s < kDtBK / 16; ++s) {
+              tc::mma_ss<tc::kFmtBF16>(dtm, tc::make_smem_desc(ab + s * 2u * lbo_a, lbo_a, 128u),
+                                       tc::make_smem_desc(bb + s * 2u * lbo_b, lbo_b, 128u), idesc, acc);
+              acc = 1;
+            }
           }
+          tc::mma_commit(&empty[st]);
         }
-        tc::mma_commit(&empty[st]);
+        tc::mma_commit(&acc_full[slot]);
       }
-      tc::mma_commit(dfull);
     }
   } else {
-    // ===== epilogue warps: thread = row = TMEM lane
-    const int row = (warp & 3) * 32 + lane;
-    const int64_t grow = (int64_t)mt * 128 + row;
-    const uint32_t tb = tmem + ((uint32_t)((warp & 3) * 32) << 16);
-    tc::mbar_wait(dfull, 0);
-    tc::tc_fence_after();
-    if (EPI == kEpiHidden) {
-      uint8_t* og = a.out_img + (int64_t)mt * a.out_KS * 2 * kDtABytes;
-#pragma unroll 1
-      for (int c = 0; c < kDtBN; c += 16) {
-        uint32_t vv[16];
-        tc::tmem_ld_x16(tb + (uint32_t)c, vv);
-        tc::tmem_ld_wait();
-        uint32_t h[8], l[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float f0 = fmaxf(__uint_as_float(vv[2 * e]) + sbias[c + 2 * e], 0.f);
-          const float f1 = fmaxf(__uint_as_float(vv[2 * e + 1]) + sbias[c + 2 * e + 1], 0.f);
-          tc::split_bf16x2(f0, f1, h[e], l[e]);
+    // ===== epilogue warps: group 0 (warps 2-5) takes the even tiles of this CTA, group 1 (warps 6-9) the odd
+    const uint32_t group = (uint32_t)(warp - 2) >> 2;
+    const int et = (tid - 64) & 127;
+    float* sbias = sbias2 + group * kDtBN;
+    uint32_t tl = 0;
+    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tl) {
+      if ((tl & 1u) != group) continue;
+      const int mt = t / NT, nt = t - mt * NT;
+      const uint32_t slot = group, aph = (tl >> 1) & 1u;
+      for (int n = et; n < kDtBN; n += 128) {  // bias of this tile's columns
+        float b = 0.f;
+        if (EPI == kEpiHidden) {
+          const int col = nt * kDtBN + n;
+          if (col < a.n_out) b = a.bias[col];
+        } else {
+          b = dt_tile_bias(a, nt, n);
         }
-#pragma unroll
-        for (int q = 0; q < 2; ++q) {
-          const int ck = (nt * kDtBN + c) / 8 + q;  // chunk index along the next Linear's K
-          if (ck < a.out_KS * 4) {
-            uint8_t* st = og + (int64_t)(ck >> 2) * 2 * kDtABytes + tc::img_off(128, row, ck & 3);
-            *reinterpret_cast<uint4*>(st) = make_uint4(h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]);
-            *reinterpret_cast<uint4*>(st + kDtABytes) = make_uint4(l[4 * q], l[4 * q + 1], l[4 * q + 2], l[4 * q + 3]);
-          }
-        }
+        sbias[n] = b;
       }
-    } else if (EPI == kEpiRqs8) {
-      float ldsum = 0.f;
-#pragma unroll 1
-      for (int di = 0; di < 10; ++di) {
-        const int dim = nt * 10 + di;
-        if (dim >= a.ndims) break;  // uniform across the CTA
-        uint32_t vv[25];
-        tc::tmem_ld_x16(tb + (uint32_t)(25 * di), vv);
-        tc::tmem_ld_x8(tb + (uint32_t)(25 * di + 16), vv + 16);
-        tc::tmem_ld_x1(tb + (uint32_t)(25 * di + 24), vv + 24);
-        tc::tmem_ld_wait();
-        if (grow < a.N) {
-          float o[25];
-#pragma unroll
-          for (int i = 0; i < 25; ++i) o[i] = __uint_as_float(vv[i]) + sbias[25 * di + i];
-          const int d = a.tp + a.dstride * dim;
-          const float xin = a.v[grow * a.D + d];
-          float nv, l1;
-          rqs_apply<INV, 8>([&](int i) { return o[i]; }, 8, a.lo, a.hi, xin, nv, l1);
-          a.v[grow * a.D + d] = nv;
-          ldsum += l1;
-        }
-      }
-      if (grow < a.N) a.ldp[grow * a.tiles + nt] = ldsum;
-    } else {
-      // Affine epilogue.  The accumulator comes out of TMEM as thread = sample row, but the state v[N, D]
-      // is row-major: a thread-per-row access touches 32 cache lines per request.  Each warp therefore
-      // transposes its 32 rows x 32 columns through shared memory (the pipeline stages are idle by now)
-      // and applies the bijector as lane = dimension, so the state is read and written in 64-byte runs;
-      // a third phase (thread = row again) sums the log-det and, for MADE stacks, writes the NEXT
-      // layer's activation image directly (bf16 hi/lo), so no separate packing pass re-reads v.
-      constexpr int TS = 36;  // row stride of the transposition tile in floats (16-byte aligned rows)
-      float* T = reinterpret_cast<float*>(stages) + (warp & 3) * 32 * TS;
-      const int r0 = (warp & 3) * 32;
-      const int k = lane & 15, hp = lane >> 4;
-      uint8_t* og = a.out_img ? a.out_img + (int64_t)mt * a.out_KS * 2 * kDtABytes : nullptr;
-      float ldsum = 0.f;
-#pragma unroll 1
-      for (int c = 0; c < kDtBN; c += 32) {
-        const int dim0 = nt * 128 + c / 2;
-        if (dim0 >= a.ndims) break;  // uniform across the CTA
-        uint32_t vv[32];
-        tc::tmem_ld_x32(tb + (uint32_t)c, vv);
-        tc::tmem_ld_wait();
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          float4 t4;
-          t4.x = __uint_as_float(vv[4 * e]) + sbias[c + 4 * e];
-          t4.y = __uint_as_float(vv[4 * e + 1]) + sbias[c + 4 * e + 1];
-          t4.z = __uint_as_float(vv[4 * e + 2]) + sbias[c + 4 * e + 2];
-          t4.w = __uint_as_float(vv[4 * e + 3]) + sbias[c + 4 * e + 3];
-          *reinterpret_cast<float4*>(T + lane * TS + 4 * e) = t4;
-        }
-        __syncwarp();
-        {  // lane = (dimension k, row parity hp)
-          const int dim = dim0 + k;
-          const bool dvalid = dim < a.ndims;
-          const int d = a.tp + a.dstride * dim;
-          float xv[16];
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const int64_t gr = (int64_t)mt * 128 + r0 + 2 * i + hp;
-            xv[i] = (dvalid && gr < a.N) ? a.v[gr * a.D + d] : 0.f;
-          }
-#pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            const int r = 2 * i + hp;
-            const int64_t gr = (int64_t)mt * 128 + r0 + r;
-            const float2 p = *reinterpret_cast<const float2*>(T + r * TS + 2 * k);
-            float nv, l1;
-            affine_apply<INV>(p.x, p.y, xv[i], nv, l1);
-            if (dvalid && gr < a.N) {
-              a.v[gr * a.D + d] = nv;
-            } else {
-              nv = 0.f;
-              l1 = 0.f;
-            }
-            *reinterpret_cast<float2*>(T + r * TS + 2 * k) = make_float2(nv, l1);
-          }
-        }
-        __syncwarp();
-        {  // thread = row again: log-det partial, next layer's activation image
-          float u[16];
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const float4 t4 = *reinterpret_cast<const float4*>(T + lane * TS + 4 * e);
-            u[2 * e] = t4.x;
-            u[2 * e + 1] = t4.z;
-            ldsum += t4.y + t4.w;
-          }
-          if (og != nullptr) {
-            uint32_t h[8], l[8];
-            int ck;
-            if (a.next_rev) {
-#pragma unroll
-              for (int e = 0; e < 8; ++e) tc::split_bf16x2(u[15 - 2 * e], u[14 - 2 * e], h[e], l[e]);
-              ck = (a.D - 16 - dim0) >> 3;
-            } else {
-#pragma unroll
-              for (int e = 0; e < 8; ++e) tc::split_bf16x2(u[2 * e], u[2 * e + 1], h[e], l[e]);
-              ck = dim0 >> 3;
-            }
-#pragma unroll
-            for (int q = 0; q < 2; ++q) {
-              uint8_t* st = og + (int64_t)((ck + q) >> 2) * 2 * kDtABytes + tc::img_off(128, row, (ck + q) & 3);
-              *reinterpret_cast<uint4*>(st) = make_uint4(h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]);
-              *reinterpret_cast<uint4*>(st + kDtABytes) = make_uint4(l[4 * q], l[4 * q + 1], l[4 * q + 2], l[4 * q + 3]);
-            }
-          }
-        }
-        __syncwarp();
-      }
-      if (grow < a.N) a.ldp[grow * a.tiles + nt] = ldsum;
+      if (group == 0) asm volatile("bar.sync 1, 128;" ::: "memory");  // this epilogue group only
+      else asm volatile("bar.sync 2, 128;" ::: "memory");
+      tc::mbar_wait(&acc_full[slot], aph);
+      tc::tc_fence_after();
+      const uint32_t tb = tmem + slot * (uint32_t)kDtBN + ((uint32_t)((warp & 3) * 32) << 16);
+      dt_epilogue<EPI, INV>(a, mt, nt, tb, sbias, Tbase + group * kDtTileScratchFloats, warp, lane);
+      tc::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&acc_empty[slot]);
+      // all four warps must be done with sbias before the group's next tile overwrites it
+      if (group == 0) asm volatile("bar.sync 1, 128;" ::: "memory");
+      else asm volatile("bar.sync 2, 128;" ::: "memory");
     }
   }
   tc::tc_fence_before();
   __syncthreads();
   if (warp == 1) {
     __syncwarp();
-    tc::tmem_dealloc(tmem, kDtBN);
+    tc::tmem_dealloc(tmem, 2 * kDtBN);
   }
 }
 
 template <int EPI, bool INV>
 static int dt_launch_gemm(const DtGemm& g, int64_t MT, int NT, cudaStream_t s) {
-  const size_t smem = (size_t)kDtStages * kDtStageBytes + kDtBN * 4 + (2 * kDtStages + 1) * 8 + 16;
   auto kern = dense_tc_gemm_kernel<EPI, INV>;
-  FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  kern<<<dim3((unsigned)MT, (unsigned)NT), kDtThreads, smem, s>>>(g);
+  constexpr size_t kSmem = DtCfg<EPI>::kSmem;
+  FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+  const int64_t tiles = MT * NT;
+  const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
+  kern<<<grid, kDtThreads, kSmem, s>>>(g, (int)MT, NT);
   FC_LAUNCH_CHECK("dense_tc_gemm_kernel");
   return FLOWCUDA_OK;
 }
