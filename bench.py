@@ -503,7 +503,13 @@ def roofline(w, res, peaks):
         ach = w.n * w.flops_per_sample / dur / 1e12
         peak = peaks["bf16_tflops"]
         unit = "TFLOP/s"
-    return {"bound": w.bound, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak, "traffic": None,
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get(w.name, {}).get("dram_bytes_per_launch")
+    except Exception:
+        pass
+    return {"bound": w.bound, "achieved": ach, "peak": peak, "unit": unit, "frac": ach / peak, "traffic": traffic,
             "peak_source": f"MEASURED_PEAKS.json ({src})" if src == "measured" else "B200_PROFILING.md fallback",
             "kernel_ms": res["kernel_ms"]}
 
