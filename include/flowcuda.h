@@ -231,6 +231,15 @@ int flowcuda_made_log_prob(const flowcuda_made_spec* spec, const float* params, 
 int flowcuda_made_sample(const flowcuda_made_spec* spec, const float* params, const float* z,
                          float* x, int64_t n, void* stream);
 
+/* value_and_grad of loss = -mean(log_prob(x)) w.r.t. the MADE flow parameters (the training
+ * step of src/maf_mnist.py:134-166 applied to the MADE flow): hand-written FP32 reverse mode over
+ * stored activations, fixed summation order (bit-reproducible).  loss[1], grad[param_count]
+ * (layout of `params`; masked-out weights get exactly 0).  Needs num_hidden == 2. */
+size_t flowcuda_made_nll_grad_workspace_bytes(const flowcuda_made_spec* spec, int64_t n);
+int flowcuda_made_nll_grad(const flowcuda_made_spec* spec, const float* params, const float* x,
+                           int64_t n, float* loss, float* grad, void* workspace,
+                           size_t workspace_bytes, void* stream);
+
 /* ------------------------------------------------------------------------------------
  * Rows #7, #9 — loss reduction and optimiser steps.
  * ---------------------------------------------------------------------------------- */

@@ -287,6 +287,24 @@ def made_sample(spec: _lib.MadeSpec, params: torch.Tensor, z: torch.Tensor) -> t
     return x
 
 
+def made_nll_grad(spec: _lib.MadeSpec, params: torch.Tensor, x: torch.Tensor, workspace: Optional[torch.Tensor] = None):
+    """(loss[1], grad[param_count]) of -mean(log_prob(x)) for the MADE flow — jax.value_and_grad(loss_fn)."""
+    x = _f32(x).reshape(x.shape[0], spec.event_dim)
+    _dev_check(params, x)
+    lib = _lib.load()
+    n = x.shape[0]
+    need = lib.flowcuda_made_nll_grad_workspace_bytes(C.byref(spec), n)
+    if need == 0:
+        raise _lib.FlowCudaError("made_nll_grad: unsupported spec (needs two hidden layers)")
+    if workspace is None or workspace.numel() * workspace.element_size() < need:
+        workspace = torch.empty((need + 3) // 4, device=x.device, dtype=torch.float32)
+    loss = torch.empty(1, device=x.device, dtype=torch.float32)
+    grad = torch.empty_like(params)
+    check(lib.flowcuda_made_nll_grad(C.byref(spec), _ptr(params), _ptr(x), n, _ptr(loss), _ptr(grad), _ptr(workspace),
+                                     workspace.numel() * workspace.element_size(), _stream()), "made_nll_grad")
+    return loss, grad
+
+
 # ---------------------------------------------------------------------------- rows #7, #9
 def sum_scaled(v: torch.Tensor, scale: float) -> torch.Tensor:
     v = _f32(v).reshape(-1)
