@@ -216,6 +216,44 @@ class MafMade(Workload):
 
         return O.maf_log_prob(self._ospec(), self._p, x)
 
+    def train(self, dev, rank, world, dist, ops, K=5, batch=4096):
+        """train samples/s: value_and_grad of -mean(log_prob) (hand-written FP32 reverse mode), gradient
+        all-reduce across ranks (NCCL sum, the step's only exchange), fused Adam (maf_mnist.py:155-166)."""
+        spec = self.model.bijector.spec()
+        p = self.model.params.clone()
+        m, v = torch.zeros_like(p), torch.zeros_like(p)
+        gen = torch.Generator().manual_seed(77 + rank)
+        xs = [self.make_inputs(gen, batch).to(dev) for _ in range(2)]
+        need = _lib_ws(ops, spec, batch)
+        ws = torch.empty((need + 3) // 4, device=dev, dtype=torch.float32)
+
+        def step(i):
+            loss, grad = ops.made_nll_grad(spec, p, xs[i % len(xs)], workspace=ws)
+            if dist is not None:
+                dist.all_reduce(grad)
+            ops.adam_step(p, grad, m, v, i + 1, 1e-4, grad_scale=1.0 / world)
+            return loss
+
+        for i in range(2):
+            step(i)
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(K):
+            loss = step(2 + i)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        if dist is not None:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = t.item()
+        return {"value": batch * world * K / (ms * 1e-3), "unit": "samples/s", "batch_per_gpu": batch, "steps": K,
+                "ms_per_step": ms / K, "final_loss": float(loss.item()), "optimizer": "adam(1e-4)",
+                "grad_allreduce_bytes": int(p.numel() * 4) if dist is not None else 0, "precision": "fp32"}
+
     def sampling(self, dev, K=3):
         """Sequential sampling (persistent kernel over the D positions), base noise resident in HBM."""
         n = 148 * 8 * 4
@@ -294,6 +332,14 @@ class Bernstein(Workload):
 
 
 WORKLOADS = {w.name: w for w in (MafToy, RealNvpToy, MafMnist, MafMade, RealNvpHand, Bernstein)}
+
+
+def _lib_ws(ops, spec, n):
+    import ctypes as C
+
+    from normalizing_flows_b200 import _lib
+
+    return _lib.load().flowcuda_made_nll_grad_workspace_bytes(C.byref(spec), n)
 
 
 # ----------------------------------------------------------------------------- clocks
@@ -596,7 +642,7 @@ def time_workload(w, dev, rank, world, dist, W, K, ops, e2e, clocks):
            "nbuf": nbuf, "clocks": clk, "launches": K * (w.launches_per_step + (2 if dist is not None else 0))}
     if e2e:
         out["e2e"] = time_e2e(w, dev, host, dist, world, max(3, K // 2))
-        out["train"] = time_train(w, dev, rank, world, dist, ops)
+        out["train"] = w.train(dev, rank, world, dist, ops) if hasattr(w, "train") else time_train(w, dev, rank, world, dist, ops)
         if hasattr(w, "sampling"):
             out["sampling"] = w.sampling(dev)
     return out

@@ -17,11 +17,21 @@ __host__ __device__ __forceinline__ int mg_hdeg(int k, int H, int D) {
   return d < 1 ? 1 : d;
 }
 
-// MADE mask of Linear `kind` (0: input->hidden, 1: hidden->hidden, 2: hidden->output) at (in i, out j)
-__device__ __forceinline__ bool mg_mask(int kind, int i, int j, int D, int Hin, int Hout) {
-  const int din = kind == 0 ? i + 1 : mg_hdeg(i, Hin, D);
-  if (kind == 2) return din < (j % D) + 1;
-  return din <= mg_hdeg(j, Hout, D);
+// MADE mask of a Linear at (in i, out j) from degree tables (NULL table: inputs have degree i+1, outputs
+// (j mod D)+1 with a STRICT comparison — the [shift | log_scale] output Linear)
+struct MgMask {
+  const int* din;   // [k_in] or NULL
+  const int* dout;  // [n_out] or NULL
+  int D, on;        // on = 0: no mask
+};
+__device__ __forceinline__ int mg_din(const MgMask& m, int i) { return m.din ? m.din[i] : i + 1; }
+__device__ __forceinline__ int mg_dout(const MgMask& m, int j) { return m.dout ? m.dout[j] : (j % m.D); }  // strict -> "<= dout-1"
+__device__ __forceinline__ bool mg_mask(const MgMask& m, int i, int j) { return mg_din(m, i) <= mg_dout(m, j); }
+// largest dout over [j0, j1] (degree tables are non-decreasing; the output Linear wraps at D)
+__device__ __forceinline__ int mg_dout_max(const MgMask& m, int j0, int j1) {
+  if (m.dout) return m.dout[j1];
+  if (j0 / m.D != j1 / m.D) return m.D - 1;
+  return j1 % m.D;
 }
 
 struct MgGemm {
@@ -33,81 +43,166 @@ struct MgGemm {
   const float* gate; int64_t ldg;    // multiply by (gate[i*ldg + j] > 0) (relu backward), or NULL
   int relu;                          // relu on the result
   int accumulate;                    // C += result
-  int mask_kind, D, Hin, Hout;       // mask_kind >= 0: weight product, apply the MADE mask with i/j roles below
+  MgMask mask;                       // mask.on: weight product, apply the MADE mask with the i/j roles below
+  int splits; float* part;           // splits > 1: split-K, raw partials to part[z][M][N]; mg_splitk_reduce finishes (fixed order)
   int mask_on_b;                     // 1: mask B(k,j) as W[k (in), j (out)];  2: mask B(k,j) as Wᵀ: in = j, out = k; 0: mask C(i,j) as W[i,j]
 };
 
-constexpr int kMgT = 64, kMgK = 16;
+constexpr int kMgT = 128, kMgK = 8, kMgSplits = 8;
 
+// C = op(A)·op(B): 128 x 128 tile, 8 k per step, 256 threads x (8 x 8) outputs held as four 4 x 4 blocks so
+// that every shared-memory read is a 128-bit load; the next step's operands are fetched into registers while
+// the current step is computed (double-buffered shared memory, one barrier per step).
 __global__ void __launch_bounds__(256) mg_sgemm_kernel(MgGemm g) {
-  __shared__ float As[kMgK][kMgT + 1];
-  __shared__ float Bs[kMgK][kMgT + 1];
+  __shared__ __align__(16) float As[2][kMgK][kMgT + 4];
+  __shared__ __align__(16) float Bs[2][kMgK][kMgT + 4];
   const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
   const int i0 = blockIdx.y * kMgT, j0 = blockIdx.x * kMgT;
-  float acc[4][4];
+  const int jl = min(j0 + kMgT, g.N) - 1;
+  // a masked Linear is block-triangular in degree order: skip what is entirely masked out
+  if (g.mask.on && g.mask_on_b == 0 && mg_din(g.mask, i0) > mg_dout_max(g.mask, j0, jl)) {
+    if (!g.accumulate && blockIdx.z == 0) {
+      for (int e = tid; e < kMgT * kMgT; e += 256) {
+        const int gi = i0 + (e >> 7), gj = j0 + (e & 127);
+        if (gi < g.M && gj < g.N) g.C[gi * g.ldc + gj] = 0.f;
+      }
+    }
+    return;
+  }
+  // the k steps this tile needs (masks make whole k ranges vanish; split-K takes a slice)
+  int64_t kbeg = 0, kend = g.K;
+  if (g.splits > 1) {
+    const int64_t chunk = ((g.K + g.splits - 1) / g.splits + kMgK - 1) & ~(int64_t)(kMgK - 1);
+    kbeg = chunk * blockIdx.z;
+    kend = min(g.K, kbeg + chunk);
+  }
+  if (g.mask.on && g.mask_on_b == 1) {  // B = W[k (in), j (out)]: inputs with degree above the tile's largest output degree
+    const int dmax = mg_dout_max(g.mask, j0, jl);
+    int64_t lo = 0, hi = g.K;  // first k with din(k) > dmax (din is non-decreasing)
+    while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if (mg_din(g.mask, (int)mid) > dmax) hi = mid; else lo = mid + 1; }
+    kend = lo;
+  } else if (g.mask.on && g.mask_on_b == 2) {  // B = Wᵀ: in = j, out = k: outputs with degree below the tile's smallest input degree
+    const int dmin = mg_din(g.mask, j0);
+    if (g.mask.dout) {
+      int64_t lo = 0, hi = g.K;  // first k with dout(k) >= dmin
+      while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if (g.mask.dout[mid] >= dmin) hi = mid; else lo = mid + 1; }
+      kbeg = lo & ~(int64_t)(kMgK - 1);
+    }
+  }
+  float acc[8][8];
 #pragma unroll
-  for (int a = 0; a < 4; ++a)
+  for (int a = 0; a < 8; ++a)
 #pragma unroll
-    for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+    for (int b = 0; b < 8; ++b) acc[a][b] = 0.f;
   const bool a_kfast = g.acs == 1, b_jfast = g.bcs == 1;
-  for (int64_t k0 = 0; k0 < g.K; k0 += kMgK) {
+  float ra[4], rb[4];
+  auto fetch = [&](int64_t k0) {
 #pragma unroll
     for (int t = 0; t < 4; ++t) {
       const int e = tid + t * 256;
       int i, k;
-      if (a_kfast) { i = e >> 4; k = e & 15; } else { i = e & 63; k = e >> 6; }
+      if (a_kfast) { i = e >> 3; k = e & 7; } else { i = e & 127; k = e >> 7; }
       const int gi = i0 + i; const int64_t gk = k0 + k;
-      As[k][i] = (gi < g.M && gk < g.K) ? g.A[gi * g.ars + gk * g.acs] : 0.f;
+      ra[t] = (gi < g.M && gk < kend) ? g.A[gi * g.ars + gk * g.acs] : 0.f;
       int j, kb;
-      if (b_jfast) { j = e & 63; kb = e >> 6; } else { j = e >> 4; kb = e & 15; }
+      if (b_jfast) { j = e & 127; kb = e >> 7; } else { j = e >> 3; kb = e & 7; }
       const int gj = j0 + j; const int64_t gkb = k0 + kb;
       float bv = 0.f;
-      if (gj < g.N && gkb < g.K) {
+      if (gj < g.N && gkb < kend) {
         bv = g.B[gkb * g.brs + gj * g.bcs];
-        if (g.mask_on_b == 1 && !mg_mask(g.mask_kind, (int)gkb, gj, g.D, g.Hin, g.Hout)) bv = 0.f;
-        if (g.mask_on_b == 2 && !mg_mask(g.mask_kind, gj, (int)gkb, g.D, g.Hin, g.Hout)) bv = 0.f;
+        if (g.mask.on && g.mask_on_b == 1 && !mg_mask(g.mask, (int)gkb, gj)) bv = 0.f;
+        if (g.mask.on && g.mask_on_b == 2 && !mg_mask(g.mask, gj, (int)gkb)) bv = 0.f;
       }
-      Bs[kb][j] = bv;
+      rb[t] = bv;
     }
-    __syncthreads();
+  };
+  auto stash = [&](int buf) {
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int e = tid + t * 256;
+      int i, k;
+      if (a_kfast) { i = e >> 3; k = e & 7; } else { i = e & 127; k = e >> 7; }
+      As[buf][k][i] = ra[t];
+      int j, kb;
+      if (b_jfast) { j = e & 127; kb = e >> 7; } else { j = e >> 3; kb = e & 7; }
+      Bs[buf][kb][j] = rb[t];
+    }
+  };
+  int buf = 0;
+  if (kbeg < kend) {
+    fetch(kbeg);
+    stash(0);
+  }
+  __syncthreads();
+  for (int64_t k0 = kbeg; k0 < kend; k0 += kMgK) {
+    const bool more = k0 + kMgK < kend;
+    if (more) fetch(k0 + kMgK);
 #pragma unroll
     for (int k = 0; k < kMgK; ++k) {
-      float av[4], bv[4];
+      const float4 a0 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 4]);
+      const float4 a1 = *reinterpret_cast<const float4*>(&As[buf][k][64 + ty * 4]);
+      const float4 b0 = *reinterpret_cast<const float4*>(&Bs[buf][k][tx * 4]);
+      const float4 b1 = *reinterpret_cast<const float4*>(&Bs[buf][k][64 + tx * 4]);
+      const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+      const float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-      for (int a = 0; a < 4; ++a) av[a] = As[k][ty * 4 + a];
+      for (int a = 0; a < 8; ++a)
 #pragma unroll
-      for (int b = 0; b < 4; ++b) bv[b] = Bs[k][tx * 4 + b];
-#pragma unroll
-      for (int a = 0; a < 4; ++a)
-#pragma unroll
-        for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(av[a], bv[b], acc[a][b]);
+        for (int b = 0; b < 8; ++b) acc[a][b] = fmaf(av[a], bv[b], acc[a][b]);
     }
+    if (more) stash(buf ^ 1);
     __syncthreads();
+    buf ^= 1;
   }
 #pragma unroll
-  for (int a = 0; a < 4; ++a) {
-    const int gi = i0 + ty * 4 + a;
+  for (int a = 0; a < 8; ++a) {
+    const int gi = i0 + (a < 4 ? ty * 4 + a : 64 + ty * 4 + a - 4);
     if (gi >= g.M) continue;
 #pragma unroll
-    for (int b = 0; b < 4; ++b) {
-      const int gj = j0 + tx * 4 + b;
+    for (int b = 0; b < 8; ++b) {
+      const int gj = j0 + (b < 4 ? tx * 4 + b : 64 + tx * 4 + b - 4);
       if (gj >= g.N) continue;
       float r = acc[a][b];
+      if (g.splits > 1) {
+        g.part[((int64_t)blockIdx.z * g.M + gi) * g.N + gj] = r;
+        continue;
+      }
       if (g.bias) r += g.bias[gj];
       if (g.relu) r = fmaxf(r, 0.f);
       if (g.gate && !(g.gate[gi * g.ldg + gj] > 0.f)) r = 0.f;
-      if (g.mask_kind >= 0 && g.mask_on_b == 0 && !mg_mask(g.mask_kind, gi, gj, g.D, g.Hin, g.Hout)) r = 0.f;
+      if (g.mask.on && g.mask_on_b == 0 && !mg_mask(g.mask, gi, gj)) r = 0.f;
       float* c = g.C + gi * g.ldc + gj;
       *c = g.accumulate ? *c + r : r;
     }
   }
 }
 
+// C[i,j] = mask ⊙ sum_z part[z][i][j]   (z in ascending order: deterministic)
+__global__ void __launch_bounds__(256) mg_splitk_reduce_kernel(MgGemm g) {
+  const int64_t tot = (int64_t)g.M * g.N;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < tot; e += (int64_t)gridDim.x * blockDim.x) {
+    const int gi = (int)(e / g.N), gj = (int)(e - (int64_t)gi * g.N);
+    float r = 0.f;
+    if (!g.mask.on || mg_mask(g.mask, gi, gj))
+      for (int z = 0; z < g.splits; ++z) r += g.part[(int64_t)z * tot + e];
+    g.C[gi * g.ldc + gj] = r;
+  }
+}
+
 static int mg_launch(const MgGemm& g, cudaStream_t s) {
-  dim3 grid((g.N + kMgT - 1) / kMgT, (g.M + kMgT - 1) / kMgT);
+  dim3 grid((g.N + kMgT - 1) / kMgT, (g.M + kMgT - 1) / kMgT, g.splits > 1 ? g.splits : 1);
   mg_sgemm_kernel<<<grid, 256, 0, s>>>(g);
   FC_LAUNCH_CHECK("mg_sgemm_kernel");
+  if (g.splits > 1) {
+    mg_splitk_reduce_kernel<<<grid_for((int64_t)g.M * g.N, 256, 8), 256, 0, s>>>(g);
+    FC_LAUNCH_CHECK("mg_splitk_reduce_kernel");
+  }
   return FLOWCUDA_OK;
+}
+
+__global__ void mg_degree_kernel(int* __restrict__ deg, int H, int D) {
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < H) deg[k] = mg_hdeg(k, H, D);
 }
 
 // out[r, c] = in[r, rev ? D-1-c : c]
@@ -171,17 +266,32 @@ __global__ void __launch_bounds__(256) mg_affine_bwd_kernel(const float* __restr
   }
 }
 
-// db[j] = sum_r dY[r, j]  (fixed order: deterministic)
+// db[j] = sum_r dY[r, j]  (fixed order: deterministic).  Block = 32 columns x 8 row groups: a warp reads 32
+// consecutive columns of one row (coalesced); thread (g, c) sums rows r = g (mod 8) in four interleaved
+// accumulators, then the 8 groups are added in a fixed order.
 __global__ void __launch_bounds__(256) mg_colsum_kernel(const float* __restrict__ dY, int64_t N, int n, float* __restrict__ db) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= n) return;
-  float s = 0.f, c = 0.f;  // Kahan: N can be 10^4..10^5
-  for (int64_t r = 0; r < N; ++r) {
-    const float y = dY[r * n + j] - c, t = s + y;
-    c = (t - s) - y;
-    s = t;
+  __shared__ double part[8][33];
+  const int c = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int j = blockIdx.x * 32 + c;
+  double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+  if (j < n) {
+    int64_t r = g;
+    for (; r + 24 < N; r += 32) {
+      a0 += (double)dY[r * n + j];
+      a1 += (double)dY[(r + 8) * n + j];
+      a2 += (double)dY[(r + 16) * n + j];
+      a3 += (double)dY[(r + 24) * n + j];
+    }
+    for (; r < N; r += 8) a0 += (double)dY[r * n + j];
   }
-  db[j] = s;
+  part[g][c] = (a0 + a1) + (a2 + a3);
+  __syncthreads();
+  if (g == 0 && j < n) {
+    double t = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += part[k][c];
+    db[j] = (float)t;
+  }
 }
 
 
@@ -190,7 +300,7 @@ struct MgLayout {
   int D, H1, H2, L;
   int64_t w1, b1, w2, b2, w3, b3, per_layer;
   size_t per_layer_act;  // floats of stored activations per layer
-  size_t off_state, off_tmp, off_ld, off_lp, off_dO, off_dH2, off_dH1, off_sum, off_act, total;  // bytes
+  size_t off_state, off_tmp, off_ld, off_lp, off_dO, off_dH2, off_dH1, off_sum, off_deg, off_part, off_act, total;  // bytes
 };
 
 static size_t mg_al(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -213,6 +323,13 @@ static bool mg_layout(const flowcuda_made_spec* sp, int64_t n, MgLayout& L) {
   L.off_dH2 = off; off = mg_al(off + (size_t)n * L.H2 * 4);
   L.off_dH1 = off; off = mg_al(off + (size_t)n * L.H1 * 4);
   L.off_sum = off; off = mg_al(off + 1024 * 8);
+  L.off_deg = off; off = mg_al(off + (size_t)(L.H1 + L.H2) * 4);
+  {
+    size_t mx = (size_t)L.D * L.H1;
+    if ((size_t)L.H1 * L.H2 > mx) mx = (size_t)L.H1 * L.H2;
+    if ((size_t)L.H2 * 2 * L.D > mx) mx = (size_t)L.H2 * 2 * L.D;
+    L.off_part = off; off = mg_al(off + mx * 4 * kMgSplits);
+  }
   L.off_act = off; off = mg_al(off + L.per_layer_act * 4 * (size_t)L.L);
   L.total = off + 256;
   return true;
@@ -222,7 +339,6 @@ static MgGemm mg_gemm(const float* A, int64_t ars, int64_t acs, const float* B, 
                       int64_t ldc, int M, int N, int64_t K) {
   MgGemm g = {};
   g.A = A; g.ars = ars; g.acs = acs; g.B = B; g.brs = brs; g.bcs = bcs; g.C = C; g.ldc = ldc; g.M = M; g.N = N; g.K = K;
-  g.mask_kind = -1;
   return g;
 }
 
@@ -252,6 +368,13 @@ static int mg_run(const flowcuda_made_spec* sp, const float* params, const float
   auto HA = [&](int l) { return XP(l) + (size_t)n * D; };
   auto HB = [&](int l) { return HA(l) + (size_t)n * H1; };
   auto OO = [&](int l) { return HB(l) + (size_t)n * H2; };
+  int* deg1 = (int*)(ws + L.off_deg);
+  int* deg2 = deg1 + H1;
+  mg_degree_kernel<<<(H1 + 255) / 256, 256, 0, s>>>(deg1, H1, D);
+  mg_degree_kernel<<<(H2 + 255) / 256, 256, 0, s>>>(deg2, H2, D);
+  float* part = (float*)(ws + L.off_part);
+  const int splits = n >= 1024 ? kMgSplits : 1;
+  const MgMask m0 = {nullptr, deg1, D, 1}, m1 = {deg1, deg2, D, 1}, m2 = {deg2, nullptr, D, 1};
   int rc;
   FC_CUDA(cudaMemcpyAsync(S, x, (size_t)n * D * 4, cudaMemcpyDeviceToDevice, s));
   // ---- forward, data -> base: layer L-1 first
@@ -260,13 +383,13 @@ static int mg_run(const flowcuda_made_spec* sp, const float* params, const float
     const float* P = params + L.per_layer * l;
     mg_copy_perm_kernel<<<eb, 256, 0, s>>>(S, XP(l), n, D, rev, 0);
     MgGemm g = mg_gemm(XP(l), D, 1, P + L.w1, H1, 1, HA(l), H1, N, H1, D);
-    g.bias = P + L.b1; g.relu = 1; g.mask_kind = 0; g.mask_on_b = 1; g.D = D; g.Hout = H1;
+    g.bias = P + L.b1; g.relu = 1; g.mask = m0; g.mask_on_b = 1;
     if ((rc = mg_launch(g, s))) return rc;
     g = mg_gemm(HA(l), H1, 1, P + L.w2, H2, 1, HB(l), H2, N, H2, H1);
-    g.bias = P + L.b2; g.relu = 1; g.mask_kind = 1; g.mask_on_b = 1; g.D = D; g.Hin = H1; g.Hout = H2;
+    g.bias = P + L.b2; g.relu = 1; g.mask = m1; g.mask_on_b = 1;
     if ((rc = mg_launch(g, s))) return rc;
     g = mg_gemm(HB(l), H2, 1, P + L.w3, 2 * D, 1, OO(l), 2 * D, N, 2 * D, H2);
-    g.bias = P + L.b3; g.mask_kind = 2; g.mask_on_b = 1; g.D = D; g.Hin = H2;
+    g.bias = P + L.b3; g.mask = m2; g.mask_on_b = 1;
     if ((rc = mg_launch(g, s))) return rc;
     mg_affine_fwd_kernel<<<rb, 256, 0, s>>>(XP(l), OO(l), T, LD, n, D, it == 0);
     mg_copy_perm_kernel<<<eb, 256, 0, s>>>(T, S, n, D, rev, 0);
@@ -285,27 +408,27 @@ static int mg_run(const flowcuda_made_spec* sp, const float* params, const float
     FC_LAUNCH_CHECK("mg_affine_bwd_kernel");
     // output Linear
     MgGemm g = mg_gemm(HB(l), 1, H2, dO, 2 * D, 1, G + L.w3, 2 * D, H2, 2 * D, n);
-    g.mask_kind = 2; g.D = D; g.Hin = H2;
+    g.mask = m2; g.splits = splits; g.part = part;
     if ((rc = mg_launch(g, s))) return rc;
-    mg_colsum_kernel<<<(2 * D + 255) / 256, 256, 0, s>>>(dO, n, 2 * D, G + L.b3);
+    mg_colsum_kernel<<<(2 * D + 31) / 32, 256, 0, s>>>(dO, n, 2 * D, G + L.b3);
     g = mg_gemm(dO, 2 * D, 1, P + L.w3, 1, 2 * D, dH2, H2, N, H2, 2 * D);
-    g.gate = HB(l); g.ldg = H2; g.mask_kind = 2; g.mask_on_b = 2; g.D = D; g.Hin = H2;
+    g.gate = HB(l); g.ldg = H2; g.mask = m2; g.mask_on_b = 2;
     if ((rc = mg_launch(g, s))) return rc;
     // hidden 2
     g = mg_gemm(HA(l), 1, H1, dH2, H2, 1, G + L.w2, H2, H1, H2, n);
-    g.mask_kind = 1; g.D = D; g.Hin = H1; g.Hout = H2;
+    g.mask = m1; g.splits = splits; g.part = part;
     if ((rc = mg_launch(g, s))) return rc;
-    mg_colsum_kernel<<<(H2 + 255) / 256, 256, 0, s>>>(dH2, n, H2, G + L.b2);
+    mg_colsum_kernel<<<(H2 + 31) / 32, 256, 0, s>>>(dH2, n, H2, G + L.b2);
     g = mg_gemm(dH2, H2, 1, P + L.w2, 1, H2, dH1, H1, N, H1, H2);
-    g.gate = HA(l); g.ldg = H1; g.mask_kind = 1; g.mask_on_b = 2; g.D = D; g.Hin = H1; g.Hout = H2;
+    g.gate = HA(l); g.ldg = H1; g.mask = m1; g.mask_on_b = 2;
     if ((rc = mg_launch(g, s))) return rc;
     // hidden 1
     g = mg_gemm(XP(l), 1, D, dH1, H1, 1, G + L.w1, H1, D, H1, n);
-    g.mask_kind = 0; g.D = D; g.Hout = H1;
+    g.mask = m0; g.splits = splits; g.part = part;
     if ((rc = mg_launch(g, s))) return rc;
-    mg_colsum_kernel<<<(H1 + 255) / 256, 256, 0, s>>>(dH1, n, H1, G + L.b1);
+    mg_colsum_kernel<<<(H1 + 31) / 32, 256, 0, s>>>(dH1, n, H1, G + L.b1);
     g = mg_gemm(dH1, H1, 1, P + L.w1, 1, H1, S, D, N, D, H1);
-    g.accumulate = 1; g.mask_kind = 0; g.mask_on_b = 2; g.D = D; g.Hout = H1;
+    g.accumulate = 1; g.mask = m0; g.mask_on_b = 2;
     if ((rc = mg_launch(g, s))) return rc;
     mg_copy_perm_kernel<<<eb, 256, 0, s>>>(S, T, n, D, rev, 0);  // back to the natural order
     FC_LAUNCH_CHECK("made_nll_grad backward");

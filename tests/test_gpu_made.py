@@ -139,6 +139,8 @@ GRAD_CASES = {
     "d32": (O.MadeSpec(32, 4, [40, 40]), 0.4, 64),
     "toy_d2": (O.MadeSpec(2, 8, [64, 64]), 0.3, 257),
     "d784": (O.MadeSpec(784, 2, [512, 512]), 0.3, 48),
+    "d50_splitk": (O.MadeSpec(50, 2, [40, 70]), 0.4, 1500),   # n >= 1024: split-K weight-gradient path
+    "d300_splitk": (O.MadeSpec(300, 2, [200, 260]), 0.3, 1100),
 }
 
 
