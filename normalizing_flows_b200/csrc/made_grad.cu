@@ -89,11 +89,13 @@ __global__ void __launch_bounds__(256) mg_sgemm_kernel(MgGemm g) {
       kbeg = lo & ~(int64_t)(kMgK - 1);
     }
   }
-  float acc[8][8];
+  // accumulators as packed pairs along j: one FFMA2 (fma.rn.f32x2) per two outputs — the 3-register scalar
+  // FFMA issues at half rate on sm_100, so the packed form is what reaches the FP32 roof
+  f2_t acc2[8][4];
 #pragma unroll
   for (int a = 0; a < 8; ++a)
 #pragma unroll
-    for (int b = 0; b < 8; ++b) acc[a][b] = 0.f;
+    for (int b = 0; b < 4; ++b) acc2[a][b] = f2_splat(0.f);
   const bool a_kfast = g.acs == 1, b_jfast = g.bcs == 1;
   float ra[4], rb[4];
   auto fetch = [&](int64_t k0) {
@@ -141,19 +143,26 @@ __global__ void __launch_bounds__(256) mg_sgemm_kernel(MgGemm g) {
     for (int k = 0; k < kMgK; ++k) {
       const float4 a0 = *reinterpret_cast<const float4*>(&As[buf][k][ty * 4]);
       const float4 a1 = *reinterpret_cast<const float4*>(&As[buf][k][64 + ty * 4]);
-      const float4 b0 = *reinterpret_cast<const float4*>(&Bs[buf][k][tx * 4]);
-      const float4 b1 = *reinterpret_cast<const float4*>(&Bs[buf][k][64 + tx * 4]);
+      const ulonglong2 b0 = *reinterpret_cast<const ulonglong2*>(&Bs[buf][k][tx * 4]);
+      const ulonglong2 b1 = *reinterpret_cast<const ulonglong2*>(&Bs[buf][k][64 + tx * 4]);
       const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
-      const float bv[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+      const f2_t bv[4] = {b0.x, b0.y, b1.x, b1.y};
 #pragma unroll
-      for (int a = 0; a < 8; ++a)
+      for (int a = 0; a < 8; ++a) {
+        const f2_t as = f2_splat(av[a]);
 #pragma unroll
-        for (int b = 0; b < 8; ++b) acc[a][b] = fmaf(av[a], bv[b], acc[a][b]);
+        for (int b = 0; b < 4; ++b) acc2[a][b] = f2_fma(as, bv[b], acc2[a][b]);
+      }
     }
     if (more) stash(buf ^ 1);
     __syncthreads();
     buf ^= 1;
   }
+  float acc[8][8];
+#pragma unroll
+  for (int a = 0; a < 8; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) f2_unpack(acc2[a][b], acc[a][2 * b], acc[a][2 * b + 1]);
 #pragma unroll
   for (int a = 0; a < 8; ++a) {
     const int gi = i0 + (a < 4 ? ty * 4 + a : 64 + ty * 4 + a - 4);
