@@ -20,18 +20,18 @@ __host__ __device__ __forceinline__ int mg_hdeg(int k, int H, int D) {
 // MADE mask of a Linear at (in i, out j) from degree tables (NULL table: inputs have degree i+1, outputs
 // (j mod D)+1 with a STRICT comparison — the [shift | log_scale] output Linear)
 struct MgMask {
-  const int* din;   // [k_in] or NULL
-  const int* dout;  // [n_out] or NULL
+  const int* din;   // [k_in] or NULL (inputs: degree i+1)
+  const int* dout;  // [n_out]; for the output Linear dout[j] = j mod D (strict "<" folded in as "<= dout")
   int D, on;        // on = 0: no mask
+  int wrap;         // 1: the output Linear, whose dout table restarts at column D
 };
 __device__ __forceinline__ int mg_din(const MgMask& m, int i) { return m.din ? m.din[i] : i + 1; }
-__device__ __forceinline__ int mg_dout(const MgMask& m, int j) { return m.dout ? m.dout[j] : (j % m.D); }  // strict -> "<= dout-1"
+__device__ __forceinline__ int mg_dout(const MgMask& m, int j) { return m.dout[j]; }
 __device__ __forceinline__ bool mg_mask(const MgMask& m, int i, int j) { return mg_din(m, i) <= mg_dout(m, j); }
 // largest dout over [j0, j1] (degree tables are non-decreasing; the output Linear wraps at D)
 __device__ __forceinline__ int mg_dout_max(const MgMask& m, int j0, int j1) {
-  if (m.dout) return m.dout[j1];
-  if (j0 / m.D != j1 / m.D) return m.D - 1;
-  return j1 % m.D;
+  if (m.wrap && j0 / m.D != j1 / m.D) return m.D - 1;
+  return m.dout[j1];
 }
 
 struct MgGemm {
@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(256) mg_sgemm_kernel(MgGemm g) {
     kend = lo;
   } else if (g.mask.on && g.mask_on_b == 2) {  // B = Wᵀ: in = j, out = k: outputs with degree below the tile's smallest input degree
     const int dmin = mg_din(g.mask, j0);
-    if (g.mask.dout) {
+    if (!g.mask.wrap) {
       int64_t lo = 0, hi = g.K;  // first k with dout(k) >= dmin
       while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if (g.mask.dout[mid] >= dmin) hi = mid; else lo = mid + 1; }
       kbeg = lo & ~(int64_t)(kMgK - 1);
@@ -98,22 +98,44 @@ __global__ void __launch_bounds__(256) mg_sgemm_kernel(MgGemm g) {
     for (int b = 0; b < 4; ++b) acc2[a][b] = f2_splat(0.f);
   const bool a_kfast = g.acs == 1, b_jfast = g.bcs == 1;
   float ra[4], rb[4];
+  // per-thread element coordinates and base pointers, hoisted out of the k loop
+  const float* ap[4]; const float* bp[4];
+  int ak[4], bk[4], bj[4];
+  bool aok[4], bok[4];
+#pragma unroll
+  for (int t = 0; t < 4; ++t) {
+    const int e = tid + t * 256;
+    int i, k;
+    if (a_kfast) { i = e >> 3; k = e & 7; } else { i = e & 127; k = e >> 7; }
+    ak[t] = k; aok[t] = i0 + i < g.M;
+    ap[t] = g.A + (int64_t)(i0 + i) * g.ars + (kbeg + k) * g.acs;
+    int j, kb;
+    if (b_jfast) { j = e & 127; kb = e >> 7; } else { j = e >> 3; kb = e & 7; }
+    bk[t] = kb; bj[t] = j0 + j; bok[t] = j0 + j < g.N;
+    bp[t] = g.B + (kbeg + kb) * g.brs + (int64_t)(j0 + j) * g.bcs;
+  }
+  const int64_t astep = (int64_t)kMgK * g.acs, bstep = (int64_t)kMgK * g.brs;
+  // smallest output degree / largest input degree of the tile's j range (the k range varies per step)
+  auto dout_min = [&](int lo, int hi) { return (g.mask.wrap && lo / g.mask.D != hi / g.mask.D) ? 0 : g.mask.dout[lo]; };
   auto fetch = [&](int64_t k0) {
+    const int64_t off = (k0 - kbeg) / kMgK;
+    bool need_mask = false;
+    if (g.mask.on && g.mask_on_b) {  // uniform: is any element of this k-block x j-range masked at all?
+      const int kl = (int)min(k0 + kMgK, kend) - 1;
+      if (g.mask_on_b == 1) need_mask = mg_din(g.mask, kl) > dout_min(j0, jl);
+      else need_mask = mg_din(g.mask, jl) > dout_min((int)k0, kl);
+    }
 #pragma unroll
     for (int t = 0; t < 4; ++t) {
-      const int e = tid + t * 256;
-      int i, k;
-      if (a_kfast) { i = e >> 3; k = e & 7; } else { i = e & 127; k = e >> 7; }
-      const int gi = i0 + i; const int64_t gk = k0 + k;
-      ra[t] = (gi < g.M && gk < kend) ? g.A[gi * g.ars + gk * g.acs] : 0.f;
-      int j, kb;
-      if (b_jfast) { j = e & 127; kb = e >> 7; } else { j = e >> 3; kb = e & 7; }
-      const int gj = j0 + j; const int64_t gkb = k0 + kb;
+      ra[t] = (aok[t] && k0 + ak[t] < kend) ? ap[t][off * astep] : 0.f;
       float bv = 0.f;
-      if (gj < g.N && gkb < kend) {
-        bv = g.B[gkb * g.brs + gj * g.bcs];
-        if (g.mask.on && g.mask_on_b == 1 && !mg_mask(g.mask, (int)gkb, gj)) bv = 0.f;
-        if (g.mask.on && g.mask_on_b == 2 && !mg_mask(g.mask, gj, (int)gkb)) bv = 0.f;
+      const int64_t gkb = k0 + bk[t];
+      if (bok[t] && gkb < kend) {
+        bv = bp[t][off * bstep];
+        if (need_mask) {
+          if (g.mask_on_b == 1 && !mg_mask(g.mask, (int)gkb, bj[t])) bv = 0.f;
+          if (g.mask_on_b == 2 && !mg_mask(g.mask, bj[t], (int)gkb)) bv = 0.f;
+        }
       }
       rb[t] = bv;
     }
@@ -212,6 +234,10 @@ static int mg_launch(const MgGemm& g, cudaStream_t s) {
 __global__ void mg_degree_kernel(int* __restrict__ deg, int H, int D) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k < H) deg[k] = mg_hdeg(k, H, D);
+}
+__global__ void mg_out_degree_kernel(int* __restrict__ deg, int D) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j < 2 * D) deg[j] = j % D;
 }
 
 // out[r, c] = in[r, rev ? D-1-c : c]
@@ -332,7 +358,7 @@ static bool mg_layout(const flowcuda_made_spec* sp, int64_t n, MgLayout& L) {
   L.off_dH2 = off; off = mg_al(off + (size_t)n * L.H2 * 4);
   L.off_dH1 = off; off = mg_al(off + (size_t)n * L.H1 * 4);
   L.off_sum = off; off = mg_al(off + 1024 * 8);
-  L.off_deg = off; off = mg_al(off + (size_t)(L.H1 + L.H2) * 4);
+  L.off_deg = off; off = mg_al(off + (size_t)(L.H1 + L.H2 + 2 * L.D) * 4);
   {
     size_t mx = (size_t)L.D * L.H1;
     if ((size_t)L.H1 * L.H2 > mx) mx = (size_t)L.H1 * L.H2;
@@ -383,7 +409,9 @@ static int mg_run(const flowcuda_made_spec* sp, const float* params, const float
   mg_degree_kernel<<<(H2 + 255) / 256, 256, 0, s>>>(deg2, H2, D);
   float* part = (float*)(ws + L.off_part);
   const int splits = n >= 1024 ? kMgSplits : 1;
-  const MgMask m0 = {nullptr, deg1, D, 1}, m1 = {deg1, deg2, D, 1}, m2 = {deg2, nullptr, D, 1};
+  int* deg3 = deg2 + H2;
+  mg_out_degree_kernel<<<(2 * D + 255) / 256, 256, 0, s>>>(deg3, D);
+  const MgMask m0 = {nullptr, deg1, D, 1, 0}, m1 = {deg1, deg2, D, 1, 0}, m2 = {deg2, deg3, D, 1, 1};
   int rc;
   FC_CUDA(cudaMemcpyAsync(S, x, (size_t)n * D * 4, cudaMemcpyDeviceToDevice, s));
   // ---- forward, data -> base: layer L-1 first
