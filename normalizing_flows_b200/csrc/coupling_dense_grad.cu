@@ -1,0 +1,275 @@
+// coupling_dense_grad.cu — row #7 for row #4 (and the C5 affine stacks): value_and_grad of
+// loss = -mean(Transformed.log_prob(x)) for distrax.MaskedCoupling flows of any event size — the training
+// step of src/maf_mnist.py:134-166 (conditioner Flatten -> MLP(512,512,512, relu, activate_final) ->
+// Linear(784*25) -> Reshape, inner bijector RationalQuadraticSpline, maf_mnist.py:34-89).
+// Hand-written FP32 reverse mode over stored activations; every product goes through the generic
+// deterministic SGEMM (mg_sgemm.cuh), the spline adjoints through rqs_grad.cuh.
+//   forward per flow layer (stored): v (layer input), h_1..h_nh, o = conditioner output [N, D*P]
+//   backward: per (sample, transformed dim) the inner bijector's adjoint gives dL/dx and dL/do; dims that
+//   pass through get dL/do = 0 and receive the conditioner's input gradient instead.
+#include "mg_sgemm.cuh"
+#include "rqs_grad.cuh"
+
+namespace flowcuda {
+
+struct CgLayout {
+  int D, nh, nlin, P, L, sizes[FLOWCUDA_MAX_HIDDEN_LAYERS + 2];
+  int64_t w_off[FLOWCUDA_MAX_HIDDEN_LAYERS + 1], b_off[FLOWCUDA_MAX_HIDDEN_LAYERS + 1], per_layer;
+  size_t act_h[FLOWCUDA_MAX_HIDDEN_LAYERS + 1];  // float offsets of h_i / o inside one layer's activation block
+  size_t per_layer_act;
+  size_t off_state, off_g, off_tmp, off_tmp2, off_ld, off_lp, off_dO, off_dh[2], off_sum, off_part, off_act, total;  // bytes
+  int hmax;
+};
+
+static size_t cg_al(size_t x) { return (x + 255) & ~(size_t)255; }
+
+static bool cg_layout(const flowcuda_coupling_spec* sp, int64_t n, CgLayout& L) {
+  if (!sp) return false;
+  if (sp->transform == FLOWCUDA_TRANSFORM_RQS) {
+    if (sp->num_bins != 8 && sp->num_bins != 12) return false;
+    L.P = 3 * sp->num_bins + 1;
+  } else if (sp->transform == FLOWCUDA_TRANSFORM_AFFINE) {
+    L.P = 2;
+  } else {
+    return false;
+  }
+  L.D = sp->event_dim; L.nh = sp->num_hidden; L.nlin = L.nh + 1; L.L = sp->num_layers;
+  if (L.nh < 1 || L.nh > FLOWCUDA_MAX_HIDDEN_LAYERS) return false;
+  L.sizes[0] = L.D;
+  L.hmax = 1;
+  for (int i = 0; i < L.nh; ++i) {
+    L.sizes[i + 1] = sp->hidden[i];
+    if (sp->hidden[i] > L.hmax) L.hmax = sp->hidden[i];
+  }
+  L.sizes[L.nh + 1] = L.D * L.P;
+  int64_t o = 0;
+  for (int i = 0; i < L.nlin; ++i) {
+    L.w_off[i] = o; o += (int64_t)L.sizes[i] * L.sizes[i + 1];
+    L.b_off[i] = o; o += L.sizes[i + 1];
+  }
+  L.per_layer = o;
+  size_t a = (size_t)n * L.D;  // v
+  for (int i = 0; i < L.nlin; ++i) { L.act_h[i] = a; a += (size_t)n * L.sizes[i + 1]; }
+  L.per_layer_act = a;
+  size_t off = 0;
+  L.off_state = off; off = cg_al(off + (size_t)n * L.D * 4);
+  L.off_g = off; off = cg_al(off + (size_t)n * L.D * 4);
+  L.off_tmp = off; off = cg_al(off + (size_t)n * L.D * 4);
+  L.off_tmp2 = off; off = cg_al(off + (size_t)n * L.D * 4);
+  L.off_ld = off; off = cg_al(off + (size_t)n * 4);
+  L.off_lp = off; off = cg_al(off + (size_t)n * 4);
+  L.off_dO = off; off = cg_al(off + (size_t)n * L.D * L.P * 4);
+  for (int j = 0; j < 2; ++j) { L.off_dh[j] = off; off = cg_al(off + (size_t)n * L.hmax * 4); }
+  L.off_sum = off; off = cg_al(off + 1024 * 8);
+  size_t mx = 0;
+  for (int i = 0; i < L.nlin; ++i) {
+    const size_t e = (size_t)L.sizes[i] * L.sizes[i + 1];
+    if (e > mx) mx = e;
+  }
+  L.off_part = off; off = cg_al(off + mx * 4 * kMgSplits);
+  L.off_act = off; off = cg_al(off + L.per_layer_act * 4 * (size_t)L.L);
+  L.total = off + 256;
+  return true;
+}
+
+// mx = v with the transformed dims (parity tp) zeroed: the conditioner's input
+__global__ void __launch_bounds__(256) cg_mask_input_kernel(const float* __restrict__ v, float* __restrict__ mx, int64_t N, int D,
+                                                           int tp) {
+  const int64_t tot = N * D;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < tot; i += (int64_t)gridDim.x * blockDim.x) {
+    const int d = (int)(i % D);
+    mx[i] = ((d & 1) == tp) ? 0.f : v[i];
+  }
+}
+
+// forward bijector on the transformed dims, one warp per row: out = y (pass-through dims copied),
+// ld[r] (+)= sum of the log-dets in lane order, then a fixed shuffle tree (deterministic)
+template <int K>
+__global__ void __launch_bounds__(256) cg_transform_fwd_kernel(const float* __restrict__ v, const float* __restrict__ o,
+                                                              float* __restrict__ out, float* __restrict__ ld, int64_t N, int D,
+                                                              int P, int tp, float lo, float hi, int first) {
+  const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (r >= N) return;
+  float s = 0.f;
+  for (int d = lane; d < D; d += 32) {
+    const float x = v[r * D + d];
+    float y = x;
+    if ((d & 1) == tp) {
+      const float* oo = o + (r * D + d) * (int64_t)P;
+      float l1;
+      if (K > 0) {
+        rqs_apply<false, K>([&](int i) { return oo[i]; }, K, lo, hi, x, y, l1);
+      } else {
+        affine_apply<false>(oo[0], oo[1], x, y, l1);
+      }
+      s += l1;
+    }
+    out[r * D + d] = y;
+  }
+  s = warp_sum(s);
+  if (lane == 0) ld[r] = first ? s : ld[r] + s;
+}
+
+// lp = base(z) + ld ; g = d(-mean lp)/dz
+__global__ void __launch_bounds__(256) cg_finish_kernel(const float* __restrict__ z, const float* __restrict__ ld,
+                                                       float* __restrict__ lp, float* __restrict__ g, int64_t N, int D, int base) {
+  const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (r >= N) return;
+  const float invn = 1.f / (float)N;
+  float s = 0.f;
+  for (int d = lane; d < D; d += 32) {
+    const float zz = z[r * D + d];
+    s += base_term(base, zz);
+    g[r * D + d] = base == FLOWCUDA_BASE_NORMAL ? zz * invn : 0.f;
+  }
+  s = warp_sum(s);
+  if (lane == 0) lp[r] = ld[r] + s;
+}
+
+// adjoint of the bijector: g (dL/d layer output) -> gin (dL/d layer input, bijector path only) and dO
+template <int K>
+__global__ void __launch_bounds__(128) cg_transform_bwd_kernel(const float* __restrict__ v, const float* __restrict__ o,
+                                                              const float* __restrict__ g, float* __restrict__ gin,
+                                                              float* __restrict__ dO, int64_t N, int D, int P, int tp, float lo,
+                                                              float hi) {
+  const int64_t tot = N * D;
+  const float ldbar = -1.f / (float)N;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < tot; i += (int64_t)gridDim.x * blockDim.x) {
+    const int d = (int)(i % D);
+    float* ob = dO + i * P;
+    if ((d & 1) != tp) {
+      gin[i] = g[i];
+      for (int p = 0; p < P; ++p) ob[p] = 0.f;
+      continue;
+    }
+    const float* oo = o + i * P;
+    float y, l1, xbar;
+    if (K > 0) {
+      float ov[3 * (K > 0 ? K : 1) + 1], obar[3 * (K > 0 ? K : 1) + 1];
+#pragma unroll
+      for (int p = 0; p < 3 * K + 1; ++p) ov[p] = oo[p];
+      rqs_fwd_bwd<(K > 0 ? K : 1)>(ov, lo, hi, v[i], g[i], ldbar, y, l1, xbar, obar);
+#pragma unroll
+      for (int p = 0; p < 3 * K + 1; ++p) ob[p] = obar[p];
+    } else {
+      float ov[2] = {oo[0], oo[1]}, obar[2];
+      affine_fwd_bwd(ov, v[i], g[i], ldbar, y, l1, xbar, obar);
+      ob[0] = obar[0];
+      ob[1] = obar[1];
+    }
+    gin[i] = xbar;
+  }
+}
+
+// gin[:, visible dims] += dmx[:, visible dims]
+__global__ void __launch_bounds__(256) cg_add_visible_kernel(const float* __restrict__ dmx, float* __restrict__ gin, int64_t N,
+                                                            int D, int tp) {
+  const int64_t tot = N * D;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < tot; i += (int64_t)gridDim.x * blockDim.x)
+    if ((int)(i % D & 1) != tp) gin[i] += dmx[i];
+}
+
+
+template <int K>
+static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const float* params, const float* x, int64_t n,
+                  float* loss, float* grad, uint8_t* ws, cudaStream_t s) {
+  const int D = L.D, P = L.P, N = (int)n, nh = L.nh;
+  float* S = (float*)(ws + L.off_state);
+  float* G = (float*)(ws + L.off_g);
+  float* MX = (float*)(ws + L.off_tmp);
+  float* DMX = (float*)(ws + L.off_tmp2);
+  float* LD = (float*)(ws + L.off_ld);
+  float* LP = (float*)(ws + L.off_lp);
+  float* dO = (float*)(ws + L.off_dO);
+  float* dH[2] = {(float*)(ws + L.off_dh[0]), (float*)(ws + L.off_dh[1])};
+  float* part = (float*)(ws + L.off_part);
+  float* act = (float*)(ws + L.off_act);
+  const int splits = n >= 1024 ? kMgSplits : 1;
+  const int eb = grid_for((int64_t)n * D, 256, 16), rb = (int)((n * 32 + 255) / 256);
+  auto V = [&](int l) { return act + (size_t)l * L.per_layer_act; };
+  auto H = [&](int l, int i) { return V(l) + L.act_h[i]; };  // i < nh: h_{i+1}; i == nh: o
+  int rc;
+  FC_CUDA(cudaMemcpyAsync(S, x, (size_t)n * D * 4, cudaMemcpyDeviceToDevice, s));
+  for (int it = 0; it < L.L; ++it) {  // data -> base: layer L-1 first (Inverse(Chain(layers)))
+    const int l = L.L - 1 - it, tp = l & 1;
+    const float* Pl = params + L.per_layer * l;
+    FC_CUDA(cudaMemcpyAsync(V(l), S, (size_t)n * D * 4, cudaMemcpyDeviceToDevice, s));
+    cg_mask_input_kernel<<<eb, 256, 0, s>>>(S, MX, n, D, tp);
+    const float* in = MX;
+    for (int i = 0; i < L.nlin; ++i) {
+      MgGemm g = mg_gemm(in, L.sizes[i], 1, Pl + L.w_off[i], L.sizes[i + 1], 1, H(l, i), L.sizes[i + 1], N, L.sizes[i + 1],
+                         L.sizes[i]);
+      g.bias = Pl + L.b_off[i];
+      g.relu = i < nh;
+      if ((rc = mg_launch(g, s))) return rc;
+      in = H(l, i);
+    }
+    cg_transform_fwd_kernel<K><<<rb, 256, 0, s>>>(V(l), H(l, nh), S, LD, n, D, P, tp, sp->range_min, sp->range_max, it == 0);
+    FC_LAUNCH_CHECK("coupling_nll_grad forward");
+  }
+  cg_finish_kernel<<<rb, 256, 0, s>>>(S, LD, LP, G, n, D, sp->base);
+  FC_LAUNCH_CHECK("cg_finish_kernel");
+  if ((rc = flowcuda_sum_scaled(LP, n, -1.0 / (double)n, loss, ws + L.off_sum, s))) return rc;
+  for (int l = 0; l < L.L; ++l) {  // backward: the layer applied last first
+    const int tp = l & 1;
+    const float* Pl = params + L.per_layer * l;
+    float* Gl = grad + L.per_layer * l;
+    cg_transform_bwd_kernel<K><<<grid_for((int64_t)n * D, 128, 32), 128, 0, s>>>(V(l), H(l, nh), G, S, dO, n, D, P, tp,
+                                                                                sp->range_min, sp->range_max);
+    FC_LAUNCH_CHECK("cg_transform_bwd_kernel");
+    cg_mask_input_kernel<<<eb, 256, 0, s>>>(V(l), MX, n, D, tp);
+    const float* dout = dO;
+    for (int i = nh; i >= 0; --i) {
+      const int kin = L.sizes[i], nout = L.sizes[i + 1];
+      const float* in = i == 0 ? MX : H(l, i - 1);
+      // dW_i = inᵀ · dout (split-K, fixed-order reduce), db_i = column sums
+      MgGemm g = mg_gemm(in, 1, kin, dout, nout, 1, Gl + L.w_off[i], nout, kin, nout, n);
+      g.splits = splits; g.part = part;
+      if ((rc = mg_launch(g, s))) return rc;
+      mg_colsum_kernel<<<(nout + 31) / 32, 256, 0, s>>>(dout, n, nout, Gl + L.b_off[i]);
+      // d in = dout · W_iᵀ (relu gate of the stored activation; the masked input has no gate)
+      float* din = i == 0 ? DMX : dH[i & 1];
+      g = mg_gemm(dout, nout, 1, Pl + L.w_off[i], 1, nout, din, kin, N, kin, nout);
+      if (i > 0) { g.gate = H(l, i - 1); g.ldg = kin; }
+      if ((rc = mg_launch(g, s))) return rc;
+      dout = din;
+    }
+    cg_add_visible_kernel<<<eb, 256, 0, s>>>(DMX, S, n, D, tp);
+    FC_LAUNCH_CHECK("coupling_nll_grad backward");
+    float* t = G; G = S; S = t;  // S held dL/d(layer input): it is the next layer's output gradient
+  }
+  return FLOWCUDA_OK;
+}
+
+bool coupling_dense_grad_supported(const flowcuda_coupling_spec* sp) {
+  CgLayout L;
+  return cg_layout(sp, 1, L);
+}
+
+size_t coupling_dense_grad_workspace_bytes(const flowcuda_coupling_spec* sp, int64_t n) {
+  CgLayout L;
+  if (!cg_layout(sp, n, L)) return 0;
+  return L.total;
+}
+
+int coupling_dense_grad_run(const flowcuda_coupling_spec* sp, const float* params, const float* x, int64_t n, float* loss,
+                            float* grad, void* workspace, size_t wsb, cudaStream_t s) {
+  CgLayout L;
+  if (!cg_layout(sp, n, L)) {
+    set_error("coupling_nll_grad: needs RQS with 8 or 12 bins or the per-dimension affine transform");
+    return FLOWCUDA_EUNSUPPORTED;
+  }
+  if (!workspace || wsb < L.total) {
+    set_error("coupling_nll_grad: workspace %zu < %zu bytes", wsb, L.total);
+    return FLOWCUDA_EWORKSPACE;
+  }
+  FC_REQUIRE(n < (1ll << 31) / (L.D * L.P > 0 ? 1 : 1), "coupling_nll_grad: n too large");
+  uint8_t* ws = (uint8_t*)(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
+  if (sp->transform == FLOWCUDA_TRANSFORM_AFFINE) return cg_run<0>(sp, L, params, x, n, loss, grad, ws, s);
+  if (sp->num_bins == 8) return cg_run<8>(sp, L, params, x, n, loss, grad, ws, s);
+  return cg_run<12>(sp, L, params, x, n, loss, grad, ws, s);
+}
+
+}  // namespace flowcuda

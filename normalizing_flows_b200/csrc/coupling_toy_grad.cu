@@ -291,9 +291,17 @@ static int tg_launch(const flowcuda_coupling_spec* sp, TgArgs a, int grid, cudaS
 
 using namespace flowcuda;
 
+namespace flowcuda {
+bool coupling_dense_grad_supported(const flowcuda_coupling_spec* sp);
+size_t coupling_dense_grad_workspace_bytes(const flowcuda_coupling_spec* sp, int64_t n);
+int coupling_dense_grad_run(const flowcuda_coupling_spec* sp, const float* params, const float* x, int64_t n, float* loss,
+                            float* grad, void* workspace, size_t wsb, cudaStream_t s);
+}
+
 extern "C" {
 
 size_t flowcuda_coupling_nll_grad_workspace_bytes(const flowcuda_coupling_spec* spec, int64_t n) {
+  if (spec && n >= 1 && !tg_supported(spec)) return coupling_dense_grad_workspace_bytes(spec, n);
   if (!tg_supported(spec) || n < 1) return 0;
   return (size_t)tg_grid(n) * (tg_pl(spec) * spec->num_layers + 1) * sizeof(float) + 256;
 }
@@ -301,9 +309,9 @@ size_t flowcuda_coupling_nll_grad_workspace_bytes(const flowcuda_coupling_spec* 
 int flowcuda_coupling_nll_grad(const flowcuda_coupling_spec* spec, const float* params, const float* x, int64_t n,
                                float* loss, float* grad, void* workspace, size_t workspace_bytes, void* stream) {
   FC_REQUIRE(spec && params && x && workspace, "coupling_nll_grad: NULL pointer");
-  if (!tg_supported(spec)) {
-    set_error("coupling_nll_grad: supported for event_dim 2 with two hidden layers <= 64 (toy flows)");
-    return FLOWCUDA_EUNSUPPORTED;
+  if (!tg_supported(spec)) {  // generic event size: stored-activation reverse mode (coupling_dense_grad.cu)
+    FC_REQUIRE(n >= 1 && loss && grad, "coupling_nll_grad: bad arguments");
+    return coupling_dense_grad_run(spec, params, x, n, loss, grad, workspace, workspace_bytes, (cudaStream_t)stream);
   }
   FC_REQUIRE(n >= 1, "coupling_nll_grad: n must be >= 1");
   FC_REQUIRE(((uintptr_t)x & 7) == 0, "coupling_nll_grad: x must be 8-byte aligned");
