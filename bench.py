@@ -216,7 +216,7 @@ class MafMade(Workload):
 
         return O.maf_log_prob(self._ospec(), self._p, x)
 
-    def train(self, dev, rank, world, dist, ops, K=5, batch=4096):
+    def train(self, dev, rank, world, dist, ops, K=5, batch=8192):
         """train samples/s: value_and_grad of -mean(log_prob) (hand-written FP32 reverse mode), gradient
         all-reduce across ranks (NCCL sum, the step's only exchange), fused Adam (maf_mnist.py:155-166)."""
         spec = self.model.bijector.spec()
@@ -652,13 +652,16 @@ def time_train(w, dev, rank, world, dist, ops, K=5, batch=1 << 18):
     """train samples/s: one step = value_and_grad of -mean(log_prob) over a batch (hand-written
     reverse mode), the gradient all-reduce across ranks (NCCL sum, only exchange of the step) and the
     fused Adam update (optax.adam, real_nvp_toy_densities.py:162-173).  Batch per GPU is fixed (weak)."""
-    if not isinstance(w, CouplingWorkload) or w._ospec().event_dim != 2:
+    if not isinstance(w, CouplingWorkload):
         return None
     from normalizing_flows_b200 import _lib
 
     sp = w._ospec()
+    if sp.event_dim != 2:
+        batch = 1024  # stored activations: 88 KB per sample and layer at the maf_mnist shape
     tr = {"affine_scalar": 0, "affine": 1, "rqs": 2}[sp.transform]
-    spec = ops.make_spec(2, sp.num_layers, sp.hidden, tr, sp.num_bins, sp.range_min, sp.range_max, _lib.BASE_NORMAL, 0)
+    spec = ops.make_spec(sp.event_dim, sp.num_layers, sp.hidden, tr, sp.num_bins, sp.range_min, sp.range_max,
+                         _lib.BASE_UNIFORM01 if sp.base == "uniform" else _lib.BASE_NORMAL, 0)
     p = w.model.params.clone()
     m, v = torch.zeros_like(p), torch.zeros_like(p)
     gen = torch.Generator().manual_seed(77 + rank)
