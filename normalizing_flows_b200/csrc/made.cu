@@ -272,7 +272,7 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 constexpr int kMsRing = 4, kMsPF = 3;
 
 template <int S, int T, int CH, int CD>
-__global__ void __launch_bounds__(T, 1) made_sample_kernel(MadeSample a) {
+__global__ void __launch_bounds__(T, S <= 4 ? 2 : 1) made_sample_kernel(MadeSample a) {
   extern __shared__ __align__(16) float sm[];
   const int D = a.D, H1 = a.H1, H2 = a.H2;
   constexpr int NC = 2 * CH + 2 * CD;  // ring components per thread and step
@@ -463,7 +463,7 @@ __global__ void __launch_bounds__(T, 1) made_sample_kernel(MadeSample a) {
   }
 }
 
-constexpr int kMsS = 8, kMsT = 512;
+constexpr int kMsS = 16, kMsT = 512;
 
 static int made_sample_run(const flowcuda_made_spec* sp, const float* params, const float* z, float* x, int64_t n,
                            cudaStream_t s) {
