@@ -241,6 +241,40 @@ int flowcuda_made_nll_grad(const flowcuda_made_spec* spec, const float* params, 
                            size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------------------
+ * §8f-2/3 — the data step on the device.  Every output is a pure function of
+ * (seed, element index): Philox4x32-10 with key = seed, counter = (index, stream tag), so a
+ * batch is reproducible, stateless and shardable by index range (`offset`).  The
+ * distributions are the reference's; the bit streams are not JAX's threefry.
+ * ---------------------------------------------------------------------------------- */
+#define FLOWCUDA_DENSITY_BANANA 0  /* src/densities/banana.py:31-41 */
+#define FLOWCUDA_DENSITY_ENERGY1 1 /* src/densities/energies.py:47-66 */
+#define FLOWCUDA_DENSITY_ENERGY2 2 /* src/densities/energies.py:69-82 */
+#define FLOWCUDA_DENSITY_ENERGY3 3 /* src/densities/energies.py:85-104 */
+#define FLOWCUDA_DENSITY_ENERGY4 4 /* src/densities/energies.py:107-127 */
+#define FLOWCUDA_DENSITY_BLOBS 5   /* src/densities/gaussian_blobs.py:34-59 */
+
+/* x[n,2] <- samples offset .. offset+n of the density's stream (replaces the host generators
+ * make_dataset_<kind>(seed, batch_size, num_batches)).  num_blobs / r: gaussian blobs only. */
+int flowcuda_density_sample(int kind, uint64_t seed, uint64_t offset, int num_blobs, float r,
+                            float* x, int64_t n, void* stream);
+
+/* out[i] = (bytes[i] + U[0,1)) / 256 — prepare_data of src/maf_mnist.py:101-106 without the
+ * host uniform draw; `offset` = index of bytes[0] in the stream (multiple of 16). */
+int flowcuda_dequantize_u8(const uint8_t* bytes, uint64_t seed, uint64_t offset, float* out,
+                           int64_t count, void* stream);
+
+/* Base noise for Transformed.sample(seed=...): N(0,1) (uniform = 0) or U[0,1) (uniform = 1);
+ * offset a multiple of 4. */
+int flowcuda_base_noise(int uniform, uint64_t seed, uint64_t offset, float* out, int64_t count,
+                        void* stream);
+
+/* §8f-4 — tutorial bijector OrthogonalProjection2D (src/rotation_flow.py:13-37, README.md:32-57):
+ * y[n,2] = x[n,2] @ R, R = [[cos,-sin],[sin,cos]]^T (inverse != 0: x @ R^T).  The reference returns
+ * the constant 1 as "log-det" (a bug; the true value is 0) — that choice lives in the host mirror. */
+int flowcuda_rotate2d(const float* x, float cos_theta, float sin_theta, int inverse, float* y,
+                      int64_t n, void* stream);
+
+/* ------------------------------------------------------------------------------------
  * Rows #7, #9 — loss reduction and optimiser steps.
  * ---------------------------------------------------------------------------------- */
 

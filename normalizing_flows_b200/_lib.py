@@ -88,6 +88,10 @@ SIGNATURES = {
     "flowcuda_made_sample": (_i, [_mspec, _p, _p, _p, _i64, _p]),
     "flowcuda_made_nll_grad_workspace_bytes": (_sz, [_mspec, _i64]),
     "flowcuda_made_nll_grad": (_i, [_mspec, _p, _p, _i64, _p, _p, _p, _sz, _p]),
+    "flowcuda_density_sample": (_i, [_i, _u64, _u64, _i, _f, _p, _i64, _p]),
+    "flowcuda_dequantize_u8": (_i, [_p, _u64, _u64, _p, _i64, _p]),
+    "flowcuda_base_noise": (_i, [_i, _u64, _u64, _p, _i64, _p]),
+    "flowcuda_rotate2d": (_i, [_p, _f, _f, _i, _p, _i64, _p]),
     "flowcuda_sum_scaled": (_i, [_p, _i64, _d, _p, _p, _p]),
     "flowcuda_sgd_step": (_i, [_p, _p, _i64, _f, _f, _p]),
     "flowcuda_adam_step": (_i, [_p, _p, _p, _p, _i64, _i64, _f, _f, _f, _f, _f, _p]),

@@ -98,6 +98,23 @@ __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ p, const 
   }
 }
 
+// ---- tutorial bijector: 2-D rotation (src/rotation_flow.py:13-37) -----------------------------
+// forward y = x @ R with R = [[c,-s],[s,c]]^T; inverse y = x @ R^T.  Two samples per thread (one 16-byte access).
+__global__ void __launch_bounds__(256) rotate2d_kernel(const float* __restrict__ x, float* __restrict__ y, int64_t n,
+                                                       float c, float s) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t pairs = n >> 1;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < pairs; i += stride) {
+    const float4 v = reinterpret_cast<const float4*>(x)[i];
+    reinterpret_cast<float4*>(y)[i] = make_float4(v.x * c - v.y * s, v.x * s + v.y * c, v.z * c - v.w * s, v.z * s + v.w * c);
+  }
+  if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+    const float a = x[2 * (n - 1)], b = x[2 * (n - 1) + 1];
+    y[2 * (n - 1)] = a * c - b * s;
+    y[2 * (n - 1) + 1] = a * s + b * c;
+  }
+}
+
 }  // namespace flowcuda
 
 using namespace flowcuda;
@@ -118,6 +135,16 @@ int flowcuda_sum_scaled(const float* v, int64_t n, double scale, float* out, voi
   FC_LAUNCH_CHECK("sum_stage1");
   sum_stage2<<<1, kSumThreads, 0, s>>>((const double*)workspace, nb, scale, out);
   FC_LAUNCH_CHECK("sum_stage2");
+  return FLOWCUDA_OK;
+}
+
+int flowcuda_rotate2d(const float* x, float cos_theta, float sin_theta, int inverse, float* y, int64_t n, void* stream) {
+  FC_REQUIRE(n >= 0 && ((x && y) || n == 0), "rotate2d: NULL pointer or negative n");
+  FC_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)y & 15) == 0, "rotate2d: buffers must be 16-byte aligned");
+  if (n == 0) return FLOWCUDA_OK;
+  rotate2d_kernel<<<grid_for(n > 1 ? n >> 1 : 1, 256), 256, 0, (cudaStream_t)stream>>>(x, y, n, cos_theta,
+                                                                                      inverse ? -sin_theta : sin_theta);
+  FC_LAUNCH_CHECK("rotate2d_kernel");
   return FLOWCUDA_OK;
 }
 

@@ -356,13 +356,29 @@ class Distribution:
         raise NotImplementedError
 
     def sample(self, *, seed, sample_shape=()) -> Array:
-        """`seed` is an int or a torch.Generator (JAX threefry keys cannot be reproduced:
-        parity is defined as same-base-noise-in -> same-sample-out)."""
+        """`seed` is an int (base noise from the library's own Philox kernel, csrc/densities.cu) or a
+        torch.Generator (JAX threefry keys cannot be reproduced: parity is defined as
+        same-base-noise-in -> same-sample-out)."""
         shape = (sample_shape,) if isinstance(sample_shape, int) else tuple(sample_shape)
         n = int(math.prod(shape)) if shape else 1
-        gen = seed if isinstance(seed, torch.Generator) else torch.Generator(device="cuda").manual_seed(int(seed))
+        gen = seed if isinstance(seed, torch.Generator) else _PhiloxSeed(int(seed))
         out = self._sample_n(gen, n)
         return out.reshape(*shape, *out.shape[1:])
+
+
+class _PhiloxSeed:
+    """An integer seed for ops.base_noise; `offset` advances so that successive draws do not overlap."""
+
+    def __init__(self, seed: int):
+        self.seed, self.offset = seed, 0
+
+
+def _draw(gen, shape, uniform: bool) -> Array:
+    if isinstance(gen, _PhiloxSeed):
+        out = ops.base_noise(shape, gen.seed, uniform=uniform, offset=gen.offset)
+        gen.offset += (out.numel() + 3) // 4 * 4
+        return out
+    return (torch.rand if uniform else torch.randn)(*shape, device="cuda", generator=gen)
 
 
 class Normal(Distribution):
@@ -373,7 +389,7 @@ class Normal(Distribution):
         self.standard = bool((self.loc == 0).all() and (self.scale == 1).all())
 
     def _sample_n(self, gen, n):
-        z = torch.randn(n, *self.batch_shape, device="cuda", generator=gen)
+        z = _draw(gen, (n, *self.batch_shape), uniform=False)
         return z if self.standard else z * self.scale.to(z.device) + self.loc.to(z.device)
 
 
@@ -385,7 +401,7 @@ class Uniform(Distribution):
         self.standard = bool((self.low == 0).all() and (self.high == 1).all())
 
     def _sample_n(self, gen, n):
-        u = torch.rand(n, *self.batch_shape, device="cuda", generator=gen)
+        u = _draw(gen, (n, *self.batch_shape), uniform=True)
         return u if self.standard else u * (self.high - self.low).to(u.device) + self.low.to(u.device)
 
 

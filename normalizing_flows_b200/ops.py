@@ -332,6 +332,62 @@ def adam_step(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor
                                          float(b2), float(eps), float(grad_scale), _stream()), "adam_step")
 
 
+# ---------------------------------------------------------------------------- data step (§8f-2, §8f-3)
+DENSITY_KINDS = {"banana": 0, "energy_1": 1, "energy_2": 2, "energy_3": 3, "energy_4": 4, "gaussian_blobs": 5}
+
+
+def density_sample(kind, seed: int, n: int, offset: int = 0, num_blobs: int = 8, r: float = 2.0,
+                   device=None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """x[n,2] = samples offset..offset+n of the density's Philox stream (csrc/densities.cu)."""
+    k = DENSITY_KINDS[kind] if isinstance(kind, str) else int(kind)
+    if out is None:
+        out = torch.empty(int(n), 2, device=device or "cuda", dtype=torch.float32)
+    _dev_check(out)
+    if out.numel() != 2 * int(n):
+        raise _lib.FlowCudaError("density_sample: out must hold n*2 floats")
+    with torch.cuda.device(out.device):
+        check(_lib.load().flowcuda_density_sample(k, int(seed) & (2 ** 64 - 1), int(offset), int(num_blobs), float(r),
+                                                  _ptr(out), int(n), _stream()), "density_sample")
+    return out
+
+
+def dequantize_u8(bytes_: torch.Tensor, seed: int, offset: int = 0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """(uint8 + U[0,1)) / 256 on the device (prepare_data, src/maf_mnist.py:101-106)."""
+    if not bytes_.is_cuda or bytes_.dtype != torch.uint8 or not bytes_.is_contiguous():
+        raise _lib.FlowCudaError("dequantize_u8 needs a contiguous CUDA uint8 tensor (there is no CPU path)")
+    if out is None:
+        out = torch.empty(bytes_.shape, device=bytes_.device, dtype=torch.float32)
+    _dev_check(out)
+    if out.numel() != bytes_.numel():
+        raise _lib.FlowCudaError("dequantize_u8: out must have as many elements as the input")
+    with torch.cuda.device(out.device):
+        check(_lib.load().flowcuda_dequantize_u8(_ptr(bytes_), int(seed) & (2 ** 64 - 1), int(offset), _ptr(out),
+                                                 bytes_.numel(), _stream()), "dequantize_u8")
+    return out
+
+
+def base_noise(shape, seed: int, uniform: bool = False, offset: int = 0, device=None) -> torch.Tensor:
+    """N(0,1) (or U[0,1)) base noise for Transformed.sample(seed=...), generated on the device."""
+    out = torch.empty(tuple(shape), device=device or "cuda", dtype=torch.float32)
+    _dev_check(out)
+    with torch.cuda.device(out.device):
+        check(_lib.load().flowcuda_base_noise(1 if uniform else 0, int(seed) & (2 ** 64 - 1), int(offset), _ptr(out),
+                                              out.numel(), _stream()), "base_noise")
+    return out
+
+
+def rotate2d(x: torch.Tensor, cos_theta: float, sin_theta: float, inverse: bool = False) -> torch.Tensor:
+    """y = x @ R (R = [[c,-s],[s,c]]^T) or x @ R^T, x[...,2] (src/rotation_flow.py:23-27)."""
+    if x.shape[-1] != 2:
+        raise _lib.FlowCudaError(f"rotate2d needs a trailing dimension of 2, got {tuple(x.shape)}")
+    xf = _f32(x)
+    _dev_check(xf)
+    y = torch.empty_like(xf)
+    check(_lib.load().flowcuda_rotate2d(_ptr(xf), float(cos_theta), float(sin_theta), 1 if inverse else 0, _ptr(y),
+                                        xf.numel() // 2, _stream()), "rotate2d")
+    return y
+
+
 # ---------------------------------------------------------------------------- diagnostics
 def selftest_umma(a: torch.Tensor, w: torch.Tensor, mode: int, want_unaligned: bool = False):
     """d[128,n] = a[128,k] @ w[k,n] through the tcgen05 primitives (mode 0 tf32x3, 1 bf16x3, 2 tf32, 3 bf16)."""

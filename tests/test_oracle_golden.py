@@ -115,3 +115,64 @@ def test_made_autoregressive_property_and_round_trip():
     # change of variables: log p(x) = log N(z) - sum alpha; check through a jacobian
     Jx = torch.autograd.functional.jacobian(lambda v: O.maf_sample(spec, p, v[None])[0], z[0])
     np.testing.assert_allclose(lp[0].item(), (O.log_prob_N01(z[:1])[0] - torch.linalg.slogdet(Jx)[1]).item(), atol=1e-9)
+
+
+# ---- device data step: Philox restatement (oracle/philox_oracle.py) ------------------------------
+def test_philox4x32_10_known_answers():
+    """Random123 kat_vectors for philox4x32-10 (Salmon et al. 2011): zero, all-ones and pi-digit inputs."""
+    from oracle import philox_oracle as P
+
+    kat = [
+        ((0, 0, 0, 0), (0, 0), (0x6627E8D5, 0xE169C58D, 0xBC57AC4C, 0x9B00DBD8)),
+        ((0xFFFFFFFF,) * 4, (0xFFFFFFFF,) * 2, (0x408F276D, 0x41C83B0E, 0xA20BC7C6, 0x6D5451FD)),
+        ((0x243F6A88, 0x85A308D3, 0x13198A2E, 0x03707344), (0xA4093822, 0x299F31D0),
+         (0xD16CFE09, 0x94FDCCEB, 0x5001E420, 0x24126EA1)),
+    ]
+    for ctr, key, want in kat:
+        got = tuple(int(x) for x in P.philox4x32_10(ctr, key))
+        assert got == want, (ctr, key, [hex(g) for g in got])
+
+
+def test_density_streams_follow_the_reference_definitions():
+    """Moments of the restated samplers against the closed forms implied by src/densities/*.py; the
+    stream is a pure function of (seed, index): a batch taken at an offset equals that slice."""
+    from oracle import philox_oracle as P
+
+    n = 400_000
+    x = P.density_sample(P.BANANA, 11, 0, n)       # x2~N(0,sqrt3), x1~N(x2^2/3-2, sqrt3/2)
+    assert abs(x[:, 1].mean()) < 0.02 and abs(x[:, 1].var() - 3.0) < 0.05
+    assert abs(x[:, 0].mean() + 1.0) < 0.02 and abs(x[:, 0].var() - 2.75) < 0.06
+    x = P.density_sample(P.ENERGY1, 11, 0, n)      # x2~N(0,2); x1 = +-(2 - x2^2/32) + 0.3 n
+    assert abs(x[:, 1].var() - 4.0) < 0.06 and abs(x[:, 0].mean()) < 0.02
+    assert abs(np.abs(x[:, 0]).mean() - (2 - 4 / 32)) < 0.02
+    x = P.density_sample(P.ENERGY2, 11, 0, n)      # x1~U(+-1.5pi), x2~N(sin(pi x1/2), .5)
+    assert x[:, 0].min() >= -1.5 * np.pi and x[:, 0].max() < 1.5 * np.pi
+    assert abs((x[:, 1] - np.sin(np.pi * x[:, 0] / 2)).var() - 0.25) < 0.01
+    for kind, bump in ((P.ENERGY3, lambda z: -P.w2(z)), (P.ENERGY4, P.w3)):
+        x = P.density_sample(kind, 11, 0, n)
+        res = x[:, 1] - P.w1(x[:, 0])              # mixture of N(0,.5) and N(bump(x1), .5)
+        want = 0.5 * bump(x[:, 0]).mean()
+        assert abs(res.mean() - want) < 0.02
+    x = P.density_sample(P.BLOBS, 11, 0, n)        # 8 blobs on a circle of radius 2, sigma .3
+    assert abs(x.mean(0)).max() < 0.02 and abs(x.var(0) - (2.0 + 0.09)).max() < 0.05
+    ang = np.round(np.arctan2(x[:, 1], x[:, 0]) / (np.pi / 4)).astype(int) % 8
+    assert np.abs(np.bincount(ang, minlength=8) / n - 0.125).max() < 0.01
+    a = P.density_sample(P.ENERGY4, 5, 0, 300)
+    b = P.density_sample(P.ENERGY4, 5, 100, 50)
+    assert np.array_equal(a[100:150], b)
+
+
+def test_dequantize_and_base_noise_restatement():
+    from oracle import philox_oracle as P
+
+    b = np.random.default_rng(0).integers(0, 256, size=(7, 28, 28, 1), dtype=np.uint8)
+    y = P.dequantize_u8(b, seed=9)
+    assert y.dtype == np.float32 and y.shape == b.shape
+    assert np.array_equal(np.floor(y.astype(np.float64) * 256).clip(0, 255).astype(np.uint8)[y < 1], b[y < 1])
+    assert (y >= 0).all() and (y <= 1).all()
+    assert np.array_equal(P.dequantize_u8(b.reshape(-1)[32:96], 9, offset=32), y.reshape(-1)[32:96])
+    z = P.base_noise(0, 3, 0, 200_001)
+    assert abs(z.mean()) < 0.01 and abs(z.var() - 1) < 0.02
+    u = P.base_noise(1, 3, 0, 200_001)
+    assert u.min() >= 0 and u.max() < 1 and abs(u.mean() - 0.5) < 0.005
+    assert np.array_equal(P.base_noise(0, 3, 8, 40), z[8:48])

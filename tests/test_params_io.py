@@ -1,0 +1,75 @@
+"""Host-side parameter interchange (normalizing_flows_b200/params_io.py): the
+haiku-named tree and the nested-list format map onto the flat buffer the kernels read, in the
+oracle's own flatten order."""
+import numpy as np
+import pytest
+import torch
+
+from normalizing_flows_b200 import params_io as io
+from oracle import flows_oracle as O
+
+
+def _tree_from_layers(params):
+    names = io.haiku_module_names(len(params), len(params[0]) - 1)
+    return {mod: {"w": W.numpy(), "b": b.numpy()} for layer, mods in zip(params, names) for (W, b), mod in zip(layer, mods)}
+
+
+def test_haiku_names_follow_creation_order():
+    names = io.haiku_module_names(3, 2)
+    assert names[0] == ["mlp/~/linear_0", "mlp/~/linear_1", "linear"]
+    assert names[1] == ["mlp_1/~/linear_0", "mlp_1/~/linear_1", "linear_1"]
+    assert names[2][-1] == "linear_2"
+
+
+@pytest.mark.parametrize("spec", [O.RQS_TOY, O.REAL_NVP_TOY, O.CouplingSpec(16, 3, [8, 8, 8], "rqs", 8, 0.0, 1.0, "uniform")])
+def test_haiku_tree_and_npz_round_trip(tmp_path, spec):
+    params = O.init_coupling_params(spec, seed=2, dtype=torch.float32)
+    flat_ref = O.flatten_layers(params)
+    tree = _tree_from_layers(params)
+    args = (spec.num_layers, spec.event_dim, spec.hidden, spec.cond_out)
+    flat = io.haiku_to_flat(tree, *args)
+    assert flat.dtype == torch.float32 and torch.equal(flat, flat_ref)
+    back = io.flat_to_haiku(flat, *args)
+    assert sorted(back) == sorted(tree)
+    for mod in tree:
+        assert np.array_equal(back[mod]["w"], tree[mod]["w"]) and np.array_equal(back[mod]["b"], tree[mod]["b"])
+    path = str(tmp_path / "params.npz")
+    io.save_haiku_npz(path, flat, *args)
+    with np.load(path) as z:
+        assert "mlp/~/linear_0/w" in z.files and f"linear_{spec.num_layers - 1}/b" in z.files
+    assert torch.equal(io.load_haiku_npz(path, *args), flat_ref)
+
+
+def test_bad_trees_fail_loudly(tmp_path):
+    spec = O.REAL_NVP_TOY
+    params = O.init_coupling_params(spec, seed=2, dtype=torch.float32)
+    args = (spec.num_layers, spec.event_dim, spec.hidden, spec.cond_out)
+    tree = _tree_from_layers(params)
+    missing = dict(tree)
+    del missing["mlp_3/~/linear_1"]
+    with pytest.raises(KeyError):
+        io.haiku_to_flat(missing, *args)
+    wrong = dict(tree)
+    wrong["linear"] = {"w": np.zeros((64, 3), np.float32), "b": np.zeros(3, np.float32)}
+    with pytest.raises(ValueError):
+        io.haiku_to_flat(wrong, *args)
+    with pytest.raises(ValueError):
+        io.flat_to_haiku(torch.zeros(5), *args)
+    path = str(tmp_path / "bad.npz")
+    np.savez(path, weights=np.zeros(3))
+    with pytest.raises(ValueError):
+        io.load_haiku_npz(path, *args)
+
+
+def test_nested_lists_of_the_hand_rolled_real_nvp():
+    """params[layer][sublayer] = [W, b] (src/real_nvp.py:188-195): 8 layers of [1,4,2] = 144 floats."""
+    params, _flips = O.init_nvp_chain_like(8, hidden=4, seed=534, dtype=torch.float32)
+    nested = [[[W.numpy(), b.numpy()] for (W, b) in layer] for layer in params]
+    flat = io.nested_to_flat(nested)
+    assert flat.numel() == 144 and torch.equal(flat, O.flatten_layers(params))
+    back = io.flat_to_nested(flat, 8, [1, 4, 2])
+    for la, lb in zip(nested, back):
+        for (Wa, ba), (Wb, bb) in zip(la, lb):
+            assert np.array_equal(Wa, Wb) and np.array_equal(ba, bb)
+    with pytest.raises(ValueError):
+        io.flat_to_nested(flat[:-1], 8, [1, 4, 2])
