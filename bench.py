@@ -174,6 +174,46 @@ class MafMnist(CouplingWorkload):
     cpu_sample = 256
 
 
+class Deep16Nvp(CouplingWorkload):
+    """configs[4]: deep per-dimension affine coupling stack at D=784."""
+    name = "deep16_nvp"
+    desc = ("configs[4]: 16x MaskedCoupling + per-dimension affine (shift, log_scale), MLP 784->512->512->1568, Normal base "
+            "(SURVEY C5); synthetic dequantised 28x28, 16384 samples/GPU, log_prob (+ sampling)")
+    data = staticmethod(mnist_like)
+    transform = "affine"
+    n = 16384
+    bytes_per_sample = 3140
+    # needed-only: visible half of the input rows, transformed half of the output columns
+    flops_per_sample = 16 * 2 * (392 * 512 + 512 * 512 + 512 * 784)
+    bound = "tensor"
+    launches_per_step = 16 * 4 + 1
+    tc_precision = 3
+    tc_launches = 3 + 16 * 5 + 1  # weight packs + per layer (pack_x, 3 GEMMs, log-det accumulate) + finish
+    tc_dtype = "bf16x3 (fp32 accumulate)"
+    cpu_sample = 512
+
+    def _ospec(self):
+        from oracle import flows_oracle as O
+
+        return O.CouplingSpec(784, 16, [512, 512], "affine")
+
+    def sampling(self, dev, K=5):
+        """Transformed.sample with the base noise resident: one forward pass of the stack (couplings invert in closed form)."""
+        n = self.n
+        z = torch.randn(n, 784, device=dev, generator=torch.Generator(device=dev).manual_seed(5))
+        for _ in range(2):
+            self.model.sample_from_noise(z)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(K):
+            x = self.model.sample_from_noise(z)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / K
+        return {"value": n / (ms * 1e-3), "unit": "samples/s", "samples_per_step_per_gpu": n, "ms_per_step": ms,
+                "finite": bool(torch.isfinite(x).all().item())}
+
+
 class MafMade(Workload):
     """Row #8: the MADE-conditioned MAF north_star names for the MNIST-shaped configs."""
     name = "maf_made"
@@ -183,13 +223,15 @@ class MafMade(Workload):
     bytes_per_sample = 3140
     bound = "tensor"
     dtype = "bf16x3 (fp32 accumulate)"
+    precision = "tc"
+    layers = 8
     launches_per_step = 3 + 8 * 5 + 1  # weight packs + per layer (pack_x, 3 GEMMs, log-det accumulate) + finish
     cpu_sample = 1024
 
     def _ospec(self):
         from oracle import flows_oracle as O
 
-        return O.MadeSpec(784, 8, [512, 512])
+        return O.MadeSpec(784, self.layers, [512, 512])
 
     @property
     def flops_per_sample(self):
@@ -271,6 +313,15 @@ class MafMade(Workload):
                 "finite": bool(torch.isfinite(x).all().item())}
 
 
+class Deep16Made(MafMade):
+    name = "deep16_made"
+    desc = ("configs[4]: 16x MADE-affine MAF at D=784 (SURVEY C5), masked MLP 784->512->512->1568; synthetic dequantised 28x28, "
+            "16384 samples/GPU, log_prob (+ sequential sampling)")
+    layers = 16
+    launches_per_step = 3 + 16 * 5 + 1
+    cpu_sample = 512
+
+
 class RealNvpHand(Workload):
     name = "realnvp_hand"
     desc = "hand-rolled Real NVP chain, 8 layers [1,4,2] leaky_relu (src/real_nvp.py); banana, 2^22 samples/GPU, log_prob"
@@ -331,7 +382,7 @@ class Bernstein(Workload):
         return O.bernstein_forward_and_log_det(O.constrain_thetas(self.raw), x)[1]
 
 
-WORKLOADS = {w.name: w for w in (MafToy, RealNvpToy, MafMnist, MafMade, RealNvpHand, Bernstein)}
+WORKLOADS = {w.name: w for w in (MafToy, RealNvpToy, MafMnist, MafMade, Deep16Nvp, Deep16Made, RealNvpHand, Bernstein)}
 
 
 def _lib_ws(ops, spec, n):

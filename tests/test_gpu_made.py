@@ -181,3 +181,18 @@ def test_made_nll_grad_matches_float64_autograd(case):
             assert (got[masks[mi] == 0] == 0).all()
             mi += 1
     assert off == g.numel()
+
+
+def test_deep16_made_stack_d784():
+    """configs[4] / SURVEY C5: all 16 MADE layers at D=784, H=512: |log_prob - float64 oracle| <= 1e-3 absolute."""
+    from normalizing_flows_b200 import ops
+
+    ospec = O.MadeSpec(784, 16, [512, 512])
+    params = O.init_made_params(ospec, seed=9, scale=0.1)
+    flat = G(O.flatten_layers(params))
+    gen = torch.Generator().manual_seed(0)
+    x = ((torch.randint(0, 256, (96, 784), generator=gen).double() + torch.rand(96, 784, generator=gen, dtype=torch.float64)) / 256).float()
+    lp, _, _ = ops.made_log_prob(_spec(ops, ospec), flat, x.cuda())
+    ref = O.maf_log_prob(ospec, params, x.double()).numpy()
+    err = np.abs(lp.double().cpu().numpy() - ref).max()
+    assert err <= 1e-3, err
