@@ -261,7 +261,10 @@ class MafMade(Workload):
     def train(self, dev, rank, world, dist, ops, K=5, batch=8192):
         """train samples/s: value_and_grad of -mean(log_prob) (hand-written FP32 reverse mode), gradient
         all-reduce across ranks (NCCL sum, the step's only exchange), fused Adam (maf_mnist.py:155-166)."""
-        spec = self.model.bijector.spec()
+        from normalizing_flows_b200 import _lib
+
+        sp = self._ospec()
+        spec = ops.make_made_spec(sp.event_dim, sp.num_layers, sp.hidden, precision=_lib.PRECISION_BF16X3)
         p = self.model.params.clone()
         m, v = torch.zeros_like(p), torch.zeros_like(p)
         gen = torch.Generator().manual_seed(77 + rank)
@@ -294,7 +297,8 @@ class MafMade(Workload):
             ms = t.item()
         return {"value": batch * world * K / (ms * 1e-3), "unit": "samples/s", "batch_per_gpu": batch, "steps": K,
                 "ms_per_step": ms / K, "final_loss": float(loss.item()), "optimizer": "adam(1e-4)",
-                "grad_allreduce_bytes": int(p.numel() * 4) if dist is not None else 0, "precision": "fp32"}
+                "grad_allreduce_bytes": int(p.numel() * 4) if dist is not None else 0,
+                "precision": "bf16x3 GEMMs (fp32 accumulate, fp32 stored activations)"}
 
     def sampling(self, dev, K=3):
         """Sequential sampling (persistent kernel over the D positions), base noise resident in HBM."""
@@ -711,8 +715,10 @@ def time_train(w, dev, rank, world, dist, ops, K=5, batch=1 << 18):
     if sp.event_dim != 2:
         batch = 1024  # stored activations: 88 KB per sample and layer at the maf_mnist shape
     tr = {"affine_scalar": 0, "affine": 1, "rqs": 2}[sp.transform]
+    tc = sp.event_dim != 2  # wide conditioners: reverse-mode GEMMs on tcgen05 (mgtc.cuh); D=2: fused FP32 kernels
     spec = ops.make_spec(sp.event_dim, sp.num_layers, sp.hidden, tr, sp.num_bins, sp.range_min, sp.range_max,
-                         _lib.BASE_UNIFORM01 if sp.base == "uniform" else _lib.BASE_NORMAL, 0)
+                         _lib.BASE_UNIFORM01 if sp.base == "uniform" else _lib.BASE_NORMAL,
+                         _lib.PRECISION_BF16X3 if tc else 0)
     p = w.model.params.clone()
     m, v = torch.zeros_like(p), torch.zeros_like(p)
     gen = torch.Generator().manual_seed(77 + rank)
@@ -743,7 +749,8 @@ def time_train(w, dev, rank, world, dist, ops, K=5, batch=1 << 18):
         ms = t.item()
     return {"value": batch * world * K / (ms * 1e-3), "unit": "samples/s", "batch_per_gpu": batch, "steps": K,
             "ms_per_step": ms / K, "final_loss": float(loss.item()), "optimizer": "adam(1e-4)",
-            "grad_allreduce_bytes": int(p.numel() * 4) if dist is not None else 0, "precision": "fp32"}
+            "grad_allreduce_bytes": int(p.numel() * 4) if dist is not None else 0,
+            "precision": "bf16x3 GEMMs (fp32 accumulate, fp32 stored activations)" if tc else "fp32"}
 
 
 def time_e2e(w, dev, host, dist, world, K):

@@ -210,7 +210,7 @@ typedef struct flowcuda_made_spec {
   int32_t num_hidden;  /* hidden Linears of each MADE */
   int32_t hidden[FLOWCUDA_MAX_HIDDEN_LAYERS];
   int32_t base;        /* FLOWCUDA_BASE_* */
-  int32_t reserved;
+  int32_t precision;   /* reverse mode (made_nll_grad): FLOWCUDA_PRECISION_FP32 or FLOWCUDA_PRECISION_BF16X3 */
 } flowcuda_made_spec;
 
 int64_t flowcuda_made_param_count(const flowcuda_made_spec* spec);

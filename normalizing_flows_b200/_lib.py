@@ -47,7 +47,7 @@ class MadeSpec(C.Structure):
         ("num_hidden", C.c_int32),
         ("hidden", C.c_int32 * MAX_HIDDEN_LAYERS),
         ("base", C.c_int32),
-        ("reserved", C.c_int32),
+        ("precision", C.c_int32),
     ]
 
 

@@ -7,7 +7,7 @@
 //   forward per flow layer (stored): v (layer input), h_1..h_nh, o = conditioner output [N, D*P]
 //   backward: per (sample, transformed dim) the inner bijector's adjoint gives dL/dx and dL/do; dims that
 //   pass through get dL/do = 0 and receive the conditioner's input gradient instead.
-#include "mg_sgemm.cuh"
+#include "mgtc.cuh"
 #include "rqs_grad.cuh"
 
 namespace flowcuda {
@@ -19,6 +19,8 @@ struct CgLayout {
   size_t per_layer_act;
   size_t off_state, off_g, off_tmp, off_tmp2, off_ld, off_lp, off_dO, off_dh[2], off_sum, off_part, off_act, total;  // bytes
   int hmax;
+  int tc;  // tensor-core engine (spec->precision == BF16X3)
+  size_t off_aimg, off_bimg, a_bytes, b_bytes, part_floats;
 };
 
 static size_t cg_al(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -66,7 +68,28 @@ static bool cg_layout(const flowcuda_coupling_spec* sp, int64_t n, CgLayout& L) 
     const size_t e = (size_t)L.sizes[i] * L.sizes[i + 1];
     if (e > mx) mx = e;
   }
-  L.off_part = off; off = cg_al(off + mx * 4 * kMgSplits);
+  L.tc = sp->precision == FLOWCUDA_PRECISION_BF16X3;
+  L.part_floats = mx * (L.tc ? kMgTcSplits : kMgSplits);
+  {
+    size_t wmax = 0;  // the column sums borrow the buffer: kMgColSlices doubles per column
+    for (int i = 0; i <= L.nlin; ++i) if ((size_t)L.sizes[i] > wmax) wmax = L.sizes[i];
+    if (L.part_floats < 2 * kMgColSlices * wmax) L.part_floats = 2 * kMgColSlices * wmax;
+  }
+  L.off_part = off; off = cg_al(off + L.part_floats * 4);
+  L.off_aimg = L.off_bimg = off; L.a_bytes = L.b_bytes = 0;
+  if (L.tc) {
+    auto upd = [&](int64_t am, int64_t ak, int64_t bn, int64_t bk) {
+      if (mgtc_a_bytes(am, ak) > L.a_bytes) L.a_bytes = mgtc_a_bytes(am, ak);
+      if (mgtc_b_bytes(bn, bk) > L.b_bytes) L.b_bytes = mgtc_b_bytes(bn, bk);
+    };
+    for (int i = 0; i < L.nlin; ++i) {
+      upd(n, L.sizes[i], L.sizes[i + 1], L.sizes[i]);      // forward
+      upd(L.sizes[i], n, L.sizes[i + 1], n);               // weight gradient
+      upd(n, L.sizes[i + 1], L.sizes[i], L.sizes[i + 1]);  // input gradient
+    }
+    L.off_aimg = off; off = cg_al(off + L.a_bytes);
+    L.off_bimg = off; off = cg_al(off + L.b_bytes);
+  }
   L.off_act = off; off = cg_al(off + L.per_layer_act * 4 * (size_t)L.L);
   L.total = off + 256;
   return true;
@@ -191,6 +214,8 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
   auto V = [&](int l) { return act + (size_t)l * L.per_layer_act; };
   auto H = [&](int l, int i) { return V(l) + L.act_h[i]; };  // i < nh: h_{i+1}; i == nh: o
   int rc;
+  const MgTcScratch sc = {ws + L.off_aimg, L.a_bytes, ws + L.off_bimg, L.b_bytes, part, L.part_floats};
+  auto mg_launch = [&](const MgGemm& g, cudaStream_t st) { return L.tc ? mgtc_launch(g, sc, st) : flowcuda::mg_launch(g, st); };
   FC_CUDA(cudaMemcpyAsync(S, x, (size_t)n * D * 4, cudaMemcpyDeviceToDevice, s));
   for (int it = 0; it < L.L; ++it) {  // data -> base: layer L-1 first (Inverse(Chain(layers)))
     const int l = L.L - 1 - it, tp = l & 1;
@@ -228,7 +253,7 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
       MgGemm g = mg_gemm(in, 1, kin, dout, nout, 1, Gl + L.w_off[i], nout, kin, nout, n);
       g.splits = splits; g.part = part;
       if ((rc = mg_launch(g, s))) return rc;
-      mg_colsum_kernel<<<(nout + 31) / 32, 256, 0, s>>>(dout, n, nout, Gl + L.b_off[i]);
+      if ((rc = mg_colsum(dout, n, nout, Gl + L.b_off[i], part, s))) return rc;
       // d in = dout · W_iᵀ (relu gate of the stored activation; the masked input has no gate)
       float* din = i == 0 ? DMX : dH[i & 1];
       g = mg_gemm(dout, nout, 1, Pl + L.w_off[i], 1, nout, din, kin, N, kin, nout);

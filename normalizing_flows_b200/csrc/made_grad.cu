@@ -6,9 +6,10 @@
 //   backward (per layer): dmu = -du·e^-alpha, dalpha = -du·u + 1/N, dx = du·e^-alpha + dh1·W1ᵀ,
 //            dW_i = mask_i ⊙ (inᵀ·dout), db_i = colsum(dout), relu masks from the stored activations.
 // Every product runs through ONE generic tiled SGEMM (strided operands, fixed-order K loop, no split-K
-// atomics), so gradients are bit-reproducible run to run.  The tensor-core density path (made.cu) is
-// not used here: training needs the stored FP32 activations.
-#include "mg_sgemm.cuh"
+// atomics), so gradients are bit-reproducible run to run.  spec->precision selects the engine behind that
+// descriptor: FP32 CUDA cores (mg_sgemm.cuh) or tcgen05 bf16x3 (mgtc.cuh); the stored activations are FP32
+// either way.
+#include "mgtc.cuh"
 
 namespace flowcuda {
 
@@ -90,6 +91,8 @@ struct MgLayout {
   int64_t w1, b1, w2, b2, w3, b3, per_layer;
   size_t per_layer_act;  // floats of stored activations per layer
   size_t off_state, off_tmp, off_ld, off_lp, off_dO, off_dH2, off_dH1, off_sum, off_deg, off_part, off_act, total;  // bytes
+  int tc;                       // tensor-core engine
+  size_t off_aimg, off_bimg, a_bytes, b_bytes, part_floats;
 };
 
 static size_t mg_al(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -117,7 +120,27 @@ static bool mg_layout(const flowcuda_made_spec* sp, int64_t n, MgLayout& L) {
     size_t mx = (size_t)L.D * L.H1;
     if ((size_t)L.H1 * L.H2 > mx) mx = (size_t)L.H1 * L.H2;
     if ((size_t)L.H2 * 2 * L.D > mx) mx = (size_t)L.H2 * 2 * L.D;
-    L.off_part = off; off = mg_al(off + mx * 4 * kMgSplits);
+    L.tc = sp->precision == FLOWCUDA_PRECISION_BF16X3;
+    L.part_floats = mx * (L.tc ? kMgTcSplits : kMgSplits);
+    size_t wmax = 2 * (size_t)L.D;  // the column sums borrow the buffer: kMgColSlices doubles per column
+    if ((size_t)L.H1 > wmax) wmax = L.H1;
+    if ((size_t)L.H2 > wmax) wmax = L.H2;
+    if (L.part_floats < 2 * kMgColSlices * wmax) L.part_floats = 2 * kMgColSlices * wmax;
+    L.off_part = off; off = mg_al(off + L.part_floats * 4);
+  }
+  L.off_aimg = L.off_bimg = off; L.a_bytes = L.b_bytes = 0;
+  if (L.tc) {
+    const int64_t D = L.D, H1 = L.H1, H2 = L.H2;
+    // A operands: activations / their gradients [n, K], and transposed activations [units, n]
+    const int64_t am[] = {n, n, n, n, n, n, H2, H1, D}, ak[] = {D, H1, H2, 2 * D, H2, H1, n, n, n};
+    // B operands: weights both ways, and transposed output gradients [cols, n]
+    const int64_t bn[] = {H1, H2, 2 * D, H2, H1, D, 2 * D, H2, H1}, bk[] = {D, H1, H2, 2 * D, H2, H1, n, n, n};
+    for (int i = 0; i < 9; ++i) {
+      if (mgtc_a_bytes(am[i], ak[i]) > L.a_bytes) L.a_bytes = mgtc_a_bytes(am[i], ak[i]);
+      if (mgtc_b_bytes(bn[i], bk[i]) > L.b_bytes) L.b_bytes = mgtc_b_bytes(bn[i], bk[i]);
+    }
+    L.off_aimg = off; off = mg_al(off + L.a_bytes);
+    L.off_bimg = off; off = mg_al(off + L.b_bytes);
   }
   L.off_act = off; off = mg_al(off + L.per_layer_act * 4 * (size_t)L.L);
   L.total = off + 256;
@@ -161,6 +184,8 @@ static int mg_run(const flowcuda_made_spec* sp, const float* params, const float
   mg_out_degree_kernel<<<(2 * D + 255) / 256, 256, 0, s>>>(deg3, D);
   const MgMask m0 = {nullptr, deg1, D, 1, 0}, m1 = {deg1, deg2, D, 1, 0}, m2 = {deg2, deg3, D, 1, 1};
   int rc;
+  const MgTcScratch sc = {ws + L.off_aimg, L.a_bytes, ws + L.off_bimg, L.b_bytes, part, L.part_floats};
+  auto mg_launch = [&](const MgGemm& g, cudaStream_t st) { return L.tc ? mgtc_launch(g, sc, st) : flowcuda::mg_launch(g, st); };
   FC_CUDA(cudaMemcpyAsync(S, x, (size_t)n * D * 4, cudaMemcpyDeviceToDevice, s));
   // ---- forward, data -> base: layer L-1 first
   for (int it = 0; it < L.L; ++it) {
@@ -195,7 +220,7 @@ static int mg_run(const flowcuda_made_spec* sp, const float* params, const float
     MgGemm g = mg_gemm(HB(l), 1, H2, dO, 2 * D, 1, G + L.w3, 2 * D, H2, 2 * D, n);
     g.mask = m2; g.splits = splits; g.part = part;
     if ((rc = mg_launch(g, s))) return rc;
-    mg_colsum_kernel<<<(2 * D + 31) / 32, 256, 0, s>>>(dO, n, 2 * D, G + L.b3);
+    if ((rc = mg_colsum(dO, n, 2 * D, G + L.b3, part, s))) return rc;
     g = mg_gemm(dO, 2 * D, 1, P + L.w3, 1, 2 * D, dH2, H2, N, H2, 2 * D);
     g.gate = HB(l); g.ldg = H2; g.mask = m2; g.mask_on_b = 2;
     if ((rc = mg_launch(g, s))) return rc;
@@ -203,7 +228,7 @@ static int mg_run(const flowcuda_made_spec* sp, const float* params, const float
     g = mg_gemm(HA(l), 1, H1, dH2, H2, 1, G + L.w2, H2, H1, H2, n);
     g.mask = m1; g.splits = splits; g.part = part;
     if ((rc = mg_launch(g, s))) return rc;
-    mg_colsum_kernel<<<(H2 + 31) / 32, 256, 0, s>>>(dH2, n, H2, G + L.b2);
+    if ((rc = mg_colsum(dH2, n, H2, G + L.b2, part, s))) return rc;
     g = mg_gemm(dH2, H2, 1, P + L.w2, 1, H2, dH1, H1, N, H1, H2);
     g.gate = HA(l); g.ldg = H1; g.mask = m1; g.mask_on_b = 2;
     if ((rc = mg_launch(g, s))) return rc;
@@ -211,7 +236,7 @@ static int mg_run(const flowcuda_made_spec* sp, const float* params, const float
     g = mg_gemm(XP(l), 1, D, dH1, H1, 1, G + L.w1, H1, D, H1, n);
     g.mask = m0; g.splits = splits; g.part = part;
     if ((rc = mg_launch(g, s))) return rc;
-    mg_colsum_kernel<<<(H1 + 31) / 32, 256, 0, s>>>(dH1, n, H1, G + L.b1);
+    if ((rc = mg_colsum(dH1, n, H1, G + L.b1, part, s))) return rc;
     g = mg_gemm(dH1, H1, 1, P + L.w1, 1, H1, S, D, N, D, H1);
     g.accumulate = 1; g.mask = m0; g.mask_on_b = 2;
     if ((rc = mg_launch(g, s))) return rc;
@@ -239,6 +264,8 @@ int flowcuda_made_nll_grad(const flowcuda_made_spec* spec, const float* params, 
   FC_REQUIRE(n >= 1 && n < (1ll << 31), "made_nll_grad: n=%lld outside [1, 2^31)", (long long)n);
   FC_REQUIRE(spec->event_dim >= 1 && spec->num_layers >= 1, "made_nll_grad: bad spec");
   FC_REQUIRE(spec->event_dim <= 32768 && spec->hidden[0] <= 32768 && spec->hidden[1] <= 32768, "made_nll_grad: sizes above 32768");
+  FC_REQUIRE(spec->precision == FLOWCUDA_PRECISION_FP32 || spec->precision == FLOWCUDA_PRECISION_BF16X3,
+             "made_nll_grad: precision %d (FP32 = 0 or BF16X3 = 3)", spec->precision);
   return mg_run(spec, params, x, n, loss, grad, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 

@@ -227,32 +227,56 @@ static int mg_launch(const MgGemm& g, cudaStream_t s) {
   return FLOWCUDA_OK;
 }
 
-// db[j] = sum_r dY[r, j]  (fixed order: deterministic).  Block = 32 columns x 8 row groups: a warp reads 32
-// consecutive columns of one row (coalesced); thread (g, c) sums rows r = g (mod 8) in four interleaved
-// accumulators, then the 8 groups are added in a fixed order.
-static __global__ void __launch_bounds__(256) mg_colsum_kernel(const float* __restrict__ dY, int64_t N, int n, float* __restrict__ db) {
-  __shared__ double part[8][33];
+// db[j] = sum_r dY[r, j]  (fixed order: deterministic), two stages so that the grid fills the machine:
+// stage 1, block (column block x, row slice z) = 32 columns x 8 row groups: a warp reads 32 consecutive columns
+// of one row (coalesced); thread (g, c) sums rows r = g (mod 8) of its slice in four interleaved double
+// accumulators, the 8 groups are added in a fixed order -> part[z][j]; stage 2 adds the slices in order.
+constexpr int kMgColSlices = 32;
+static __global__ void __launch_bounds__(256) mg_colsum_stage1(const float* __restrict__ dY, int64_t N, int n,
+                                                              double* __restrict__ part) {
+  __shared__ double sm[8][33];
   const int c = threadIdx.x & 31, g = threadIdx.x >> 5;
   const int j = blockIdx.x * 32 + c;
+  const int64_t chunk = ((N + gridDim.y - 1) / gridDim.y + 7) & ~(int64_t)7;
+  const int64_t r0 = chunk * blockIdx.y, r1 = min(N, r0 + chunk);
   double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
   if (j < n) {
-    int64_t r = g;
-    for (; r + 24 < N; r += 32) {
+    int64_t r = r0 + g;
+    for (; r + 24 < r1; r += 32) {
       a0 += (double)dY[r * n + j];
       a1 += (double)dY[(r + 8) * n + j];
       a2 += (double)dY[(r + 16) * n + j];
       a3 += (double)dY[(r + 24) * n + j];
     }
-    for (; r < N; r += 8) a0 += (double)dY[r * n + j];
+    for (; r < r1; r += 8) a0 += (double)dY[r * n + j];
   }
-  part[g][c] = (a0 + a1) + (a2 + a3);
+  sm[g][c] = (a0 + a1) + (a2 + a3);
   __syncthreads();
   if (g == 0 && j < n) {
     double t = 0.0;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) t += part[k][c];
-    db[j] = (float)t;
+    for (int k = 0; k < 8; ++k) t += sm[k][c];
+    part[(int64_t)blockIdx.y * n + j] = t;
   }
+}
+static __global__ void __launch_bounds__(256) mg_colsum_stage2(const double* __restrict__ part, int slices, int n,
+                                                              float* __restrict__ db) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  double t = 0.0;
+  for (int z = 0; z < slices; ++z) t += part[(int64_t)z * n + j];
+  db[j] = (float)t;
+}
+// scratch: kMgColSlices * n doubles
+static int mg_colsum(const float* dY, int64_t N, int n, float* db, void* scratch, cudaStream_t s) {
+  int slices = (int)((N + 255) / 256);
+  if (slices > kMgColSlices) slices = kMgColSlices;
+  if (slices < 1) slices = 1;
+  mg_colsum_stage1<<<dim3((n + 31) / 32, slices), 256, 0, s>>>(dY, N, n, (double*)scratch);
+  FC_LAUNCH_CHECK("mg_colsum_stage1");
+  mg_colsum_stage2<<<(n + 255) / 256, 256, 0, s>>>((const double*)scratch, slices, n, db);
+  FC_LAUNCH_CHECK("mg_colsum_stage2");
+  return FLOWCUDA_OK;
 }
 
 static MgGemm mg_gemm(const float* A, int64_t ars, int64_t acs, const float* B, int64_t brs, int64_t bcs, float* C,

@@ -1,0 +1,336 @@
+// mgtc.cuh — tensor-core engine for the reverse-mode GEMMs (made_grad.cu, coupling_dense_grad.cu).
+//
+// Runs the SAME problem descriptor as the FP32 engine (MgGemm, mg_sgemm.cuh) — C = op(A)·op(B) with strided
+// operands, bias / relu / relu-gate / accumulate epilogue, MADE masks, deterministic split-K — on tcgen05
+// with bf16 operands in error-compensated 3-pass form (hi·hi + hi·lo + lo·hi, fp32 accumulate in TMEM), the
+// arithmetic of the density path (dense_tc.cuh).  Per product:
+//   1. mgtc_pack_kernel (x2): op(A) -> [m_tile][k_stage][hi|lo] 128-row tile images, op(B) -> 256-row tile
+//      images with the MADE mask folded in.  Strides are generic, so Xᵀ·dY and dY·Wᵀ need no transposes.
+//   2. mgtc_gemm_kernel: persistent (one CTA per SM), TMA-bulk ring of 48 KB stages, two 256-column TMEM
+//      accumulators alternating between two epilogue warpgroups; a work item is (split, m tile, n tile) and
+//      walks only the K stages its split and its mask need (a masked Linear is block-triangular).
+//   3. split-K (weight gradients: K = batch, few output tiles): raw partials, then mg_splitk_reduce_kernel
+//      adds them in ascending order and applies the mask — bit-reproducible.
+#pragma once
+#include "dense_tc.cuh"
+#include "mg_sgemm.cuh"
+
+namespace flowcuda {
+
+constexpr int kMgTcSplits = 16;
+constexpr int kMgTcStages = 4;
+constexpr size_t kMgTcSmem = (size_t)kMgTcStages * kDtStageBytes + (2 * kMgTcStages + 4) * 8 + 16;
+
+// image row r (tiles of TR rows), K index k  <-  src[r*rs + k*cs]  (r < R, k < K; zero padding)
+// mask_mode 1: the element is W[in = k, out = r]; 2: W[in = r, out = k]; 0: none.
+template <int TR>
+static __global__ void __launch_bounds__(256) mgtc_pack_kernel(const float* __restrict__ src, int64_t rs, int64_t cs,
+                                                              int R, int64_t K, int KS, int tiles, MgMask mask,
+                                                              int mask_mode, uint8_t* __restrict__ img) {
+  constexpr int kHalf = TR * kDtBK * 2;  // bytes of one of hi/lo of a stage
+  const int64_t rows = (int64_t)tiles * TR;
+  const int64_t total = rows * (KS * 4);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = i % rows;
+    const int ck = (int)(i / rows);  // chunk of 8 along K
+    float f[8];
+    const float* p = src + row * rs;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int64_t k = (int64_t)ck * 8 + e;
+      float v = 0.f;
+      if (row < R && k < K) {
+        v = p[k * cs];
+        if (mask_mode == 1 && !mg_mask(mask, (int)k, (int)row)) v = 0.f;
+        if (mask_mode == 2 && !mg_mask(mask, (int)row, (int)k)) v = 0.f;
+      }
+      f[e] = v;
+    }
+    uint32_t h[4], l[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) tc::split_bf16x2(f[2 * e], f[2 * e + 1], h[e], l[e]);
+    const int64_t t = row / TR;
+    const int ks = ck >> 2, c = ck & 3;
+    uint8_t* st = img + ((t * KS + ks) * 2) * (int64_t)kHalf + tc::img_off(TR, (int)(row % TR), c);
+    *reinterpret_cast<uint4*>(st) = make_uint4(h[0], h[1], h[2], h[3]);
+    *reinterpret_cast<uint4*>(st + kHalf) = make_uint4(l[0], l[1], l[2], l[3]);
+  }
+}
+
+struct MgTcArgs {
+  const uint8_t* a_img;
+  const uint8_t* b_img;
+  int KS, MT, NT, S, ks_chunk;
+  MgGemm g;
+};
+
+// K stages [ks0, ks1) of work item (z, nt): the split's slice intersected with what the mask leaves.
+__device__ __forceinline__ void mgtc_krange(const MgTcArgs& a, int z, int mt, int nt, int& ks0, int& ks1) {
+  ks0 = z * a.ks_chunk;
+  ks1 = min(a.KS, ks0 + a.ks_chunk);
+  const MgGemm& g = a.g;
+  if (!g.mask.on) return;
+  const int j0 = nt * kDtBN, jl = min(j0 + kDtBN, g.N) - 1;
+  if (g.mask_on_b == 1) {  // B = W[k (in), j (out)]: inputs with degree above the tile's largest output degree never count
+    const int dmax = mg_dout_max(g.mask, j0, jl);
+    int64_t lo = 0, hi = g.K;  // first k with din(k) > dmax
+    while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if (mg_din(g.mask, (int)mid) > dmax) hi = mid; else lo = mid + 1; }
+    ks1 = min(ks1, (int)((lo + kDtBK - 1) / kDtBK));
+    if (ks1 <= ks0) ks1 = ks0 + 1;  // keep one (all-zero) stage: the accumulator must be written
+  } else if (g.mask_on_b == 2 && !g.mask.wrap) {  // B = Wᵀ (in = j, out = k): outputs below the tile's smallest input degree
+    const int dmin = mg_din(g.mask, j0);
+    int64_t lo = 0, hi = g.K;  // first k with dout(k) >= dmin
+    while (lo < hi) { const int64_t mid = (lo + hi) >> 1; if (g.mask.dout[mid] >= dmin) hi = mid; else lo = mid + 1; }
+    ks0 = max(ks0, min((int)(lo / kDtBK), ks1 - 1));
+  } else if (g.mask_on_b == 0 && a.S > 1) {  // weight gradient: a tile the mask empties is never reduced
+    if (mg_din(g.mask, mt * 128) > mg_dout_max(g.mask, j0, jl)) ks1 = ks0;
+  }
+}
+
+static __global__ void __launch_bounds__(kDtThreads, 1) mgtc_gemm_kernel(MgTcArgs a) {
+  extern __shared__ __align__(128) uint8_t smem[];
+  uint8_t* stages = smem;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kMgTcStages * kDtStageBytes);
+  uint64_t* empty = full + kMgTcStages;
+  uint64_t* acc_full = empty + kMgTcStages;
+  uint64_t* acc_empty = acc_full + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int per_split = a.MT * a.NT, nitems = per_split * a.S;
+
+  if (warp == 1) tc::tmem_alloc(tmem_slot, 2 * kDtBN);
+  if (tid == 0) {
+    for (int s = 0; s < kMgTcStages; ++s) {
+      tc::mbar_init(&full[s], 1);
+      tc::mbar_init(&empty[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      tc::mbar_init(&acc_full[s], 1);
+      tc::mbar_init(&acc_empty[s], 4);
+    }
+    tc::fence_mbar_init();
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {  // ===== TMA loader
+      uint32_t it = 0;
+      for (int t = blockIdx.x; t < nitems; t += gridDim.x) {
+        const int z = t / per_split, r = t - z * per_split, mt = r / a.NT, nt = r - mt * a.NT;
+        int ks0, ks1;
+        mgtc_krange(a, z, mt, nt, ks0, ks1);
+        const uint8_t* ag = a.a_img + (int64_t)mt * a.KS * 2 * kDtABytes;
+        const uint8_t* bg = a.b_img + (int64_t)nt * a.KS * 2 * kDtBBytes;
+        for (int ks = ks0; ks < ks1; ++ks, ++it) {
+          const uint32_t st = it % kMgTcStages, ph = (it / kMgTcStages) & 1u;
+          tc::mbar_wait(&empty[st], ph ^ 1u);
+          uint8_t* dst = stages + st * kDtStageBytes;
+          tc::mbar_arrive_expect_tx(&full[st], kDtStageBytes);
+          tc::tma_bulk_g2s(dst, ag + (int64_t)ks * 2 * kDtABytes, 2 * kDtABytes, &full[st]);
+          tc::tma_bulk_g2s(dst + 2 * kDtABytes, bg + (int64_t)ks * 2 * kDtBBytes, 2 * kDtBBytes, &full[st]);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {  // ===== MMA issuer
+      constexpr uint32_t idesc = tc::make_idesc(tc::kFmtBF16, 128, kDtBN);
+      constexpr uint32_t lbo_a = 16u * 128u, lbo_b = (uint32_t)(kDtBN >> 3) * 128u;
+      uint32_t it = 0, tl = 0;
+      for (int t = blockIdx.x; t < nitems; t += gridDim.x) {
+        const int z = t / per_split, r = t - z * per_split, mt = r / a.NT, nt = r - mt * a.NT;
+        int ks0, ks1;
+        mgtc_krange(a, z, mt, nt, ks0, ks1);
+        if (ks1 <= ks0) continue;
+        const uint32_t slot = tl & 1u, aph = (tl >> 1) & 1u;
+        ++tl;
+        tc::mbar_wait(&acc_empty[slot], aph ^ 1u);
+        tc::tc_fence_after();
+        const uint32_t dtm = tmem + slot * (uint32_t)kDtBN;
+        uint32_t acc = 0;
+        for (int ks = ks0; ks < ks1; ++ks, ++it) {
+          const uint32_t st = it % kMgTcStages, ph = (it / kMgTcStages) & 1u;
+          tc::mbar_wait(&full[st], ph);
+          tc::tc_fence_after();
+          const uint32_t sa = tc::smem_u32(stages + st * kDtStageBytes), sb = sa + 2 * kDtABytes;
+#pragma unroll
+          for (int pass = 0; pass < 3; ++pass) {
+            const uint32_t ab = sa + (pass == 2 ? kDtABytes : 0), bb = sb + (pass == 1 ? kDtBBytes : 0);
+#pragma unroll
+            for (int s = 0; s < kDtBK / 16; ++s) {
+              tc::mma_ss<tc::kFmtBF16>(dtm, tc::make_smem_desc(ab + s * 2u * lbo_a, lbo_a, 128u),
+                                       tc::make_smem_desc(bb + s * 2u * lbo_b, lbo_b, 128u), idesc, acc);
+              acc = 1;
+            }
+          }
+          tc::mma_commit(&empty[st]);
+        }
+        tc::mma_commit(&acc_full[slot]);
+      }
+    }
+  } else {
+    // ===== epilogue warps: group 0 (warps 2-5) takes this CTA's even items, group 1 (warps 6-9) the odd ones
+    const uint32_t group = (uint32_t)(warp - 2) >> 2;
+    const MgGemm& g = a.g;
+    const bool vec = (((uintptr_t)g.C | (uintptr_t)g.part | (uintptr_t)g.gate) & 15) == 0 && (g.ldc & 3) == 0 &&
+                     (g.ldg & 3) == 0 && (g.N & 3) == 0;
+    uint32_t tl = 0;
+    for (int t = blockIdx.x; t < nitems; t += gridDim.x) {
+      const int z = t / per_split, r = t - z * per_split, mt = r / a.NT, nt = r - mt * a.NT;
+      int ks0, ks1;
+      mgtc_krange(a, z, mt, nt, ks0, ks1);
+      if (ks1 <= ks0) continue;
+      const uint32_t mine = tl & 1u, aph = (tl >> 1) & 1u;
+      ++tl;
+      if (mine != group) continue;
+      const uint32_t slot = group;
+      tc::mbar_wait(&acc_full[slot], aph);
+      tc::tc_fence_after();
+      const uint32_t tb = tmem + slot * (uint32_t)kDtBN + ((uint32_t)((warp & 3) * 32) << 16);
+      const int row = mt * 128 + (warp & 3) * 32 + lane;
+      const bool rok = row < g.M;
+      const int jend = min(kDtBN, g.N - nt * kDtBN);  // valid columns of this tile (uniform)
+      float* crow = a.S > 1 ? g.part + ((int64_t)z * g.M + row) * g.N : g.C + (int64_t)row * g.ldc;
+      const float* grow = g.gate ? g.gate + (int64_t)row * g.ldg : nullptr;
+#pragma unroll 1
+      for (int c = 0; c < jend; c += 16) {
+        uint32_t vv[16];
+        tc::tmem_ld_x16(tb + (uint32_t)c, vv);
+        tc::tmem_ld_wait();
+        if (!rok) continue;
+        const int col = nt * kDtBN + c;
+        float o[16];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) o[e] = __uint_as_float(vv[e]);
+        if (a.S == 1) {
+          if (g.bias) {
+#pragma unroll
+            for (int e = 0; e < 16; ++e)
+              if (col + e < g.N) o[e] += __ldg(g.bias + col + e);
+          }
+          if (g.relu) {
+#pragma unroll
+            for (int e = 0; e < 16; ++e) o[e] = fmaxf(o[e], 0.f);
+          }
+          if (grow) {
+            if (vec && c + 16 <= jend) {
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const float4 gv = *reinterpret_cast<const float4*>(grow + col + 4 * q);
+                if (!(gv.x > 0.f)) o[4 * q] = 0.f;
+                if (!(gv.y > 0.f)) o[4 * q + 1] = 0.f;
+                if (!(gv.z > 0.f)) o[4 * q + 2] = 0.f;
+                if (!(gv.w > 0.f)) o[4 * q + 3] = 0.f;
+              }
+            } else {
+#pragma unroll
+              for (int e = 0; e < 16; ++e)
+                if (col + e < g.N && !(grow[col + e] > 0.f)) o[e] = 0.f;
+            }
+          }
+          if (g.mask.on && g.mask_on_b == 0) {
+#pragma unroll
+            for (int e = 0; e < 16; ++e)
+              if (col + e < g.N && !mg_mask(g.mask, row, col + e)) o[e] = 0.f;
+          }
+        }
+        const bool accum = a.S == 1 && g.accumulate;
+        if (vec && c + 16 <= jend) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            float4* dst = reinterpret_cast<float4*>(crow + col + 4 * q);
+            float4 w = make_float4(o[4 * q], o[4 * q + 1], o[4 * q + 2], o[4 * q + 3]);
+            if (accum) {
+              const float4 old = *dst;
+              w.x += old.x; w.y += old.y; w.z += old.z; w.w += old.w;
+            }
+            *dst = w;
+          }
+        } else {
+#pragma unroll
+          for (int e = 0; e < 16; ++e)
+            if (col + e < g.N) crow[col + e] = accum ? crow[col + e] + o[e] : o[e];
+        }
+      }
+      tc::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&acc_empty[slot]);
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    tc::tmem_dealloc(tmem, 2 * kDtBN);
+  }
+}
+
+struct MgTcScratch {
+  uint8_t* a_img; size_t a_bytes;
+  uint8_t* b_img; size_t b_bytes;
+  float* part; size_t part_floats;
+};
+
+static inline size_t mgtc_a_bytes(int64_t M, int64_t K) {
+  return (size_t)((M + 127) / 128) * (size_t)((K + kDtBK - 1) / kDtBK) * 2 * kDtABytes;
+}
+static inline size_t mgtc_b_bytes(int64_t N, int64_t K) {
+  return (size_t)((N + kDtBN - 1) / kDtBN) * (size_t)((K + kDtBK - 1) / kDtBK) * 2 * kDtBBytes;
+}
+
+// Same contract as mg_launch (g.splits > 1 asks for split-K; the engine picks how many).
+static int mgtc_launch(MgGemm g, const MgTcScratch& sc, cudaStream_t s) {
+  MgTcArgs a = {};
+  a.MT = (g.M + 127) / 128;
+  a.NT = (g.N + kDtBN - 1) / kDtBN;
+  a.KS = (int)((g.K + kDtBK - 1) / kDtBK);
+  if (a.KS < 1) a.KS = 1;
+  a.S = 1;
+  if (g.splits > 1) {
+    int want = sm_count() / (a.MT * a.NT);
+    if (want > kMgTcSplits) want = kMgTcSplits;
+    if (want > a.KS) want = a.KS;
+    if (want < 1) want = 1;
+    while (want > 1 && (size_t)want * g.M * g.N > sc.part_floats) --want;
+    a.S = want;
+  }
+  a.ks_chunk = (a.KS + a.S - 1) / a.S;
+  a.S = (a.KS + a.ks_chunk - 1) / a.ks_chunk;
+  const size_t ab = mgtc_a_bytes(g.M, g.K), bb = mgtc_b_bytes(g.N, g.K);
+  if (ab > sc.a_bytes || bb > sc.b_bytes) {
+    set_error("mgtc_launch: operand images (%zu, %zu bytes) exceed the scratch (%zu, %zu)", ab, bb, sc.a_bytes, sc.b_bytes);
+    return FLOWCUDA_EWORKSPACE;
+  }
+  const MgMask none = {};
+  {
+    const int64_t total = (int64_t)a.MT * 128 * a.KS * 4;
+    mgtc_pack_kernel<128><<<grid_for(total, 256, 8), 256, 0, s>>>(g.A, g.ars, g.acs, g.M, g.K, a.KS, a.MT, none, 0, sc.a_img);
+    FC_LAUNCH_CHECK("mgtc_pack_kernel<A>");
+  }
+  {
+    const int64_t total = (int64_t)a.NT * kDtBN * a.KS * 4;
+    // B(k, j) = B[k*brs + j*bcs]: image row j, K index k
+    mgtc_pack_kernel<kDtBN><<<grid_for(total, 256, 8), 256, 0, s>>>(g.B, g.bcs, g.brs, g.N, g.K, a.KS, a.NT, g.mask,
+                                                                   g.mask.on ? g.mask_on_b : 0, sc.b_img);
+    FC_LAUNCH_CHECK("mgtc_pack_kernel<B>");
+  }
+  a.a_img = sc.a_img;
+  a.b_img = sc.b_img;
+  g.splits = a.S;
+  g.part = a.S > 1 ? sc.part : nullptr;
+  a.g = g;
+  FC_CUDA(cudaFuncSetAttribute(mgtc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMgTcSmem));
+  const int items = a.MT * a.NT * a.S;
+  const int grid = items < sm_count() ? items : sm_count();
+  mgtc_gemm_kernel<<<grid, kDtThreads, kMgTcSmem, s>>>(a);
+  FC_LAUNCH_CHECK("mgtc_gemm_kernel");
+  if (a.S > 1) {
+    mg_splitk_reduce_kernel<<<grid_for((int64_t)g.M * g.N, 256, 8), 256, 0, s>>>(g);
+    FC_LAUNCH_CHECK("mg_splitk_reduce_kernel");
+  }
+  return FLOWCUDA_OK;
+}
+
+}  // namespace flowcuda

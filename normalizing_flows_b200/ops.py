@@ -239,7 +239,9 @@ def coupling_nll_grad(spec: CouplingSpec, params: torch.Tensor, x: torch.Tensor)
 
 
 # ---------------------------------------------------------------------------- row #8
-def make_made_spec(event_dim: int, num_layers: int, hidden: Sequence[int], base: int = _lib.BASE_NORMAL) -> _lib.MadeSpec:
+def make_made_spec(event_dim: int, num_layers: int, hidden: Sequence[int], base: int = _lib.BASE_NORMAL,
+                   precision: int = _lib.PRECISION_FP32) -> _lib.MadeSpec:
+    """`precision` selects the engine of made_nll_grad's GEMMs: FP32 CUDA cores or tcgen05 bf16x3."""
     if len(hidden) > _lib.MAX_HIDDEN_LAYERS:
         raise ValueError("at most %d hidden layers" % _lib.MAX_HIDDEN_LAYERS)
     sp = _lib.MadeSpec()
@@ -247,6 +249,7 @@ def make_made_spec(event_dim: int, num_layers: int, hidden: Sequence[int], base:
     for i, h in enumerate(hidden):
         sp.hidden[i] = h
     sp.base = base
+    sp.precision = precision
     return sp
 
 

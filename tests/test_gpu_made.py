@@ -144,12 +144,14 @@ GRAD_CASES = {
 }
 
 
+@pytest.mark.parametrize("engine", ["fp32", "bf16x3"])
 @pytest.mark.parametrize("case", sorted(GRAD_CASES))
-def test_made_nll_grad_matches_float64_autograd(case):
+def test_made_nll_grad_matches_float64_autograd(case, engine):
     """Hand-written reverse mode (csrc/made_grad.cu) vs autograd of the float64 oracle:
     loss within 1e-5 relative, every gradient entry within 1e-4 of the largest entry of its tensor,
-    masked-out weights exactly zero; bit-identical when run twice."""
-    from normalizing_flows_b200 import ops
+    masked-out weights exactly zero; bit-identical when run twice.  Both GEMM engines (FP32 CUDA cores,
+    tcgen05 bf16x3 — mgtc.cuh) are held to the same bound."""
+    from normalizing_flows_b200 import _lib, ops
 
     ospec, scale, n = GRAD_CASES[case]
     params = O.init_made_params(ospec, seed=8, scale=scale)
@@ -162,7 +164,8 @@ def test_made_nll_grad_matches_float64_autograd(case):
         return O.maf_log_prob(ospec, p, x)
 
     loss_ref, grads_ref = O.nll_and_grads(lp_fn, leaves)
-    spec = _spec(ops, ospec)
+    spec = ops.make_made_spec(ospec.event_dim, ospec.num_layers, ospec.hidden,
+                              precision=_lib.PRECISION_BF16X3 if engine == "bf16x3" else _lib.PRECISION_FP32)
     flat = G(O.flatten_layers(params))
     loss, grad = ops.made_nll_grad(spec, flat, x.float().cuda())
     loss2, grad2 = ops.made_nll_grad(spec, flat, x.float().cuda())
