@@ -713,7 +713,7 @@ def time_train(w, dev, rank, world, dist, ops, K=5, batch=1 << 18):
 
     sp = w._ospec()
     if sp.event_dim != 2:
-        batch = 1024  # stored activations: 88 KB per sample and layer at the maf_mnist shape
+        batch = 4096  # stored activations: 88 KB per sample and layer at the maf_mnist shape (2.9 GB)
     tr = {"affine_scalar": 0, "affine": 1, "rqs": 2}[sp.transform]
     tc = sp.event_dim != 2  # wide conditioners: reverse-mode GEMMs on tcgen05 (mgtc.cuh); D=2: fused FP32 kernels
     spec = ops.make_spec(sp.event_dim, sp.num_layers, sp.hidden, tr, sp.num_bins, sp.range_min, sp.range_max,

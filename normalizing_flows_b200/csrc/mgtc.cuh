@@ -267,6 +267,25 @@ static __global__ void __launch_bounds__(kDtThreads, 1) mgtc_gemm_kernel(MgTcArg
   }
 }
 
+// C = epilogue(sum_z part[z])   (z ascending: deterministic); the epilogue of the unsplit path: bias, relu,
+// relu gate, MADE mask on C, accumulate.  Masked-out weight gradients never read their partials (their tiles
+// were skipped).
+static __global__ void __launch_bounds__(256) mgtc_reduce_kernel(MgGemm g) {
+  const int64_t tot = (int64_t)g.M * g.N;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < tot; e += (int64_t)gridDim.x * blockDim.x) {
+    const int gi = (int)(e / g.N), gj = (int)(e - (int64_t)gi * g.N);
+    float r = 0.f;
+    if (!(g.mask.on && g.mask_on_b == 0) || mg_mask(g.mask, gi, gj)) {
+      for (int z = 0; z < g.splits; ++z) r += g.part[(int64_t)z * tot + e];
+      if (g.bias) r += g.bias[gj];
+      if (g.relu) r = fmaxf(r, 0.f);
+      if (g.gate && !(g.gate[gi * g.ldg + gj] > 0.f)) r = 0.f;
+    }
+    float* c = g.C + gi * g.ldc + gj;
+    *c = g.accumulate ? *c + r : r;
+  }
+}
+
 struct MgTcScratch {
   uint8_t* a_img; size_t a_bytes;
   uint8_t* b_img; size_t b_bytes;
@@ -280,7 +299,7 @@ static inline size_t mgtc_b_bytes(int64_t N, int64_t K) {
   return (size_t)((N + kDtBN - 1) / kDtBN) * (size_t)((K + kDtBK - 1) / kDtBK) * 2 * kDtBBytes;
 }
 
-// Same contract as mg_launch (g.splits > 1 asks for split-K; the engine picks how many).
+// Same contract as mg_launch; the engine itself decides whether and how far to split K.
 static int mgtc_launch(MgGemm g, const MgTcScratch& sc, cudaStream_t s) {
   MgTcArgs a = {};
   a.MT = (g.M + 127) / 128;
@@ -288,10 +307,12 @@ static int mgtc_launch(MgGemm g, const MgTcScratch& sc, cudaStream_t s) {
   a.KS = (int)((g.K + kDtBK - 1) / kDtBK);
   if (a.KS < 1) a.KS = 1;
   a.S = 1;
-  if (g.splits > 1) {
+  {
+    // split K whenever the output tiles alone leave most SMs idle (weight gradients: K = batch; input
+    // gradients of a wide last Linear: K = its width) and every split keeps a few stages
     int want = sm_count() / (a.MT * a.NT);
     if (want > kMgTcSplits) want = kMgTcSplits;
-    if (want > a.KS) want = a.KS;
+    if (want > a.KS / 4) want = a.KS / 4;
     if (want < 1) want = 1;
     while (want > 1 && (size_t)want * g.M * g.N > sc.part_floats) --want;
     a.S = want;
@@ -327,8 +348,8 @@ static int mgtc_launch(MgGemm g, const MgTcScratch& sc, cudaStream_t s) {
   mgtc_gemm_kernel<<<grid, kDtThreads, kMgTcSmem, s>>>(a);
   FC_LAUNCH_CHECK("mgtc_gemm_kernel");
   if (a.S > 1) {
-    mg_splitk_reduce_kernel<<<grid_for((int64_t)g.M * g.N, 256, 8), 256, 0, s>>>(g);
-    FC_LAUNCH_CHECK("mg_splitk_reduce_kernel");
+    mgtc_reduce_kernel<<<grid_for((int64_t)g.M * g.N, 256, 8), 256, 0, s>>>(g);
+    FC_LAUNCH_CHECK("mgtc_reduce_kernel");
   }
   return FLOWCUDA_OK;
 }
