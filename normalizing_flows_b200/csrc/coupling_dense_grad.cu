@@ -110,7 +110,7 @@ __global__ void __launch_bounds__(256) cg_mask_input_kernel(const float* __restr
 template <int K>
 __global__ void __launch_bounds__(256) cg_transform_fwd_kernel(const float* __restrict__ v, const float* __restrict__ o,
                                                               float* __restrict__ out, float* __restrict__ ld, int64_t N, int D,
-                                                              int P, int tp, float lo, float hi, int first) {
+                                                              int P, int tp, float lo, float hi, int first, int64_t ldo) {
   const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (r >= N) return;
@@ -119,7 +119,8 @@ __global__ void __launch_bounds__(256) cg_transform_fwd_kernel(const float* __re
     const float x = v[r * D + d];
     float y = x;
     if ((d & 1) == tp) {
-      const float* oo = o + (r * D + d) * (int64_t)P;
+      // ldo != 0: compact conditioner output, only the transformed dims' blocks, row stride ldo
+      const float* oo = ldo ? o + r * ldo + (int64_t)(d >> 1) * P : o + (r * D + d) * (int64_t)P;
       float l1;
       if (K > 0) {
         rqs_apply<false, K>([&](int i) { return oo[i]; }, K, lo, hi, x, y, l1);
@@ -156,18 +157,20 @@ template <int K>
 __global__ void __launch_bounds__(128) cg_transform_bwd_kernel(const float* __restrict__ v, const float* __restrict__ o,
                                                               const float* __restrict__ g, float* __restrict__ gin,
                                                               float* __restrict__ dO, int64_t N, int D, int P, int tp, float lo,
-                                                              float hi) {
+                                                              float hi, int64_t ldo) {
   const int64_t tot = N * D;
   const float ldbar = -1.f / (float)N;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < tot; i += (int64_t)gridDim.x * blockDim.x) {
     const int d = (int)(i % D);
-    float* ob = dO + i * P;
+    const int64_t r = i / D;
+    float* ob = ldo ? dO + r * ldo + (int64_t)(d >> 1) * P : dO + i * P;
     if ((d & 1) != tp) {
       gin[i] = g[i];
-      for (int p = 0; p < P; ++p) ob[p] = 0.f;
+      if (!ldo)
+        for (int p = 0; p < P; ++p) ob[p] = 0.f;
       continue;
     }
-    const float* oo = o + i * P;
+    const float* oo = ldo ? o + r * ldo + (int64_t)(d >> 1) * P : o + i * P;
     float y, l1, xbar;
     if (K > 0) {
       float ov[3 * (K > 0 ? K : 1) + 1], obar[3 * (K > 0 ? K : 1) + 1];
@@ -223,15 +226,20 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
     FC_CUDA(cudaMemcpyAsync(V(l), S, (size_t)n * D * 4, cudaMemcpyDeviceToDevice, s));
     cg_mask_input_kernel<<<eb, 256, 0, s>>>(S, MX, n, D, tp);
     const float* in = MX;
+    const int ncomp = ((D - tp + 1) / 2) * P;  // conditioner columns of the dims this layer transforms
+    const int64_t ldo = L.tc ? ncomp : 0;       // tensor-core engine: only those columns exist (compact o / dO)
+    const MgColMap cm = {0, P, 2 * P, tp * P};
     for (int i = 0; i < L.nlin; ++i) {
-      MgGemm g = mg_gemm(in, L.sizes[i], 1, Pl + L.w_off[i], L.sizes[i + 1], 1, H(l, i), L.sizes[i + 1], N, L.sizes[i + 1],
-                         L.sizes[i]);
+      const bool last = i == nh && L.tc;
+      const int nout = last ? ncomp : L.sizes[i + 1];
+      MgGemm g = mg_gemm(in, L.sizes[i], 1, Pl + L.w_off[i], L.sizes[i + 1], 1, H(l, i), nout, N, nout, L.sizes[i]);
       g.bias = Pl + L.b_off[i];
       g.relu = i < nh;
+      if (last) { g.map = cm; g.map.mode = 1; }
       if ((rc = mg_launch(g, s))) return rc;
       in = H(l, i);
     }
-    cg_transform_fwd_kernel<K><<<rb, 256, 0, s>>>(V(l), H(l, nh), S, LD, n, D, P, tp, sp->range_min, sp->range_max, it == 0);
+    cg_transform_fwd_kernel<K><<<rb, 256, 0, s>>>(V(l), H(l, nh), S, LD, n, D, P, tp, sp->range_min, sp->range_max, it == 0, ldo);
     FC_LAUNCH_CHECK("coupling_nll_grad forward");
   }
   cg_finish_kernel<<<rb, 256, 0, s>>>(S, LD, LP, G, n, D, sp->base);
@@ -241,22 +249,31 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
     const int tp = l & 1;
     const float* Pl = params + L.per_layer * l;
     float* Gl = grad + L.per_layer * l;
+    const int ncomp = ((D - tp + 1) / 2) * P;
+    const int64_t ldo = L.tc ? ncomp : 0;
+    const MgColMap cm = {0, P, 2 * P, tp * P};
     cg_transform_bwd_kernel<K><<<grid_for((int64_t)n * D, 128, 32), 128, 0, s>>>(V(l), H(l, nh), G, S, dO, n, D, P, tp,
-                                                                                sp->range_min, sp->range_max);
+                                                                                sp->range_min, sp->range_max, ldo);
     FC_LAUNCH_CHECK("cg_transform_bwd_kernel");
     cg_mask_input_kernel<<<eb, 256, 0, s>>>(V(l), MX, n, D, tp);
     const float* dout = dO;
     for (int i = nh; i >= 0; --i) {
-      const int kin = L.sizes[i], nout = L.sizes[i + 1];
+      const bool last = i == nh && L.tc;  // compact dO: the other columns' gradients are exactly zero
+      const int kin = L.sizes[i], nfull = L.sizes[i + 1], nout = last ? ncomp : nfull;
       const float* in = i == 0 ? MX : H(l, i - 1);
       // dW_i = inᵀ · dout (split-K, fixed-order reduce), db_i = column sums
-      MgGemm g = mg_gemm(in, 1, kin, dout, nout, 1, Gl + L.w_off[i], nout, kin, nout, n);
+      if (last) FC_CUDA(cudaMemsetAsync(Gl + L.w_off[i], 0, ((size_t)kin * nfull + nfull) * sizeof(float), s));
+      MgGemm g = mg_gemm(in, 1, kin, dout, nout, 1, Gl + L.w_off[i], nfull, kin, nout, n);
       g.splits = splits; g.part = part;
+      if (last) { g.map = cm; g.map.mode = 3; }
       if ((rc = mg_launch(g, s))) return rc;
-      if ((rc = mg_colsum(dout, n, nout, Gl + L.b_off[i], part, s))) return rc;
+      MgColMap bm = cm;
+      bm.mode = last ? 3 : 0;
+      if ((rc = mg_colsum(dout, n, nout, Gl + L.b_off[i], part, s, bm))) return rc;
       // d in = dout · W_iᵀ (relu gate of the stored activation; the masked input has no gate)
       float* din = i == 0 ? DMX : dH[i & 1];
-      g = mg_gemm(dout, nout, 1, Pl + L.w_off[i], 1, nout, din, kin, N, kin, nout);
+      g = mg_gemm(dout, nout, 1, Pl + L.w_off[i], 1, nfull, din, kin, N, kin, nout);
+      if (last) { g.map = cm; g.map.mode = 2; }
       if (i > 0) { g.gate = H(l, i - 1); g.ldg = kin; }
       if ((rc = mg_launch(g, s))) return rc;
       dout = din;

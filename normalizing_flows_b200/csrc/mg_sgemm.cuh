@@ -30,6 +30,18 @@ __device__ __forceinline__ int mg_dout_max(const MgMask& m, int j0, int j1) {
   return m.dout[j1];
 }
 
+// Block-strided column subset: compact column j stands for full column off + (j / blk)*stride + j % blk.
+// (The last Linear of a coupling layer only needs the columns of the dims it transforms: blocks of P every 2P.)
+// Understood by the tensor-core engine only (mgtc.cuh); mode 0 = none.
+struct MgColMap {
+  int mode;  // 1: B's columns j and the bias; 2: B's K index; 3: C's columns
+  int blk, stride, off;
+};
+__host__ __device__ __forceinline__ int mg_full_col(const MgColMap& m, int j) {
+  const int b = j / m.blk;
+  return m.off + b * m.stride + (j - b * m.blk);
+}
+
 struct MgGemm {
   const float* A; int64_t ars, acs;  // A(i,k) = A[i*ars + k*acs]
   const float* B; int64_t brs, bcs;  // B(k,j) = B[k*brs + j*bcs]
@@ -42,6 +54,7 @@ struct MgGemm {
   MgMask mask;                       // mask.on: weight product, apply the MADE mask with the i/j roles below
   int splits; float* part;           // splits > 1: split-K, raw partials to part[z][M][N]; mg_splitk_reduce finishes (fixed order)
   int mask_on_b;                     // 1: mask B(k,j) as W[k (in), j (out)];  2: mask B(k,j) as Wᵀ: in = j, out = k; 0: mask C(i,j) as W[i,j]
+  MgColMap map;                      // tensor-core engine only
 };
 
 constexpr int kMgT = 128, kMgK = 8, kMgSplits = 8;
@@ -217,6 +230,10 @@ static __global__ void __launch_bounds__(256) mg_splitk_reduce_kernel(MgGemm g) 
 }
 
 static int mg_launch(const MgGemm& g, cudaStream_t s) {
+  if (g.map.mode) {
+    set_error("mg_launch: column maps need the tensor-core engine");
+    return FLOWCUDA_EUNSUPPORTED;
+  }
   dim3 grid((g.N + kMgT - 1) / kMgT, (g.M + kMgT - 1) / kMgT, g.splits > 1 ? g.splits : 1);
   mg_sgemm_kernel<<<grid, 256, 0, s>>>(g);
   FC_LAUNCH_CHECK("mg_sgemm_kernel");
@@ -260,21 +277,21 @@ static __global__ void __launch_bounds__(256) mg_colsum_stage1(const float* __re
   }
 }
 static __global__ void __launch_bounds__(256) mg_colsum_stage2(const double* __restrict__ part, int slices, int n,
-                                                              float* __restrict__ db) {
+                                                              float* __restrict__ db, MgColMap map) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= n) return;
   double t = 0.0;
   for (int z = 0; z < slices; ++z) t += part[(int64_t)z * n + j];
-  db[j] = (float)t;
+  db[map.mode ? mg_full_col(map, j) : j] = (float)t;
 }
 // scratch: kMgColSlices * n doubles
-static int mg_colsum(const float* dY, int64_t N, int n, float* db, void* scratch, cudaStream_t s) {
+static int mg_colsum(const float* dY, int64_t N, int n, float* db, void* scratch, cudaStream_t s, MgColMap map = MgColMap{}) {
   int slices = (int)((N + 255) / 256);
   if (slices > kMgColSlices) slices = kMgColSlices;
   if (slices < 1) slices = 1;
   mg_colsum_stage1<<<dim3((n + 31) / 32, slices), 256, 0, s>>>(dY, N, n, (double*)scratch);
   FC_LAUNCH_CHECK("mg_colsum_stage1");
-  mg_colsum_stage2<<<(n + 255) / 256, 256, 0, s>>>((const double*)scratch, slices, n, db);
+  mg_colsum_stage2<<<(n + 255) / 256, 256, 0, s>>>((const double*)scratch, slices, n, db, map);
   FC_LAUNCH_CHECK("mg_colsum_stage2");
   return FLOWCUDA_OK;
 }

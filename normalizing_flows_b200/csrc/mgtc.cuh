@@ -26,7 +26,7 @@ constexpr size_t kMgTcSmem = (size_t)kMgTcStages * kDtStageBytes + (2 * kMgTcSta
 template <int TR>
 static __global__ void __launch_bounds__(256) mgtc_pack_kernel(const float* __restrict__ src, int64_t rs, int64_t cs,
                                                               int R, int64_t K, int KS, int tiles, MgMask mask,
-                                                              int mask_mode, uint8_t* __restrict__ img) {
+                                                              int mask_mode, MgColMap map, uint8_t* __restrict__ img) {
   constexpr int kHalf = TR * kDtBK * 2;  // bytes of one of hi/lo of a stage
   const int64_t rows = (int64_t)tiles * TR;
   const int64_t total = rows * (KS * 4);
@@ -34,13 +34,13 @@ static __global__ void __launch_bounds__(256) mgtc_pack_kernel(const float* __re
     const int64_t row = i % rows;
     const int ck = (int)(i / rows);  // chunk of 8 along K
     float f[8];
-    const float* p = src + row * rs;
+    const float* p = src + (map.mode == 1 && row < R ? (int64_t)mg_full_col(map, (int)row) : row) * rs;
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       const int64_t k = (int64_t)ck * 8 + e;
       float v = 0.f;
       if (row < R && k < K) {
-        v = p[k * cs];
+        v = p[(map.mode == 2 ? (int64_t)mg_full_col(map, (int)k) : k) * cs];
         if (mask_mode == 1 && !mg_mask(mask, (int)k, (int)row)) v = 0.f;
         if (mask_mode == 2 && !mg_mask(mask, (int)row, (int)k)) v = 0.f;
       }
@@ -175,7 +175,8 @@ static __global__ void __launch_bounds__(kDtThreads, 1) mgtc_gemm_kernel(MgTcArg
     const uint32_t group = (uint32_t)(warp - 2) >> 2;
     const MgGemm& g = a.g;
     const bool vec = (((uintptr_t)g.C | (uintptr_t)g.part | (uintptr_t)g.gate) & 15) == 0 && (g.ldc & 3) == 0 &&
-                     (g.ldg & 3) == 0 && (g.N & 3) == 0;
+                     (g.ldg & 3) == 0 && (g.N & 3) == 0 && !(g.map.mode == 3 && a.S == 1);
+    const bool cmap = g.map.mode == 3 && a.S == 1;
     uint32_t tl = 0;
     for (int t = blockIdx.x; t < nitems; t += gridDim.x) {
       const int z = t / per_split, r = t - z * per_split, mt = r / a.NT, nt = r - mt * a.NT;
@@ -208,7 +209,7 @@ static __global__ void __launch_bounds__(kDtThreads, 1) mgtc_gemm_kernel(MgTcArg
           if (g.bias) {
 #pragma unroll
             for (int e = 0; e < 16; ++e)
-              if (col + e < g.N) o[e] += __ldg(g.bias + col + e);
+              if (col + e < g.N) o[e] += __ldg(g.bias + (g.map.mode == 1 ? mg_full_col(g.map, col + e) : col + e));
           }
           if (g.relu) {
 #pragma unroll
@@ -251,7 +252,10 @@ static __global__ void __launch_bounds__(kDtThreads, 1) mgtc_gemm_kernel(MgTcArg
         } else {
 #pragma unroll
           for (int e = 0; e < 16; ++e)
-            if (col + e < g.N) crow[col + e] = accum ? crow[col + e] + o[e] : o[e];
+            if (col + e < g.N) {
+              float* dst = crow + (cmap ? mg_full_col(g.map, col + e) : col + e);
+              *dst = accum ? *dst + o[e] : o[e];
+            }
         }
       }
       tc::tc_fence_before();
@@ -277,11 +281,11 @@ static __global__ void __launch_bounds__(256) mgtc_reduce_kernel(MgGemm g) {
     float r = 0.f;
     if (!(g.mask.on && g.mask_on_b == 0) || mg_mask(g.mask, gi, gj)) {
       for (int z = 0; z < g.splits; ++z) r += g.part[(int64_t)z * tot + e];
-      if (g.bias) r += g.bias[gj];
+      if (g.bias) r += g.bias[g.map.mode == 1 ? mg_full_col(g.map, gj) : gj];
       if (g.relu) r = fmaxf(r, 0.f);
       if (g.gate && !(g.gate[gi * g.ldg + gj] > 0.f)) r = 0.f;
     }
-    float* c = g.C + gi * g.ldc + gj;
+    float* c = g.C + gi * g.ldc + (g.map.mode == 3 ? mg_full_col(g.map, gj) : gj);
     *c = g.accumulate ? *c + r : r;
   }
 }
@@ -327,14 +331,16 @@ static int mgtc_launch(MgGemm g, const MgTcScratch& sc, cudaStream_t s) {
   const MgMask none = {};
   {
     const int64_t total = (int64_t)a.MT * 128 * a.KS * 4;
-    mgtc_pack_kernel<128><<<grid_for(total, 256, 8), 256, 0, s>>>(g.A, g.ars, g.acs, g.M, g.K, a.KS, a.MT, none, 0, sc.a_img);
+    mgtc_pack_kernel<128><<<grid_for(total, 256, 8), 256, 0, s>>>(g.A, g.ars, g.acs, g.M, g.K, a.KS, a.MT, none, 0, MgColMap{},
+                                                                  sc.a_img);
     FC_LAUNCH_CHECK("mgtc_pack_kernel<A>");
   }
   {
     const int64_t total = (int64_t)a.NT * kDtBN * a.KS * 4;
     // B(k, j) = B[k*brs + j*bcs]: image row j, K index k
     mgtc_pack_kernel<kDtBN><<<grid_for(total, 256, 8), 256, 0, s>>>(g.B, g.bcs, g.brs, g.N, g.K, a.KS, a.NT, g.mask,
-                                                                   g.mask.on ? g.mask_on_b : 0, sc.b_img);
+                                                                   g.mask.on ? g.mask_on_b : 0,
+                                                                   g.map.mode == 3 ? MgColMap{} : g.map, sc.b_img);
     FC_LAUNCH_CHECK("mgtc_pack_kernel<B>");
   }
   a.a_img = sc.a_img;
