@@ -19,7 +19,7 @@ namespace flowcuda {
 
 constexpr int kMgTcSplits = 16;
 constexpr int kMgTcStages = 4;
-constexpr size_t kMgTcSmem = (size_t)kMgTcStages * kDtStageBytes + (2 * kMgTcStages + 4) * 8 + 16;
+constexpr size_t kMgTcSmem = (size_t)kMgTcStages * kDtStageBytes + 2 * kDtBN * 4 + (2 * kMgTcStages + 4) * 8 + 16;
 
 // image row r (tiles of TR rows), K index k  <-  src[r*rs + k*cs]  (r < R, k < K; zero padding)
 // mask_mode 1: the element is W[in = k, out = r]; 2: W[in = r, out = k]; 0: none.
@@ -90,7 +90,8 @@ __device__ __forceinline__ void mgtc_krange(const MgTcArgs& a, int z, int mt, in
 static __global__ void __launch_bounds__(kDtThreads, 1) mgtc_gemm_kernel(MgTcArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
   uint8_t* stages = smem;
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + kMgTcStages * kDtStageBytes);
+  float* sbias = reinterpret_cast<float*>(smem + kMgTcStages * kDtStageBytes);  // [2][256]
+  uint64_t* full = reinterpret_cast<uint64_t*>(sbias + 2 * kDtBN);
   uint64_t* empty = full + kMgTcStages;
   uint64_t* acc_full = empty + kMgTcStages;
   uint64_t* acc_empty = acc_full + 2;
@@ -195,21 +196,27 @@ static __global__ void __launch_bounds__(kDtThreads, 1) mgtc_gemm_kernel(MgTcArg
       const int jend = min(kDtBN, g.N - nt * kDtBN);  // valid columns of this tile (uniform)
       float* crow = a.S > 1 ? g.part + ((int64_t)z * g.M + row) * g.N : g.C + (int64_t)row * g.ldc;
       const float* grow = g.gate ? g.gate + (int64_t)row * g.ldg : nullptr;
-#pragma unroll 1
-      for (int c = 0; c < jend; c += 16) {
-        uint32_t vv[16];
-        tc::tmem_ld_x16(tb + (uint32_t)c, vv);
-        tc::tmem_ld_wait();
-        if (!rok) continue;
+      const bool has_bias = a.S == 1 && g.bias != nullptr;
+      float* sb = sbias + group * kDtBN;
+      if (has_bias) {  // this tile's bias columns, remapped once
+        for (int n = (tid - 64) & 127; n < kDtBN; n += 128) {
+          const int col = nt * kDtBN + n;
+          sb[n] = col < g.N ? g.bias[g.map.mode == 1 ? mg_full_col(g.map, col) : col] : 0.f;
+        }
+        if (group == 0) asm volatile("bar.sync 1, 128;" ::: "memory");
+        else asm volatile("bar.sync 2, 128;" ::: "memory");
+      }
+      const bool accum = a.S == 1 && g.accumulate;
+      // 16 columns of this thread's row: epilogue + store
+      auto emit = [&](const uint32_t* vv, int c) {
         const int col = nt * kDtBN + c;
         float o[16];
 #pragma unroll
         for (int e = 0; e < 16; ++e) o[e] = __uint_as_float(vv[e]);
         if (a.S == 1) {
-          if (g.bias) {
+          if (has_bias) {
 #pragma unroll
-            for (int e = 0; e < 16; ++e)
-              if (col + e < g.N) o[e] += __ldg(g.bias + (g.map.mode == 1 ? mg_full_col(g.map, col + e) : col + e));
+            for (int e = 0; e < 16; ++e) o[e] += sb[c + e];
           }
           if (g.relu) {
 #pragma unroll
@@ -237,7 +244,6 @@ static __global__ void __launch_bounds__(kDtThreads, 1) mgtc_gemm_kernel(MgTcArg
               if (col + e < g.N && !mg_mask(g.mask, row, col + e)) o[e] = 0.f;
           }
         }
-        const bool accum = a.S == 1 && g.accumulate;
         if (vec && c + 16 <= jend) {
 #pragma unroll
           for (int q = 0; q < 4; ++q) {
@@ -257,6 +263,22 @@ static __global__ void __launch_bounds__(kDtThreads, 1) mgtc_gemm_kernel(MgTcArg
               *dst = accum ? *dst + o[e] : o[e];
             }
         }
+      };
+#pragma unroll 1
+      for (int c = 0; c < jend; c += 32) {
+        uint32_t v0[16], v1[16];
+        const bool two = c + 16 < jend;  // uniform
+        tc::tmem_ld_x16(tb + (uint32_t)c, v0);
+        if (two) tc::tmem_ld_x16(tb + (uint32_t)(c + 16), v1);
+        tc::tmem_ld_wait();
+        if (rok) {
+          emit(v0, c);
+          if (two) emit(v1, c + 16);
+        }
+      }
+      if (has_bias) {  // everyone is done with sb before the group's next tile rewrites it
+        if (group == 0) asm volatile("bar.sync 1, 128;" ::: "memory");
+        else asm volatile("bar.sync 2, 128;" ::: "memory");
       }
       tc::tc_fence_before();
       __syncwarp();
@@ -313,10 +335,10 @@ static int mgtc_launch(MgGemm g, const MgTcScratch& sc, cudaStream_t s) {
   a.S = 1;
   {
     // split K whenever the output tiles alone leave most SMs idle (weight gradients: K = batch; input
-    // gradients of a wide last Linear: K = its width) and every split keeps a few stages
+    // gradients of a wide last Linear: K = its width) and every split keeps at least 16 stages
     int want = sm_count() / (a.MT * a.NT);
     if (want > kMgTcSplits) want = kMgTcSplits;
-    if (want > a.KS / 4) want = a.KS / 4;
+    if (want > a.KS / 16) want = a.KS / 16;  // a split must outweigh its pass over the partials
     if (want < 1) want = 1;
     while (want > 1 && (size_t)want * g.M * g.N > sc.part_floats) --want;
     a.S = want;
