@@ -184,9 +184,12 @@ int flowcuda_coupling_sample(const flowcuda_coupling_spec* spec, const float* pa
 
 /* value_and_grad of loss = -mean(Transformed.log_prob(x)) w.r.t. the flow parameters
  * (real_nvp_toy_densities.py:139-151,170; maf_toy_densities.py:140-152,171): hand-written
- * reverse mode, deterministic two-stage reduction.  loss[1], grad[param_count] (layout of
- * `params`).  Available for event_dim 2 with two hidden layers <= 64 (the toy flows);
- * FLOWCUDA_EUNSUPPORTED otherwise. */
+ * reverse mode, deterministic reductions (bit-identical run to run).  loss[1],
+ * grad[param_count] (layout of `params`).
+ *   event_dim 2, two hidden layers <= 64 (the toy flows): one fused FP32 kernel pair;
+ *   any other shape with TRANSFORM_AFFINE / TRANSFORM_RQS (8 or 12 bins) — the
+ *   maf_mnist.py:134-166 step: stored-activation reverse mode whose GEMMs run on FP32 CUDA
+ *   cores (spec->precision = FP32) or on tcgen05 bf16x3 (spec->precision = BF16X3). */
 size_t flowcuda_coupling_nll_grad_workspace_bytes(const flowcuda_coupling_spec* spec, int64_t n);
 int flowcuda_coupling_nll_grad(const flowcuda_coupling_spec* spec, const float* params, const float* x,
                                int64_t n, float* loss, float* grad, void* workspace,
