@@ -34,16 +34,17 @@ __global__ void __launch_bounds__(256) mg_copy_perm_kernel(const float* __restri
 }
 
 // forward affine: u = (xp - mu) e^-alpha ; ld[r] (+)= -sum_q alpha   (one warp per row)
+// flip_out: u is written with the dims reversed — the next layer's ordering (consecutive layers alternate)
 __global__ void __launch_bounds__(256) mg_affine_fwd_kernel(const float* __restrict__ xp, const float* __restrict__ o,
                                                            float* __restrict__ u, float* __restrict__ ld, int64_t N, int D,
-                                                           int first) {
+                                                           int first, int flip_out) {
   const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   if (r >= N) return;
   float s = 0.f;
   for (int q = lane; q < D; q += 32) {
     const float mu = o[r * 2 * D + q], al = o[r * 2 * D + D + q];
-    u[r * D + q] = (xp[r * D + q] - mu) * expf(-al);
+    u[r * D + (flip_out ? D - 1 - q : q)] = (xp[r * D + q] - mu) * expf(-al);
     s -= al;
   }
   s = warp_sum(s);
@@ -67,19 +68,21 @@ __global__ void __launch_bounds__(256) mg_finish_kernel(const float* __restrict_
   if (lane == 0) lp[r] = ld[r] + s;
 }
 
-// backward affine: given du (in place -> dx_direct), writes dO = [dmu, dalpha]
+// backward affine: du = gin (read with the dims reversed when flip_in: gin is in the previous layer's ordering)
+// -> dx_direct = du·e^-alpha, dO = [dmu, dalpha]
 __global__ void __launch_bounds__(256) mg_affine_bwd_kernel(const float* __restrict__ xp, const float* __restrict__ o,
-                                                           float* __restrict__ du, float* __restrict__ dO, int64_t N, int D) {
+                                                           const float* __restrict__ gin, int flip_in, float* __restrict__ dx,
+                                                           float* __restrict__ dO, int64_t N, int D) {
   const int64_t tot = N * D;
   const float invn = 1.f / (float)N;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < tot; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t r = i / D; const int q = (int)(i - r * D);
     const float mu = o[r * 2 * D + q], al = o[r * 2 * D + D + q];
-    const float e = expf(-al), g = du[i];
+    const float e = expf(-al), g = gin[r * D + (flip_in ? D - 1 - q : q)];
     const float uu = (xp[i] - mu) * e;
     dO[r * 2 * D + q] = -g * e;
     dO[r * 2 * D + D + q] = fmaf(-g, uu, invn);  // d(-mean ld)/dalpha = +1/N
-    du[i] = g * e;
+    dx[i] = g * e;
   }
 }
 
@@ -191,7 +194,7 @@ static int mg_run(const flowcuda_made_spec* sp, const float* params, const float
   for (int it = 0; it < L.L; ++it) {
     const int l = L.L - 1 - it, rev = l & 1;
     const float* P = params + L.per_layer * l;
-    mg_copy_perm_kernel<<<eb, 256, 0, s>>>(S, XP(l), n, D, rev, 0);
+    if (it == 0) mg_copy_perm_kernel<<<eb, 256, 0, s>>>(S, XP(l), n, D, rev, 0);  // later layers: written by the affine kernel
     MgGemm g = mg_gemm(XP(l), D, 1, P + L.w1, H1, 1, HA(l), H1, N, H1, D);
     g.bias = P + L.b1; g.relu = 1; g.mask = m0; g.mask_on_b = 1;
     if ((rc = mg_launch(g, s))) return rc;
@@ -201,20 +204,24 @@ static int mg_run(const flowcuda_made_spec* sp, const float* params, const float
     g = mg_gemm(HB(l), H2, 1, P + L.w3, 2 * D, 1, OO(l), 2 * D, N, 2 * D, H2);
     g.bias = P + L.b3; g.mask = m2; g.mask_on_b = 1;
     if ((rc = mg_launch(g, s))) return rc;
-    mg_affine_fwd_kernel<<<rb, 256, 0, s>>>(XP(l), OO(l), T, LD, n, D, it == 0);
-    mg_copy_perm_kernel<<<eb, 256, 0, s>>>(T, S, n, D, rev, 0);
+    // u goes straight into the next layer's input block, in that layer's ordering (the reverse of this one);
+    // layer 0 sees the natural ordering, so the base point lands in S as is
+    mg_affine_fwd_kernel<<<rb, 256, 0, s>>>(XP(l), OO(l), l > 0 ? XP(l - 1) : S, LD, n, D, it == 0, l > 0);
     FC_LAUNCH_CHECK("made_nll_grad forward");
   }
   mg_finish_kernel<<<rb, 256, 0, s>>>(S, LD, LP, T, n, D);  // T = d loss / d base point (natural order)
   FC_LAUNCH_CHECK("mg_finish_kernel");
   if ((rc = flowcuda_sum_scaled(LP, n, -1.0 / (double)n, loss, ws + L.off_sum, s))) return rc;
   // ---- backward: layer 0 first
+  float* const S0 = S; float* const T0 = T;
   for (int l = 0; l < L.L; ++l) {
-    const int rev = l & 1;
     const float* P = params + L.per_layer * l;
     float* G = grad + L.per_layer * l;
-    mg_copy_perm_kernel<<<eb, 256, 0, s>>>(T, S, n, D, rev, 0);  // S = gradient in the layer's ordering
-    mg_affine_bwd_kernel<<<eb, 256, 0, s>>>(XP(l), OO(l), S, dO, n, D);
+    // the gradient travels in the ordering of the layer that produced it: T (natural = layer 0's) first, then
+    // the two buffers alternate and every layer reads its input gradient reversed
+    float* gin = (l & 1) ? S0 : T0;
+    float* S = (l & 1) ? T0 : S0;
+    mg_affine_bwd_kernel<<<eb, 256, 0, s>>>(XP(l), OO(l), gin, l > 0, S, dO, n, D);
     FC_LAUNCH_CHECK("mg_affine_bwd_kernel");
     // output Linear
     MgGemm g = mg_gemm(HB(l), 1, H2, dO, 2 * D, 1, G + L.w3, 2 * D, H2, 2 * D, n);
@@ -240,7 +247,6 @@ static int mg_run(const flowcuda_made_spec* sp, const float* params, const float
     g = mg_gemm(dH1, H1, 1, P + L.w1, 1, H1, S, D, N, D, H1);
     g.accumulate = 1; g.mask = m0; g.mask_on_b = 2;
     if ((rc = mg_launch(g, s))) return rc;
-    mg_copy_perm_kernel<<<eb, 256, 0, s>>>(S, T, n, D, rev, 0);  // back to the natural order
     FC_LAUNCH_CHECK("made_nll_grad backward");
   }
   return FLOWCUDA_OK;

@@ -23,28 +23,50 @@ constexpr size_t kMgTcSmem = (size_t)kMgTcStages * kDtStageBytes + 2 * kDtBN * 4
 
 // image row r (tiles of TR rows), K index k  <-  src[r*rs + k*cs]  (r < R, k < K; zero padding)
 // mask_mode 1: the element is W[in = k, out = r]; 2: W[in = r, out = k]; 0: none.
-template <int TR>
+// KC (cs == 1, K contiguous in memory): four lanes take the four 8-element chunks of one row's K stage, so a
+// warp reads eight full 128-byte lines and writes four 128-byte runs of the image.  Otherwise (rows contiguous:
+// a transposed source) consecutive lanes take consecutive rows: every load and the store are coalesced.
+template <int TR, bool KC>
 static __global__ void __launch_bounds__(256) mgtc_pack_kernel(const float* __restrict__ src, int64_t rs, int64_t cs,
                                                               int R, int64_t K, int KS, int tiles, MgMask mask,
                                                               int mask_mode, MgColMap map, uint8_t* __restrict__ img) {
   constexpr int kHalf = TR * kDtBK * 2;  // bytes of one of hi/lo of a stage
   const int64_t rows = (int64_t)tiles * TR;
   const int64_t total = rows * (KS * 4);
+  const bool vec = KC && map.mode != 2 && (rs & 3) == 0 && ((uintptr_t)src & 15) == 0;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t row = i % rows;
-    const int ck = (int)(i / rows);  // chunk of 8 along K
+    int64_t row;
+    int ck;  // chunk of 8 along K
+    if (KC) {
+      const int64_t t = i >> 2;
+      row = t % rows;
+      ck = (int)(t / rows) * 4 + (int)(i & 3);
+    } else {
+      row = i % rows;
+      ck = (int)(i / rows);
+    }
     float f[8];
     const float* p = src + (map.mode == 1 && row < R ? (int64_t)mg_full_col(map, (int)row) : row) * rs;
+    const int64_t k0 = (int64_t)ck * 8;
+    if (vec && row < R && k0 + 8 <= K) {
+      const float4 lo4 = *reinterpret_cast<const float4*>(p + k0), hi4 = *reinterpret_cast<const float4*>(p + k0 + 4);
+      f[0] = lo4.x; f[1] = lo4.y; f[2] = lo4.z; f[3] = lo4.w; f[4] = hi4.x; f[5] = hi4.y; f[6] = hi4.z; f[7] = hi4.w;
+    } else {
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const int64_t k = (int64_t)ck * 8 + e;
-      float v = 0.f;
-      if (row < R && k < K) {
-        v = p[(map.mode == 2 ? (int64_t)mg_full_col(map, (int)k) : k) * cs];
-        if (mask_mode == 1 && !mg_mask(mask, (int)k, (int)row)) v = 0.f;
-        if (mask_mode == 2 && !mg_mask(mask, (int)row, (int)k)) v = 0.f;
+      for (int e = 0; e < 8; ++e) {
+        const int64_t k = k0 + e;
+        f[e] = (row < R && k < K) ? p[(map.mode == 2 ? (int64_t)mg_full_col(map, (int)k) : k) * cs] : 0.f;
       }
-      f[e] = v;
+    }
+    if (mask_mode != 0 && row < R) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int64_t k = k0 + e;
+        if (k < K) {
+          if (mask_mode == 1 && !mg_mask(mask, (int)k, (int)row)) f[e] = 0.f;
+          if (mask_mode == 2 && !mg_mask(mask, (int)row, (int)k)) f[e] = 0.f;
+        }
+      }
     }
     uint32_t h[4], l[4];
 #pragma unroll
@@ -353,16 +375,23 @@ static int mgtc_launch(MgGemm g, const MgTcScratch& sc, cudaStream_t s) {
   const MgMask none = {};
   {
     const int64_t total = (int64_t)a.MT * 128 * a.KS * 4;
-    mgtc_pack_kernel<128><<<grid_for(total, 256, 8), 256, 0, s>>>(g.A, g.ars, g.acs, g.M, g.K, a.KS, a.MT, none, 0, MgColMap{},
-                                                                  sc.a_img);
+    const int gr = grid_for(total, 256, 8);
+    if (g.acs == 1)
+      mgtc_pack_kernel<128, true><<<gr, 256, 0, s>>>(g.A, g.ars, g.acs, g.M, g.K, a.KS, a.MT, none, 0, MgColMap{}, sc.a_img);
+    else
+      mgtc_pack_kernel<128, false><<<gr, 256, 0, s>>>(g.A, g.ars, g.acs, g.M, g.K, a.KS, a.MT, none, 0, MgColMap{}, sc.a_img);
     FC_LAUNCH_CHECK("mgtc_pack_kernel<A>");
   }
   {
     const int64_t total = (int64_t)a.NT * kDtBN * a.KS * 4;
     // B(k, j) = B[k*brs + j*bcs]: image row j, K index k
-    mgtc_pack_kernel<kDtBN><<<grid_for(total, 256, 8), 256, 0, s>>>(g.B, g.bcs, g.brs, g.N, g.K, a.KS, a.NT, g.mask,
-                                                                   g.mask.on ? g.mask_on_b : 0,
-                                                                   g.map.mode == 3 ? MgColMap{} : g.map, sc.b_img);
+    const int gr = grid_for(total, 256, 8);
+    const MgColMap bm = g.map.mode == 3 ? MgColMap{} : g.map;
+    const int mm = g.mask.on ? g.mask_on_b : 0;
+    if (g.brs == 1)
+      mgtc_pack_kernel<kDtBN, true><<<gr, 256, 0, s>>>(g.B, g.bcs, g.brs, g.N, g.K, a.KS, a.NT, g.mask, mm, bm, sc.b_img);
+    else
+      mgtc_pack_kernel<kDtBN, false><<<gr, 256, 0, s>>>(g.B, g.bcs, g.brs, g.N, g.K, a.KS, a.NT, g.mask, mm, bm, sc.b_img);
     FC_LAUNCH_CHECK("mgtc_pack_kernel<B>");
   }
   a.a_img = sc.a_img;
