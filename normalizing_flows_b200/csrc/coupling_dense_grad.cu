@@ -115,6 +115,26 @@ __global__ void __launch_bounds__(256) cg_transform_fwd_kernel(const float* __re
   const int lane = threadIdx.x & 31;
   if (r >= N) return;
   float s = 0.f;
+  if (ldo) {  // compact conditioner output: lanes walk the transformed dims only (no idle half)
+    const int nd = (D - tp + 1) / 2;
+    for (int k = lane; k < nd; k += 32) {
+      const int d = tp + 2 * k, dp = d ^ 1;
+      const float* oo = o + r * ldo + (int64_t)k * P;
+      float y, l1;
+      if (K > 0) {
+        rqs_apply<false, K>([&](int i) { return oo[i]; }, K, lo, hi, v[r * D + d], y, l1);
+      } else {
+        affine_apply<false>(oo[0], oo[1], v[r * D + d], y, l1);
+      }
+      s += l1;
+      out[r * D + d] = y;
+      if (dp < D) out[r * D + dp] = v[r * D + dp];
+      if (tp == 1 && (D & 1) && k == nd - 1) out[r * D + D - 1] = v[r * D + D - 1];
+    }
+    s = warp_sum(s);
+    if (lane == 0) ld[r] = first ? s : ld[r] + s;
+    return;
+  }
   for (int d = lane; d < D; d += 32) {
     const float x = v[r * D + d];
     float y = x;
@@ -189,6 +209,58 @@ __global__ void __launch_bounds__(128) cg_transform_bwd_kernel(const float* __re
   }
 }
 
+// The same adjoint on the COMPACT layout (tensor-core engine): item i = (sample r, k-th transformed dim) owns
+// the contiguous block o[i*PP .. i*PP+PP), so a warp's 32 items are one contiguous run.  The run is staged
+// through shared memory in both directions: global loads and stores are full 128-byte lines, each lane then
+// reads / writes its PP parameters at stride PP (odd: bank-conflict free).  Every lane works (the full-layout
+// kernel idles the pass-through half); it also forwards the gradient of its pass-through neighbour dim.
+template <int K>
+__global__ void __launch_bounds__(128) cg_transform_bwd_compact_kernel(const float* __restrict__ v, const float* __restrict__ o,
+                                                                      const float* __restrict__ g, float* __restrict__ gin,
+                                                                      float* __restrict__ dO, int64_t N, int D, int tp, float lo,
+                                                                      float hi) {
+  constexpr int PP = K > 0 ? 3 * K + 1 : 2;
+  __shared__ __align__(16) float sm[4][32 * PP];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nd = (D - tp + 1) / 2;
+  const int64_t items = N * nd, nwarps = (items + 31) / 32;
+  const float ldbar = -1.f / (float)N;
+  float* buf = sm[warp];
+  for (int64_t w = (int64_t)blockIdx.x * 4 + warp; w < nwarps; w += (int64_t)gridDim.x * 4) {
+    const int64_t i0 = w * 32;
+    const int cnt = (int)min((int64_t)32, items - i0);
+    const float* src = o + i0 * PP;
+    for (int e = lane; e < cnt * PP; e += 32) buf[e] = src[e];
+    __syncwarp();
+    const int64_t i = i0 + lane;
+    float obar[PP];
+    if (lane < cnt) {
+      const int64_t r = i / nd;
+      const int k = (int)(i - r * nd), d = tp + 2 * k;
+      const int64_t xi = r * D + d;
+      float ov[PP];
+#pragma unroll
+      for (int p = 0; p < PP; ++p) ov[p] = buf[lane * PP + p];
+      float y, l1, xbar;
+      if (K > 0) rqs_fwd_bwd<(K > 0 ? K : 1)>(ov, lo, hi, v[xi], g[xi], ldbar, y, l1, xbar, obar);
+      else affine_fwd_bwd(ov, v[xi], g[xi], ldbar, y, l1, xbar, obar);
+      gin[xi] = xbar;
+      const int dp = d ^ 1;  // the pass-through neighbour
+      if (dp < D) gin[r * D + dp] = g[r * D + dp];
+      if (tp == 1 && (D & 1) && k == nd - 1) gin[r * D + D - 1] = g[r * D + D - 1];  // odd D: the last dim has no pair
+    }
+    __syncwarp();
+    if (lane < cnt) {
+#pragma unroll
+      for (int p = 0; p < PP; ++p) buf[lane * PP + p] = obar[p];
+    }
+    __syncwarp();
+    float* dst = dO + i0 * PP;
+    for (int e = lane; e < cnt * PP; e += 32) dst[e] = buf[e];
+    __syncwarp();
+  }
+}
+
 // gin[:, visible dims] += dmx[:, visible dims]
 __global__ void __launch_bounds__(256) cg_add_visible_kernel(const float* __restrict__ dmx, float* __restrict__ gin, int64_t N,
                                                             int D, int tp) {
@@ -252,8 +324,12 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
     const int ncomp = ((D - tp + 1) / 2) * P;
     const int64_t ldo = L.tc ? ncomp : 0;
     const MgColMap cm = {0, P, 2 * P, tp * P};
-    cg_transform_bwd_kernel<K><<<grid_for((int64_t)n * D, 128, 32), 128, 0, s>>>(V(l), H(l, nh), G, S, dO, n, D, P, tp,
-                                                                                sp->range_min, sp->range_max, ldo);
+    if (ldo)
+      cg_transform_bwd_compact_kernel<K><<<grid_for(((int64_t)n * (ncomp / P) + 31) / 32, 4, 16), 128, 0, s>>>(
+          V(l), H(l, nh), G, S, dO, n, D, tp, sp->range_min, sp->range_max);
+    else
+      cg_transform_bwd_kernel<K><<<grid_for((int64_t)n * D, 128, 32), 128, 0, s>>>(V(l), H(l, nh), G, S, dO, n, D, P, tp,
+                                                                                  sp->range_min, sp->range_max, ldo);
     FC_LAUNCH_CHECK("cg_transform_bwd_kernel");
     cg_mask_input_kernel<<<eb, 256, 0, s>>>(V(l), MX, n, D, tp);
     const float* dout = dO;
