@@ -356,14 +356,22 @@ static int mgtc_launch(MgGemm g, const MgTcScratch& sc, cudaStream_t s) {
   if (a.KS < 1) a.KS = 1;
   a.S = 1;
   {
-    // split K whenever the output tiles alone leave most SMs idle (weight gradients: K = batch; input
-    // gradients of a wide last Linear: K = its width) and every split keeps at least 16 stages
-    int want = sm_count() / (a.MT * a.NT);
-    if (want > kMgTcSplits) want = kMgTcSplits;
-    if (want > a.KS / 16) want = a.KS / 16;  // a split must outweigh its pass over the partials
-    if (want < 1) want = 1;
-    while (want > 1 && (size_t)want * g.M * g.N > sc.part_floats) --want;
-    a.S = want;
+    // Split K when that shortens the schedule: cost(S) = waves(S) x stages per item + the pass over the
+    // partials, in units of one K stage (~0.65 us per CTA measured; the reduce streams (S+1) x M x N floats
+    // at ~3 TB/s).  Weight gradients (K = batch, few output tiles), the input gradient of a wide last Linear
+    // (K = its width) and tile counts just above the SM count (a two-wave tail) are the cases that split.
+    const int sms = sm_count(), items = a.MT * a.NT;
+    int smax = a.KS / 16;  // a split keeps at least 16 stages
+    if (smax > kMgTcSplits) smax = kMgTcSplits;
+    double best = 0.0;
+    for (int S = 1; S <= (smax < 1 ? 1 : smax); ++S) {
+      if (S > 1 && (size_t)S * g.M * g.N > sc.part_floats) break;
+      const int chunk = (a.KS + S - 1) / S;
+      const int Se = (a.KS + chunk - 1) / chunk;
+      double cost = (double)(((int64_t)items * Se + sms - 1) / sms) * chunk;
+      if (Se > 1) cost += (double)(Se + 1) * g.M * g.N * 4.0 / 3.0e12 / 0.65e-6;
+      if (S == 1 || cost < best) { best = cost; a.S = Se; }
+    }
   }
   a.ks_chunk = (a.KS + a.S - 1) / a.S;
   a.S = (a.KS + a.ks_chunk - 1) / a.ks_chunk;
