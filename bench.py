@@ -578,6 +578,7 @@ def main():
                        "l2": f"inputs rotate over {res['nbuf']} distinct batches ({res['nbuf'] * w.n * w.bytes_per_sample / 1e6:.0f} MB > 126 MB L2)"},
             "roofline": roofline(w, res, peaks),
             "e2e": res["e2e"],
+            **({"e2e_uint8": res["e2e_uint8"]} if res.get("e2e_uint8") else {}),
             "gpu_launches": res["launches"],
             "clocks": res["clocks"],
             "train": res.get("train"),
@@ -697,6 +698,8 @@ def time_workload(w, dev, rank, world, dist, W, K, ops, e2e, clocks):
            "nbuf": nbuf, "clocks": clk, "launches": K * (w.launches_per_step + (2 if dist is not None else 0))}
     if e2e:
         out["e2e"] = time_e2e(w, dev, host, dist, world, max(3, K // 2))
+        if getattr(w, "bytes_per_sample", 0) == 3140:  # the D=784 image workloads
+            out["e2e_uint8"] = time_e2e_u8(w, dev, rank, dist, world, max(3, K // 2), ops)
         out["train"] = w.train(dev, rank, world, dist, ops) if hasattr(w, "train") else time_train(w, dev, rank, world, dist, ops)
         if hasattr(w, "sampling"):
             out["sampling"] = w.sampling(dev)
@@ -753,11 +756,91 @@ def time_train(w, dev, rank, world, dist, ops, K=5, batch=1 << 18):
             "precision": "bf16x3 GEMMs (fp32 accumulate, fp32 stored activations)" if tc else "fp32"}
 
 
+def _capture(fn, stream):
+    """Capture `fn()` (the public-API call on fixed device buffers) into a CUDA graph replayed on `stream`;
+    None when FLOWCUDA_BENCH_GRAPH=0 or the capture fails (then the call is issued eagerly)."""
+    if os.environ.get("FLOWCUDA_BENCH_GRAPH", "1") == "0":
+        return None
+    try:
+        with torch.cuda.stream(stream):
+            fn()
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=stream):
+            out = fn()
+        torch.cuda.synchronize()
+        return g, out
+    except Exception as e:
+        print(f"bench: e2e CUDA-graph capture failed ({e!r}); eager launches", file=sys.stderr)
+        return None
+
+
+def _e2e_pipeline(w, dev, host, prep, dist, world, K, h2d_bytes, note=None):
+    """One API call per step (the D=784 workloads: ~45 short kernels), depth-2 pipeline: two device staging
+    buffers, each with its API call captured in a CUDA graph; step i+1's host->device copy runs under step i's
+    kernels and step i-1's read-back.  A slot is reissued only after its previous results reached the host."""
+    s_in, s_cmp, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    slots = []
+    for _ in range(2):
+        d = torch.empty_like(host[0], device=dev)
+        call = prep(d)
+        slots.append({"d": d, "call": call, "cap": _capture(call, s_cmp), "out": torch.empty(w.n, dtype=torch.float32).pin_memory(),
+                      "done": None})
+
+    def issue(i):
+        sl = slots[i % 2]
+        if sl["done"] is not None:
+            sl["done"].synchronize()
+        with torch.cuda.stream(s_in):
+            sl["d"].copy_(host[i % len(host)], non_blocking=True)
+            e_in = torch.cuda.Event()
+            e_in.record(s_in)
+        with torch.cuda.stream(s_cmp):
+            s_cmp.wait_event(e_in)
+            if sl["cap"]:
+                sl["cap"][0].replay()
+                lp = sl["cap"][1]
+            else:
+                lp = sl["call"]()
+            e_c = torch.cuda.Event()
+            e_c.record(s_cmp)
+        with torch.cuda.stream(s_out):
+            s_out.wait_event(e_c)
+            sl["out"].copy_(lp.reshape(-1), non_blocking=True)
+            sl["done"] = torch.cuda.Event()
+            sl["done"].record(s_out)
+        sl["keep"] = lp
+
+    for i in range(4):
+        issue(i)
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for i in range(K):
+        issue(i)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    if dist is not None:
+        t = torch.tensor([dt], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = t.item()
+    out = {"value": w.n * world * K / dt, "unit": "samples/s", "h2d_bytes_per_step": int(h2d_bytes),
+           "d2h_bytes_per_step": int(w.n * 4), "steps": K, "chunks": 1, "pipeline_depth": 2,
+           "finite": bool(torch.isfinite(slots[0]["out"]).all().item()),
+           "launch": "cuda-graph replay of the API call" if slots[0]["cap"] else "eager"}
+    if note:
+        out["input"] = note
+    return out
+
+
 def time_e2e(w, dev, host, dist, world, K):
     """Same metric through the public API with HOST buffers: every step copies its inputs from
     pinned host memory, runs log_prob, and reads the per-sample log_prob back to pinned host
     memory.  Chunked over three streams so that H2D, compute and D2H overlap."""
     chunks = 8 if w.n >= (1 << 16) else 1
+    if chunks == 1:
+        return _e2e_pipeline(w, dev, host, lambda d: (lambda: w.run(d)), dist, world, max(K, 6), host[0].numel() * 4)
     cs = w.n // chunks
     s_in, s_cmp, s_out = torch.cuda.Stream(dev), torch.cuda.Stream(dev), torch.cuda.Stream(dev)
     out_host = torch.empty(w.n, dtype=torch.float32).pin_memory()
@@ -800,7 +883,27 @@ def time_e2e(w, dev, host, dist, world, K):
         dt = t.item()
     del keep
     return {"value": w.n * world * K / dt, "unit": "samples/s", "h2d_bytes_per_step": int(host[0].numel() * 4),
-            "d2h_bytes_per_step": int(w.n * 4), "steps": K, "chunks": chunks}
+            "d2h_bytes_per_step": int(w.n * 4), "steps": K, "chunks": chunks, "launch": "eager"}
+
+
+def time_e2e_u8(w, dev, rank, dist, world, K, ops):
+    """The D=784 pipelines as the reference feeds them (src/maf_mnist.py:101-118): the HOST holds uint8 images;
+    every step copies the bytes (a quarter of the float32 image) from pinned memory, dequantises on the device
+    (`(u8 + U[0,1)) / 256`, Philox, csrc/densities.cu), runs log_prob and reads the result back."""
+    gen = torch.Generator().manual_seed(4242 + rank)
+    host = [torch.randint(0, 256, (w.n, 784), generator=gen, dtype=torch.uint8).pin_memory() for _ in range(3)]
+
+    def prep(d):
+        f = torch.empty(w.n, 784, device=dev, dtype=torch.float32)
+
+        def call():
+            ops.dequantize_u8(d, 7, offset=0, out=f)
+            return w.run(f)
+
+        return call
+
+    return _e2e_pipeline(w, dev, host, prep, dist, world, max(K, 6), w.n * 784,
+                         note="uint8 images in pinned host memory, dequantised on the device")
 
 
 if __name__ == "__main__":

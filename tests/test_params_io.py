@@ -73,3 +73,27 @@ def test_nested_lists_of_the_hand_rolled_real_nvp():
             assert np.array_equal(Wa, Wb) and np.array_equal(ba, bb)
     with pytest.raises(ValueError):
         io.flat_to_nested(flat[:-1], 8, [1, 4, 2])
+
+
+def test_density_generators_shard_the_stream_by_rank(monkeypatch):
+    """Host logic of densities.make_dataset_* (no GPU): batch b of a `world_size`-way run takes samples
+    [b*batch + rank*local, +local) of the stream, so the ranks' slices tile the single-rank batch."""
+    from normalizing_flows_b200 import densities, ops
+
+    calls = []
+
+    def fake(kind, seed, n, offset=0, device=None, **kw):
+        calls.append((kind, seed, n, offset, kw))
+        return torch.zeros(n, 2)
+
+    monkeypatch.setattr(ops, "density_sample", fake)
+    list(densities.make_dataset_energy_3(9, batch_size=96, num_batches=2))
+    assert [(c[2], c[3]) for c in calls] == [(96, 0), (96, 96)]
+    calls.clear()
+    for rank in range(3):
+        list(densities.make_dataset_gaussian_blobs(9, batch_size=96, num_batches=2, num_blobs=5, r=1.5, rank=rank, world_size=3))
+    spans = sorted((c[3], c[3] + c[2]) for c in calls)
+    assert spans == [(0, 32), (32, 64), (64, 96), (96, 128), (128, 160), (160, 192)]
+    assert all(c[0] == "gaussian_blobs" and c[4] == {"num_blobs": 5, "r": 1.5} for c in calls)
+    with pytest.raises(ValueError):
+        list(densities.make_dataset_banana(1, batch_size=10, world_size=4))
