@@ -355,6 +355,18 @@ __global__ void __launch_bounds__(kDtThreads, 1) dense_tc_gemm_kernel(DtGemm a, 
       }
       if (group == 0) asm volatile("bar.sync 1, 128;" ::: "memory");  // this epilogue group only
       else asm volatile("bar.sync 2, 128;" ::: "memory");
+      if (EPI != kEpiHidden) {
+        // the bijector reads this tile's slice of the state v (it left L2 while the Linears streamed their
+        // images): pull the thread's row of the slice into L2 now, under the tile's MMAs
+        const int64_t prow = (int64_t)mt * 128 + (warp & 3) * 32 + lane;
+        const int dlo = nt * a.dpt, nd = min(a.dpt, a.ndims - dlo);
+        if (prow < a.N && nd > 0) {
+          const float* p0 = a.v + prow * a.D + a.tp + a.dstride * dlo;
+          const uintptr_t q1 = (uintptr_t)(p0 + a.dstride * (nd - 1));
+          for (uintptr_t q = (uintptr_t)p0 & ~(uintptr_t)127; q <= q1; q += 128)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
+        }
+      }
       tc::mbar_wait(&acc_full[slot], aph);
       tc::tc_fence_after();
       const uint32_t tb = tmem + slot * (uint32_t)kDtBN + ((uint32_t)((warp & 3) * 32) << 16);
