@@ -579,6 +579,7 @@ def main():
             "roofline": roofline(w, res, peaks),
             "e2e": res["e2e"],
             **({"e2e_uint8": res["e2e_uint8"]} if res.get("e2e_uint8") else {}),
+            **({"prepared": res["prepared"]} if res.get("prepared") else {}),
             "gpu_launches": res["launches"],
             "clocks": res["clocks"],
             "train": res.get("train"),
@@ -698,6 +699,8 @@ def time_workload(w, dev, rank, world, dist, W, K, ops, e2e, clocks):
            "nbuf": nbuf, "clocks": clk, "launches": K * (w.launches_per_step + (2 if dist is not None else 0))}
     if e2e:
         out["e2e"] = time_e2e(w, dev, host, dist, world, max(3, K // 2))
+        if getattr(w, "bytes_per_sample", 0) == 3140 and hasattr(w.model, "prepare"):
+            out["prepared"] = time_prepared(w, bufs, K)
         if getattr(w, "bytes_per_sample", 0) == 3140:  # the D=784 image workloads
             out["e2e_uint8"] = time_e2e_u8(w, dev, rank, dist, world, max(3, K // 2), ops)
         out["train"] = w.train(dev, rank, world, dist, ops) if hasattr(w, "train") else time_train(w, dev, rank, world, dist, ops)
@@ -754,6 +757,34 @@ def time_train(w, dev, rank, world, dist, ops, K=5, batch=1 << 18):
             "ms_per_step": ms / K, "final_loss": float(loss.item()), "optimizer": "adam(1e-4)",
             "grad_allreduce_bytes": int(p.numel() * 4) if dist is not None else 0,
             "precision": "bf16x3 GEMMs (fp32 accumulate, fp32 stored activations)" if tc else "fp32"}
+
+
+def time_prepared(w, bufs, K):
+    """Serving variant of the same step: the weights are packed into tile images ONCE (Transformed.prepare —
+    parameters do not change between inference calls) instead of on every call; inputs resident, graph replay."""
+    w.model.prepare(w.n)
+    side = torch.cuda.Stream()
+    try:
+        outs = []
+        for b in bufs[:2]:
+            cap = _capture(lambda b=b: w.run(b), side)
+            if cap is None:
+                return None
+            outs.append(cap)
+        for g, _ in outs:
+            g.replay()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(K):
+            outs[i % 2][0].replay()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / K
+        return {"value": w.n / (ms * 1e-3), "unit": "samples/s per GPU", "ms_per_step": ms,
+                "note": "weights pre-packed once (Transformed.prepare); the headline value re-packs them every call"}
+    finally:
+        w.model.invalidate()
 
 
 def _capture(fn, stream):

@@ -182,6 +182,23 @@ int flowcuda_coupling_sample(const flowcuda_coupling_spec* spec, const float* pa
                              int layer_begin, int layer_end,
                              void* workspace, size_t workspace_bytes, void* stream);
 
+/* Serving (precision BF16X3): repeated calls with UNCHANGED parameters need not re-pack the
+ * weights into tile images.  pack_weights writes the images into `workspace` (they sit at
+ * its start, independent of n; size the workspace for the largest batch to come); the
+ * *_packed calls are log_prob / sample without that pass.  The caller promises that
+ * `params`, `spec` and `workspace` are the ones given to pack_weights and that the
+ * parameters have not changed since (biases are still read from `params`). */
+int flowcuda_coupling_pack_weights(const flowcuda_coupling_spec* spec, const float* params,
+                                   void* workspace, size_t workspace_bytes, void* stream);
+int flowcuda_coupling_log_prob_packed(const flowcuda_coupling_spec* spec, const float* params,
+                                      const float* x, float* log_prob, float* z, float* log_det,
+                                      int64_t n, int layer_begin, int layer_end, int with_base,
+                                      void* workspace, size_t workspace_bytes, void* stream);
+int flowcuda_coupling_sample_packed(const flowcuda_coupling_spec* spec, const float* params,
+                                    const float* z, float* x, float* log_det, int64_t n,
+                                    int layer_begin, int layer_end,
+                                    void* workspace, size_t workspace_bytes, void* stream);
+
 /* value_and_grad of loss = -mean(Transformed.log_prob(x)) w.r.t. the flow parameters
  * (real_nvp_toy_densities.py:139-151,170; maf_toy_densities.py:140-152,171): hand-written
  * reverse mode, deterministic reductions (bit-identical run to run).  loss[1],
@@ -238,6 +255,14 @@ int flowcuda_made_sample(const flowcuda_made_spec* spec, const float* params, co
  * step of src/maf_mnist.py:134-166 applied to the MADE flow): hand-written FP32 reverse mode over
  * stored activations, fixed summation order (bit-reproducible).  loss[1], grad[param_count]
  * (layout of `params`; masked-out weights get exactly 0).  Needs num_hidden == 2. */
+/* Serving: as flowcuda_coupling_pack_weights / _log_prob_packed, for the MADE flow. */
+int flowcuda_made_pack_weights(const flowcuda_made_spec* spec, const float* params, void* workspace,
+                               size_t workspace_bytes, void* stream);
+int flowcuda_made_log_prob_packed(const flowcuda_made_spec* spec, const float* params, const float* x,
+                                  float* log_prob, float* u, float* log_det, int64_t n,
+                                  int with_base, void* workspace, size_t workspace_bytes,
+                                  void* stream);
+
 size_t flowcuda_made_nll_grad_workspace_bytes(const flowcuda_made_spec* spec, int64_t n);
 int flowcuda_made_nll_grad(const flowcuda_made_spec* spec, const float* params, const float* x,
                            int64_t n, float* loss, float* grad, void* workspace,

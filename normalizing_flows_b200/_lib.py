@@ -87,6 +87,11 @@ SIGNATURES = {
     "flowcuda_made_log_prob": (_i, [_mspec, _p, _p, _p, _p, _p, _i64, _i, _p, _sz, _p]),
     "flowcuda_made_sample": (_i, [_mspec, _p, _p, _p, _i64, _p]),
     "flowcuda_made_nll_grad_workspace_bytes": (_sz, [_mspec, _i64]),
+    "flowcuda_coupling_pack_weights": (_i, [_spec, _p, _p, _sz, _p]),
+    "flowcuda_coupling_log_prob_packed": (_i, [_spec, _p, _p, _p, _p, _p, _i64, _i, _i, _i, _p, _sz, _p]),
+    "flowcuda_coupling_sample_packed": (_i, [_spec, _p, _p, _p, _p, _i64, _i, _i, _p, _sz, _p]),
+    "flowcuda_made_pack_weights": (_i, [_mspec, _p, _p, _sz, _p]),
+    "flowcuda_made_log_prob_packed": (_i, [_mspec, _p, _p, _p, _p, _p, _i64, _i, _p, _sz, _p]),
     "flowcuda_made_nll_grad": (_i, [_mspec, _p, _p, _i64, _p, _p, _p, _sz, _p]),
     "flowcuda_density_sample": (_i, [_i, _u64, _u64, _i, _f, _p, _i64, _p]),
     "flowcuda_dequantize_u8": (_i, [_p, _u64, _u64, _p, _i64, _p]),

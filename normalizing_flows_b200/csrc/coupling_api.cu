@@ -14,7 +14,7 @@ bool coupling_dense_tc_supported(const flowcuda_coupling_spec* sp);
 size_t coupling_dense_tc_workspace_bytes(const flowcuda_coupling_spec* sp, int64_t n);
 int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params, const float* in, float* out_v,
                           float* out_lp, float* out_ld, int64_t n, int layer_begin, int layer_end, int with_base,
-                          bool inverse, void* workspace, size_t workspace_bytes, cudaStream_t s);
+                          bool inverse, void* workspace, size_t workspace_bytes, cudaStream_t s, int mode);
 int64_t coupling_param_count(const flowcuda_coupling_spec* sp);
 size_t coupling_dense_workspace_bytes(const flowcuda_coupling_spec* sp, int64_t n);
 int coupling_dense_run(const flowcuda_coupling_spec* sp, const float* params, const float* in, float* out_v,
@@ -45,7 +45,7 @@ static bool toy_eligible(const flowcuda_coupling_spec* sp) {
 
 static int run(const flowcuda_coupling_spec* sp, const float* params, const float* in, float* out_v, float* out_lp,
                float* out_ld, int64_t n, int lb, int le, int with_base, bool inverse, void* ws, size_t wsb,
-               cudaStream_t s) {
+               cudaStream_t s, int mode = 0) {
   int rc = check_spec(sp);
   if (rc) return rc;
   FC_REQUIRE(n >= 0, "coupling: negative n");
@@ -53,7 +53,8 @@ static int run(const flowcuda_coupling_spec* sp, const float* params, const floa
   FC_REQUIRE(params && in, "coupling: NULL params or input");
   FC_REQUIRE(lb >= 0 && le <= sp->num_layers && lb <= le, "coupling: layer range [%d,%d) outside [0,%d]", lb, le, sp->num_layers);
   if (sp->precision == FLOWCUDA_PRECISION_BF16X3)
-    return coupling_dense_tc_run(sp, params, in, out_v, out_lp, out_ld, n, lb, le, with_base, inverse, ws, wsb, s);
+    return coupling_dense_tc_run(sp, params, in, out_v, out_lp, out_ld, n, lb, le, with_base, inverse, ws, wsb, s, mode);
+  FC_REQUIRE(mode == 0, "coupling: packed weight images exist for precision BF16X3 only");
   if (sp->precision != FLOWCUDA_PRECISION_FP32) {
     FC_REQUIRE(sp->precision == FLOWCUDA_PRECISION_3XTF32 && toy_eligible(sp) && le > lb,
                "coupling: precision %d is not available for this flow shape (3xTF32 needs event_dim 2, two hidden layers <= 64)",
@@ -116,6 +117,35 @@ int flowcuda_coupling_sample(const flowcuda_coupling_spec* spec, const float* pa
   FC_REQUIRE(x || log_det, "coupling_sample: no output requested");
   return run(spec, params, z, x, nullptr, log_det, n, layer_begin, layer_end, 0, true, workspace, workspace_bytes,
              (cudaStream_t)stream);
+}
+
+int flowcuda_coupling_pack_weights(const flowcuda_coupling_spec* spec, const float* params, void* workspace,
+                                   size_t workspace_bytes, void* stream) {
+  int rc = check_spec(spec);
+  if (rc) return rc;
+  FC_REQUIRE(params && workspace, "coupling_pack_weights: NULL params or workspace");
+  FC_REQUIRE(spec->precision == FLOWCUDA_PRECISION_BF16X3, "coupling_pack_weights: precision BF16X3 only");
+  return coupling_dense_tc_run(spec, params, nullptr, nullptr, nullptr, nullptr, 0, 0, spec->num_layers, 0, false, workspace,
+                               workspace_bytes, (cudaStream_t)stream, 2);
+}
+
+int flowcuda_coupling_log_prob_packed(const flowcuda_coupling_spec* spec, const float* params, const float* x,
+                                      float* log_prob, float* z, float* log_det, int64_t n, int layer_begin,
+                                      int layer_end, int with_base, void* workspace, size_t workspace_bytes,
+                                      void* stream) {
+  if (n == 0) return FLOWCUDA_OK;
+  FC_REQUIRE(log_prob || z || log_det, "coupling_log_prob_packed: no output requested");
+  return run(spec, params, x, z, log_prob, log_det, n, layer_begin, layer_end, with_base, false, workspace,
+             workspace_bytes, (cudaStream_t)stream, 1);
+}
+
+int flowcuda_coupling_sample_packed(const flowcuda_coupling_spec* spec, const float* params, const float* z, float* x,
+                                    float* log_det, int64_t n, int layer_begin, int layer_end, void* workspace,
+                                    size_t workspace_bytes, void* stream) {
+  if (n == 0) return FLOWCUDA_OK;
+  FC_REQUIRE(x || log_det, "coupling_sample_packed: no output requested");
+  return run(spec, params, z, x, nullptr, log_det, n, layer_begin, layer_end, 0, true, workspace, workspace_bytes,
+             (cudaStream_t)stream, 1);
 }
 
 }  // extern "C"

@@ -110,6 +110,12 @@ static bool dt_layout(const flowcuda_coupling_spec* sp, int64_t n, DtLayout& L) 
     L.NT[i] = i < nh ? (L.sizes[i + 1] + kDtBN - 1) / kDtBN : L.tiles;
   }
   size_t off = 0;
+  // the weight images come first: their offsets do not depend on n, so a workspace packed once
+  // (flowcuda_*_pack_weights) serves every later batch size that fits it
+  for (int i = 0; i < L.nlin; ++i) {
+    L.off_w[i] = off;
+    off = dt_al256(off + (size_t)sp->num_layers * L.NT[i] * L.KS[i] * 2 * kDtBBytes);
+  }
   L.off_v = off; off = dt_al256(off + (size_t)n * D * 4);
   L.off_ld = off; off = dt_al256(off + (size_t)n * 4);
   L.off_ldp = off; off = dt_al256(off + (size_t)n * L.tiles * 4);
@@ -117,10 +123,6 @@ static bool dt_layout(const flowcuda_coupling_spec* sp, int64_t n, DtLayout& L) 
   int ksh = 1;
   for (int i = 1; i < L.nlin; ++i) ksh = L.KS[i] > ksh ? L.KS[i] : ksh;
   for (int j = 0; j < 2; ++j) { L.off_h[j] = off; off = dt_al256(off + (size_t)L.MT * ksh * 2 * kDtABytes); }
-  for (int i = 0; i < L.nlin; ++i) {
-    L.off_w[i] = off;
-    off = dt_al256(off + (size_t)sp->num_layers * L.NT[i] * L.KS[i] * 2 * kDtBBytes);
-  }
   L.total = off + 256;
   return true;
 }
@@ -138,7 +140,8 @@ size_t coupling_dense_tc_workspace_bytes(const flowcuda_coupling_spec* sp, int64
 
 int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params, const float* in, float* out_v,
                           float* out_lp, float* out_ld, int64_t n, int layer_begin, int layer_end, int with_base,
-                          bool inverse, void* workspace, size_t workspace_bytes, cudaStream_t s) {
+                          bool inverse, void* workspace, size_t workspace_bytes, cudaStream_t s, int mode) {
+  // mode 0: pack the weights, then run; 1: the workspace already holds this flow's weight images; 2: pack only
   DtLayout L;
   if (!dt_layout(sp, n, L)) {
     set_error("coupling(bf16x3): needs RQS with 8 bins or per-dimension affine and >= 1 hidden layer");
@@ -153,9 +156,9 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
   float* v = (float*)(ws + L.off_v);
   float* ld = (float*)(ws + L.off_ld);
   float* ldp = (float*)(ws + L.off_ldp);
-  FC_CUDA(cudaMemcpyAsync(v, in, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  if (mode != 2) FC_CUDA(cudaMemcpyAsync(v, in, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToDevice, s));
   // pack every Linear of every layer (masks folded in)
-  for (int i = 0; i < L.nlin; ++i) {
+  for (int i = 0; i < L.nlin && mode != 1; ++i) {
     DtPackW p;
     p.params = params; p.per_layer = L.per_layer; p.w_off = L.w_off[i];
     p.k_in = L.sizes[i]; p.n_out = L.sizes[i + 1];
@@ -166,6 +169,7 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
     dense_tc_pack_w_kernel<<<dim3(blocks, L.NT[i], sp->num_layers), 256, 0, s>>>(p);
     FC_LAUNCH_CHECK("dense_tc_pack_w_kernel");
   }
+  if (mode == 2) return FLOWCUDA_OK;
   const int nl = layer_end - layer_begin;
   for (int it = 0; it < nl; ++it) {
     const int l = inverse ? layer_begin + it : layer_end - 1 - it;

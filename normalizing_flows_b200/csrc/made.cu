@@ -64,6 +64,12 @@ static bool made_layout(const flowcuda_made_spec* sp, int64_t n, MadeLayout& L) 
     if (L.KS[i] > 255) return false;  // ks_tile entries are bytes
   }
   size_t off = 0;
+  // the weight images come first: their offsets do not depend on n, so a workspace packed once
+  // (flowcuda_*_pack_weights) serves every later batch size that fits it
+  for (int i = 0; i < L.nlin; ++i) {
+    L.off_w[i] = off;
+    off = dt_al256(off + (size_t)sp->num_layers * L.NT[i] * L.KS[i] * 2 * kDtBBytes);
+  }
   L.off_v = off; off = dt_al256(off + (size_t)n * D * 4);
   L.off_ld = off; off = dt_al256(off + (size_t)n * 4);
   L.off_ldp = off; off = dt_al256(off + (size_t)n * L.tiles * 4);
@@ -71,10 +77,6 @@ static bool made_layout(const flowcuda_made_spec* sp, int64_t n, MadeLayout& L) 
   int ksh = 1;
   for (int i = 1; i < L.nlin; ++i) ksh = L.KS[i] > ksh ? L.KS[i] : ksh;
   for (int j = 0; j < 2; ++j) { L.off_h[j] = off; off = dt_al256(off + (size_t)L.MT * ksh * 2 * kDtABytes); }
-  for (int i = 0; i < L.nlin; ++i) {
-    L.off_w[i] = off;
-    off = dt_al256(off + (size_t)sp->num_layers * L.NT[i] * L.KS[i] * 2 * kDtBBytes);
-  }
   L.total = off + 256;
   return true;
 }
@@ -169,7 +171,8 @@ static int made_check(const flowcuda_made_spec* sp) {
 
 static int made_log_prob_run(const flowcuda_made_spec* sp, const float* params, const float* x, float* out_lp,
                              float* out_u, float* out_ld, int64_t n, int with_base, void* workspace,
-                             size_t workspace_bytes, cudaStream_t s) {
+                             size_t workspace_bytes, cudaStream_t s, int mode = 0) {
+  // mode 0: pack the weights, then run; 1: the workspace already holds this flow's weight images; 2: pack only
   MadeLayout L;
   if (!made_layout(sp, n, L)) {
     set_error("made: layer too wide for the packed K-stage table");
@@ -184,8 +187,8 @@ static int made_log_prob_run(const flowcuda_made_spec* sp, const float* params, 
   float* v = (float*)(ws + L.off_v);
   float* ld = (float*)(ws + L.off_ld);
   float* ldp = (float*)(ws + L.off_ldp);
-  FC_CUDA(cudaMemcpyAsync(v, x, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToDevice, s));
-  for (int i = 0; i < L.nlin; ++i) {
+  if (mode != 2) FC_CUDA(cudaMemcpyAsync(v, x, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  for (int i = 0; i < L.nlin && mode != 1; ++i) {
     MadePackW p;
     p.params = params; p.per_layer = L.per_layer; p.w_off = L.w_off[i];
     p.k_in = L.sizes[i]; p.n_out = L.sizes[i + 1];
@@ -196,6 +199,7 @@ static int made_log_prob_run(const flowcuda_made_spec* sp, const float* params, 
     made_tc_pack_w_kernel<<<dim3(blocks, L.NT[i], sp->num_layers), 256, 0, s>>>(p);
     FC_LAUNCH_CHECK("made_tc_pack_w_kernel");
   }
+  if (mode == 2) return FLOWCUDA_OK;
   for (int it = 0; it < sp->num_layers; ++it) {
     const int l = sp->num_layers - 1 - it;  // data -> base: last layer first
     const bool rev = (l & 1) != 0;
@@ -522,6 +526,28 @@ int flowcuda_made_log_prob(const flowcuda_made_spec* spec, const float* params, 
   FC_REQUIRE(log_prob || u || log_det, "made_log_prob: no output requested");
   return made_log_prob_run(spec, params, x, log_prob, u, log_det, n, with_base, workspace, workspace_bytes,
                            (cudaStream_t)stream);
+}
+
+int flowcuda_made_pack_weights(const flowcuda_made_spec* spec, const float* params, void* workspace, size_t workspace_bytes,
+                               void* stream) {
+  int rc = made_check(spec);
+  if (rc) return rc;
+  FC_REQUIRE(params && workspace, "made_pack_weights: NULL params or workspace");
+  return made_log_prob_run(spec, params, nullptr, nullptr, nullptr, nullptr, 0, 0, workspace, workspace_bytes,
+                           (cudaStream_t)stream, 2);
+}
+
+int flowcuda_made_log_prob_packed(const flowcuda_made_spec* spec, const float* params, const float* x, float* log_prob,
+                                  float* u, float* log_det, int64_t n, int with_base, void* workspace,
+                                  size_t workspace_bytes, void* stream) {
+  int rc = made_check(spec);
+  if (rc) return rc;
+  FC_REQUIRE(n >= 0, "made_log_prob_packed: negative n");
+  if (n == 0) return FLOWCUDA_OK;
+  FC_REQUIRE(params && x, "made_log_prob_packed: NULL params or input");
+  FC_REQUIRE(log_prob || u || log_det, "made_log_prob_packed: no output requested");
+  return made_log_prob_run(spec, params, x, log_prob, u, log_det, n, with_base, workspace, workspace_bytes,
+                           (cudaStream_t)stream, 1);
 }
 
 int flowcuda_made_sample(const flowcuda_made_spec* spec, const float* params, const float* z, float* x, int64_t n,

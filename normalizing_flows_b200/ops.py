@@ -190,9 +190,53 @@ def _workspace(spec: CouplingSpec, n: int, device) -> Tuple[Optional[torch.Tenso
     return ws, ws.numel() * 4
 
 
+class PackedWeights:
+    """A workspace whose head holds a flow's weights as tensor-core tile images (flowcuda_*_pack_weights), sized
+    for batches up to `max_batch`.  Passing it to log_prob / sample skips the per-call packing pass; valid only
+    while the parameters it was packed from are unchanged (the caller's promise — the library cannot see
+    writes through raw pointers, e.g. its own optimiser kernels)."""
+
+    def __init__(self, workspace: torch.Tensor, max_batch: int, kind: str):
+        self.workspace, self.max_batch, self.kind = workspace, int(max_batch), kind
+
+    @property
+    def nbytes(self) -> int:
+        return self.workspace.numel() * self.workspace.element_size()
+
+
+def coupling_pack_weights(spec: CouplingSpec, params: torch.Tensor, max_batch: int) -> PackedWeights:
+    _dev_check(params)
+    lib = _lib.load()
+    need = lib.flowcuda_coupling_workspace_bytes(C.byref(spec), int(max_batch))
+    ws = torch.empty((need + 3) // 4, device=params.device, dtype=torch.float32)
+    check(lib.flowcuda_coupling_pack_weights(C.byref(spec), _ptr(params), _ptr(ws), ws.numel() * 4, _stream()),
+          "coupling_pack_weights")
+    return PackedWeights(ws, max_batch, "coupling")
+
+
+def made_pack_weights(spec: "_lib.MadeSpec", params: torch.Tensor, max_batch: int) -> PackedWeights:
+    _dev_check(params)
+    lib = _lib.load()
+    need = lib.flowcuda_made_workspace_bytes(C.byref(spec), int(max_batch))
+    ws = torch.empty((need + 3) // 4, device=params.device, dtype=torch.float32)
+    check(lib.flowcuda_made_pack_weights(C.byref(spec), _ptr(params), _ptr(ws), ws.numel() * 4, _stream()),
+          "made_pack_weights")
+    return PackedWeights(ws, max_batch, "made")
+
+
+def _use_packed(packed: Optional[PackedWeights], kind: str, n: int) -> bool:
+    if packed is None:
+        return False
+    if packed.kind != kind:
+        raise _lib.FlowCudaError(f"packed weights of a {packed.kind} flow given to a {kind} call")
+    if n > packed.max_batch:
+        raise _lib.FlowCudaError(f"batch {n} exceeds the packed workspace's max_batch {packed.max_batch}")
+    return True
+
+
 def coupling_log_prob(spec: CouplingSpec, params: torch.Tensor, x: torch.Tensor, want_z: bool = False,
                       want_log_det: bool = False, want_log_prob: bool = True, layers: Optional[Tuple[int, int]] = None,
-                      with_base: bool = True):
+                      with_base: bool = True, packed: Optional[PackedWeights] = None):
     """Data -> base direction (Transformed.log_prob).  Returns (log_prob, z, log_det) with None
     for outputs that were not requested."""
     x = _f32(x).reshape(x.shape[0], -1)
@@ -202,6 +246,11 @@ def coupling_log_prob(spec: CouplingSpec, params: torch.Tensor, x: torch.Tensor,
     lp = torch.empty(n, device=x.device, dtype=torch.float32) if want_log_prob else None
     z = torch.empty_like(x) if want_z else None
     ld = torch.empty(n, device=x.device, dtype=torch.float32) if want_log_det else None
+    if _use_packed(packed, "coupling", n):
+        check(_lib.load().flowcuda_coupling_log_prob_packed(C.byref(spec), _ptr(params), _ptr(x), _ptr(lp), _ptr(z), _ptr(ld),
+                                                            n, lb, le, int(with_base), _ptr(packed.workspace), packed.nbytes,
+                                                            _stream()), "coupling_log_prob_packed")
+        return lp, z, ld
     ws, wsb = _workspace(spec, n, x.device)
     check(_lib.load().flowcuda_coupling_log_prob(C.byref(spec), _ptr(params), _ptr(x), _ptr(lp), _ptr(z), _ptr(ld), n,
                                                  lb, le, int(with_base), _ptr(ws), wsb, _stream()), "coupling_log_prob")
@@ -209,7 +258,7 @@ def coupling_log_prob(spec: CouplingSpec, params: torch.Tensor, x: torch.Tensor,
 
 
 def coupling_sample(spec: CouplingSpec, params: torch.Tensor, z: torch.Tensor, want_log_det: bool = False,
-                    layers: Optional[Tuple[int, int]] = None):
+                    layers: Optional[Tuple[int, int]] = None, packed: Optional[PackedWeights] = None):
     """Base -> data direction (Transformed.sample with the noise given).  Returns (x, log_det)."""
     z = _f32(z).reshape(z.shape[0], -1)
     _dev_check(params, z)
@@ -217,6 +266,11 @@ def coupling_sample(spec: CouplingSpec, params: torch.Tensor, z: torch.Tensor, w
     lb, le = layers if layers is not None else (0, spec.num_layers)
     x = torch.empty_like(z)
     ld = torch.empty(n, device=z.device, dtype=torch.float32) if want_log_det else None
+    if _use_packed(packed, "coupling", n):
+        check(_lib.load().flowcuda_coupling_sample_packed(C.byref(spec), _ptr(params), _ptr(z), _ptr(x), _ptr(ld), n, lb, le,
+                                                          _ptr(packed.workspace), packed.nbytes, _stream()),
+              "coupling_sample_packed")
+        return x, ld
     ws, wsb = _workspace(spec, n, z.device)
     check(_lib.load().flowcuda_coupling_sample(C.byref(spec), _ptr(params), _ptr(z), _ptr(x), _ptr(ld), n, lb, le,
                                                _ptr(ws), wsb, _stream()), "coupling_sample")
@@ -262,7 +316,7 @@ def made_param_count(spec: _lib.MadeSpec) -> int:
 
 def made_log_prob(spec: _lib.MadeSpec, params: torch.Tensor, x: torch.Tensor, want_u: bool = False,
                   want_log_det: bool = False, want_log_prob: bool = True, with_base: bool = True,
-                  workspace: Optional[torch.Tensor] = None):
+                  workspace: Optional[torch.Tensor] = None, packed: Optional[PackedWeights] = None):
     """MAF density pass (data -> base).  Returns (log_prob, u, log_det), None where not requested."""
     x = _f32(x).reshape(x.shape[0], spec.event_dim)
     _dev_check(params, x)
@@ -271,6 +325,11 @@ def made_log_prob(spec: _lib.MadeSpec, params: torch.Tensor, x: torch.Tensor, wa
     lp = torch.empty(n, device=x.device, dtype=torch.float32) if want_log_prob else None
     u = torch.empty_like(x) if want_u else None
     ld = torch.empty(n, device=x.device, dtype=torch.float32) if want_log_det else None
+    if _use_packed(packed, "made", n):
+        check(lib.flowcuda_made_log_prob_packed(C.byref(spec), _ptr(params), _ptr(x), _ptr(lp), _ptr(u), _ptr(ld), n,
+                                                int(with_base), _ptr(packed.workspace), packed.nbytes, _stream()),
+              "made_log_prob_packed")
+        return lp, u, ld
     need = lib.flowcuda_made_workspace_bytes(C.byref(spec), n)
     if workspace is None or workspace.numel() * workspace.element_size() < need:
         workspace = torch.empty((need + 3) // 4, device=x.device, dtype=torch.float32)

@@ -199,3 +199,48 @@ def test_deep16_made_stack_d784():
     ref = O.maf_log_prob(ospec, params, x.double()).numpy()
     err = np.abs(lp.double().cpu().numpy() - ref).max()
     assert err <= 1e-3, err
+
+
+def test_packed_weights_serving_path_is_bit_identical():
+    """flowcuda_*_pack_weights + *_log_prob_packed (serving: parameters unchanged between calls): same bits as
+    the repacking call, for several batch sizes against ONE packed workspace; a too-large batch is refused;
+    stale images are the caller's responsibility (prepare again after an update) and are detectable."""
+    from normalizing_flows_b200 import _lib, flows, ops
+
+    ospec = O.MadeSpec(160, 3, [96, 200])
+    params = O.init_made_params(ospec, seed=12, scale=0.3)
+    flat = G(O.flatten_layers(params))
+    spec = _spec(ops, ospec)
+    pk = ops.made_pack_weights(spec, flat, 500)
+    for n in (1, 130, 500):
+        x = torch.randn(n, 160, generator=torch.Generator().manual_seed(n)).cuda()
+        a = ops.made_log_prob(spec, flat, x, want_u=True, want_log_det=True)
+        b = ops.made_log_prob(spec, flat, x, want_u=True, want_log_det=True, packed=pk)
+        assert all(torch.equal(p, q) for p, q in zip(a, b))
+    with pytest.raises(_lib.FlowCudaError):
+        ops.made_log_prob(spec, flat, torch.zeros(501, 160, device="cuda"), packed=pk)
+    # the host mirror: prepare() / invalidate()
+    model = flows.make_maf_model((160,), 3, [96, 200], params=flat)
+    x = torch.randn(77, 160, generator=torch.Generator().manual_seed(5)).cuda()
+    ref = model.log_prob(x)
+    assert torch.equal(model.prepare(128).log_prob(x), ref)
+    model.bijector.params.mul_(1.5)                       # an update the library cannot see
+    stale = model.log_prob(x)
+    model.invalidate()
+    fresh = model.log_prob(x)
+    assert not torch.equal(stale, fresh)
+    assert torch.equal(model.prepare(128).log_prob(x), fresh)
+    # coupling stacks (bf16x3)
+    cspec_o = O.CouplingSpec(40, 2, [32, 32, 32], "rqs", 8, 0.0, 1.0, "uniform")
+    cp = G(O.flatten_layers(O.init_coupling_params(cspec_o, seed=3, scale=0.3)))
+    cspec = ops.make_spec(40, 2, [32, 32, 32], 2, 8, 0.0, 1.0, _lib.BASE_UNIFORM01, _lib.PRECISION_BF16X3)
+    cpk = ops.coupling_pack_weights(cspec, cp, 300)
+    xc = torch.rand(300, 40, generator=torch.Generator().manual_seed(1)).cuda()
+    a = ops.coupling_log_prob(cspec, cp, xc, want_z=True, want_log_det=True)
+    b = ops.coupling_log_prob(cspec, cp, xc, want_z=True, want_log_det=True, packed=cpk)
+    assert all(torch.equal(p, q) for p, q in zip(a, b))
+    sa, _ = ops.coupling_sample(cspec, cp, xc[:50])
+    sb, _ = ops.coupling_sample(cspec, cp, xc[:50], packed=cpk)
+    assert torch.equal(sa, sb)
+    with pytest.raises(_lib.FlowCudaError):
+        ops.coupling_pack_weights(ops.make_spec(40, 2, [32, 32, 32], 2, 8, 0.0, 1.0, _lib.BASE_UNIFORM01, 0), cp, 10)
