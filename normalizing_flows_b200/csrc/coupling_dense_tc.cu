@@ -118,7 +118,7 @@ static bool dt_layout(const flowcuda_coupling_spec* sp, int64_t n, DtLayout& L) 
   }
   L.off_v = off; off = dt_al256(off + (size_t)n * D * 4);
   L.off_ld = off; off = dt_al256(off + (size_t)n * 4);
-  L.off_ldp = off; off = dt_al256(off + (size_t)n * L.tiles * 4);
+  L.off_ldp = off; off = dt_al256(off + (size_t)n * L.tiles * 2 * 4);  // two partials per (row, tile)
   L.off_x = off; off = dt_al256(off + (size_t)L.MT * L.KS[0] * 2 * kDtABytes);
   int ksh = 1;
   for (int i = 1; i < L.nlin; ++i) ksh = L.KS[i] > ksh ? L.KS[i] : ksh;
@@ -192,7 +192,7 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
       g.n_out = L.sizes[i + 1];
       g.out_img = nullptr; g.out_KS = 0;
       g.v = v; g.ldp = ldp; g.N = n; g.D = D; g.tp = tp; g.dstride = 2; g.ndims = ndims; g.dpt = L.dpt; g.ppd = L.ppd;
-      g.tiles = L.tiles; g.lo = sp->range_min; g.hi = sp->range_max;
+      g.tiles = 2 * L.tiles; g.lo = sp->range_min; g.hi = sp->range_max;
       int rc;
       if (i < nh) {
         g.out_img = ws + L.off_h[i & 1];
@@ -206,7 +206,7 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
         else
           rc = inverse ? dt_launch_gemm<kEpiAffine, true>(g, L.MT, used, s) : dt_launch_gemm<kEpiAffine, false>(g, L.MT, used, s);
         if (rc) return rc;
-        dense_tc_ld_accum_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(ldp, L.tiles, used, ld, n, it == 0);
+        dense_tc_ld_accum_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, s>>>(ldp, 2 * L.tiles, 2 * used, ld, n, it == 0);
         FC_LAUNCH_CHECK("dense_tc_ld_accum_kernel");
       }
       if (rc) return rc;

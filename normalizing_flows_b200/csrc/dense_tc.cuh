@@ -8,7 +8,7 @@
 // shared-memory tile images (tc.cuh), so a pipeline stage is two cp.async.bulk (TMA) copies:
 //   A image  [m_tile][k_stage][hi|lo][4 chunks][128 rows][16 B]   (activations, 32 K per stage)
 //   B image  [n_tile][k_stage][hi|lo][4 chunks][256 rows][16 B]   (weights, masks folded in)
-// CTA = loader warp + MMA warp + 4 epilogue warps, persistent (one per SM) with two TMEM accumulators so
+// CTA = loader warp + MMA warp + 2 x 8 epilogue warps, persistent (one per SM) with two TMEM accumulators so
 // that a tile's epilogue overlaps the next tile's MMAs.  Epilogues (thread = sample row = TMEM lane):
 //   hidden: +bias, relu, bf16 hi/lo split, written straight into the next Linear's A image;
 //   last:   the inner bijector (RQS / affine) on the tile's dims, state updated in place,
@@ -21,7 +21,8 @@
 
 namespace flowcuda {
 
-constexpr int kDtBN = 256, kDtBK = 32, kDtThreads = 320;
+constexpr int kDtBN = 256, kDtBK = 32;
+// threads per CTA: loader warp, MMA warp, two epilogue groups of DtCfg<EPI>::kEpiWarps warps
 constexpr int kDtABytes = 128 * kDtBK * 2;   // one of hi/lo of an A stage (8 KB)
 constexpr int kDtBBytes = kDtBN * kDtBK * 2; // one of hi/lo of a B stage (16 KB)
 constexpr int kDtStageBytes = 2 * kDtABytes + 2 * kDtBBytes;  // 48 KB
@@ -91,15 +92,17 @@ __device__ __forceinline__ float dt_tile_bias(const DtGemm& a, int nt, int n) {
 
 // One 128 x 256 accumulator tile -> its epilogue (thread = sample row = TMEM lane).  `tb` is the TMEM
 // address of this warp's lane quarter of the accumulator, `Tbase` the CTA's transposition scratch.
+// Eight warps share a tile: `half` selects columns [128*half, 128*half + 128) (two warps per TMEM lane quarter).
 template <int EPI, bool INV>
 __device__ __forceinline__ void dt_epilogue(const DtGemm& a, int mt, int nt, uint32_t tb, const float* __restrict__ sbias,
-                                            float* Tbase, int warp, int lane) {
+                                            float* Tbase, int warp, int lane, int half) {
   const int row = (warp & 3) * 32 + lane;
   const int64_t grow = (int64_t)mt * 128 + row;
+  const int c_lo = half * (kDtBN / 2), c_hi = c_lo + kDtBN / 2;
   if (EPI == kEpiHidden) {
     uint8_t* og = a.out_img + (int64_t)mt * a.out_KS * 2 * kDtABytes;
 #pragma unroll 1
-    for (int c = 0; c < kDtBN; c += 16) {
+    for (int c = c_lo; c < c_hi; c += 16) {
       uint32_t vv[16];
       tc::tmem_ld_x16(tb + (uint32_t)c, vv);
       tc::tmem_ld_wait();
@@ -123,7 +126,7 @@ __device__ __forceinline__ void dt_epilogue(const DtGemm& a, int mt, int nt, uin
   } else if (EPI == kEpiRqs8) {
     float ldsum = 0.f;
 #pragma unroll 1
-    for (int di = 0; di < 10; ++di) {
+    for (int di = 5 * half; di < 5 * half + 5; ++di) {
       const int dim = nt * 10 + di;
       if (dim >= a.ndims) break;  // uniform across the CTA
       uint32_t vv[25];
@@ -143,7 +146,7 @@ __device__ __forceinline__ void dt_epilogue(const DtGemm& a, int mt, int nt, uin
         ldsum += l1;
       }
     }
-    if (grow < a.N) a.ldp[grow * a.tiles + nt] = ldsum;
+    if (grow < a.N) a.ldp[grow * a.tiles + 2 * nt + half] = ldsum;
   } else {
     // Affine epilogue.  The accumulator comes out of TMEM as thread = sample row, but the state v[N, D]
     // is row-major: a thread-per-row access touches 32 cache lines per request.  Each warp therefore
@@ -152,13 +155,13 @@ __device__ __forceinline__ void dt_epilogue(const DtGemm& a, int mt, int nt, uin
     // a third phase (thread = row again) sums the log-det and, for MADE stacks, writes the NEXT
     // layer's activation image directly (bf16 hi/lo), so no separate packing pass re-reads v.
     constexpr int TS = 36;  // row stride of the transposition tile in floats (16-byte aligned rows)
-    float* T = Tbase + (warp & 3) * 32 * TS;
+    float* T = Tbase + (half * 4 + (warp & 3)) * 32 * TS;
     const int r0 = (warp & 3) * 32;
     const int k = lane & 15, hp = lane >> 4;
     uint8_t* og = a.out_img ? a.out_img + (int64_t)mt * a.out_KS * 2 * kDtABytes : nullptr;
     float ldsum = 0.f;
 #pragma unroll 1
-    for (int c = 0; c < kDtBN; c += 32) {
+    for (int c = c_lo; c < c_hi; c += 32) {
       const int dim0 = nt * 128 + c / 2;
       if (dim0 >= a.ndims) break;  // uniform across the CTA
       uint32_t vv[32];
@@ -232,14 +235,22 @@ __device__ __forceinline__ void dt_epilogue(const DtGemm& a, int mt, int nt, uin
       }
       __syncwarp();
     }
-    if (grow < a.N) a.ldp[grow * a.tiles + nt] = ldsum;
+    if (grow < a.N) a.ldp[grow * a.tiles + 2 * nt + half] = ldsum;
   }
 }
 
-constexpr int kDtTileScratchFloats = 4 * 32 * 36;  // per-warp 32 x 36 transposition tiles of the affine epilogue
+constexpr int kDtTileScratchFloats = 8 * 32 * 36;  // per-warp 32 x 36 transposition tiles of one epilogue group (affine)
 // The affine epilogue needs the transposition scratch (two epilogue groups) and runs a 3-stage ring; the
 // other epilogues have the room for 4 stages.
-template <int EPI> struct DtCfg {
+template <int EPI, bool WIDE> struct DtCfg {
+  // Warps per epilogue group.  Hidden and affine epilogues are bound by single-warp issue: eight warps share a
+  // tile (two per TMEM lane quarter, 128 columns each; maf_made log_prob 1.28 -> 1.10 ms).  The RQS epilogue
+  // keeps four (measured slower with eight: 1.23 -> 1.32 ms at the maf_mnist shape; its 25-parameter spline
+  // needs the registers the larger CTA takes away).
+  // WIDE is chosen per launch: RQS never, the others when a CTA gets more than one tile (a 64-tile hidden
+  // Linear at batch 4096 ran 2 us slower with the larger CTA).
+  static constexpr int kEpiWarps = WIDE ? 8 : 4;
+  static constexpr int kThreads = 64 + 2 * 32 * kEpiWarps;
   static constexpr int kStages = EPI == 2 ? 3 : 4;
   static constexpr int kScratch = EPI == 2 ? 2 * kDtTileScratchFloats : 0;
   static constexpr size_t kSmem = (size_t)kStages * kDtStageBytes + kScratch * 4 + 2 * kDtBN * 4 + (2 * kStages + 4) * 8 + 16;
@@ -248,13 +259,15 @@ template <int EPI> struct DtCfg {
 // Persistent kernel: one CTA per SM walks the (m tile, n tile) list; a TMA ring feeds the MMA warp across
 // tile boundaries, and the two 256-column TMEM accumulators alternate between two epilogue warpgroups, so
 // an epilogue may take twice the MMA time of a tile before it stalls the tensor pipe.
-template <int EPI, bool INV>
-__global__ void __launch_bounds__(kDtThreads, 1) dense_tc_gemm_kernel(DtGemm a, int MT, int NT) {
-  constexpr int kDtStages = DtCfg<EPI>::kStages;
+template <int EPI, bool INV, bool WIDE>
+__global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_kernel(DtGemm a, int MT, int NT) {
+  using Cfg = DtCfg<EPI, WIDE>;
+  constexpr int kDtStages = Cfg::kStages;
+  constexpr int EW = Cfg::kEpiWarps;
   extern __shared__ __align__(128) uint8_t smem[];
   uint8_t* stages = smem;                                                          // [stages][48 KB]
   float* Tbase = reinterpret_cast<float*>(smem + kDtStages * kDtStageBytes);       // epilogue scratch
-  float* sbias2 = Tbase + DtCfg<EPI>::kScratch;                                    // [2][256]
+  float* sbias2 = Tbase + Cfg::kScratch;                                    // [2][256]
   uint64_t* full = reinterpret_cast<uint64_t*>(sbias2 + 2 * kDtBN);                // [stages]
   uint64_t* empty = full + kDtStages;                                              // [stages]
   uint64_t* acc_full = empty + kDtStages;                                          // [2]
@@ -271,7 +284,7 @@ __global__ void __launch_bounds__(kDtThreads, 1) dense_tc_gemm_kernel(DtGemm a, 
     }
     for (int s = 0; s < 2; ++s) {
       tc::mbar_init(&acc_full[s], 1);
-      tc::mbar_init(&acc_empty[s], 4);  // one arrival per epilogue warp
+      tc::mbar_init(&acc_empty[s], EW);  // one arrival per epilogue warp of the group
     }
     tc::fence_mbar_init();
   }
@@ -334,16 +347,23 @@ __global__ void __launch_bounds__(kDtThreads, 1) dense_tc_gemm_kernel(DtGemm a, 
       }
     }
   } else {
-    // ===== epilogue warps: group 0 (warps 2-5) takes the even tiles of this CTA, group 1 (warps 6-9) the odd
-    const uint32_t group = (uint32_t)(warp - 2) >> 2;
-    const int et = (tid - 64) & 127;
+    // ===== epilogue warps: group 0 (warps 2-9) takes the even tiles of this CTA, group 1 (warps 10-17) the odd;
+    // inside a group, warps 0-3 take the tile's columns 0-127 and warps 4-7 columns 128-255 (two warps per TMEM
+    // lane quarter).  With only four warps per tile the epilogues were bound by single-warp issue.
+    const uint32_t group = (uint32_t)(warp - 2) / EW;
+    const int half = ((warp - 2) >> 2) & 1;  // EW == 8 only
+    const int et = (tid - 64) % (EW * 32);
+    auto group_sync = [&]() {  // this epilogue group only
+      if (group == 0) asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory");
+      else asm volatile("bar.sync 2, %0;" ::"n"(EW * 32) : "memory");
+    };
     float* sbias = sbias2 + group * kDtBN;
     uint32_t tl = 0;
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tl) {
       if ((tl & 1u) != group) continue;
       const int mt = t / NT, nt = t - mt * NT;
       const uint32_t slot = group, aph = (tl >> 1) & 1u;
-      for (int n = et; n < kDtBN; n += 128) {  // bias of this tile's columns
+      for (int n = et; n < kDtBN; n += EW * 32) {  // bias of this tile's columns
         float b = 0.f;
         if (EPI == kEpiHidden) {
           const int col = nt * kDtBN + n;
@@ -353,9 +373,8 @@ __global__ void __launch_bounds__(kDtThreads, 1) dense_tc_gemm_kernel(DtGemm a, 
         }
         sbias[n] = b;
       }
-      if (group == 0) asm volatile("bar.sync 1, 128;" ::: "memory");  // this epilogue group only
-      else asm volatile("bar.sync 2, 128;" ::: "memory");
-      if (EPI != kEpiHidden) {
+      group_sync();
+      if (EPI != kEpiHidden && (EW == 4 || half == 0)) {
         // the bijector reads this tile's slice of the state v (it left L2 while the Linears streamed their
         // images): pull the thread's row of the slice into L2 now, under the tile's MMAs
         const int64_t prow = (int64_t)mt * 128 + (warp & 3) * 32 + lane;
@@ -370,13 +389,18 @@ __global__ void __launch_bounds__(kDtThreads, 1) dense_tc_gemm_kernel(DtGemm a, 
       tc::mbar_wait(&acc_full[slot], aph);
       tc::tc_fence_after();
       const uint32_t tb = tmem + slot * (uint32_t)kDtBN + ((uint32_t)((warp & 3) * 32) << 16);
-      dt_epilogue<EPI, INV>(a, mt, nt, tb, sbias, Tbase + group * kDtTileScratchFloats, warp, lane);
+      if (EW == 8) {
+        dt_epilogue<EPI, INV>(a, mt, nt, tb, sbias, Tbase + group * kDtTileScratchFloats, warp, lane, half);
+      } else {
+#pragma unroll 1  // one copy of the epilogue code (the spline is large; two copies cost instruction-cache misses)
+        for (int h = 0; h < 2; ++h)
+          dt_epilogue<EPI, INV>(a, mt, nt, tb, sbias, Tbase + group * kDtTileScratchFloats, warp, lane, h);
+      }
       tc::tc_fence_before();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(&acc_empty[slot]);
-      // all four warps must be done with sbias before the group's next tile overwrites it
-      if (group == 0) asm volatile("bar.sync 1, 128;" ::: "memory");
-      else asm volatile("bar.sync 2, 128;" ::: "memory");
+      // every warp of the group must be done with sbias before the group's next tile overwrites it
+      group_sync();
     }
   }
   tc::tc_fence_before();
@@ -387,26 +411,35 @@ __global__ void __launch_bounds__(kDtThreads, 1) dense_tc_gemm_kernel(DtGemm a, 
   }
 }
 
-template <int EPI, bool INV>
-static int dt_launch_gemm(const DtGemm& g, int64_t MT, int NT, cudaStream_t s) {
-  auto kern = dense_tc_gemm_kernel<EPI, INV>;
-  constexpr size_t kSmem = DtCfg<EPI>::kSmem;
+template <int EPI, bool INV, bool WIDE>
+static int dt_launch_gemm_w(const DtGemm& g, int64_t MT, int NT, cudaStream_t s) {
+  auto kern = dense_tc_gemm_kernel<EPI, INV, WIDE>;
+  constexpr size_t kSmem = DtCfg<EPI, WIDE>::kSmem;
   FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
   const int64_t tiles = MT * NT;
   const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
-  kern<<<grid, kDtThreads, kSmem, s>>>(g, (int)MT, NT);
+  kern<<<grid, DtCfg<EPI, WIDE>::kThreads, kSmem, s>>>(g, (int)MT, NT);
   FC_LAUNCH_CHECK("dense_tc_gemm_kernel");
   return FLOWCUDA_OK;
+}
+
+template <int EPI, bool INV>
+static int dt_launch_gemm(const DtGemm& g, int64_t MT, int NT, cudaStream_t s) {
+  if (EPI != kEpiRqs8 && MT * NT > sm_count()) return dt_launch_gemm_w<EPI, INV, true>(g, MT, NT, s);
+  return dt_launch_gemm_w<EPI, INV, false>(g, MT, NT, s);
 }
 
 // ---- log-det bookkeeping (fixed summation order: deterministic) ----------------------------------
 static __global__ void __launch_bounds__(256) dense_tc_ld_accum_kernel(const float* __restrict__ ldp, int tiles, int used,
                                                                       float* __restrict__ ld, int64_t N, int first) {
-  int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  // one warp per row: coalesced reads of the row's partials, fixed lane order + fixed shuffle tree
+  const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
   if (r >= N) return;
-  float s = first ? 0.f : ld[r];
-  for (int t = 0; t < used; ++t) s += ldp[r * tiles + t];
-  ld[r] = s;
+  float s = 0.f;
+  for (int t = lane; t < used; t += 32) s += ldp[r * tiles + t];
+  s = warp_sum(s);
+  if (lane == 0) ld[r] = first ? s : ld[r] + s;
 }
 
 static __global__ void __launch_bounds__(256) dense_tc_finish_kernel(const float* __restrict__ v, const float* __restrict__ ld,

@@ -72,7 +72,7 @@ static bool made_layout(const flowcuda_made_spec* sp, int64_t n, MadeLayout& L) 
   }
   L.off_v = off; off = dt_al256(off + (size_t)n * D * 4);
   L.off_ld = off; off = dt_al256(off + (size_t)n * 4);
-  L.off_ldp = off; off = dt_al256(off + (size_t)n * L.tiles * 4);
+  L.off_ldp = off; off = dt_al256(off + (size_t)n * L.tiles * 2 * 4);  // two partials per (row, tile)
   L.off_x = off; off = dt_al256(off + (size_t)L.MT * L.KS[0] * 2 * kDtABytes);
   int ksh = 1;
   for (int i = 1; i < L.nlin; ++i) ksh = L.KS[i] > ksh ? L.KS[i] : ksh;
@@ -221,7 +221,7 @@ static int made_log_prob_run(const flowcuda_made_spec* sp, const float* params, 
       g.KS = L.KS[i];
       g.n_out = L.sizes[i + 1];
       g.v = v; g.ldp = ldp; g.N = n; g.D = D; g.tp = 0; g.dstride = 1; g.ndims = D; g.dpt = 128; g.ppd = 2;
-      g.tiles = L.tiles; g.made = 1; g.rev = rev ? 1 : 0;
+      g.tiles = 2 * L.tiles; g.made = 1; g.rev = rev ? 1 : 0;
       for (int t = 0; t < L.NT[i] && t < kDtMaxKsTiles; ++t) g.ks_tile[t] = (unsigned char)made_ks_needed(L, i, t, rev);
       int rc;
       if (i < nh) {
@@ -237,7 +237,7 @@ static int made_log_prob_run(const flowcuda_made_spec* sp, const float* params, 
         }
         rc = dt_launch_gemm<kEpiAffine, true>(g, L.MT, L.tiles, s);
         if (rc) return rc;
-        dense_tc_ld_accum_kernel<<<(int)((n + 255) / 256), 256, 0, s>>>(ldp, L.tiles, L.tiles, ld, n, it == 0);
+        dense_tc_ld_accum_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, s>>>(ldp, 2 * L.tiles, 2 * L.tiles, ld, n, it == 0);
         FC_LAUNCH_CHECK("dense_tc_ld_accum_kernel");
       }
       if (rc) return rc;

@@ -19,6 +19,7 @@ namespace flowcuda {
 
 constexpr int kMgTcSplits = 16;
 constexpr int kMgTcStages = 4;
+constexpr int kMgTcThreads = 320;  // loader warp, MMA warp, two epilogue groups of four warps
 constexpr size_t kMgTcSmem = (size_t)kMgTcStages * kDtStageBytes + 2 * kDtBN * 4 + (2 * kMgTcStages + 4) * 8 + 16;
 
 // image row r (tiles of TR rows), K index k  <-  src[r*rs + k*cs]  (r < R, k < K; zero padding)
@@ -109,7 +110,7 @@ __device__ __forceinline__ void mgtc_krange(const MgTcArgs& a, int z, int mt, in
   }
 }
 
-static __global__ void __launch_bounds__(kDtThreads, 1) mgtc_gemm_kernel(MgTcArgs a) {
+static __global__ void __launch_bounds__(kMgTcThreads, 1) mgtc_gemm_kernel(MgTcArgs a) {
   extern __shared__ __align__(128) uint8_t smem[];
   uint8_t* stages = smem;
   float* sbias = reinterpret_cast<float*>(smem + kMgTcStages * kDtStageBytes);  // [2][256]
@@ -410,7 +411,7 @@ static int mgtc_launch(MgGemm g, const MgTcScratch& sc, cudaStream_t s) {
   FC_CUDA(cudaFuncSetAttribute(mgtc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMgTcSmem));
   const int items = a.MT * a.NT * a.S;
   const int grid = items < sm_count() ? items : sm_count();
-  mgtc_gemm_kernel<<<grid, kDtThreads, kMgTcSmem, s>>>(a);
+  mgtc_gemm_kernel<<<grid, kMgTcThreads, kMgTcSmem, s>>>(a);
   FC_LAUNCH_CHECK("mgtc_gemm_kernel");
   if (a.S > 1) {
     mgtc_reduce_kernel<<<grid_for((int64_t)g.M * g.N, 256, 8), 256, 0, s>>>(g);
