@@ -181,21 +181,27 @@ __device__ __forceinline__ void dt_epilogue(const DtGemm& a, int mt, int nt, uin
         const int dim = dim0 + k;
         const bool dvalid = dim < a.ndims;
         const int d = a.tp + a.dstride * dim;
+        // this lane's column of the state: rows r0 + hp, r0 + hp + 2, ...  — one pointer walked by a constant
+        // stride (per-element 64-bit index arithmetic was a quarter of the kernel's instructions)
+        const int64_t row0 = (int64_t)mt * 128 + r0;
+        const int64_t left = a.N - row0;
+        const int nrows = dvalid ? (left < 32 ? (left < 0 ? 0 : (int)left) : 32) : 0;  // rows of this block the lane may touch
+        float* vp = a.v + (row0 + hp) * a.D + d;
+        const int64_t rstride = 2 * (int64_t)a.D;
         float xv[16];
+        {
+          const float* q = vp;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const int64_t gr = (int64_t)mt * 128 + r0 + 2 * i + hp;
-          xv[i] = (dvalid && gr < a.N) ? a.v[gr * a.D + d] : 0.f;
+          for (int i = 0; i < 16; ++i, q += rstride) xv[i] = (2 * i + hp < nrows) ? *q : 0.f;
         }
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
+        for (int i = 0; i < 16; ++i, vp += rstride) {
           const int r = 2 * i + hp;
-          const int64_t gr = (int64_t)mt * 128 + r0 + r;
           const float2 p = *reinterpret_cast<const float2*>(T + r * TS + 2 * k);
           float nv, l1;
           affine_apply<INV>(p.x, p.y, xv[i], nv, l1);
-          if (dvalid && gr < a.N) {
-            a.v[gr * a.D + d] = nv;
+          if (r < nrows) {
+            *vp = nv;
           } else {
             nv = 0.f;
             l1 = 0.f;
