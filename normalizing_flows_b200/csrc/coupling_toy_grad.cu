@@ -298,10 +298,16 @@ int coupling_dense_grad_run(const flowcuda_coupling_spec* sp, const float* param
                             float* grad, void* workspace, size_t wsb, cudaStream_t s);
 }
 
+// The stored-activation engine serves every shape the fused toy kernel does not, and the toy shapes too when
+// the caller asks for the tensor-core GEMMs (precision BF16X3).
+static bool tg_use_dense(const flowcuda_coupling_spec* sp) {
+  return !tg_supported(sp) || (sp->precision == FLOWCUDA_PRECISION_BF16X3 && coupling_dense_grad_supported(sp));
+}
+
 extern "C" {
 
 size_t flowcuda_coupling_nll_grad_workspace_bytes(const flowcuda_coupling_spec* spec, int64_t n) {
-  if (spec && n >= 1 && !tg_supported(spec)) return coupling_dense_grad_workspace_bytes(spec, n);
+  if (spec && n >= 1 && tg_use_dense(spec)) return coupling_dense_grad_workspace_bytes(spec, n);
   if (!tg_supported(spec) || n < 1) return 0;
   return (size_t)tg_grid(n) * (tg_pl(spec) * spec->num_layers + 1) * sizeof(float) + 256;
 }
@@ -309,7 +315,7 @@ size_t flowcuda_coupling_nll_grad_workspace_bytes(const flowcuda_coupling_spec* 
 int flowcuda_coupling_nll_grad(const flowcuda_coupling_spec* spec, const float* params, const float* x, int64_t n,
                                float* loss, float* grad, void* workspace, size_t workspace_bytes, void* stream) {
   FC_REQUIRE(spec && params && x && workspace, "coupling_nll_grad: NULL pointer");
-  if (!tg_supported(spec)) {  // generic event size: stored-activation reverse mode (coupling_dense_grad.cu)
+  if (tg_use_dense(spec)) {  // generic event size: stored-activation reverse mode (coupling_dense_grad.cu)
     FC_REQUIRE(n >= 1 && loss && grad, "coupling_nll_grad: bad arguments");
     return coupling_dense_grad_run(spec, params, x, n, loss, grad, workspace, workspace_bytes, (cudaStream_t)stream);
   }

@@ -116,3 +116,24 @@ def test_dense_coupling_nll_grad_matches_autograd(case, engine):
         # within the north_star budget for the tensor-core path (1e-3 absolute, here 2e-3 of the largest).
         assert np.quantile(np.abs(g - gr), 0.999) / scale <= 1e-4
         assert np.abs(g - gr).max() / scale <= 2e-3
+
+
+@pytest.mark.parametrize("n", [130, 3000])
+def test_toy_rqs_nll_grad_on_the_tensor_core_engine(n):
+    """precision = BF16X3 routes even the event_dim = 2 flows through the stored-activation engine
+    (K = 2 operand images, 12-bin compact adjoint): same loss and gradient as the float64 oracle."""
+    from normalizing_flows_b200 import _lib, ops
+
+    ospec, scale, xs = COUPLING_CASES["rqs_toy"]
+    params = O.init_coupling_params(ospec, seed=21, scale=scale)
+    x = (torch.randn(n, 2, generator=torch.Generator().manual_seed(n + 3), dtype=torch.float64) * xs).float()
+    loss_ref, grad_ref = oracle_loss_and_grad(ospec, params, x.double())
+    p = G(O.flatten_layers(params))
+    loss, grad = ops.coupling_nll_grad(_spec_pair(ops, ospec, precision=_lib.PRECISION_BF16X3), p, x.cuda())
+    assert abs(loss.item() - loss_ref.item()) <= 2e-5 * max(1.0, abs(loss_ref.item()))
+    g, gr = grad.double().cpu().numpy(), grad_ref.numpy()
+    scale_g = max(1e-6, np.abs(gr).max())
+    assert np.quantile(np.abs(g - gr), 0.999) / scale_g <= 1e-4
+    assert np.abs(g - gr).max() / scale_g <= 2e-3
+    fused, gfused = ops.coupling_nll_grad(_spec_pair(ops, ospec), p, x.cuda())
+    assert abs(fused.item() - loss.item()) <= 2e-5 * max(1.0, abs(fused.item()))
