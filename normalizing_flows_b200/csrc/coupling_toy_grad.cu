@@ -16,6 +16,9 @@
 namespace flowcuda {
 
 constexpr int kTgThreads = 128, kTgH = 64, kTgMaxL = 32;
+// row stride of the staged activation / adjoint tiles: odd, so that the batch reductions — 16 or 32 different
+// rows read at the same sample index by the lanes of a warp — hit distinct banks (stride 128 was a 16-way conflict)
+constexpr int kTgLd = kTgThreads + 1;
 
 struct TgArgs {
   const float* params;
@@ -97,9 +100,9 @@ __global__ void __launch_bounds__(kTgThreads) coupling_toy_grad_kernel(TgArgs a)
   extern __shared__ __align__(16) float smem[];
   float* sw = smem;                                  // layer image
   float* bufH = sw + ((I::total + 3) & ~3);          // [64][128] h2, later dh1
-  float* bufG = bufH + kTgH * kTgThreads;            // [64][128] dh2
-  float* bufO = bufG + kTgH * kTgThreads;            // [OP][128] d(conditioner out)
-  float* sxm = bufO + OP * kTgThreads;               // [128] visible coordinate
+  float* bufG = bufH + kTgH * kTgLd;                 // [64][129] dh2
+  float* bufO = bufG + kTgH * kTgLd;                 // [OP][129] d(conditioner out)
+  float* sxm = bufO + OP * kTgLd;                    // [128] visible coordinate
   float* sst = sxm + kTgThreads;                     // [L+1][2][128] states
   float* sred = sst + (a.L + 1) * 2 * kTgThreads;    // [4] loss reduction
   const int tid = threadIdx.x, L = a.L;
@@ -155,21 +158,21 @@ __global__ void __launch_bounds__(kTgThreads) coupling_toy_grad_kernel(TgArgs a)
         if constexpr (TR == FLOWCUDA_TRANSFORM_RQS) rqs_fwd_bwd<KT>(o, a.lo, a.hi, xt, t ? a1 : a0, -live, yy, ll, xbar, obar);
         else affine_fwd_bwd(o, xt, t ? a1 : a0, -live, yy, ll, xbar, obar);
 #pragma unroll
-        for (int i = 0; i < OP; ++i) bufO[i * kTgThreads + tid] = i < NEED ? obar[i] : 0.f;
+        for (int i = 0; i < OP; ++i) bufO[i * kTgLd + tid] = i < NEED ? obar[i] : 0.f;
 #pragma unroll 4
         for (int k = 0; k < kTgH; ++k) {
           float g = 0.f;
 #pragma unroll
           for (int i = 0; i < NEED; ++i) g = fmaf(sw[I::W3 + k * OP + i], obar[i], g);
-          bufH[k * kTgThreads + tid] = h2[k];
-          bufG[k * kTgThreads + tid] = h2[k] > 0.f ? g : 0.f;
+          bufH[k * kTgLd + tid] = h2[k];
+          bufG[k * kTgLd + tid] = h2[k] > 0.f ? g : 0.f;
         }
       }
       __syncthreads();
       float* pl = part + PL * l;
       float* gW1 = pl; float* gb1 = gW1 + 2 * h1; float* gW2 = gb1 + h1; float* gb2 = gW2 + (size_t)h1 * h2n;
       float* gW3 = gb2 + h2n; float* gb3 = gW3 + (size_t)h2n * of;
-      {  // C1: dW3 = H2^T dO, db3, dW2 = H1^T dH2, db2 — thread owns row k = tid/2 and half of the columns
+      {  // C1: dW3 = H2^T dO, db3, dW2 = H1^T dH2, db2 — thread owns row k = tid/2 and every second column
         const int k = tid >> 1, half = tid & 1;
         constexpr int HC = OP / 2;
         float acc3[HC];
@@ -181,25 +184,25 @@ __global__ void __launch_bounds__(kTgThreads) coupling_toy_grad_kernel(TgArgs a)
         const float w1k = sw[I::w1 + k], b1k = sw[I::b1 + k];
         float accb = 0.f;
         for (int s = 0; s < kTgThreads; ++s) {
-          const float hk = bufH[k * kTgThreads + s];
+          const float hk = bufH[k * kTgLd + s];
 #pragma unroll
-          for (int i = 0; i < HC; ++i) acc3[i] = fmaf(hk, bufO[(half * HC + i) * kTgThreads + s], acc3[i]);
+          for (int i = 0; i < HC; ++i) acc3[i] = fmaf(hk, bufO[(2 * i + half) * kTgLd + s], acc3[i]);
           const float h1k = fmaxf(fmaf(sxm[s], w1k, b1k), 0.f);  // recomputed first-layer activation, row k
 #pragma unroll
-          for (int i = 0; i < 32; ++i) acc2[i] = fmaf(h1k, bufG[(half * 32 + i) * kTgThreads + s], acc2[i]);
-          accb += half ? bufG[k * kTgThreads + s] : (k < OP ? bufO[k * kTgThreads + s] : 0.f);
+          for (int i = 0; i < 32; ++i) acc2[i] = fmaf(h1k, bufG[(2 * i + half) * kTgLd + s], acc2[i]);
+          accb += half ? bufG[k * kTgLd + s] : (k < OP ? bufO[k * kTgLd + s] : 0.f);
         }
         if (k < h2n) {
 #pragma unroll
           for (int i = 0; i < HC; ++i) {
-            const int c = half * HC + i;
+            const int c = 2 * i + half;
             if (c < NEED) gW3[(size_t)k * of + col0 + c] += acc3[i];
           }
         }
         if (k < h1) {
 #pragma unroll
           for (int i = 0; i < 32; ++i) {
-            const int c = half * 32 + i;
+            const int c = 2 * i + half;
             if (c < h2n) gW2[(size_t)k * h2n + c] += acc2[i];
           }
         }
@@ -211,15 +214,24 @@ __global__ void __launch_bounds__(kTgThreads) coupling_toy_grad_kernel(TgArgs a)
       {  // S2: dh1 = relu'(h1) * (W2 dh2), dxm = w1 . dh1   (bufH is free now: reuse for dh1)
         float g2[kTgH];
 #pragma unroll
-        for (int k = 0; k < kTgH; ++k) g2[k] = bufG[k * kTgThreads + tid];
+        for (int k = 0; k < kTgH; ++k) g2[k] = bufG[k * kTgLd + tid];
 #pragma unroll 2
         for (int j = 0; j < kTgH; ++j) {
-          float g = 0.f;
+          // four interleaved partial sums: one 64-long dependent FMA chain per output left the four warps of
+          // the CTA waiting on the FMA latency
+          float ga = 0.f, gb = 0.f, gc = 0.f, gd = 0.f;
 #pragma unroll
-          for (int k = 0; k < kTgH; ++k) g = fmaf(sw[I::W2 + j * 64 + k], g2[k], g);
+          for (int k = 0; k < kTgH; k += 4) {
+            const float4 w4 = *reinterpret_cast<const float4*>(sw + I::W2 + j * 64 + k);
+            ga = fmaf(w4.x, g2[k], ga);
+            gb = fmaf(w4.y, g2[k + 1], gb);
+            gc = fmaf(w4.z, g2[k + 2], gc);
+            gd = fmaf(w4.w, g2[k + 3], gd);
+          }
+          float g = (ga + gb) + (gc + gd);
           const float pre = fmaf(xm, sw[I::w1 + j], sw[I::b1 + j]);
           g = pre > 0.f ? g : 0.f;
-          bufH[j * kTgThreads + tid] = g;
+          bufH[j * kTgLd + tid] = g;
           dxm = fmaf(sw[I::w1 + j], g, dxm);
         }
       }
@@ -227,7 +239,7 @@ __global__ void __launch_bounds__(kTgThreads) coupling_toy_grad_kernel(TgArgs a)
       if (tid < 2 * kTgH) {  // C2: dW1 (visible row) and db1
         const int j = tid & 63, isb = tid >> 6;
         float acc = 0.f;
-        for (int s = 0; s < kTgThreads; ++s) acc = fmaf(isb ? 1.f : sxm[s], bufH[j * kTgThreads + s], acc);
+        for (int s = 0; s < kTgThreads; ++s) acc = fmaf(isb ? 1.f : sxm[s], bufH[j * kTgLd + s], acc);
         if (j < h1) {
           if (isb) gb1[j] += acc; else gW1[(1 - t) * h1 + j] += acc;
         }
@@ -279,7 +291,7 @@ static int tg_grid(int64_t n) {
 template <int TR, int KT, int OP>
 static int tg_launch(const flowcuda_coupling_spec* sp, TgArgs a, int grid, cudaStream_t s) {
   using I = TgImg<OP>;
-  size_t fl = ((I::total + 3) & ~3) + 2 * kTgH * kTgThreads + OP * kTgThreads + kTgThreads + (size_t)(a.L + 1) * 2 * kTgThreads + 4;
+  size_t fl = ((I::total + 3) & ~3) + 2 * kTgH * kTgLd + OP * kTgLd + kTgThreads + (size_t)(a.L + 1) * 2 * kTgThreads + 4;
   auto kern = coupling_toy_grad_kernel<TR, KT, OP>;
   FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(fl * 4)));
   kern<<<grid, kTgThreads, fl * 4, s>>>(a);
