@@ -92,27 +92,31 @@ __device__ __forceinline__ void tg_cond(const float* sw, float xm, float* h2, fl
   }
 }
 
-// TR/KT as in coupling_toy.cu; OP = padded needed-output count.
-template <int TR, int KT, int OP>
-__global__ void __launch_bounds__(kTgThreads) coupling_toy_grad_kernel(TgArgs a) {
+// TR/KT as in coupling_toy.cu; OP = padded needed-output count; T = threads = samples per tile (128 or 256:
+// the larger tile doubles the warps per SM — shared memory allows one CTA — and halves the weight staging
+// per sample; it needs (L+1)*2*T floats of states, so deep stacks fall back to 128).
+template <int TR, int KT, int OP, int T>
+__global__ void __launch_bounds__(T) coupling_toy_grad_kernel(TgArgs a) {
   using I = TgImg<OP>;
+  constexpr int kT = T, kLd = T + 1;
+  constexpr int R = T / kTgH;  // threads per weight-gradient row
   constexpr int NEED = TR == FLOWCUDA_TRANSFORM_RQS ? 3 * KT + 1 : 2;
   extern __shared__ __align__(16) float smem[];
   float* sw = smem;                                  // layer image
   float* bufH = sw + ((I::total + 3) & ~3);          // [64][128] h2, later dh1
-  float* bufG = bufH + kTgH * kTgLd;                 // [64][129] dh2
-  float* bufO = bufG + kTgH * kTgLd;                 // [OP][129] d(conditioner out)
-  float* sxm = bufO + OP * kTgLd;                    // [128] visible coordinate
-  float* sst = sxm + kTgThreads;                     // [L+1][2][128] states
-  float* sred = sst + (a.L + 1) * 2 * kTgThreads;    // [4] loss reduction
+  float* bufG = bufH + kTgH * kLd;                 // [64][129] dh2
+  float* bufO = bufG + kTgH * kLd;                 // [OP][129] d(conditioner out)
+  float* sxm = bufO + OP * kLd;                    // [128] visible coordinate
+  float* sst = sxm + kT;                     // [L+1][2][128] states
+  float* sred = sst + (a.L + 1) * 2 * kT;    // [T/32] loss reduction
   const int tid = threadIdx.x, L = a.L;
   const int h1 = a.h1, h2n = a.h2, of = a.of;
   const size_t PL = (size_t)2 * h1 + h1 + (size_t)h1 * h2n + h2n + (size_t)h2n * of + of;
   float* part = a.partial + (size_t)blockIdx.x * (PL * L + 1);
   float loss_acc = 0.f;
-  const int64_t ntiles = (a.n + kTgThreads - 1) / kTgThreads;
+  const int64_t ntiles = (a.n + kT - 1) / kT;
   for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-    const int64_t idx = tile * kTgThreads + tid;
+    const int64_t idx = tile * kT + tid;
     const float live = idx < a.n ? 1.f : 0.f;
     float2 xv = idx < a.n ? reinterpret_cast<const float2*>(a.x)[idx] : make_float2(0.f, 0.f);
     float c0 = xv.x, c1 = xv.y, ldsum = 0.f;
@@ -123,8 +127,8 @@ __global__ void __launch_bounds__(kTgThreads) coupling_toy_grad_kernel(TgArgs a)
       __syncthreads();
       tg_stage<OP>(sw, a, l, col0, NEED);
       __syncthreads();
-      sst[(it * 2 + 0) * kTgThreads + tid] = c0;
-      sst[(it * 2 + 1) * kTgThreads + tid] = c1;
+      sst[(it * 2 + 0) * kT + tid] = c0;
+      sst[(it * 2 + 1) * kT + tid] = c1;
       float h2[kTgH], o[NEED];
       tg_cond<OP, NEED>(sw, t ? c0 : c1, h2, o);
       float nv, l1;
@@ -147,7 +151,7 @@ __global__ void __launch_bounds__(kTgThreads) coupling_toy_grad_kernel(TgArgs a)
       const int col0 = TR == FLOWCUDA_TRANSFORM_AFFINE_SCALAR ? 0 : t * NEED;
       __syncthreads();
       tg_stage<OP>(sw, a, l, col0, NEED);
-      const float s0 = sst[(it * 2 + 0) * kTgThreads + tid], s1 = sst[(it * 2 + 1) * kTgThreads + tid];
+      const float s0 = sst[(it * 2 + 0) * kT + tid], s1 = sst[(it * 2 + 1) * kT + tid];
       const float xm = t ? s0 : s1, xt = t ? s1 : s0;
       sxm[tid] = xm;
       __syncthreads();
@@ -158,14 +162,14 @@ __global__ void __launch_bounds__(kTgThreads) coupling_toy_grad_kernel(TgArgs a)
         if constexpr (TR == FLOWCUDA_TRANSFORM_RQS) rqs_fwd_bwd<KT>(o, a.lo, a.hi, xt, t ? a1 : a0, -live, yy, ll, xbar, obar);
         else affine_fwd_bwd(o, xt, t ? a1 : a0, -live, yy, ll, xbar, obar);
 #pragma unroll
-        for (int i = 0; i < OP; ++i) bufO[i * kTgLd + tid] = i < NEED ? obar[i] : 0.f;
+        for (int i = 0; i < OP; ++i) bufO[i * kLd + tid] = i < NEED ? obar[i] : 0.f;
 #pragma unroll 4
         for (int k = 0; k < kTgH; ++k) {
           float g = 0.f;
 #pragma unroll
           for (int i = 0; i < NEED; ++i) g = fmaf(sw[I::W3 + k * OP + i], obar[i], g);
-          bufH[k * kTgLd + tid] = h2[k];
-          bufG[k * kTgLd + tid] = h2[k] > 0.f ? g : 0.f;
+          bufH[k * kLd + tid] = h2[k];
+          bufG[k * kLd + tid] = h2[k] > 0.f ? g : 0.f;
         }
       }
       __syncthreads();
@@ -173,48 +177,48 @@ __global__ void __launch_bounds__(kTgThreads) coupling_toy_grad_kernel(TgArgs a)
       float* gW1 = pl; float* gb1 = gW1 + 2 * h1; float* gW2 = gb1 + h1; float* gb2 = gW2 + (size_t)h1 * h2n;
       float* gW3 = gb2 + h2n; float* gb3 = gW3 + (size_t)h2n * of;
       {  // C1: dW3 = H2^T dO, db3, dW2 = H1^T dH2, db2 — thread owns row k = tid/2 and every second column
-        const int k = tid >> 1, half = tid & 1;
-        constexpr int HC = OP / 2;
+        const int k = tid / R, half = tid % R;  // `half`: which of the row's R interleaved column sets
+        constexpr int HC = OP / R, C2N = kTgH / R;
         float acc3[HC];
 #pragma unroll
         for (int i = 0; i < HC; ++i) acc3[i] = 0.f;
-        float acc2[32];
+        float acc2[C2N];
 #pragma unroll
-        for (int i = 0; i < 32; ++i) acc2[i] = 0.f;
+        for (int i = 0; i < C2N; ++i) acc2[i] = 0.f;
         const float w1k = sw[I::w1 + k], b1k = sw[I::b1 + k];
         float accb = 0.f;
-        for (int s = 0; s < kTgThreads; ++s) {
-          const float hk = bufH[k * kTgLd + s];
+        for (int s = 0; s < kT; ++s) {
+          const float hk = bufH[k * kLd + s];
 #pragma unroll
-          for (int i = 0; i < HC; ++i) acc3[i] = fmaf(hk, bufO[(2 * i + half) * kTgLd + s], acc3[i]);
+          for (int i = 0; i < HC; ++i) acc3[i] = fmaf(hk, bufO[(R * i + half) * kLd + s], acc3[i]);
           const float h1k = fmaxf(fmaf(sxm[s], w1k, b1k), 0.f);  // recomputed first-layer activation, row k
 #pragma unroll
-          for (int i = 0; i < 32; ++i) acc2[i] = fmaf(h1k, bufG[(2 * i + half) * kTgLd + s], acc2[i]);
-          accb += half ? bufG[k * kTgLd + s] : (k < OP ? bufO[k * kTgLd + s] : 0.f);
+          for (int i = 0; i < C2N; ++i) acc2[i] = fmaf(h1k, bufG[(R * i + half) * kLd + s], acc2[i]);
+          if (half < 2) accb += half ? bufG[k * kLd + s] : (k < OP ? bufO[k * kLd + s] : 0.f);
         }
         if (k < h2n) {
 #pragma unroll
           for (int i = 0; i < HC; ++i) {
-            const int c = 2 * i + half;
+            const int c = R * i + half;
             if (c < NEED) gW3[(size_t)k * of + col0 + c] += acc3[i];
           }
         }
         if (k < h1) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const int c = 2 * i + half;
+          for (int i = 0; i < C2N; ++i) {
+            const int c = R * i + half;
             if (c < h2n) gW2[(size_t)k * h2n + c] += acc2[i];
           }
         }
-        if (half) { if (k < h2n) gb2[k] += accb; }
-        else if (k < NEED) gb3[col0 + k] += accb;
+        if (half == 1) { if (k < h2n) gb2[k] += accb; }
+        else if (half == 0 && k < NEED) gb3[col0 + k] += accb;
       }
       __syncthreads();
       float dxm = 0.f;
       {  // S2: dh1 = relu'(h1) * (W2 dh2), dxm = w1 . dh1   (bufH is free now: reuse for dh1)
         float g2[kTgH];
 #pragma unroll
-        for (int k = 0; k < kTgH; ++k) g2[k] = bufG[k * kTgLd + tid];
+        for (int k = 0; k < kTgH; ++k) g2[k] = bufG[k * kLd + tid];
 #pragma unroll 2
         for (int j = 0; j < kTgH; ++j) {
           // four interleaved partial sums: one 64-long dependent FMA chain per output left the four warps of
@@ -231,7 +235,7 @@ __global__ void __launch_bounds__(kTgThreads) coupling_toy_grad_kernel(TgArgs a)
           float g = (ga + gb) + (gc + gd);
           const float pre = fmaf(xm, sw[I::w1 + j], sw[I::b1 + j]);
           g = pre > 0.f ? g : 0.f;
-          bufH[j * kTgLd + tid] = g;
+          bufH[j * kLd + tid] = g;
           dxm = fmaf(sw[I::w1 + j], g, dxm);
         }
       }
@@ -239,7 +243,7 @@ __global__ void __launch_bounds__(kTgThreads) coupling_toy_grad_kernel(TgArgs a)
       if (tid < 2 * kTgH) {  // C2: dW1 (visible row) and db1
         const int j = tid & 63, isb = tid >> 6;
         float acc = 0.f;
-        for (int s = 0; s < kTgThreads; ++s) acc = fmaf(isb ? 1.f : sxm[s], bufH[j * kTgLd + s], acc);
+        for (int s = 0; s < kT; ++s) acc = fmaf(isb ? 1.f : sxm[s], bufH[j * kLd + s], acc);
         if (j < h1) {
           if (isb) gb1[j] += acc; else gW1[(1 - t) * h1 + j] += acc;
         }
@@ -252,7 +256,12 @@ __global__ void __launch_bounds__(kTgThreads) coupling_toy_grad_kernel(TgArgs a)
   __syncthreads();
   if ((tid & 31) == 0) sred[tid >> 5] = ls;
   __syncthreads();
-  if (tid == 0) part[PL * L] += (sred[0] + sred[1]) + (sred[2] + sred[3]);
+  if (tid == 0) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < T / 32; ++w) t += sred[w];
+    part[PL * L] += t;
+  }
 }
 
 // out[c] = scale * sum_rows partial[r][c] in double, fixed order; column `cols-1` is the loss.
@@ -288,15 +297,27 @@ static int tg_grid(int64_t n) {
   return (int)(tiles < 1 ? 1 : (tiles < cap ? tiles : cap));
 }
 
+template <int TR, int KT, int OP, int T>
+static int tg_launch_t(TgArgs a, size_t fl, cudaStream_t s) {
+  auto kern = coupling_toy_grad_kernel<TR, KT, OP, T>;
+  FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(fl * 4)));
+  const int64_t tiles = (a.n + T - 1) / T;
+  const int grid = (int)(tiles < sm_count() ? tiles : sm_count());  // never more rows than tg_grid(n) zeroed
+  kern<<<grid, T, fl * 4, s>>>(a);
+  FC_LAUNCH_CHECK("coupling_toy_grad_kernel");
+  return FLOWCUDA_OK;
+}
+
 template <int TR, int KT, int OP>
 static int tg_launch(const flowcuda_coupling_spec* sp, TgArgs a, int grid, cudaStream_t s) {
   using I = TgImg<OP>;
-  size_t fl = ((I::total + 3) & ~3) + 2 * kTgH * kTgLd + OP * kTgLd + kTgThreads + (size_t)(a.L + 1) * 2 * kTgThreads + 4;
-  auto kern = coupling_toy_grad_kernel<TR, KT, OP>;
-  FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(fl * 4)));
-  kern<<<grid, kTgThreads, fl * 4, s>>>(a);
-  FC_LAUNCH_CHECK("coupling_toy_grad_kernel");
-  return FLOWCUDA_OK;
+  (void)sp; (void)grid;
+  auto floats = [&](int T) {
+    return (size_t)((I::total + 3) & ~3) + 2 * (size_t)kTgH * (T + 1) + (size_t)OP * (T + 1) + T + (size_t)(a.L + 1) * 2 * T + 8;
+  };
+  // 256-sample tiles when every SM still gets a tile and the states fit the 227 KB of shared memory
+  if (a.n >= (int64_t)256 * sm_count() && floats(256) * 4 <= 232448) return tg_launch_t<TR, KT, OP, 256>(a, floats(256), s);
+  return tg_launch_t<TR, KT, OP, 128>(a, floats(128), s);
 }
 
 }  // namespace flowcuda
