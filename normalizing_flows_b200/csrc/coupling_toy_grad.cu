@@ -65,31 +65,46 @@ __device__ __forceinline__ void tg_cond(const float* sw, float xm, float* h2, fl
   float h1[kTgH];
 #pragma unroll
   for (int j = 0; j < kTgH; ++j) h1[j] = fmaxf(fmaf(xm, sw[I::w1 + j], sw[I::b1 + j]), 0.f);
+  // packed accumulators: one FFMA2 (fma.rn.f32x2) per two outputs — a weight row arrives as 128-bit loads of two
+  // packed pairs, the activation is splatted once per row (scalar FFMA issues at half rate on sm_100)
+  f2_t h2p[kTgH / 2];
 #pragma unroll
-  for (int k = 0; k < kTgH; ++k) h2[k] = sw[I::b2 + k];
+  for (int k = 0; k < kTgH / 2; ++k) h2p[k] = *reinterpret_cast<const f2_t*>(sw + I::b2 + 2 * k);
 #pragma unroll 4
   for (int j = 0; j < kTgH; ++j) {
-    const float hj = h1[j];
-    const float4* wr = reinterpret_cast<const float4*>(sw + I::W2 + j * 64);
+    const f2_t hj = f2_splat(h1[j]);
+    const ulonglong2* wr = reinterpret_cast<const ulonglong2*>(sw + I::W2 + j * 64);
 #pragma unroll
     for (int k4 = 0; k4 < 16; ++k4) {
-      const float4 w = wr[k4];
-      h2[4 * k4] = fmaf(hj, w.x, h2[4 * k4]);
-      h2[4 * k4 + 1] = fmaf(hj, w.y, h2[4 * k4 + 1]);
-      h2[4 * k4 + 2] = fmaf(hj, w.z, h2[4 * k4 + 2]);
-      h2[4 * k4 + 3] = fmaf(hj, w.w, h2[4 * k4 + 3]);
+      const ulonglong2 w = wr[k4];
+      h2p[2 * k4] = f2_fma(hj, w.x, h2p[2 * k4]);
+      h2p[2 * k4 + 1] = f2_fma(hj, w.y, h2p[2 * k4 + 1]);
     }
   }
 #pragma unroll
-  for (int k = 0; k < kTgH; ++k) h2[k] = fmaxf(h2[k], 0.f);
+  for (int k = 0; k < kTgH / 2; ++k) {
+    float lo, hi;
+    f2_unpack(h2p[k], lo, hi);
+    h2[2 * k] = fmaxf(lo, 0.f);
+    h2[2 * k + 1] = fmaxf(hi, 0.f);
+  }
+  constexpr int NP = NEED / 2;  // packed output pairs (+ one scalar when NEED is odd)
+  f2_t op[NP > 0 ? NP : 1];
 #pragma unroll
-  for (int i = 0; i < NEED; ++i) o[i] = sw[I::b3 + i];
+  for (int i = 0; i < NP; ++i) op[i] = *reinterpret_cast<const f2_t*>(sw + I::b3 + 2 * i);
+  float olast = (NEED & 1) ? sw[I::b3 + NEED - 1] : 0.f;
 #pragma unroll 4
   for (int k = 0; k < kTgH; ++k) {
     const float hk = h2[k];
+    const f2_t hk2 = f2_splat(hk);
+    const f2_t* wr = reinterpret_cast<const f2_t*>(sw + I::W3 + k * OP);
 #pragma unroll
-    for (int i = 0; i < NEED; ++i) o[i] = fmaf(hk, sw[I::W3 + k * OP + i], o[i]);
+    for (int i = 0; i < NP; ++i) op[i] = f2_fma(hk2, wr[i], op[i]);
+    if (NEED & 1) olast = fmaf(hk, sw[I::W3 + k * OP + NEED - 1], olast);
   }
+#pragma unroll
+  for (int i = 0; i < NP; ++i) f2_unpack(op[i], o[2 * i], o[2 * i + 1]);
+  if (NEED & 1) o[NEED - 1] = olast;
 }
 
 // TR/KT as in coupling_toy.cu; OP = padded needed-output count; T = threads = samples per tile (128 or 256:
