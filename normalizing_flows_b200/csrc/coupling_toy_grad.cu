@@ -16,9 +16,8 @@
 namespace flowcuda {
 
 constexpr int kTgThreads = 128, kTgH = 64, kTgMaxL = 32;
-// row stride of the staged activation / adjoint tiles: odd, so that the batch reductions — 16 or 32 different
-// rows read at the same sample index by the lanes of a warp — hit distinct banks (stride 128 was a 16-way conflict)
-constexpr int kTgLd = kTgThreads + 1;
+// Row stride of the staged activation / adjoint tiles is T + 4 (see the kernel): the batch reductions read 8-16
+// different rows at the same sample index from the lanes of a warp — a 16-way bank conflict at stride 128.
 
 struct TgArgs {
   const float* params;
@@ -113,7 +112,7 @@ __device__ __forceinline__ void tg_cond(const float* sw, float xm, float* h2, fl
 template <int TR, int KT, int OP, int T>
 __global__ void __launch_bounds__(T) coupling_toy_grad_kernel(TgArgs a) {
   using I = TgImg<OP>;
-  constexpr int kT = T, kLd = T + 1;
+  constexpr int kT = T, kLd = T + 4;  // row stride = 4 (mod 32): the 128-bit reads of the batch reductions are conflict-free
   constexpr int R = T / kTgH;  // threads per weight-gradient row
   constexpr int NEED = TR == FLOWCUDA_TRANSFORM_RQS ? 3 * KT + 1 : 2;
   extern __shared__ __align__(16) float smem[];
@@ -202,14 +201,29 @@ __global__ void __launch_bounds__(T) coupling_toy_grad_kernel(TgArgs a) {
         for (int i = 0; i < C2N; ++i) acc2[i] = 0.f;
         const float w1k = sw[I::w1 + k], b1k = sw[I::b1 + k];
         float accb = 0.f;
-        for (int s = 0; s < kT; ++s) {
-          const float hk = bufH[k * kLd + s];
+        for (int s = 0; s < kT; s += 4) {  // four samples per 128-bit shared-memory read
+          const float4 hk = *reinterpret_cast<const float4*>(bufH + k * kLd + s);
 #pragma unroll
-          for (int i = 0; i < HC; ++i) acc3[i] = fmaf(hk, bufO[(R * i + half) * kLd + s], acc3[i]);
-          const float h1k = fmaxf(fmaf(sxm[s], w1k, b1k), 0.f);  // recomputed first-layer activation, row k
+          for (int i = 0; i < HC; ++i) {
+            const float4 o4 = *reinterpret_cast<const float4*>(bufO + (R * i + half) * kLd + s);
+            acc3[i] = fmaf(hk.w, o4.w, fmaf(hk.z, o4.z, fmaf(hk.y, o4.y, fmaf(hk.x, o4.x, acc3[i]))));
+          }
+          const float4 x4 = *reinterpret_cast<const float4*>(sxm + s);
+          float4 h1k;  // recomputed first-layer activation, row k
+          h1k.x = fmaxf(fmaf(x4.x, w1k, b1k), 0.f);
+          h1k.y = fmaxf(fmaf(x4.y, w1k, b1k), 0.f);
+          h1k.z = fmaxf(fmaf(x4.z, w1k, b1k), 0.f);
+          h1k.w = fmaxf(fmaf(x4.w, w1k, b1k), 0.f);
 #pragma unroll
-          for (int i = 0; i < C2N; ++i) acc2[i] = fmaf(h1k, bufG[(R * i + half) * kLd + s], acc2[i]);
-          if (half < 2) accb += half ? bufG[k * kLd + s] : (k < OP ? bufO[k * kLd + s] : 0.f);
+          for (int i = 0; i < C2N; ++i) {
+            const float4 g4 = *reinterpret_cast<const float4*>(bufG + (R * i + half) * kLd + s);
+            acc2[i] = fmaf(h1k.w, g4.w, fmaf(h1k.z, g4.z, fmaf(h1k.y, g4.y, fmaf(h1k.x, g4.x, acc2[i]))));
+          }
+          if (half < 2) {
+            const float4 b4 = half ? *reinterpret_cast<const float4*>(bufG + k * kLd + s)
+                                   : (k < OP ? *reinterpret_cast<const float4*>(bufO + k * kLd + s) : make_float4(0.f, 0.f, 0.f, 0.f));
+            accb += (b4.x + b4.y) + (b4.z + b4.w);
+          }
         }
         if (k < h2n) {
 #pragma unroll
@@ -328,7 +342,7 @@ static int tg_launch(const flowcuda_coupling_spec* sp, TgArgs a, int grid, cudaS
   using I = TgImg<OP>;
   (void)sp; (void)grid;
   auto floats = [&](int T) {
-    return (size_t)((I::total + 3) & ~3) + 2 * (size_t)kTgH * (T + 1) + (size_t)OP * (T + 1) + T + (size_t)(a.L + 1) * 2 * T + 8;
+    return (size_t)((I::total + 3) & ~3) + 2 * (size_t)kTgH * (T + 4) + (size_t)OP * (T + 4) + T + (size_t)(a.L + 1) * 2 * T + 8;
   };
   // 256-sample tiles when every SM still gets a tile and the states fit the 227 KB of shared memory
   if (a.n >= (int64_t)256 * sm_count() && floats(256) * 4 <= 232448) return tg_launch_t<TR, KT, OP, 256>(a, floats(256), s);
