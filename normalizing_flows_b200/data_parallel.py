@@ -63,11 +63,13 @@ class DataParallelTrainer:
 
 
 def cuda_grad_fn(spec):
-    """libflowcuda gradient of the SUM of -log_prob over the local shard."""
-    from . import ops
+    """libflowcuda gradient of the SUM of -log_prob over the local shard (coupling or MADE spec)."""
+    from . import _lib, ops
+
+    nll_grad = ops.made_nll_grad if isinstance(spec, _lib.MadeSpec) else ops.coupling_nll_grad
 
     def fn(params, x_local):
-        loss, grad = ops.coupling_nll_grad(spec, params, x_local)
+        loss, grad = nll_grad(spec, params, x_local)
         n = float(x_local.shape[0])
         return loss * n, grad * n
 
