@@ -124,6 +124,23 @@ int flowcuda_bernstein_inverse(const float* theta, int order, int64_t n_events, 
 int flowcuda_bernstein_flow_log_prob(const float* theta, int order, const float* scal,
                                      const float* x, float* log_prob, int64_t n, void* stream);
 
+/* Reverse mode of flowcuda_bernstein_forward_and_log_det — what jax.grad computes through
+ * BernsteinBijector.forward_and_log_det (BernsteinBijector.py:82-96; maf_mwe.py:96-113,143).
+ * Cotangents ybar[n], ldbar[n] (either may be NULL = zero) -> xbar[n] (d/dx, zero where the clip
+ * is active) and thetabar (d/dtheta of the CONSTRAINED thetas): [M] summed over the elements when
+ * theta_stride = 0 (bit-reproducible fixed-order reduction), [n, theta_stride] rows otherwise.
+ * xbar or thetabar may be NULL.  workspace: flowcuda_bernstein_vjp_workspace_bytes (0 for rows). */
+size_t flowcuda_bernstein_vjp_workspace_bytes(int order, int64_t theta_stride, int64_t n);
+int flowcuda_bernstein_forward_and_log_det_vjp(const float* theta, int order, int64_t theta_stride,
+                                               const float* x, const float* ybar, const float* ldbar,
+                                               float* xbar, float* thetabar, int64_t n, void* workspace,
+                                               size_t workspace_bytes, void* stream);
+
+/* Reverse mode of flowcuda_bernstein_constrain_thetas: thetabar[rows,M] -> rawbar[rows,M],
+ * rawbar_0 = sum_j thetabar_j, rawbar_k = sigmoid(raw_k) * sum_{j>=k} thetabar_j. */
+int flowcuda_bernstein_constrain_thetas_vjp(const float* theta_raw, const float* thetabar, float* rawbar,
+                                            int64_t rows, int order, void* stream);
+
 /* ------------------------------------------------------------------------------------
  * Rows #2, #3, #4, #6 — distrax MaskedCoupling flows
  * (src/real_nvp_toy_densities.py:56-110, src/maf_toy_densities.py:55-111,

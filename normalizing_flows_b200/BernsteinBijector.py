@@ -9,9 +9,58 @@ from . import ops
 from .distrax_api import Bijector
 
 
+class _ConstrainThetas(torch.autograd.Function):
+    """constrain_thetas with its reverse mode (bg_constrain_vjp_kernel)."""
+
+    @staticmethod
+    def forward(ctx, raw):
+        ctx.save_for_backward(raw)
+        return ops.bernstein_constrain_thetas(raw)
+
+    @staticmethod
+    def backward(ctx, thetabar):
+        (raw,) = ctx.saved_tensors
+        return ops.bernstein_constrain_thetas_vjp(raw, thetabar.contiguous())
+
+
+class _ForwardAndLogDet(torch.autograd.Function):
+    """forward_and_log_det with its reverse mode (csrc/bernstein_grad.cu) — what jax.grad differentiates in
+    src/maf_mwe.py:96-113,143.  Differentiable once (the backward is a kernel, not a graph)."""
+
+    @staticmethod
+    def forward(ctx, theta, x):
+        ctx.save_for_backward(theta, x)
+        y, ld = ops.bernstein_forward_and_log_det(theta, x)
+        return y, ld
+
+    @staticmethod
+    def backward(ctx, ybar, ldbar):
+        theta, x = ctx.saved_tensors
+        need_t, need_x = ctx.needs_input_grad
+        xbar, tbar = ops.bernstein_forward_and_log_det_vjp(theta, x, ybar, ldbar, want_xbar=need_x, want_thetabar=need_t)
+        return tbar, xbar
+
+
+def _tracked(*ts):
+    return torch.is_grad_enabled() and any(isinstance(t, torch.Tensor) and t.requires_grad for t in ts)
+
+
+def _fwd(theta, x):
+    """(y, log_det); recorded for autograd when theta or x asks for gradients."""
+    x = _cuda(x)
+    if _tracked(theta, x):
+        if theta.dim() > 1 and tuple(theta.shape[:-1]) != tuple(x.shape):
+            theta = theta.expand(*x.shape, theta.shape[-1])
+        return _ForwardAndLogDet.apply(theta.contiguous(), x.contiguous())
+    return ops.bernstein_forward_and_log_det(theta, x)
+
+
 def constrain_thetas(theta_unconstrained, range_min=None, range_max=None, fn=None):
     """BernsteinBijector.py:60-71 (range_min/range_max/fn are unused there too)."""
-    return ops.bernstein_constrain_thetas(torch.as_tensor(theta_unconstrained, dtype=torch.float32, device="cuda"))
+    raw = torch.as_tensor(theta_unconstrained, dtype=torch.float32).to("cuda")
+    if _tracked(raw):
+        return _ConstrainThetas.apply(raw.contiguous())
+    return ops.bernstein_constrain_thetas(raw)
 
 
 def get_bernstein_poly(theta):
@@ -46,13 +95,17 @@ class BernsteinBijector(Bijector):
         self.thetas = constrain_thetas(thetas)
 
     def forward(self, x):
+        if _tracked(self.thetas, x):
+            return _fwd(self.thetas, x)[0]
         return ops.bernstein_forward_and_log_det(self.thetas, _cuda(x), want_ld=False)[0]
 
     def forward_log_det_jacobian(self, x):
+        if _tracked(self.thetas, x):
+            return _fwd(self.thetas, x)[1]
         return ops.bernstein_forward_and_log_det(self.thetas, _cuda(x), want_y=False)[1]
 
     def forward_and_log_det(self, x):
-        return ops.bernstein_forward_and_log_det(self.thetas, _cuda(x))
+        return _fwd(self.thetas, x)
 
     def inverse(self, y):
         return ops.bernstein_inverse(self.thetas, _cuda(y))

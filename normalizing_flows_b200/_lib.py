@@ -76,6 +76,9 @@ SIGNATURES = {
     "flowcuda_bernstein_forward_and_log_det": (_i, [_p, _i, _i64, _p, _p, _p, _i64, _p]),
     "flowcuda_bernstein_inverse": (_i, [_p, _i, _i64, _i, _p, _p, _i64, _p, _p]),
     "flowcuda_bernstein_flow_log_prob": (_i, [_p, _i, _p, _p, _p, _i64, _p]),
+    "flowcuda_bernstein_vjp_workspace_bytes": (_sz, [_i, _i64, _i64]),
+    "flowcuda_bernstein_forward_and_log_det_vjp": (_i, [_p, _i, _i64, _p, _p, _p, _p, _p, _i64, _p, _sz, _p]),
+    "flowcuda_bernstein_constrain_thetas_vjp": (_i, [_p, _p, _p, _i64, _i, _p]),
     "flowcuda_coupling_param_count": (_i64, [_spec]),
     "flowcuda_coupling_workspace_bytes": (_sz, [_spec, _i64]),
     "flowcuda_coupling_log_prob": (_i, [_spec, _p, _p, _p, _p, _p, _i64, _i, _i, _i, _p, _sz, _p]),

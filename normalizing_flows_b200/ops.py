@@ -133,6 +133,46 @@ def bernstein_forward_and_log_det(theta: torch.Tensor, x: torch.Tensor, want_y: 
     return y, ld
 
 
+def bernstein_forward_and_log_det_vjp(theta: torch.Tensor, x: torch.Tensor, ybar=None, ldbar=None,
+                                      want_xbar: bool = True, want_thetabar: bool = True):
+    """Reverse mode of bernstein_forward_and_log_det (csrc/bernstein_grad.cu): cotangents ybar / ldbar (shape of
+    x, either may be None) -> (xbar, thetabar); thetabar is [M] for a shared theta, theta's shape for rows."""
+    theta, x = _f32(theta), _f32(x)
+    _dev_check(theta, x)
+    order = theta.shape[-1]
+    shared = theta.dim() == 1
+    if not shared and tuple(theta.shape[:-1]) != tuple(x.shape):
+        raise ValueError("bernstein vjp: per-element theta must be [*x.shape, M]")
+    if ybar is not None:
+        ybar = _f32(ybar.expand_as(x))
+        _dev_check(ybar)
+    if ldbar is not None:
+        ldbar = _f32(ldbar.expand_as(x))
+        _dev_check(ldbar)
+    lib = _lib.load()
+    stride = 0 if shared else order
+    xbar = torch.empty_like(x) if want_xbar else None
+    tbar = torch.empty_like(theta) if want_thetabar else None
+    nbytes = lib.flowcuda_bernstein_vjp_workspace_bytes(order, stride, x.numel()) if want_thetabar else 0
+    ws = torch.empty(max(nbytes, 16) // 4, device=x.device, dtype=torch.float32)
+    check(lib.flowcuda_bernstein_forward_and_log_det_vjp(_ptr(theta), order, stride, _ptr(x), _ptr(ybar), _ptr(ldbar),
+                                                         _ptr(xbar), _ptr(tbar), x.numel(), _ptr(ws), ws.numel() * 4,
+                                                         _stream()), "bernstein_forward_and_log_det_vjp")
+    return xbar, tbar
+
+
+def bernstein_constrain_thetas_vjp(theta_raw: torch.Tensor, thetabar: torch.Tensor) -> torch.Tensor:
+    t, tb = _f32(theta_raw), _f32(thetabar)
+    _dev_check(t, tb)
+    if t.shape != tb.shape:
+        raise ValueError("bernstein_constrain_thetas_vjp: thetabar must have theta_raw's shape")
+    order = t.shape[-1]
+    out = torch.empty_like(t)
+    check(_lib.load().flowcuda_bernstein_constrain_thetas_vjp(_ptr(t), _ptr(tb), _ptr(out), t.numel() // order, order,
+                                                              _stream()), "bernstein_constrain_thetas_vjp")
+    return out
+
+
 def bernstein_inverse(theta: torch.Tensor, y: torch.Tensor, n_points: int = 200) -> torch.Tensor:
     """theta [E,M] (or [M] with E=1), y [N,E] -> x [E,N] (the reference's vmap output layout)."""
     theta, y = _f32(theta), _f32(y)
