@@ -1,39 +1,55 @@
 // coupling_toy_tc.cu — rows #2/#3/#6 at event_dim = 2 on the 5th-gen tensor cores
 // (FLOWCUDA_PRECISION_3XTF32): the whole distrax MaskedCoupling stack of
 // src/real_nvp_toy_densities.py:74-110 / src/maf_toy_densities.py:73-111 in ONE persistent
-// kernel, the two hidden Linears of every conditioner as tcgen05.mma kind::tf32 in
-// error-compensated 3-pass form (hi·hi + hi·lo + lo·hi, fp32 accumulate in TMEM).
+// kernel, the two hidden Linears of every conditioner as tcgen05.mma in error-compensated 3-pass form
+// (hi·hi + hi·lo + lo·hi, fp32 accumulate in TMEM).
 //
-// CTA = 2 sample warpgroups + 2 MMA-issuer warps (one per warpgroup) + 1 weight-loader warp, one CTA per SM.
+// Operand format: fp16 hi/lo pairs under kind::f16.  fp16 carries the same 11 significant bits as tf32, so
+// the three passes give the same ~2^-21 relative products as a tf32 split — but an operand element takes
+// 16 bits, which (a) halves the A operand's TMEM footprint: a tile needs 32 (A hi) + 32 (A lo) + 64 (D)
+// = 128 columns, so FOUR tiles are resident in the 512 columns instead of two and every sample warpgroup
+// owns its TMEM slot outright (no slot hand-off between warpgroups: in the tf32 version 30 % of the sample
+// warps' time was spent waiting for the partner to drain the shared slot); (b) doubles the MMA K per
+// instruction (12 MMAs per GEMM instead of 24); (c) halves the weight images in shared memory.
+// fp16's narrow exponent is handled by scaling: each layer's W2 / W3 are multiplied by a power of two that
+// puts max|W| in [2^13, 2^14) before the split (undone exactly in the epilogue's FMA); activations are relu
+// outputs, clamped at 65504 (fp16 max — far outside anything a flow's hidden layer produces); lo parts that
+// fall into fp16's subnormal range lose bits below 2^-25 ABSOLUTE, which is under fp32's own rounding of
+// the sums they enter.
+//
+// CTA = 4 sample warpgroups + 4 MMA-issuer warps (one per warpgroup) + 1 weight-loader warp, one CTA per SM.
 // A warpgroup owns a 128-sample tile: thread = sample = TMEM lane.  Per flow layer
-//   L1  (2->64, only the visible coordinate contributes): CUDA cores, result split into tf32
+//   L1  (2->64, only the visible coordinate contributes): CUDA cores, result split into fp16
 //       hi/lo and written straight into TMEM as the A operand (tcgen05.st) — activations never
 //       touch shared or global memory;
-//   L2  (64->64): 24 MMAs M128 N64 K8, A from TMEM, W2 (hi/lo tile images) from shared memory;
-//   epilogue 2: tcgen05.ld, +bias, relu, split, tcgen05.st back as the next A operand;
-//   L3  (64->needed columns only, padded to N3): 24 MMAs M128 N{48,32,16};
+//   L2  (64->64): 12 MMAs M128 N64 K16, A from TMEM, W2 (hi/lo tile images) from shared memory;
+//   epilogue 2: tcgen05.ld, scale, +bias, relu, split, tcgen05.st back as the next A operand;
+//   L3  (64->needed columns only, padded to N3): 12 MMAs M128 N{48,32,16};
 //   epilogue 3: tcgen05.ld of the 3K+1 spline (or 2 affine) parameters of the transformed
 //       coordinate, inner bijector, log-det accumulation.
-// The two warpgroups' tiles interleave on the tensor pipe (one computes its epilogue while the
-// other's MMAs run).  Weights of a layer are one contiguous pre-packed image fetched by a single
-// cp.async.bulk (TMA) into a double-buffered slot and shared by T tile pairs whose per-sample
-// state (x0, x1, log-det) waits in shared memory, so a chunk of T*256 samples reads each layer's
+// The four warpgroups' tiles interleave on the tensor pipe (one computes its epilogue while the
+// others' MMAs run).  Weights of a layer are one contiguous pre-packed image fetched by a single
+// cp.async.bulk (TMA) into a double-buffered slot and shared by T tile quads whose per-sample
+// state (x0, x1, log-det) waits in shared memory, so a chunk of T*512 samples reads each layer's
 // weights once.  HBM traffic: x in, log_prob (and/or z) out.
+#include <cuda_fp16.h>
+
 #include "tc.cuh"
 #include "transforms.cuh"
 
 namespace flowcuda {
 
-constexpr int kTcThreads = 4 * 128 + 96;  // warps 0-15: WG0-3 (WG g works in TMEM slot g&1), 16/17: MMA issuers of slot 0/1, 18: loader
+constexpr int kTcThreads = 4 * 128 + 160;  // warps 0-15: WG0-3 (WG g owns TMEM slot g), 16-19: their MMA issuers, 20: loader
+constexpr uint32_t kFmtF16 = 0;            // kind::f16 operand format code of fp16 (bf16 = 1)
 constexpr int kTcMaxT = 8;       // tile pairs per chunk
 
 template <int N3>
 struct ToyTcImg {  // per-layer packed image (bytes)
-  static constexpr int w2 = 64 * 64 * 4;                  // one of hi / lo
-  static constexpr int w3 = N3 * 64 * 4;
+  static constexpr int w2 = 64 * 64 * 2;                  // one of hi / lo (fp16)
+  static constexpr int w3 = N3 * 64 * 2;
   static constexpr int off_w2hi = 0, off_w2lo = w2, off_w3hi = 2 * w2, off_w3lo = 2 * w2 + w3;
   static constexpr int wbytes = 2 * w2 + 2 * w3;          // the TMA-fetched part
-  static constexpr int small_floats = 192 + N3;           // w1(visible row)[64] b1[64] b2[64] b3[N3]
+  static constexpr int small_floats = 192 + N3 + 4;       // w1(visible row)[64] b1[64] b2[64] b3[N3] {1/s2, 1/s3, -, -}
   static constexpr int bytes = (wbytes + small_floats * 4 + 127) & ~127;
 };
 
@@ -70,29 +86,57 @@ __global__ void __launch_bounds__(256) toy_tc_pack_kernel(const float* __restric
   uint8_t* out = img + (size_t)l * I::bytes;
   const int t = l & 1;  // transformed coordinate; the visible one is 1 - t
   const int col0 = TR == FLOWCUDA_TRANSFORM_AFFINE_SCALAR ? 0 : t * NEED;
-  for (int i = threadIdx.x; i < 64 * 16; i += blockDim.x) {  // W2: rows n (out), 16 K chunks
+  // power-of-two scales that put max|W| in [2^13, 2^14): the fp16 lo parts stay in the normal range
+  __shared__ int smax[2];
+  if (threadIdx.x < 2) smax[threadIdx.x] = 0;
+  __syncthreads();
+  float m2 = 0.f, m3 = 0.f;
+  for (int i = threadIdx.x; i < h1 * h2; i += blockDim.x) m2 = fmaxf(m2, fabsf(pW2[i]));
+  for (int i = threadIdx.x; i < h2 * NEED; i += blockDim.x) m3 = fmaxf(m3, fabsf(pW3[(size_t)(i / NEED) * of + col0 + i % NEED]));
+  atomicMax(&smax[0], __float_as_int(m2));  // non-negative floats order like their bit patterns
+  atomicMax(&smax[1], __float_as_int(m3));
+  __syncthreads();
+  m2 = __int_as_float(smax[0]);
+  m3 = __int_as_float(smax[1]);
+  const int e2 = (m2 > 0.f && isfinite(m2)) ? ilogbf(m2) : 13, e3 = (m3 > 0.f && isfinite(m3)) ? ilogbf(m3) : 13;
+  const float s2 = ldexpf(1.f, 13 - e2), s3 = ldexpf(1.f, 13 - e3);
+  auto split8 = [](const float* w, uint4& hi, uint4& lo) {
+    __half2 h[4], l[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      h[e] = __floats2half2_rn(w[2 * e], w[2 * e + 1]);  // element 2e in the low half
+      l[e] = __floats2half2_rn(w[2 * e] - __low2float(h[e]), w[2 * e + 1] - __high2float(h[e]));
+    }
+    hi = *reinterpret_cast<uint4*>(h);
+    lo = *reinterpret_cast<uint4*>(l);
+  };
+  for (int i = threadIdx.x; i < 64 * 8; i += blockDim.x) {  // W2: rows n (out), 8 K chunks of 8
     const int n = i & 63, kc = i >> 6;
-    float h[4], lo[4];
+    float w[8];
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const int k = kc * 4 + e;
-      tc::split_tf32_rn((k < h1 && n < h2) ? pW2[(size_t)k * h2 + n] : 0.f, h[e], lo[e]);
+    for (int e = 0; e < 8; ++e) {
+      const int k = kc * 8 + e;
+      w[e] = (k < h1 && n < h2) ? pW2[(size_t)k * h2 + n] * s2 : 0.f;
     }
+    uint4 hi, lo;
+    split8(w, hi, lo);
     const uint32_t off = tc::img_off(64, n, kc);
-    *reinterpret_cast<float4*>(out + I::off_w2hi + off) = make_float4(h[0], h[1], h[2], h[3]);
-    *reinterpret_cast<float4*>(out + I::off_w2lo + off) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+    *reinterpret_cast<uint4*>(out + I::off_w2hi + off) = hi;
+    *reinterpret_cast<uint4*>(out + I::off_w2lo + off) = lo;
   }
-  for (int i = threadIdx.x; i < N3 * 16; i += blockDim.x) {  // W3: needed columns only
+  for (int i = threadIdx.x; i < N3 * 8; i += blockDim.x) {  // W3: needed columns only
     const int n = i % N3, kc = i / N3;
-    float h[4], lo[4];
+    float w[8];
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const int k = kc * 4 + e;
-      tc::split_tf32_rn((k < h2 && n < NEED) ? pW3[(size_t)k * of + col0 + n] : 0.f, h[e], lo[e]);
+    for (int e = 0; e < 8; ++e) {
+      const int k = kc * 8 + e;
+      w[e] = (k < h2 && n < NEED) ? pW3[(size_t)k * of + col0 + n] * s3 : 0.f;
     }
+    uint4 hi, lo;
+    split8(w, hi, lo);
     const uint32_t off = tc::img_off(N3, n, kc);
-    *reinterpret_cast<float4*>(out + I::off_w3hi + off) = make_float4(h[0], h[1], h[2], h[3]);
-    *reinterpret_cast<float4*>(out + I::off_w3lo + off) = make_float4(lo[0], lo[1], lo[2], lo[3]);
+    *reinterpret_cast<uint4*>(out + I::off_w3hi + off) = hi;
+    *reinterpret_cast<uint4*>(out + I::off_w3lo + off) = lo;
   }
   float* sm = reinterpret_cast<float*>(out + I::wbytes);
   for (int i = threadIdx.x; i < I::small_floats; i += blockDim.x) {
@@ -100,7 +144,9 @@ __global__ void __launch_bounds__(256) toy_tc_pack_kernel(const float* __restric
     if (i < 64) v = i < h1 ? pW1[(1 - t) * h1 + i] : 0.f;
     else if (i < 128) v = (i - 64) < h1 ? pb1[i - 64] : 0.f;
     else if (i < 192) v = (i - 128) < h2 ? pb2[i - 128] : 0.f;
-    else v = (i - 192) < NEED ? pb3[col0 + i - 192] : 0.f;
+    else if (i < 192 + N3) v = (i - 192) < NEED ? pb3[col0 + i - 192] : 0.f;
+    else if (i == 192 + N3) v = 1.f / s2;
+    else if (i == 192 + N3 + 1) v = 1.f / s3;
     sm[i] = v;
   }
 }
@@ -124,6 +170,17 @@ __device__ __forceinline__ void tmem_load_cols(uint32_t taddr, uint32_t* o) {
   tc::tmem_ld_wait();
 }
 
+// relu clamped at fp16's largest finite value
+__device__ __forceinline__ float act_f16(float x) { return fminf(fmaxf(x, 0.f), 65504.f); }
+// two non-negative fp32 values -> fp16 hi pair and lo pair (element 0 in the low half).  hi = x with the low 13
+// mantissa bits cleared (11 significant bits: exactly an fp16 value inside its normal range), lo = rn(x - hi).
+__device__ __forceinline__ void split_f16x2(float x0, float x1, uint32_t& hi, uint32_t& lo) {
+  const float h0 = __uint_as_float(__float_as_uint(x0) & 0xFFFFE000u), h1 = __uint_as_float(__float_as_uint(x1) & 0xFFFFE000u);
+  const __half2 h = __floats2half2_rn(h0, h1), l = __floats2half2_rn(x0 - h0, x1 - h1);
+  hi = *reinterpret_cast<const uint32_t*>(&h);
+  lo = *reinterpret_cast<const uint32_t*>(&l);
+}
+
 template <int TR, int KT, bool INV>
 __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArgs a) {
   constexpr int NEED = toy_need(TR, KT), N3 = toy_n3(TR, KT);
@@ -140,21 +197,21 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
   float* sx1 = sx0 + T * 512;
   float* sld = sx1 + T * 512;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sld + T * 512);
-  uint64_t* a_ready = bars;       // [2] count 128: a warpgroup's A operand is in TMEM
-  uint64_t* d_full = bars + 2;    // [2] count 1: the MMAs of a warpgroup's request completed
-  uint64_t* w_full = bars + 4;    // [2] count 1 + tx: weight image landed
-  uint64_t* w_free = bars + 6;    // [2] count 1: every MMA reading the slot completed
-  uint64_t* slot_free = bars + 8; // [2] count 128: the slot's current warpgroup has drained its accumulator
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+  uint64_t* a_ready = bars;       // [4] count 128: warpgroup g's A operand is in TMEM
+  uint64_t* d_full = bars + 4;    // [4] count 1: the MMAs of warpgroup g's request completed
+  uint64_t* w_full = bars + 8;    // [2] count 1 + tx: weight image landed
+  uint64_t* w_free = bars + 10;   // [2] count 4: every issuer's MMAs reading the weight slot completed
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
 
   if (warp == 16) tc::tmem_alloc(tmem_slot, 512);
   if (tid == 0) {
-    for (int g = 0; g < 2; ++g) {
+    for (int g = 0; g < 4; ++g) {
       tc::mbar_init(&a_ready[g], 128);
       tc::mbar_init(&d_full[g], 1);
-      tc::mbar_init(&w_full[g], 1);
-      tc::mbar_init(&w_free[g], 2);
-      tc::mbar_init(&slot_free[g], 128);
+    }
+    for (int b = 0; b < 2; ++b) {
+      tc::mbar_init(&w_full[b], 1);
+      tc::mbar_init(&w_free[b], 4);
     }
     tc::fence_mbar_init();
   }
@@ -173,7 +230,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
   const int my_chunks = blockIdx.x < nchunks ? (int)((nchunks - 1 - blockIdx.x) / gridDim.x + 1) : 0;
   const int Q = my_chunks * nl;  // layer steps this CTA runs
 
-  if (warp == 18) {
+  if (warp == 20) {
     // ===== weight loader: one cp.async.bulk per layer step into slot q&1 =====
     if (lane == 0) {
       for (int q = 0; q < Q; ++q) {
@@ -185,17 +242,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
       }
     }
   } else if (warp >= 16) {
-    // ===== MMA issuers: warp 8 serves warpgroup 0, warp 9 warpgroup 1 (blocking waits, no polling) =====
+    // ===== MMA issuers: warp 16+g serves warpgroup g (blocking waits, no polling) =====
     if (lane == 0) {
-      constexpr uint32_t idesc2 = tc::make_idesc(tc::kFmtTF32, 128, 64);
-      constexpr uint32_t idesc3 = tc::make_idesc(tc::kFmtTF32, 128, N3);
-      const int g = warp - 16;  // TMEM slot served
-      const uint32_t tb = tmem + (uint32_t)g * 192u;  // A hi [0,64) A lo [64,128) D [128,192)
+      constexpr uint32_t idesc2 = tc::make_idesc(kFmtF16, 128, 64);
+      constexpr uint32_t idesc3 = tc::make_idesc(kFmtF16, 128, N3);
+      const int g = warp - 16;  // warpgroup / TMEM slot served
+      const uint32_t tb = tmem + (uint32_t)g * 128u;  // A hi [0,32) A lo [32,64) D [64,128)
       uint32_t r = 0;
       for (int q = 0; q < Q; ++q) {
         const int b = q & 1;
         const uint32_t wb = tc::smem_u32(wbuf + b * I::wbytes);
-        for (int t = 0; t < 2 * T; ++t) {  // the slot's two warpgroups alternate, T tiles each
+        for (int t = 0; t < T; ++t) {
 #pragma unroll 1
           for (int p = 0; p < 2; ++p, ++r) {
             tc::mbar_wait(&a_ready[g], r & 1);
@@ -207,27 +264,27 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
             uint32_t acc = 0;
 #pragma unroll 1
             for (int pass = 0; pass < 3; ++pass) {
-              const uint32_t at = tb + (pass == 2 ? 64u : 0u);
+              const uint32_t at = tb + (pass == 2 ? 32u : 0u);
               // descriptor of K step s = descriptor of step 0 + (s * 2 * LBO) >> 4 in the address field
               const uint64_t d0 = tc::make_smem_desc(pass == 1 ? bl : bh, lbo, 128u);
               const uint64_t dstep = (uint64_t)((2u * lbo) >> 4);
 #pragma unroll
-              for (int s = 0; s < 8; ++s) {
-                tc::mma_ts<tc::kFmtTF32>(tb + 128u, at + 8u * s, d0 + dstep * (uint64_t)s, idesc, acc);
+              for (int s = 0; s < 4; ++s) {  // K = 16 per instruction: 8 TMEM columns of fp16 pairs, 2 smem chunks
+                // (template tag selects the kind::f16 instruction; the fp16 format code is in idesc)
+                tc::mma_ts<tc::kFmtBF16>(tb + 64u, at + 8u * s, d0 + dstep * (uint64_t)s, idesc, acc);
                 acc = 1;
               }
             }
             tc::mma_commit(&d_full[g]);
           }
         }
-        tc::mma_commit(&w_free[b]);  // this issuer's MMAs on slot b are done (count 2: both issuers)
+        tc::mma_commit(&w_free[b]);  // this issuer's MMAs on weight slot b are done (count 4: all issuers)
       }
     }
   } else {
     // ===== sample warpgroups =====
-    const int g = warp >> 2, sl = g & 1, row = tid & 127;
-    const uint32_t tb = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)sl * 192u;
-    uint32_t use = (uint32_t)(g >> 1);  // this warpgroup's next turn in its slot (turns alternate g, g^2)
+    const int g = warp >> 2, sl = g, row = tid & 127;
+    const uint32_t tb = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)g * 128u;
     for (int ci = 0; ci < my_chunks; ++ci) {
       const int64_t base = ((int64_t)blockIdx.x + (int64_t)ci * gridDim.x) * chunk_samples;
       for (int t = 0; t < T; ++t) {
@@ -248,52 +305,43 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
           const float x0 = sx0[slot], x1 = sx1[slot];
           const float xm = td ? x0 : x1;  // visible value
           const float xt = td ? x1 : x0;  // value to transform
-          if (use > 0) tc::mbar_wait(&slot_free[sl], (use - 1) & 1);  // previous user drained the slot
-          tc::tc_fence_after();
           // ---- L1: Linear(2->64)+relu on where(mask, x, 0); split; A operand -> TMEM
 #pragma unroll
-          for (int c = 0; c < 4; ++c) {
+          for (int c = 0; c < 2; ++c) {
             uint32_t hi[16], lo[16];
 #pragma unroll
-            for (int e4 = 0; e4 < 4; ++e4) {
-              const float4 w = *reinterpret_cast<const float4*>(sm + 16 * c + 4 * e4);
-              const float4 b = *reinterpret_cast<const float4*>(sm + 64 + 16 * c + 4 * e4);
-              const float h[4] = {fmaxf(fmaf(xm, w.x, b.x), 0.f), fmaxf(fmaf(xm, w.y, b.y), 0.f),
-                                  fmaxf(fmaf(xm, w.z, b.z), 0.f), fmaxf(fmaf(xm, w.w, b.w), 0.f)};
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                float fh, fl;
-                tc::split_tf32(h[e], fh, fl);
-                hi[4 * e4 + e] = __float_as_uint(fh);
-                lo[4 * e4 + e] = __float_as_uint(fl);
-              }
+            for (int e4 = 0; e4 < 8; ++e4) {
+              const float4 w = *reinterpret_cast<const float4*>(sm + 32 * c + 4 * e4);
+              const float4 b = *reinterpret_cast<const float4*>(sm + 64 + 32 * c + 4 * e4);
+              split_f16x2(act_f16(fmaf(xm, w.x, b.x)), act_f16(fmaf(xm, w.y, b.y)), hi[2 * e4], lo[2 * e4]);
+              split_f16x2(act_f16(fmaf(xm, w.z, b.z)), act_f16(fmaf(xm, w.w, b.w)), hi[2 * e4 + 1], lo[2 * e4 + 1]);
             }
             tc::tmem_st_x16(tb + 16u * c, hi);
-            tc::tmem_st_x16(tb + 64u + 16u * c, lo);
+            tc::tmem_st_x16(tb + 32u + 16u * c, lo);
           }
           tc::tmem_st_wait();
           tc::tc_fence_before();
           tc::mbar_arrive(&a_ready[sl]);
           tc::mbar_wait(&d_full[sl], 0);
           tc::tc_fence_after();
-          // ---- epilogue 2: +b2, relu, split, next A operand -> TMEM
+          // ---- epilogue 2: unscale, +b2, relu, split, next A operand -> TMEM
           {
+            const float inv2 = sm[192 + N3];
             uint32_t v[64];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) tc::tmem_ld_x16(tb + 128u + 16u * c, v + 16 * c);
+            for (int c = 0; c < 4; ++c) tc::tmem_ld_x16(tb + 64u + 16u * c, v + 16 * c);
             tc::tmem_ld_wait();
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
+            for (int c = 0; c < 2; ++c) {
               uint32_t hi[16], lo[16];
 #pragma unroll
               for (int e = 0; e < 16; ++e) {
-                float fh, fl;
-                tc::split_tf32(fmaxf(__uint_as_float(v[16 * c + e]) + sm[128 + 16 * c + e], 0.f), fh, fl);
-                hi[e] = __float_as_uint(fh);
-                lo[e] = __float_as_uint(fl);
+                const int k = 32 * c + 2 * e;
+                split_f16x2(act_f16(fmaf(__uint_as_float(v[k]), inv2, sm[128 + k])),
+                            act_f16(fmaf(__uint_as_float(v[k + 1]), inv2, sm[128 + k + 1])), hi[e], lo[e]);
               }
               tc::tmem_st_x16(tb + 16u * c, hi);
-              tc::tmem_st_x16(tb + 64u + 16u * c, lo);
+              tc::tmem_st_x16(tb + 32u + 16u * c, lo);
             }
           }
           tc::tmem_st_wait();
@@ -304,14 +352,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
           // ---- epilogue 3: inner bijector on the transformed coordinate
           float o[NEED];
           {
+            const float inv3 = sm[192 + N3 + 1];
             uint32_t v[NEED];
-            tmem_load_cols<NEED>(tb + 128u, v);
+            tmem_load_cols<NEED>(tb + 64u, v);
 #pragma unroll
-            for (int i = 0; i < NEED; ++i) o[i] = __uint_as_float(v[i]) + sm[192 + i];
+            for (int i = 0; i < NEED; ++i) o[i] = fmaf(__uint_as_float(v[i]), inv3, sm[192 + i]);
           }
-          tc::tc_fence_before();
-          tc::mbar_arrive(&slot_free[sl]);  // hand the slot to the partner warpgroup
-          use += 2;
+          tc::tc_fence_before();  // the accumulator is drained before this warpgroup's next A operand / MMA
           float nv, l1;
           if (TR == FLOWCUDA_TRANSFORM_RQS) {
             rqs_apply<INV, KT>([&](int i) { return o[i]; }, KT, a.lo, a.hi, xt, nv, l1);
@@ -348,7 +395,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
 template <int TR, int KT>
 static size_t toy_tc_smem(int nl, int T) {
   using I = ToyTcImg<toy_n3(TR, KT)>;
-  return (size_t)2 * I::wbytes + (size_t)((nl * I::small_floats + 3) & ~3) * 4 + (size_t)3 * T * 512 * 4 + 10 * 8 + 16;
+  return (size_t)2 * I::wbytes + (size_t)((nl * I::small_floats + 3) & ~3) * 4 + (size_t)3 * T * 512 * 4 + 12 * 8 + 16;
 }
 
 template <int TR, int KT, bool INV>
