@@ -75,7 +75,7 @@ class Workload:
     dtype = "f32"
     launches_per_step = 1
     tc_launches = 2      # weight pack + fused stack kernel
-    tc_dtype = "tf32x3 (fp32 accumulate)"
+    tc_dtype = "fp16x3 (fp16 hi/lo split, 3 passes, fp32 accumulate)"
     cpu_sample = 1 << 16
 
     def make_inputs(self, gen, n):
@@ -96,7 +96,7 @@ class CouplingWorkload(Workload):
     ospec_name = "RQS_TOY"
     data = staticmethod(gaussian_blobs)
     transform = "rqs"
-    precision = "tc"   # "tc": tensor-core path (3xTF32 at event_dim 2); "fp32": CUDA-core FP32 path
+    precision = "tc"   # "tc": tensor-core path (3-pass fp16 hi/lo split at event_dim 2); "fp32": CUDA-core FP32 path
     tc_precision = 1   # FLOWCUDA_PRECISION_3XTF32
 
     def _ospec(self):

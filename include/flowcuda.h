@@ -157,7 +157,12 @@ int flowcuda_bernstein_constrain_thetas_vjp(const float* theta_raw, const float*
 #define FLOWCUDA_MAX_HIDDEN_LAYERS 4
 
 #define FLOWCUDA_PRECISION_FP32 0   /* CUDA-core FP32 FMA conditioner */
-#define FLOWCUDA_PRECISION_3XTF32 1 /* tcgen05 kind::tf32, error-compensated 3-pass split */
+#define FLOWCUDA_PRECISION_3XTF32 1 /* tcgen05 error-compensated 3-pass split with 11-bit operand halves (the
+                                     * accuracy of a tf32 split: ~2^-21 relative products, fp32 accumulate).
+                                     * Since r01 the event_dim-2 kernel carries the halves as fp16 under
+                                     * kind::f16 (same significand as tf32, half the TMEM/smem footprint);
+                                     * the constant keeps its name for ABI stability. */
+#define FLOWCUDA_PRECISION_3PASS FLOWCUDA_PRECISION_3XTF32
 #define FLOWCUDA_PRECISION_TF32 2   /* tcgen05 kind::tf32 single pass (reserved) */
 #define FLOWCUDA_PRECISION_BF16X3 3 /* tcgen05 kind::f16 bf16, error-compensated 3-pass split (wide conditioners) */
 

@@ -13,7 +13,8 @@
 // instruction (12 MMAs per GEMM instead of 24); (c) halves the weight images in shared memory.
 // fp16's narrow exponent is handled by scaling: each layer's W2 / W3 are multiplied by a power of two that
 // puts max|W| in [2^13, 2^14) before the split (undone exactly in the epilogue's FMA); activations are relu
-// outputs, clamped at 65504 (fp16 max — far outside anything a flow's hidden layer produces); lo parts that
+// outputs, saturated at 65504 (fp16 max — far outside anything a flow's hidden layer produces) by the packing
+// conversion itself, which also applies the relu (F2FP.SATFINITE.RELU); lo parts that
 // fall into fp16's subnormal range lose bits below 2^-25 ABSOLUTE, which is under fp32's own rounding of
 // the sums they enter.
 //
@@ -170,15 +171,14 @@ __device__ __forceinline__ void tmem_load_cols(uint32_t taddr, uint32_t* o) {
   tc::tmem_ld_wait();
 }
 
-// relu clamped at fp16's largest finite value
-__device__ __forceinline__ float act_f16(float x) { return fminf(fmaxf(x, 0.f), 65504.f); }
-// two non-negative fp32 values -> fp16 hi pair and lo pair (element 0 in the low half).  hi = x with the low 13
-// mantissa bits cleared (11 significant bits: exactly an fp16 value inside its normal range), lo = rn(x - hi).
-__device__ __forceinline__ void split_f16x2(float x0, float x1, uint32_t& hi, uint32_t& lo) {
+// relu + fp16 hi/lo split of two PRE-activations in six instructions (element 0 in the low half).
+// hi = the value with its low 13 mantissa bits cleared (11 significant bits: exactly an fp16 value inside the
+// normal range), lo = rn(x - hi).  The relu and the clamp at fp16's largest finite value ride on the packing
+// conversion (F2FP.SATFINITE.RELU): for x < 0 the truncated hi is <= 0 and x - hi <= 0, so both halves become 0.
+__device__ __forceinline__ void relu_split_f16x2(float x0, float x1, uint32_t& hi, uint32_t& lo) {
   const float h0 = __uint_as_float(__float_as_uint(x0) & 0xFFFFE000u), h1 = __uint_as_float(__float_as_uint(x1) & 0xFFFFE000u);
-  const __half2 h = __floats2half2_rn(h0, h1), l = __floats2half2_rn(x0 - h0, x1 - h1);
-  hi = *reinterpret_cast<const uint32_t*>(&h);
-  lo = *reinterpret_cast<const uint32_t*>(&l);
+  asm("cvt.rn.relu.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(hi) : "f"(h1), "f"(h0));
+  asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(x1 - h1), "f"(x0 - h0));
 }
 
 template <int TR, int KT, bool INV>
@@ -313,8 +313,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
             for (int e4 = 0; e4 < 8; ++e4) {
               const float4 w = *reinterpret_cast<const float4*>(sm + 32 * c + 4 * e4);
               const float4 b = *reinterpret_cast<const float4*>(sm + 64 + 32 * c + 4 * e4);
-              split_f16x2(act_f16(fmaf(xm, w.x, b.x)), act_f16(fmaf(xm, w.y, b.y)), hi[2 * e4], lo[2 * e4]);
-              split_f16x2(act_f16(fmaf(xm, w.z, b.z)), act_f16(fmaf(xm, w.w, b.w)), hi[2 * e4 + 1], lo[2 * e4 + 1]);
+              relu_split_f16x2(fmaf(xm, w.x, b.x), fmaf(xm, w.y, b.y), hi[2 * e4], lo[2 * e4]);
+              relu_split_f16x2(fmaf(xm, w.z, b.z), fmaf(xm, w.w, b.w), hi[2 * e4 + 1], lo[2 * e4 + 1]);
             }
             tc::tmem_st_x16(tb + 16u * c, hi);
             tc::tmem_st_x16(tb + 32u + 16u * c, lo);
@@ -337,8 +337,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
 #pragma unroll
               for (int e = 0; e < 16; ++e) {
                 const int k = 32 * c + 2 * e;
-                split_f16x2(act_f16(fmaf(__uint_as_float(v[k]), inv2, sm[128 + k])),
-                            act_f16(fmaf(__uint_as_float(v[k + 1]), inv2, sm[128 + k + 1])), hi[e], lo[e]);
+                relu_split_f16x2(fmaf(__uint_as_float(v[k]), inv2, sm[128 + k]),
+                                 fmaf(__uint_as_float(v[k + 1]), inv2, sm[128 + k + 1]), hi[e], lo[e]);
               }
               tc::tmem_st_x16(tb + 16u * c, hi);
               tc::tmem_st_x16(tb + 32u + 16u * c, lo);
