@@ -50,7 +50,7 @@ struct ToyTcImg {  // per-layer packed image (bytes)
   static constexpr int w3 = N3 * 64 * 2;
   static constexpr int off_w2hi = 0, off_w2lo = w2, off_w3hi = 2 * w2, off_w3lo = 2 * w2 + w3;
   static constexpr int wbytes = 2 * w2 + 2 * w3;          // the TMA-fetched part
-  static constexpr int small_floats = 192 + N3 + 4;       // w1(visible row)[64] b1[64] b2[64] b3[N3] {1/s2, 1/s3, -, -}
+  static constexpr int small_floats = 192 + N3 + 4;       // w1(visible row)[64] b1[64] b2[64] b3[N3] {1/s2, 1/s3, log2e/s3, -}
   static constexpr int bytes = (wbytes + small_floats * 4 + 127) & ~127;
 };
 
@@ -67,6 +67,7 @@ struct ToyTcArgs {
   int with_base, base;
   float lo, hi;
   int T;               // tile pairs per chunk
+  float koff[13];      // RQS: lo + i * min_bin_size (read from the constant bank by rqs_apply_mufu)
 };
 
 // params (haiku order) -> per-layer image.  One CTA per flow layer.
@@ -145,9 +146,11 @@ __global__ void __launch_bounds__(256) toy_tc_pack_kernel(const float* __restric
     if (i < 64) v = i < h1 ? pW1[(1 - t) * h1 + i] : 0.f;
     else if (i < 128) v = (i - 64) < h1 ? pb1[i - 64] : 0.f;
     else if (i < 192) v = (i - 128) < h2 ? pb2[i - 128] : 0.f;
-    else if (i < 192 + N3) v = (i - 192) < NEED ? pb3[col0 + i - 192] : 0.f;
+    // RQS: the 2K bin logits are delivered in log2 units (rqs_apply_mufu), so their bias and unscale carry log2(e)
+    else if (i < 192 + N3) v = (i - 192) < NEED ? pb3[col0 + i - 192] * ((TR == FLOWCUDA_TRANSFORM_RQS && (i - 192) < 2 * KT) ? kLog2e : 1.f) : 0.f;
     else if (i == 192 + N3) v = 1.f / s2;
     else if (i == 192 + N3 + 1) v = 1.f / s3;
+    else if (i == 192 + N3 + 2) v = kLog2e / s3;
     sm[i] = v;
   }
 }
@@ -352,16 +355,17 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
           // ---- epilogue 3: inner bijector on the transformed coordinate
           float o[NEED];
           {
-            const float inv3 = sm[192 + N3 + 1];
+            const float inv3 = sm[192 + N3 + 1], inv3l2 = sm[192 + N3 + 2];
             uint32_t v[NEED];
             tmem_load_cols<NEED>(tb + 64u, v);
 #pragma unroll
-            for (int i = 0; i < NEED; ++i) o[i] = fmaf(__uint_as_float(v[i]), inv3, sm[192 + i]);
+            for (int i = 0; i < NEED; ++i)
+              o[i] = fmaf(__uint_as_float(v[i]), (TR == FLOWCUDA_TRANSFORM_RQS && i < 2 * KT) ? inv3l2 : inv3, sm[192 + i]);
           }
           tc::tc_fence_before();  // the accumulator is drained before this warpgroup's next A operand / MMA
           float nv, l1;
           if (TR == FLOWCUDA_TRANSFORM_RQS) {
-            rqs_apply<INV, KT>([&](int i) { return o[i]; }, KT, a.lo, a.hi, xt, nv, l1);
+            rqs_apply_mufu<INV, (KT > 0 ? KT : 1)>([&](int i) { return o[i]; }, a.koff, a.lo, a.hi, xt, nv, l1);
           } else {
             affine_apply<INV>(o[0], o[1], xt, nv, l1);
           }
@@ -446,6 +450,7 @@ int coupling_toy_tc_dispatch(const flowcuda_coupling_spec* sp, const float* para
   a.img = nullptr; a.in = in; a.out_v = out_v; a.out_lp = out_lp; a.n = n;
   a.layer_begin = layer_begin; a.layer_end = layer_end; a.with_base = with_base; a.base = sp->base;
   a.lo = sp->range_min; a.hi = sp->range_max; a.T = 1;
+  for (int i = 0; i < 13; ++i) a.koff[i] = sp->range_min + (float)i * kRqsMinBin;
   switch (sp->transform) {
     case FLOWCUDA_TRANSFORM_AFFINE_SCALAR:
       return inverse ? toy_tc_launch<FLOWCUDA_TRANSFORM_AFFINE_SCALAR, 0, true>(sp, params, a, ws, wsb, s)

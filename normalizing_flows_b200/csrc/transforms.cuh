@@ -109,6 +109,112 @@ __device__ __forceinline__ void rqs_apply(Get p, int Krt, float lo, float hi, fl
   }
 }
 
+// ---- MUFU-based variant for the tensor-core toy path (coupling_toy_tc.cu) -------------------------
+// Same spline, restated to cut the instruction count of the epilogue (ncu: the RQS was 680 of the
+// 1340 thread-instructions per sample and layer, mostly the range-reduction code around 24 expf,
+// 3 logf and 5 IEEE divisions):
+//   * p(i), i < 2K arrive PRE-MULTIPLIED by log2(e) (folded into the unscale FMA of the epilogue), so a
+//     softmax term is FADD + MUFU.EX2;
+//   * the softmax denominators come out of the knot prefix sums, every knot is one FFMA of its prefix sum
+//     (independent, not a serial chain); koff[i] = lo + i*min_bin_size is read from the constant bank;
+//   * divisions are MUFU.RCP + FMUL (1 ulp), the three logs of the log-det are one MUFU.LG2 of the ratio;
+//   * the two knot slopes keep log1pf (their relative accuracy enters the log-det directly).
+__device__ __forceinline__ float lg2_approx(float x) {
+  float r;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+__device__ __forceinline__ float rqs_slope_mufu(float u) {
+  const float x = u + kRqsSlopeOffset;
+  return fmaxf(x, 0.f) + log1pf(ex2_ftz(-fabsf(x) * kLog2e)) + kRqsMinSlope;
+}
+
+template <bool INV, int K, typename Get>
+__device__ __forceinline__ void rqs_apply_mufu(Get p, const float* __restrict__ koff, float lo, float hi, float v,
+                                               float& out, float& ld) {
+  const float scale = (hi - lo) - (float)K * kRqsMinBin;
+  float mw = p(0), mh = p(K);
+#pragma unroll
+  for (int i = 1; i < K; ++i) {
+    mw = fmaxf(mw, p(i));
+    mh = fmaxf(mh, p(K + i));
+  }
+  float ew[K], eh[K];  // inclusive prefix sums of the unnormalised bin sizes
+  float aw = 0.f, ah = 0.f;
+#pragma unroll
+  for (int i = 0; i < K; ++i) {
+    aw += ex2_ftz(p(i) - mw);
+    ah += ex2_ftz(p(K + i) - mh);
+    ew[i] = aw;
+    eh[i] = ah;
+  }
+  const float cw = scale * rcp_approx(aw), ch = scale * rcp_approx(ah);
+  // bin = last i whose left knot is <= v (bin 0 when v lies left of the range)
+  float xl = lo, yl = lo;
+  float xr = (K == 1) ? hi : fmaf(ew[0], cw, koff[1]);
+  float yr = (K == 1) ? hi : fmaf(eh[0], ch, koff[1]);
+  float ul = p(2 * K), ur = p(2 * K + 1);
+  float xi = xr, yi = yr;
+#pragma unroll
+  for (int i = 1; i < K; ++i) {
+    const float xn = (i == K - 1) ? hi : fmaf(ew[i], cw, koff[i + 1]);
+    const float yn = (i == K - 1) ? hi : fmaf(eh[i], ch, koff[i + 1]);
+    const bool take = v >= (INV ? yi : xi);
+    xl = take ? xi : xl;
+    xr = take ? xn : xr;
+    yl = take ? yi : yl;
+    yr = take ? yn : yr;
+    ul = take ? p(2 * K + i) : ul;
+    ur = take ? p(2 * K + i + 1) : ur;
+    xi = xn;
+    yi = yn;
+  }
+  const float sl_l = rqs_slope_mufu(ul), sl_r = rqs_slope_mufu(ur);
+  const float w = xr - xl, h = yr - yl;
+  const float rw = rcp_approx(w);
+  const float s = h * rw;
+  const float t = sl_r + sl_l - 2.f * s;
+  float z;
+  if (INV) {
+    float om = fminf(fmaxf((v - yl) * rcp_approx(h), 0.f), 1.f);
+    float c = -s * om;
+    float b = sl_l - t * om;
+    float a = s - b;
+    z = fminf(fmaxf(-2.f * c * rcp_approx(b + sqrtf(b * b - 4.f * a * c)), 0.f), 1.f);
+    out = fmaf(w, z, xl);
+  } else {
+    z = fminf(fmaxf((v - xl) * rw, 0.f), 1.f);
+  }
+  const float sq_z = z * z;
+  const float z1mz = z - sq_z;
+  const float omz = 1.f - z;
+  const float rden = rcp_approx(fmaf(t, z1mz, s));
+  const float num = fmaf(sl_r, sq_z, fmaf(2.f * s, z1mz, sl_l * omz * omz));
+  const float sr = s * rden;
+  const float fld = kLn2 * lg2_approx(sr * sr * num);
+  if (INV) {
+    ld = -fld;
+  } else {
+    out = fmaf(h * fmaf(s, sq_z, sl_l * z1mz), rden, yl);
+    ld = fld;
+  }
+  // linear tails outside [lo, hi]
+  if (v <= lo) {
+    float s0 = rqs_slope(p(2 * K));
+    out = INV ? (v - lo) / s0 + lo : fmaf(v - lo, s0, lo);
+    ld = INV ? -logf(s0) : logf(s0);
+  } else if (v >= hi) {
+    float sK = rqs_slope(p(3 * K));
+    out = INV ? (v - hi) / sK + hi : fmaf(v - hi, sK, hi);
+    ld = INV ? -logf(sK) : logf(sK);
+  }
+}
+
 // Independent(Normal(0,1)) / Independent(Uniform(0,1)) contribution of one coordinate.
 __device__ __forceinline__ float base_term(int base, float z) {
   if (base == FLOWCUDA_BASE_NORMAL) return fmaf(-0.5f * z, z, -kHalfLog2Pi);
