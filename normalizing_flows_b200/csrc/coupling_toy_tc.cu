@@ -40,7 +40,10 @@
 
 namespace flowcuda {
 
-constexpr int kTcThreads = 4 * 128 + 160;  // warps 0-15: WG0-3 (WG g owns TMEM slot g), 16-19: their MMA issuers, 20: loader
+// warps 0-15: WG0-3 (WG g owns TMEM slot g), 16-19: their MMA issuers; issuer 0 also fetches the weight images.
+// 20 warps = 5 per scheduler: a 21st (a separate loader warp) put six on one scheduler's 16 K-register file and
+// capped the kernel at 80 registers per thread (spills in the epilogues); 640 threads allow 96.
+constexpr int kTcThreads = 4 * 128 + 128;
 constexpr uint32_t kFmtF16 = 0;            // kind::f16 operand format code of fp16 (bf16 = 1)
 constexpr int kTcMaxT = 8;       // tile pairs per chunk
 
@@ -233,18 +236,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
   const int my_chunks = blockIdx.x < nchunks ? (int)((nchunks - 1 - blockIdx.x) / gridDim.x + 1) : 0;
   const int Q = my_chunks * nl;  // layer steps this CTA runs
 
-  if (warp == 20) {
-    // ===== weight loader: one cp.async.bulk per layer step into slot q&1 =====
-    if (lane == 0) {
-      for (int q = 0; q < Q; ++q) {
-        const int it = q % nl, b = q & 1;
-        const int l = INV ? a.layer_begin + it : a.layer_end - 1 - it;
-        if (q >= 2) tc::mbar_wait(&w_free[b], (uint32_t)(((q >> 1) - 1) & 1));
-        tc::mbar_arrive_expect_tx(&w_full[b], I::wbytes);
-        tc::tma_bulk_g2s(wbuf + b * I::wbytes, a.img + (size_t)l * I::bytes, I::wbytes, &w_full[b]);
-      }
-    }
-  } else if (warp >= 16) {
+  if (warp >= 16) {
     // ===== MMA issuers: warp 16+g serves warpgroup g (blocking waits, no polling) =====
     if (lane == 0) {
       constexpr uint32_t idesc2 = tc::make_idesc(kFmtF16, 128, 64);
@@ -252,12 +244,37 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
       const int g = warp - 16;  // warpgroup / TMEM slot served
       const uint32_t tb = tmem + (uint32_t)g * 128u;  // A hi [0,32) A lo [32,64) D [64,128)
       uint32_t r = 0;
+      // weight images: one cp.async.bulk per layer step into slot q&1, issued by issuer 0 as soon as every issuer's
+      // MMAs on that slot (two steps earlier) have completed — probed without blocking between its own MMA batches,
+      // waited for only when the step that needs the image begins
+      int q_loaded = 0;
+      auto load_next = [&](bool block) {
+        if (q_loaded >= Q) return;
+        const int it = q_loaded % nl, b = q_loaded & 1;
+        if (q_loaded >= 2) {
+          const uint32_t par = (uint32_t)(((q_loaded >> 1) - 1) & 1);
+          if (block) tc::mbar_wait(&w_free[b], par);
+          else if (!tc::mbar_test_wait(&w_free[b], par)) return;
+        }
+        const int l = INV ? a.layer_begin + it : a.layer_end - 1 - it;
+        tc::mbar_arrive_expect_tx(&w_full[b], I::wbytes);
+        tc::tma_bulk_g2s(wbuf + b * I::wbytes, a.img + (size_t)l * I::bytes, I::wbytes, &w_full[b]);
+        ++q_loaded;
+      };
+      if (g == 0) {
+        load_next(true);
+        load_next(true);
+      }
       for (int q = 0; q < Q; ++q) {
         const int b = q & 1;
         const uint32_t wb = tc::smem_u32(wbuf + b * I::wbytes);
         for (int t = 0; t < T; ++t) {
 #pragma unroll 1
           for (int p = 0; p < 2; ++p, ++r) {
+            if (g == 0) {
+              while (q_loaded <= q) load_next(true);
+              load_next(false);
+            }
             tc::mbar_wait(&a_ready[g], r & 1);
             if (t == 0 && p == 0) tc::mbar_wait(&w_full[b], (uint32_t)((q >> 1) & 1));
             tc::tc_fence_after();
@@ -298,6 +315,36 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
         sx1[slot] = v.y;
         sld[slot] = 0.f;
       }
+      // Software pipeline over the (layer, tile) steps of this warpgroup: once the accumulator of step k's last
+      // Linear sits in registers the whole TMEM slot is free, so step k+1's L1 is written and its MMAs are started
+      // BEFORE step k's inner bijector runs — the bijector (~360 instructions per sample) hides that MMA wait.
+      // Step k+1 is another tile of the same layer, or tile 0 of the next layer (whose bijector finished T-1 steps
+      // ago); with a single tile per chunk (T == 1) the next step needs this one's result and the order is serial.
+      auto stage1 = [&](int it, int t) {
+        const int l = INV ? a.layer_begin + it : a.layer_end - 1 - it;
+        const float* sm = smalls + it * SF;
+        const int slot = t * 512 + g * 128 + row;
+        const float xm = (l & 1) ? sx0[slot] : sx1[slot];  // visible value
+        // ---- L1: Linear(2->64)+relu on where(mask, x, 0); split; A operand -> TMEM
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t hi[16], lo[16];
+#pragma unroll
+          for (int e4 = 0; e4 < 8; ++e4) {
+            const float4 w = *reinterpret_cast<const float4*>(sm + 32 * c + 4 * e4);
+            const float4 b = *reinterpret_cast<const float4*>(sm + 64 + 32 * c + 4 * e4);
+            relu_split_f16x2(fmaf(xm, w.x, b.x), fmaf(xm, w.y, b.y), hi[2 * e4], lo[2 * e4]);
+            relu_split_f16x2(fmaf(xm, w.z, b.z), fmaf(xm, w.w, b.w), hi[2 * e4 + 1], lo[2 * e4 + 1]);
+          }
+          tc::tmem_st_x16(tb + 16u * c, hi);
+          tc::tmem_st_x16(tb + 32u + 16u * c, lo);
+        }
+        tc::tmem_st_wait();
+        tc::tc_fence_before();
+        tc::mbar_arrive(&a_ready[sl]);
+      };
+      const bool pipelined = T > 1;
+      stage1(0, 0);
       for (int it = 0; it < nl; ++it) {
         const int l = INV ? a.layer_begin + it : a.layer_end - 1 - it;
         const int td = l & 1;  // transformed coordinate (mask = arange(2)%2 on even layers, negated on odd)
@@ -305,26 +352,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
 #pragma unroll 1
         for (int t = 0; t < T; ++t) {
           const int slot = t * 512 + g * 128 + row;
-          const float x0 = sx0[slot], x1 = sx1[slot];
-          const float xm = td ? x0 : x1;  // visible value
-          const float xt = td ? x1 : x0;  // value to transform
-          // ---- L1: Linear(2->64)+relu on where(mask, x, 0); split; A operand -> TMEM
-#pragma unroll
-          for (int c = 0; c < 2; ++c) {
-            uint32_t hi[16], lo[16];
-#pragma unroll
-            for (int e4 = 0; e4 < 8; ++e4) {
-              const float4 w = *reinterpret_cast<const float4*>(sm + 32 * c + 4 * e4);
-              const float4 b = *reinterpret_cast<const float4*>(sm + 64 + 32 * c + 4 * e4);
-              relu_split_f16x2(fmaf(xm, w.x, b.x), fmaf(xm, w.y, b.y), hi[2 * e4], lo[2 * e4]);
-              relu_split_f16x2(fmaf(xm, w.z, b.z), fmaf(xm, w.w, b.w), hi[2 * e4 + 1], lo[2 * e4 + 1]);
-            }
-            tc::tmem_st_x16(tb + 16u * c, hi);
-            tc::tmem_st_x16(tb + 32u + 16u * c, lo);
-          }
-          tc::tmem_st_wait();
-          tc::tc_fence_before();
-          tc::mbar_arrive(&a_ready[sl]);
+          const int nt = t + 1 == T ? 0 : t + 1, nit = t + 1 == T ? it + 1 : it;  // the next step
           tc::mbar_wait(&d_full[sl], 0);
           tc::tc_fence_after();
           // ---- epilogue 2: unscale, +b2, relu, split, next A operand -> TMEM
@@ -363,6 +391,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
               o[i] = fmaf(__uint_as_float(v[i]), (TR == FLOWCUDA_TRANSFORM_RQS && i < 2 * KT) ? inv3l2 : inv3, sm[192 + i]);
           }
           tc::tc_fence_before();  // the accumulator is drained before this warpgroup's next A operand / MMA
+          if (pipelined && nit < nl) stage1(nit, nt);
+          const float xt = td ? sx1[slot] : sx0[slot];  // value to transform
           float nv, l1;
           if (TR == FLOWCUDA_TRANSFORM_RQS) {
             rqs_apply_mufu<INV, (KT > 0 ? KT : 1)>([&](int i) { return o[i]; }, a.koff, a.lo, a.hi, xt, nv, l1);
@@ -371,6 +401,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
           }
           if (td) sx1[slot] = nv; else sx0[slot] = nv;
           sld[slot] += l1;
+          if (!pipelined && nit < nl) stage1(nit, nt);
         }
       }
       for (int t = 0; t < T; ++t) {
