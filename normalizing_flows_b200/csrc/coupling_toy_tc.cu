@@ -187,6 +187,18 @@ __device__ __forceinline__ void relu_split_f16x2(float x0, float x1, uint32_t& h
   asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(x1 - h1), "f"(x0 - h0));
 }
 
+// The same on a packed pair (one 64-bit register pair holding two fp32): the pre-activation FMA and the
+// x - hi subtraction (as hi * -1 + x) are single f32x2 instructions, so a pair costs FFMA2 + 2 LOP3 + FFMA2 + 2 F2FP.
+__device__ __forceinline__ void relu_split_f16x2(f2_t x, f2_t minus1, uint32_t& hi, uint32_t& lo) {
+  const f2_t h = x & 0xFFFFE000FFFFE000ull;
+  const f2_t l = f2_fma(h, minus1, x);
+  float h0, h1, l0, l1;
+  f2_unpack(h, h0, h1);
+  f2_unpack(l, l0, l1);
+  asm("cvt.rn.relu.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(hi) : "f"(h1), "f"(h0));
+  asm("cvt.rn.relu.f16x2.f32 %0, %1, %2;" : "=r"(lo) : "f"(l1), "f"(l0));
+}
+
 template <int TR, int KT, bool INV>
 __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArgs a) {
   constexpr int NEED = toy_need(TR, KT), N3 = toy_n3(TR, KT);
@@ -324,17 +336,18 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
         const int l = INV ? a.layer_begin + it : a.layer_end - 1 - it;
         const float* sm = smalls + it * SF;
         const int slot = t * 512 + g * 128 + row;
-        const float xm = (l & 1) ? sx0[slot] : sx1[slot];  // visible value
+        const f2_t xm = f2_splat((l & 1) ? sx0[slot] : sx1[slot]);  // visible value
+        const f2_t minus1 = f2_splat(-1.f);
         // ---- L1: Linear(2->64)+relu on where(mask, x, 0); split; A operand -> TMEM
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
           uint32_t hi[16], lo[16];
 #pragma unroll
           for (int e4 = 0; e4 < 8; ++e4) {
-            const float4 w = *reinterpret_cast<const float4*>(sm + 32 * c + 4 * e4);
-            const float4 b = *reinterpret_cast<const float4*>(sm + 64 + 32 * c + 4 * e4);
-            relu_split_f16x2(fmaf(xm, w.x, b.x), fmaf(xm, w.y, b.y), hi[2 * e4], lo[2 * e4]);
-            relu_split_f16x2(fmaf(xm, w.z, b.z), fmaf(xm, w.w, b.w), hi[2 * e4 + 1], lo[2 * e4 + 1]);
+            const ulonglong2 w = *reinterpret_cast<const ulonglong2*>(sm + 32 * c + 4 * e4);
+            const ulonglong2 b = *reinterpret_cast<const ulonglong2*>(sm + 64 + 32 * c + 4 * e4);
+            relu_split_f16x2(f2_fma(xm, w.x, b.x), minus1, hi[2 * e4], lo[2 * e4]);
+            relu_split_f16x2(f2_fma(xm, w.y, b.y), minus1, hi[2 * e4 + 1], lo[2 * e4 + 1]);
           }
           tc::tmem_st_x16(tb + 16u * c, hi);
           tc::tmem_st_x16(tb + 32u + 16u * c, lo);
@@ -357,7 +370,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
           tc::tc_fence_after();
           // ---- epilogue 2: unscale, +b2, relu, split, next A operand -> TMEM
           {
-            const float inv2 = sm[192 + N3];
+            const f2_t inv2 = f2_splat(sm[192 + N3]), minus1 = f2_splat(-1.f);
             uint32_t v[64];
 #pragma unroll
             for (int c = 0; c < 4; ++c) tc::tmem_ld_x16(tb + 64u + 16u * c, v + 16 * c);
@@ -368,8 +381,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
 #pragma unroll
               for (int e = 0; e < 16; ++e) {
                 const int k = 32 * c + 2 * e;
-                relu_split_f16x2(fmaf(__uint_as_float(v[k]), inv2, sm[128 + k]),
-                                 fmaf(__uint_as_float(v[k + 1]), inv2, sm[128 + k + 1]), hi[e], lo[e]);
+                const f2_t b2 = *reinterpret_cast<const f2_t*>(sm + 128 + k);
+                relu_split_f16x2(f2_fma(f2_pack(__uint_as_float(v[k]), __uint_as_float(v[k + 1])), inv2, b2), minus1,
+                                 hi[e], lo[e]);
               }
               tc::tmem_st_x16(tb + 16u * c, hi);
               tc::tmem_st_x16(tb + 32u + 16u * c, lo);
