@@ -193,6 +193,7 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
       g.out_img = nullptr; g.out_KS = 0;
       g.v = v; g.ldp = ldp; g.N = n; g.D = D; g.tp = tp; g.dstride = 2; g.ndims = ndims; g.dpt = L.dpt; g.ppd = L.ppd;
       g.tiles = 2 * L.tiles; g.lo = sp->range_min; g.hi = sp->range_max;
+      for (int i = 0; i < 9; ++i) g.koff[i] = sp->range_min + (float)i * kRqsMinBin;
       int rc;
       if (i < nh) {
         g.out_img = ws + L.off_h[i & 1];

@@ -74,6 +74,7 @@ struct DtGemm {
   int next_rev;          // affine epilogue with out_img: the next layer reads the dims reversed
   int made, rev;         // made: bias columns are [shift_0..shift_{D-1}, log_scale_0..]; rev: this layer sees dims reversed
   float lo, hi;
+  float koff[9];         // RQS epilogue: lo + i * min_bin_size (constant-bank operands of rqs_apply_mufu)
   unsigned char ks_tile[kDtMaxKsTiles];  // K stages n tile nt really needs (0 = all KS)
 };
 
@@ -137,11 +138,12 @@ __device__ __forceinline__ void dt_epilogue(const DtGemm& a, int mt, int nt, uin
       if (grow < a.N) {
         float o[25];
 #pragma unroll
-        for (int i = 0; i < 25; ++i) o[i] = __uint_as_float(vv[i]) + sbias[25 * di + i];
+        for (int i = 0; i < 25; ++i)
+          o[i] = i < 16 ? fmaf(__uint_as_float(vv[i]), kLog2e, sbias[25 * di + i]) : __uint_as_float(vv[i]) + sbias[25 * di + i];
         const int d = a.tp + a.dstride * dim;
         const float xin = a.v[grow * a.D + d];
         float nv, l1;
-        rqs_apply<INV, 8>([&](int i) { return o[i]; }, 8, a.lo, a.hi, xin, nv, l1);
+        rqs_apply_mufu<INV, 8>([&](int i) { return o[i]; }, a.koff, a.lo, a.hi, xin, nv, l1);
         a.v[grow * a.D + d] = nv;
         ldsum += l1;
       }
@@ -376,6 +378,8 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
           if (col < a.n_out) b = a.bias[col];
         } else {
           b = dt_tile_bias(a, nt, n);
+          // RQS: the 16 bin logits of a dimension reach the spline in log2 units (rqs_apply_mufu)
+          if (EPI == kEpiRqs8 && n % 25 < 16) b *= kLog2e;
         }
         sbias[n] = b;
       }
