@@ -552,6 +552,8 @@ def main():
         import torch.distributed as dist_mod
 
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        # NCCL writes its debug lines ("NCCL version ...") to stdout by default; stdout carries the one JSON line
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist_mod.init_process_group("nccl", device_id=dev)
         dist = dist_mod
     from normalizing_flows_b200 import ops

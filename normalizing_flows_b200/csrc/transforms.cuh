@@ -16,13 +16,15 @@ constexpr float kRqsSlopeOffset = 0.54116539f;
 __device__ __forceinline__ float rqs_slope(float u) { return softplus_f(u + kRqsSlopeOffset) + kRqsMinSlope; }
 
 // ScalarAffine.  INV=false: y = x·exp(ls)+shift, ld = ls;  INV=true: x = (y-shift)·exp(-ls), ld = -ls.
+// exp(±ls) is FMUL + bare MUFU.EX2 (relative error ~1e-7·max(1,|ls|), inside every parity budget for the
+// log-scales a flow produces; libm's expf costs ~10 instructions per element in epilogues that are issue-bound).
 template <bool INV>
 __device__ __forceinline__ void affine_apply(float shift, float ls, float v, float& out, float& ld) {
   if (INV) {
-    out = (v - shift) * expf(-ls);
+    out = (v - shift) * ex2_ftz(-kLog2e * ls);
     ld = -ls;
   } else {
-    out = fmaf(v, expf(ls), shift);
+    out = fmaf(v, ex2_ftz(kLog2e * ls), shift);
     ld = ls;
   }
 }
