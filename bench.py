@@ -944,4 +944,12 @@ def time_e2e_u8(w, dev, rank, dist, world, K, ops):
 
 
 if __name__ == "__main__":
+    # stdout carries exactly one JSON line.  Libraries write to file descriptor 1 behind Python's back (NCCL prints
+    # "NCCL version ..." there when NCCL_DEBUG=VERSION and ignores NCCL_DEBUG_FILE at that level), so descriptor 1
+    # is pointed at stderr for the whole run and Python's sys.stdout keeps the real one.
+    sys.stdout.flush()
+    _real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = _real_stdout
     main()
+    _real_stdout.flush()
