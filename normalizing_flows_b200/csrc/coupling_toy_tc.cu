@@ -159,7 +159,7 @@ __global__ void __launch_bounds__(256) toy_tc_pack_kernel(const float* __restric
 }
 
 // load NEED consecutive TMEM columns of this thread's lane into o[]
-template <int NEED>
+template <int NEED, bool WAIT = true>
 __device__ __forceinline__ void tmem_load_cols(uint32_t taddr, uint32_t* o) {
   constexpr int c32 = NEED >= 32 ? 32 : 0;
   constexpr int c16 = (NEED - c32) >= 16 ? 16 : 0;
@@ -174,7 +174,7 @@ __device__ __forceinline__ void tmem_load_cols(uint32_t taddr, uint32_t* o) {
   if (c4) tc::tmem_ld_x4(taddr + c32 + c16 + c8, o + c32 + c16 + c8);
   if (c2) tc::tmem_ld_x2(taddr + c32 + c16 + c8 + c4, o + c32 + c16 + c8 + c4);
   if (c1) tc::tmem_ld_x1(taddr + c32 + c16 + c8 + c4 + c2, o + c32 + c16 + c8 + c4 + c2);
-  tc::tmem_ld_wait();
+  if (WAIT) tc::tmem_ld_wait();
 }
 
 // relu + fp16 hi/lo split of two PRE-activations in six instructions (element 0 in the low half).
@@ -372,11 +372,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
           {
             const f2_t inv2 = f2_splat(sm[192 + N3]), minus1 = f2_splat(-1.f);
             uint32_t v[64];
-#pragma unroll
-            for (int c = 0; c < 4; ++c) tc::tmem_ld_x16(tb + 64u + 16u * c, v + 16 * c);
+            // the second half of the accumulator is fetched while the first half is processed
+            tc::tmem_ld_x32(tb + 64u, v);
             tc::tmem_ld_wait();
+            tc::tmem_ld_x32(tb + 96u, v + 32);
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
+              if (c == 1) tc::tmem_ld_wait();
               uint32_t hi[16], lo[16];
 #pragma unroll
               for (int e = 0; e < 16; ++e) {
@@ -399,10 +401,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) coupling_toy_tc_kernel(ToyTcArg
           {
             const float inv3 = sm[192 + N3 + 1], inv3l2 = sm[192 + N3 + 2];
             uint32_t v[NEED];
-            tmem_load_cols<NEED>(tb + 64u, v);
+            constexpr int FIRST = NEED > 32 ? 32 : NEED;  // columns past 32 are fetched while the first 32 are unscaled
+            tmem_load_cols<FIRST>(tb + 64u, v);
+            if (NEED > FIRST) tmem_load_cols<(NEED > FIRST ? NEED - FIRST : 1), false>(tb + 64u + FIRST, v + FIRST);
 #pragma unroll
-            for (int i = 0; i < NEED; ++i)
+            for (int i = 0; i < NEED; ++i) {
+              if (i == FIRST) tc::tmem_ld_wait();
               o[i] = fmaf(__uint_as_float(v[i]), (TR == FLOWCUDA_TRANSFORM_RQS && i < 2 * KT) ? inv3l2 : inv3, sm[192 + i]);
+            }
           }
           tc::tc_fence_before();  // the accumulator is drained before this warpgroup's next A operand / MMA
           if (pipelined && nit < nl) stage1(nit, nt);
