@@ -141,17 +141,22 @@ class CouplingWorkload(Workload):
             z = torch.randn(n, sp.event_dim, device=dev, generator=gen)
         else:
             z = torch.rand(n, sp.event_dim, device=dev, generator=gen)
-        for _ in range(2):
+        for _ in range(3):
             self.model.sample_from_noise(z)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(K):
-            x = self.model.sample_from_noise(z)
-        e1.record()
         torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1) / K
+        # per-call events, median: these are eager public-API calls (each allocates its output), and a single
+        # allocator / host hiccup otherwise dominates a five-call mean (seen: 1.8 ms typical, 20 ms mean once)
+        K = max(K, 9)
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+        for e0, e1 in evs:
+            e0.record()
+            x = self.model.sample_from_noise(z)
+            e1.record()
+        torch.cuda.synchronize()
+        times = sorted(e0.elapsed_time(e1) for e0, e1 in evs)
+        ms = times[len(times) // 2]
         return {"value": n / (ms * 1e-3), "unit": "samples/s", "samples_per_step_per_gpu": n, "ms_per_step": ms,
-                "finite": bool(torch.isfinite(x).all().item())}
+                "ms_min_max": [times[0], times[-1]], "calls": K, "finite": bool(torch.isfinite(x).all().item())}
 
     def cpu_run(self, x):
         from oracle import flows_oracle as O
