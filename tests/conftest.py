@@ -28,3 +28,13 @@ def pytest_collection_modifyitems(config, items):
 
 
 GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_sessionfinish(session, exitstatus):
+    """GPU parity tests record the error bound each case achieved (tests/parity_util.py)."""
+    try:
+        import parity_util
+
+        parity_util.dump()
+    except Exception:
+        pass

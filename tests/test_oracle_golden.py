@@ -176,3 +176,93 @@ def test_dequantize_and_base_noise_restatement():
     u = P.base_noise(1, 3, 0, 200_001)
     assert u.min() >= 0 and u.max() < 1 and abs(u.mean() - 0.5) < 0.005
     assert np.array_equal(P.base_noise(0, 3, 8, 40), z[8:48])
+
+
+# ---------------------------------------------------------------------------------------------
+# Rows #2-#4 and §8f-1: golden produced by executing the reference's own make_flow_model /
+# make_conditioner / log_prob / sample (tests/golden/make_golden_flows.py) under numpy stand-ins
+# for jax / haiku / distrax / TFP (tests/golden/ref_shim.py).  Pins the model WIRING (masks, flips,
+# 3n+1, Flatten/Reshape, Inverse(Chain), bases, haiku names); the library primitives are restated.
+# ---------------------------------------------------------------------------------------------
+import sys
+
+sys.path.insert(0, GOLDEN)
+import mnist_params as MP  # noqa: E402
+
+
+def unflatten_coupling(spec, flat):
+    flat = T(flat)
+    out, o = [], 0
+    for _ in range(spec.num_layers):
+        layer = []
+        for m, n in spec.layer_shapes():
+            W = flat[o : o + m * n].reshape(m, n); o += m * n
+            b = flat[o : o + n]; o += n
+            layer.append((W, b))
+        out.append(layer)
+    assert o == flat.numel()
+    return out
+
+
+def test_coupling_toy_oracle_matches_reference_make_flow_model():
+    g = np.load(os.path.join(GOLDEN, "coupling_toy_golden.npz"))
+    for key, spec in (("rnvp", O.REAL_NVP_TOY), ("maf", O.RQS_TOY)):
+        params = unflatten_coupling(spec, g[f"{key}_flat"])
+        lp = O.coupling_flow_log_prob(spec, params, T(g[f"{key}_x"]))
+        np.testing.assert_allclose(lp.numpy(), g[f"{key}_log_prob"], rtol=1e-10, atol=1e-10)
+        xs = O.coupling_flow_sample(spec, params, T(g[f"{key}_z"]))
+        np.testing.assert_allclose(xs.numpy(), g[f"{key}_sample"], rtol=1e-9, atol=1e-9)
+
+
+def test_haiku_names_are_the_reference_tree():
+    """params_io.haiku_module_names must list exactly the modules the reference's make_flow_model created
+    (the generator asserted its own tree against mnist_params.module_shapes and stored the names)."""
+    from normalizing_flows_b200 import params_io
+
+    g = np.load(os.path.join(GOLDEN, "coupling_toy_golden.npz"))
+    ours = [n for layer in params_io.haiku_module_names(8, 2) for n in layer]
+    assert ours == [str(s) for s in g["rnvp_names"]]
+
+
+def mnist_golden_params():
+    g = np.load(os.path.join(GOLDEN, "coupling_mnist_golden.npz"))
+    tree = MP.make_tree(int(g["mnist_seed"]), 8, 784, [512, 512, 512], 19600, scale=float(g["mnist_scale"]))
+    np.testing.assert_allclose(MP.tree_checksum(tree), g["mnist_checksum"], rtol=1e-12,
+                               err_msg="numpy RNG stream differs from the one the golden file was made with")
+    return g, MP.tree_to_flat(tree, 8, 784, [512, 512, 512], 19600)
+
+
+def test_coupling_mnist_oracle_matches_reference_make_flow_model():
+    g, flat = mnist_golden_params()
+    spec = O.RQS_MNIST
+    # float64 copies layer by layer (88 M parameters)
+    params, o = [], 0
+    for _ in range(spec.num_layers):
+        layer = []
+        for m, n in spec.layer_shapes():
+            W = torch.from_numpy(flat[o : o + m * n].reshape(m, n)).double(); o += m * n
+            b = torch.from_numpy(flat[o : o + n]).double(); o += n
+            layer.append((W, b))
+        params.append(layer)
+    x = T(g["mnist_x"])  # [N, 28, 28, 1]
+    lp = O.coupling_flow_log_prob(spec, params, x).numpy()
+    ref = g["mnist_log_prob"]
+    assert np.isneginf(ref[-1]) and np.isneginf(lp[-1])  # outside the Uniform(0,1) support
+    np.testing.assert_allclose(lp[:-1], ref[:-1], rtol=1e-10, atol=1e-9)
+    xs = O.coupling_flow_sample(spec, params, T(g["mnist_z"]))
+    np.testing.assert_allclose(xs.numpy(), g["mnist_sample"].reshape(xs.shape), rtol=1e-9, atol=1e-9)
+
+
+def test_bflow_oracle_matches_reference_script_prefix():
+    g = np.load(os.path.join(GOLDEN, "bflow_golden.npz"))
+    lp = O.bernstein_flow_log_prob(T(g["bflow_a"]), T(g["bflow_b"]), T(g["bflow_theta"]), T(g["bflow_alpha"]),
+                                   T(g["bflow_beta"]), T(g["bflow_x"]))
+    np.testing.assert_allclose(lp.numpy(), g["bflow_log_prob"], rtol=1e-9, atol=1e-9)
+    X = T(g["bflow_X"])
+    lp2 = O.bernstein_flow_log_prob(T(g["bflow_a"]), T(g["bflow_b"]), T(g["bflow_theta"]), T(g["bflow_alpha"]),
+                                    T(g["bflow_beta"]), X).sum(-1)  # Block(ndims=1) + MVNDiag base (bflow.py:133-135)
+    np.testing.assert_allclose(lp2.numpy(), g["bflow_mvn_log_prob"], rtol=1e-9, atol=1e-9)
+    # SoftClip on its own (T2)
+    y, ld = O.softclip_forward_and_log_det(T(g["bflow_T2_x"]))
+    np.testing.assert_allclose(y.numpy(), g["bflow_T2_y"], rtol=1e-12, atol=1e-12)
+    np.testing.assert_allclose(ld.numpy(), g["bflow_T2_ld"], rtol=1e-10, atol=1e-12)
