@@ -21,7 +21,7 @@ GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
 sys.path.insert(0, GOLDEN)
 import mnist_params as MP  # noqa: E402
 
-FP32, TOY_TC, BF16X3 = 0, 1, 2  # FLOWCUDA_PRECISION_*
+FP32, TOY_TC, BF16X3 = 0, 1, 3  # FLOWCUDA_PRECISION_FP32 / _3XTF32 (fp16x3 toy kernel) / _BF16X3
 
 
 def G(a):
