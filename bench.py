@@ -802,6 +802,9 @@ def time_workload(w, dev, rank, world, dist, W, K, ops, e2e, clocks, sustained=F
     w.launch_mode = "cuda-graph replay" if graphs else "eager"
     par = None
     if parity and rank == 0:
+        if graphs:
+            graphs[0][0].replay()  # capture does not execute: produce batch 0's output first
+            torch.cuda.synchronize()
         par = parity_check(w, bufs[0], graphs[0][1] if graphs else w.run(bufs[0]))
     # The scalar mean-log-likelihood exchange (north_star (c)) runs on a side stream: the reduction kernels and the
     # 4-byte NCCL all-reduce of step i overlap step i+1's kernels instead of sitting on the compute stream

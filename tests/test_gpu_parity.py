@@ -89,8 +89,11 @@ def test_realnvp_golden(ops):
     p32 = [[[W.float(), b.float()] for W, b in layer] for layer in p64]
     flips = [bool(f) for f in g["flips"]]
     s32 = O.sample_nvp_chain(p32, flips, T64(g["z"]).float()).numpy()
-    # the golden chain has weights ~N(0, 0.5²): exp(log_scale) amplifies fp32 rounding of the inputs (stress case)
-    hold("golden_realnvp_hand_sample", ops.realnvp_sample(params, L, H, fm, z), g["sample"], 1e-4, ref32=s32, kind="stress")
+    # the golden chain has weights ~N(0, 0.5²): exp(log_scale) over 8 layers overflows for some z (the reference's own
+    # float64 output holds inf/nan there — close() demands non-finite results at those entries) and amplifies the
+    # fp32 rounding of the inputs elsewhere: fixed ceiling 6e-5 (the float32 oracle itself is at 1.4e-5 on these inputs)
+    close(ops.realnvp_sample(params, L, H, fm, z), g["sample"], tol=6e-5, what="sample_nvp_chain")
+    del s32
     close(ops.realnvp_forward(params[0:P], H, False, z), g["fwd0"], what="forward_nvp l0")
     close(ops.realnvp_forward(params[P : 2 * P].contiguous(), H, True, z), g["fwd1"], what="forward_nvp l1 flip")
     x0, ls0 = ops.realnvp_inverse(params[0:P], H, False, y)
@@ -242,7 +245,7 @@ COUPLING_CASES = {
 # the float32 oracle's own error on the same inputs is recorded beside each measurement in parity_report.json.
 CEIL = {
     "realnvp_toy": (1e-5, 1e-5), "affine_toy": (1e-5, 1e-5), "affine_d6": (1e-5, 1e-5), "scalar_d5": (1e-5, 1e-5),
-    "rqs_toy": (2e-4, 6e-5), "rqs_toy_k8": (5e-5, 2e-5), "rqs_d7": (1e-4, 1e-4), "rqs_d40_uniform": (1e-4, 1e-4),
+    "rqs_toy": (2e-4, 6e-5), "rqs_toy_k8": (5e-5, 2e-5), "rqs_d7": (5e-5, 5e-5), "rqs_d40_uniform": (5e-5, 5e-5),
 }
 
 
