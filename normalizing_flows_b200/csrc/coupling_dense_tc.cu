@@ -15,7 +15,7 @@
 //   hidden: +bias, relu, bf16 hi/lo split, written straight into the next Linear's A image;
 //   last:   the inner bijector (RQS / affine) on the tile's dims, state updated in place,
 //           log-det partial per (row, tile) — the [N, 19600] conditioner output never exists.
-#include "dense_tc.cuh"
+#include "dense_tc2.cuh"
 
 namespace flowcuda {
 
@@ -103,7 +103,7 @@ static bool dt_layout(const flowcuda_coupling_spec* sp, int64_t n, DtLayout& L) 
   L.per_layer = o;
   const int ndmax = (D + 1) / 2;
   L.tiles = (ndmax + L.dpt - 1) / L.dpt;
-  L.MT = (n + 127) / 128;
+  L.MT = 2 * ((n + 255) / 256);  // 128-row tiles, even: a CTA pair works on 256 rows (dense_tc2.cuh)
   for (int i = 0; i < L.nlin; ++i) {
     const int kin = i == 0 ? ndmax : L.sizes[i];
     L.KS[i] = (kin + kDtBK - 1) / kDtBK;
@@ -195,17 +195,18 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
       g.tiles = 2 * L.tiles; g.lo = sp->range_min; g.hi = sp->range_max;
       for (int i = 0; i < 9; ++i) g.koff[i] = sp->range_min + (float)i * kRqsMinBin;
       int rc;
+      const Dt2Launch dl = {L.MT, (int64_t)sp->num_layers * L.NT[i], (int64_t)l * L.NT[i]};
       if (i < nh) {
         g.out_img = ws + L.off_h[i & 1];
         g.out_KS = L.KS[i + 1];
-        rc = dt_launch_gemm<kEpiHidden, false>(g, L.MT, L.NT[i], s);
+        rc = dt2_launch_gemm<kEpiHidden, false>(g, dl, L.MT, L.NT[i], s);
         aimg = g.out_img;
       } else {
         const int used = (ndims + L.dpt - 1) / L.dpt;
         if (sp->transform == FLOWCUDA_TRANSFORM_RQS)
-          rc = inverse ? dt_launch_gemm<kEpiRqs8, true>(g, L.MT, used, s) : dt_launch_gemm<kEpiRqs8, false>(g, L.MT, used, s);
+          rc = inverse ? dt2_launch_gemm<kEpiRqs8, true>(g, dl, L.MT, used, s) : dt2_launch_gemm<kEpiRqs8, false>(g, dl, L.MT, used, s);
         else
-          rc = inverse ? dt_launch_gemm<kEpiAffine, true>(g, L.MT, used, s) : dt_launch_gemm<kEpiAffine, false>(g, L.MT, used, s);
+          rc = inverse ? dt2_launch_gemm<kEpiAffine, true>(g, dl, L.MT, used, s) : dt2_launch_gemm<kEpiAffine, false>(g, dl, L.MT, used, s);
         if (rc) return rc;
         dense_tc_ld_accum_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, s>>>(ldp, 2 * L.tiles, 2 * used, ld, n, it == 0);
         FC_LAUNCH_CHECK("dense_tc_ld_accum_kernel");

@@ -35,7 +35,7 @@ constexpr int kDtMaxKsTiles = 48;
 static __global__ void __launch_bounds__(256) dense_tc_pack_x_kernel(const float* __restrict__ v, int64_t N, int D,
                                                                     int off, int stride, int nk, int KS,
                                                                     uint8_t* __restrict__ img) {
-  const int64_t rows = (N + 127) / 128 * 128;
+  const int64_t rows = (N + 255) / 256 * 256;  // whole CTA-pair tiles (dense_tc2.cuh): MT is always even
   const int64_t total = rows * (KS * 4);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int64_t row = i % rows;
@@ -247,6 +247,81 @@ __device__ __forceinline__ void dt_epilogue(const DtGemm& a, int mt, int nt, uin
   }
 }
 
+// RQS epilogue of a whole 128 x 256 tile by one warp per TMEM lane quarter (thread = sample row, 10 dims x 25 spline
+// parameters): dims (di, di + 5) are evaluated as a pair of independent splines (rqs_apply_mufu_x2), their 2 x 25
+// accumulator columns fetched together; `xin` holds the row's 10 state values, loaded BEFORE the accumulator was
+// waited for (they do not depend on it) — the thread-per-row state access touches 32 cache lines per warp request and
+// its latency used to sit inside every spline.  Log-det partials keep the two-per-tile layout and summation order of the
+// half-tile form (dims 0-4 | 5-9), so results are bit-identical to it.
+template <bool INV>
+__device__ __forceinline__ void dt_epilogue_rqs_tile(const DtGemm& a, int mt, int nt, uint32_t tb, const float* __restrict__ sbias,
+                                                     int warp, int lane, const float (&xin)[10]) {
+  const int row = (warp & 3) * 32 + lane;
+  const int64_t grow = (int64_t)mt * 128 + row;
+  float ldsum[2] = {0.f, 0.f};
+  // the loop below is not unrolled (one copy of the spline code), so the state values are consumed from the head of two
+  // register queues that shift by one per iteration — a runtime index would put the array in local memory
+  float xa[5], xb[5];
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    xa[i] = xin[i];
+    xb[i] = xin[i + 5];
+  }
+#pragma unroll 1
+  for (int di = 0; di < 5; ++di) {
+    const int dim0 = nt * 10 + di, dim1 = dim0 + 5;
+    if (dim0 >= a.ndims) break;  // uniform across the CTA
+    const bool two = dim1 < a.ndims;
+    uint32_t vv[2][25];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const uint32_t c = (uint32_t)(25 * (di + 5 * u));
+      tc::tmem_ld_x16(tb + c, vv[u]);
+      tc::tmem_ld_x8(tb + c + 16, vv[u] + 16);
+      tc::tmem_ld_x1(tb + c + 24, vv[u] + 24);
+    }
+    tc::tmem_ld_wait();
+    if (grow < a.N) {
+      float o[2][25];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const float* sb = sbias + 25 * (di + 5 * u);
+#pragma unroll
+        for (int i = 0; i < 25; ++i)
+          o[u][i] = i < 16 ? fmaf(__uint_as_float(vv[u][i]), kLog2e, sb[i]) : __uint_as_float(vv[u][i]) + sb[i];
+      }
+      const float v2[2] = {xa[0], two ? xb[0] : 0.5f * (a.lo + a.hi)};
+      float nv[2], l2[2];
+      rqs_apply_mufu_x2<INV, 8>(o[0], o[1], a.koff, a.lo, a.hi, v2, nv, l2);
+      a.v[grow * a.D + a.tp + a.dstride * dim0] = nv[0];
+      ldsum[0] += l2[0];
+      if (two) {
+        a.v[grow * a.D + a.tp + a.dstride * dim1] = nv[1];
+        ldsum[1] += l2[1];
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      xa[i] = xa[i + 1];
+      xb[i] = xb[i + 1];
+    }
+  }
+  if (grow < a.N) {
+    a.ldp[grow * a.tiles + 2 * nt] = ldsum[0];
+    a.ldp[grow * a.tiles + 2 * nt + 1] = ldsum[1];
+  }
+}
+
+// the row's 10 state values of tile nt (issued before the accumulator wait)
+__device__ __forceinline__ void dt_rqs_load_x(const DtGemm& a, int mt, int nt, int warp, int lane, float (&xin)[10]) {
+  const int64_t grow = (int64_t)mt * 128 + (warp & 3) * 32 + lane;
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    const int dim = nt * 10 + i;
+    xin[i] = (grow < a.N && dim < a.ndims) ? a.v[grow * a.D + a.tp + a.dstride * dim] : 0.f;
+  }
+}
+
 constexpr int kDtTileScratchFloats = 8 * 32 * 36;  // per-warp 32 x 36 transposition tiles of one epilogue group (affine)
 // The affine epilogue needs the transposition scratch (two epilogue groups) and runs a 3-stage ring; the
 // other epilogues have the room for 4 stages.
@@ -267,9 +342,14 @@ template <int EPI, bool WIDE> struct DtCfg {
 // Persistent kernel: one CTA per SM walks the (m tile, n tile) list; a TMA ring feeds the MMA warp across
 // tile boundaries, and the two 256-column TMEM accumulators alternate between two epilogue warpgroups, so
 // an epilogue may take twice the MMA time of a tile before it stalls the tensor pipe.
-template <int EPI, bool INV, bool WIDE>
+// NH ("n halves", hidden epilogue only): a CTA computes 128 x 128 — one half of an n tile — so that a launch with few
+// tiles (the 512-wide hidden Linears at batch 4096: 64 tiles for 148 SMs, each a latency-bound serial chain of 16 K
+// stages) becomes twice as many CTAs of half the MMA time; the tile's B half is eight 2 KB runs of the weight image.
+template <int EPI, bool INV, bool WIDE, bool NH = false>
 __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_kernel(DtGemm a, int MT, int NT) {
   using Cfg = DtCfg<EPI, WIDE>;
+  static_assert(!NH || (EPI == kEpiHidden && !WIDE), "n-half tiles exist for the hidden epilogue with 4-warp groups");
+  constexpr int BNC = NH ? kDtBN / 2 : kDtBN;  // accumulator columns of a CTA tile
   constexpr int kDtStages = Cfg::kStages;
   constexpr int EW = Cfg::kEpiWarps;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -282,7 +362,8 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
   uint64_t* acc_empty = acc_full + 2;                                              // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int ntiles = MT * NT;
+  const int NTH = NH ? 2 * NT : NT;  // tile columns (n tile, half)
+  const int ntiles = MT * NTH;
 
   if (warp == 1) tc::tmem_alloc(tmem_slot, 2 * kDtBN);
   if (tid == 0) {
@@ -305,7 +386,8 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
     if (lane == 0) {  // ===== TMA loader
       uint32_t it = 0;
       for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
-        const int mt = t / NT, nt = t - mt * NT;
+        const int mt = t / NTH, ntc = t - mt * NTH;
+        const int nt = NH ? ntc >> 1 : ntc, hh = NH ? ntc & 1 : 0;
         int KS = a.KS;
         if (nt < kDtMaxKsTiles && a.ks_tile[nt] != 0) KS = a.ks_tile[nt];
         const uint8_t* ag = a.a_img + (int64_t)mt * a.KS * 2 * kDtABytes;
@@ -314,19 +396,29 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
           const uint32_t st = it % kDtStages, ph = (it / kDtStages) & 1u;
           tc::mbar_wait(&empty[st], ph ^ 1u);  // passes at once on a fresh barrier
           uint8_t* dst = stages + st * kDtStageBytes;
-          tc::mbar_arrive_expect_tx(&full[st], kDtStageBytes);
-          tc::tma_bulk_g2s(dst, ag + (int64_t)ks * 2 * kDtABytes, 2 * kDtABytes, &full[st]);
-          tc::tma_bulk_g2s(dst + 2 * kDtABytes, bg + (int64_t)ks * 2 * kDtBBytes, 2 * kDtBBytes, &full[st]);
+          if (NH) {
+            tc::mbar_arrive_expect_tx(&full[st], 4 * kDtABytes);
+            tc::tma_bulk_g2s(dst, ag + (int64_t)ks * 2 * kDtABytes, 2 * kDtABytes, &full[st]);
+            // rows 128 hh .. 128 hh + 127 of each of the 2 x 4 K chunks: 2 KB runs, 4 KB apart in the image
+            const uint8_t* bs = bg + (int64_t)ks * 2 * kDtBBytes + hh * 2048;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) tc::tma_bulk_g2s(dst + 2 * kDtABytes + c * 2048, bs + c * 4096, 2048, &full[st]);
+          } else {
+            tc::mbar_arrive_expect_tx(&full[st], kDtStageBytes);
+            tc::tma_bulk_g2s(dst, ag + (int64_t)ks * 2 * kDtABytes, 2 * kDtABytes, &full[st]);
+            tc::tma_bulk_g2s(dst + 2 * kDtABytes, bg + (int64_t)ks * 2 * kDtBBytes, 2 * kDtBBytes, &full[st]);
+          }
         }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {  // ===== MMA issuer: 3 passes x 2 K steps per stage
-      constexpr uint32_t idesc = tc::make_idesc(tc::kFmtBF16, 128, kDtBN);
-      constexpr uint32_t lbo_a = 16u * 128u, lbo_b = (uint32_t)(kDtBN >> 3) * 128u;
+      constexpr uint32_t idesc = tc::make_idesc(tc::kFmtBF16, 128, BNC);
+      constexpr uint32_t lbo_a = 16u * 128u, lbo_b = (uint32_t)(BNC >> 3) * 128u;
+      constexpr uint32_t kBLo = NH ? kDtABytes : kDtBBytes;  // offset of the lo image inside the staged B
       uint32_t it = 0, tl = 0;
       for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tl) {
-        const int nt = t % NT;
+        const int nt = NH ? (t % NTH) >> 1 : t % NT;
         int KS = a.KS;
         if (nt < kDtMaxKsTiles && a.ks_tile[nt] != 0) KS = a.ks_tile[nt];
         const uint32_t slot = tl & 1u, aph = (tl >> 1) & 1u;
@@ -341,7 +433,7 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
           const uint32_t sa = tc::smem_u32(stages + st * kDtStageBytes), sb = sa + 2 * kDtABytes;
 #pragma unroll
           for (int pass = 0; pass < 3; ++pass) {
-            const uint32_t ab = sa + (pass == 2 ? kDtABytes : 0), bb = sb + (pass == 1 ? kDtBBytes : 0);
+            const uint32_t ab = sa + (pass == 2 ? kDtABytes : 0), bb = sb + (pass == 1 ? kBLo : 0);
 #pragma unroll
             for (int s = 0; s < kDtBK / 16; ++s) {
               tc::mma_ss<tc::kFmtBF16>(dtm, tc::make_smem_desc(ab + s * 2u * lbo_a, lbo_a, 128u),
@@ -369,7 +461,8 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
     uint32_t tl = 0;
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tl) {
       if ((tl & 1u) != group) continue;
-      const int mt = t / NT, nt = t - mt * NT;
+      const int mt = t / NTH, ntc = t - mt * NTH;
+      const int nt = NH ? ntc >> 1 : ntc, hh = NH ? ntc & 1 : 0;
       const uint32_t slot = group, aph = (tl >> 1) & 1u;
       for (int n = et; n < kDtBN; n += EW * 32) {  // bias of this tile's columns
         float b = 0.f;
@@ -384,7 +477,9 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
         sbias[n] = b;
       }
       group_sync();
-      if (EPI != kEpiHidden && (EW == 4 || half == 0)) {
+      float xin[10];
+      if (EPI == kEpiRqs8) dt_rqs_load_x(a, mt, nt, warp, lane, xin);
+      if (EPI == kEpiAffine && (EW == 4 || half == 0)) {
         // the bijector reads this tile's slice of the state v (it left L2 while the Linears streamed their
         // images): pull the thread's row of the slice into L2 now, under the tile's MMAs
         const int64_t prow = (int64_t)mt * 128 + (warp & 3) * 32 + lane;
@@ -399,10 +494,15 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
       tc::mbar_wait(&acc_full[slot], aph);
       tc::tc_fence_after();
       const uint32_t tb = tmem + slot * (uint32_t)kDtBN + ((uint32_t)((warp & 3) * 32) << 16);
-      if (EW == 8) {
+      if (EPI == kEpiRqs8) {
+        dt_epilogue_rqs_tile<INV>(a, mt, nt, tb, sbias, warp, lane, xin);
+      } else if (NH) {
+        // the accumulator holds columns [128 hh, 128 hh + 128) of the n tile at TMEM columns 0..127
+        dt_epilogue<EPI, INV>(a, mt, nt, tb - (uint32_t)(hh * (kDtBN / 2)), sbias, Tbase, warp, lane, hh);
+      } else if (EW == 8) {
         dt_epilogue<EPI, INV>(a, mt, nt, tb, sbias, Tbase + group * kDtTileScratchFloats, warp, lane, half);
       } else {
-#pragma unroll 1  // one copy of the epilogue code (the spline is large; two copies cost instruction-cache misses)
+#pragma unroll 1  // one copy of the epilogue code
         for (int h = 0; h < 2; ++h)
           dt_epilogue<EPI, INV>(a, mt, nt, tb, sbias, Tbase + group * kDtTileScratchFloats, warp, lane, h);
       }
@@ -425,7 +525,11 @@ template <int EPI, bool INV, bool WIDE>
 static int dt_launch_gemm_w(const DtGemm& g, int64_t MT, int NT, cudaStream_t s) {
   auto kern = dense_tc_gemm_kernel<EPI, INV, WIDE>;
   constexpr size_t kSmem = DtCfg<EPI, WIDE>::kSmem;
-  FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+  static bool configured = false;  // one-time per template instance
+  if (!configured) {
+    FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+    configured = true;
+  }
   const int64_t tiles = MT * NT;
   const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
   kern<<<grid, DtCfg<EPI, WIDE>::kThreads, kSmem, s>>>(g, (int)MT, NT);
@@ -434,7 +538,27 @@ static int dt_launch_gemm_w(const DtGemm& g, int64_t MT, int NT, cudaStream_t s)
 }
 
 template <int EPI, bool INV>
+static int dt_launch_gemm_nh(const DtGemm& g, int64_t MT, int NT, cudaStream_t s) {
+  auto kern = dense_tc_gemm_kernel<EPI, INV, false, true>;
+  constexpr size_t kSmem = DtCfg<EPI, false>::kSmem;
+  static bool configured = false;
+  if (!configured) {
+    FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+    configured = true;
+  }
+  const int64_t tiles = MT * NT * 2;
+  const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
+  kern<<<grid, DtCfg<EPI, false>::kThreads, kSmem, s>>>(g, (int)MT, NT);
+  FC_LAUNCH_CHECK("dense_tc_gemm_kernel(n halves)");
+  return FLOWCUDA_OK;
+}
+
+template <int EPI, bool INV>
 static int dt_launch_gemm(const DtGemm& g, int64_t MT, int NT, cudaStream_t s) {
+  if (EPI == kEpiHidden) {
+    // fewer tiles than SMs: split every n tile in two (128 x 128 CTA tiles) when that fills more of the device
+    if (MT * NT < sm_count() * 3 / 4) return dt_launch_gemm_nh<kEpiHidden, false>(g, MT, NT, s);
+  }
   if (EPI != kEpiRqs8 && MT * NT > sm_count()) return dt_launch_gemm_w<EPI, INV, true>(g, MT, NT, s);
   return dt_launch_gemm_w<EPI, INV, false>(g, MT, NT, s);
 }

@@ -19,7 +19,7 @@
 // registers and are updated INCREMENTALLY (rank-1 updates as x_q, then the hidden units whose
 // degree has just completed, become known), so a layer costs one conditioner evaluation's worth of
 // FMAs instead of D of them.
-#include "dense_tc.cuh"
+#include "dense_tc2.cuh"
 
 namespace flowcuda {
 
@@ -57,7 +57,7 @@ static bool made_layout(const flowcuda_made_spec* sp, int64_t n, MadeLayout& L) 
   }
   L.per_layer = o;
   L.tiles = (D + 127) / 128;
-  L.MT = (n + 127) / 128;
+  L.MT = 2 * ((n + 255) / 256);  // 128-row tiles, even: a CTA pair works on 256 rows (dense_tc2.cuh)
   for (int i = 0; i < L.nlin; ++i) {
     L.KS[i] = (L.sizes[i] + kDtBK - 1) / kDtBK;
     L.NT[i] = i < nh ? (L.sizes[i + 1] + kDtBN - 1) / kDtBN : L.tiles;
@@ -224,10 +224,11 @@ static int made_log_prob_run(const flowcuda_made_spec* sp, const float* params, 
       g.tiles = 2 * L.tiles; g.made = 1; g.rev = rev ? 1 : 0;
       for (int t = 0; t < L.NT[i] && t < kDtMaxKsTiles; ++t) g.ks_tile[t] = (unsigned char)made_ks_needed(L, i, t, rev);
       int rc;
+      const Dt2Launch dl = {L.MT, (int64_t)sp->num_layers * L.NT[i], (int64_t)l * L.NT[i]};
       if (i < nh) {
         g.out_img = ws + L.off_h[i & 1];
         g.out_KS = L.KS[i + 1];
-        rc = dt_launch_gemm<kEpiHidden, false>(g, L.MT, L.NT[i], s);
+        rc = dt2_launch_gemm<kEpiHidden, false>(g, dl, L.MT, L.NT[i], s);
         aimg = g.out_img;
       } else {
         if (fuse_x && it + 1 < sp->num_layers) {
@@ -235,7 +236,7 @@ static int made_log_prob_run(const flowcuda_made_spec* sp, const float* params, 
           g.out_KS = L.KS[0];
           g.next_rev = ((l - 1) & 1) != 0;
         }
-        rc = dt_launch_gemm<kEpiAffine, true>(g, L.MT, L.tiles, s);
+        rc = dt2_launch_gemm<kEpiAffine, true>(g, dl, L.MT, L.tiles, s);
         if (rc) return rc;
         dense_tc_ld_accum_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, s>>>(ldp, 2 * L.tiles, 2 * L.tiles, ld, n, it == 0);
         FC_LAUNCH_CHECK("dense_tc_ld_accum_kernel");

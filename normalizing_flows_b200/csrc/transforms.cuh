@@ -217,6 +217,123 @@ __device__ __forceinline__ void rqs_apply_mufu(Get p, const float* __restrict__ 
   }
 }
 
+// Two independent splines evaluated in lockstep (same arithmetic, same order per spline as rqs_apply_mufu: results are
+// bit-identical).  The D=784 spline epilogue is a dependent chain of ~360 instructions per (sample, dim) with one or two
+// warps per scheduler: issue-active was 27 % and the epilogue, not the MMAs, bounded the kernel.  Writing every step for
+// both splines side by side gives the scheduler two independent chains per thread; the rare linear tails are patched up
+// after the common path so that they do not split it into basic blocks.  p0 / p1: the 3K+1 conditioner outputs of each.
+template <bool INV, int K>
+__device__ __forceinline__ void rqs_apply_mufu_x2(const float* __restrict__ p0, const float* __restrict__ p1,
+                                                  const float* __restrict__ koff, float lo, float hi, const float (&v)[2],
+                                                  float (&out)[2], float (&ld)[2]) {
+  const float scale = (hi - lo) - (float)K * kRqsMinBin;
+  const float* p[2] = {p0, p1};
+  float mw[2], mh[2];
+#pragma unroll
+  for (int u = 0; u < 2; ++u) {
+    mw[u] = p[u][0];
+    mh[u] = p[u][K];
+  }
+#pragma unroll
+  for (int i = 1; i < K; ++i) {
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      mw[u] = fmaxf(mw[u], p[u][i]);
+      mh[u] = fmaxf(mh[u], p[u][K + i]);
+    }
+  }
+  float ew[2][K], eh[2][K];
+  float aw[2] = {0.f, 0.f}, ah[2] = {0.f, 0.f};
+#pragma unroll
+  for (int i = 0; i < K; ++i) {
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      aw[u] += ex2_ftz(p[u][i] - mw[u]);
+      ah[u] += ex2_ftz(p[u][K + i] - mh[u]);
+      ew[u][i] = aw[u];
+      eh[u][i] = ah[u];
+    }
+  }
+  float cw[2], ch[2], xl[2], yl[2], xr[2], yr[2], ul[2], ur[2], xi[2], yi[2];
+#pragma unroll
+  for (int u = 0; u < 2; ++u) {
+    cw[u] = scale * rcp_approx(aw[u]);
+    ch[u] = scale * rcp_approx(ah[u]);
+    xl[u] = lo;
+    yl[u] = lo;
+    xr[u] = (K == 1) ? hi : fmaf(ew[u][0], cw[u], koff[1]);
+    yr[u] = (K == 1) ? hi : fmaf(eh[u][0], ch[u], koff[1]);
+    ul[u] = p[u][2 * K];
+    ur[u] = p[u][2 * K + 1];
+    xi[u] = xr[u];
+    yi[u] = yr[u];
+  }
+#pragma unroll
+  for (int i = 1; i < K; ++i) {
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const float xn = (i == K - 1) ? hi : fmaf(ew[u][i], cw[u], koff[i + 1]);
+      const float yn = (i == K - 1) ? hi : fmaf(eh[u][i], ch[u], koff[i + 1]);
+      const bool take = v[u] >= (INV ? yi[u] : xi[u]);
+      xl[u] = take ? xi[u] : xl[u];
+      xr[u] = take ? xn : xr[u];
+      yl[u] = take ? yi[u] : yl[u];
+      yr[u] = take ? yn : yr[u];
+      ul[u] = take ? p[u][2 * K + i] : ul[u];
+      ur[u] = take ? p[u][2 * K + i + 1] : ur[u];
+      xi[u] = xn;
+      yi[u] = yn;
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < 2; ++u) {
+    const float sl_l = rqs_slope_mufu(ul[u]), sl_r = rqs_slope_mufu(ur[u]);
+    const float w = xr[u] - xl[u], h = yr[u] - yl[u];
+    const float rw = rcp_approx(w);
+    const float s = h * rw;
+    const float t = sl_r + sl_l - 2.f * s;
+    float z;
+    if (INV) {
+      float om = fminf(fmaxf((v[u] - yl[u]) * rcp_approx(h), 0.f), 1.f);
+      float c = -s * om;
+      float b = sl_l - t * om;
+      float a = s - b;
+      z = fminf(fmaxf(-2.f * c * rcp_approx(b + sqrtf(b * b - 4.f * a * c)), 0.f), 1.f);
+      out[u] = fmaf(w, z, xl[u]);
+    } else {
+      z = fminf(fmaxf((v[u] - xl[u]) * rw, 0.f), 1.f);
+    }
+    const float sq_z = z * z;
+    const float z1mz = z - sq_z;
+    const float omz = 1.f - z;
+    const float rden = rcp_approx(fmaf(t, z1mz, s));
+    const float num = fmaf(sl_r, sq_z, fmaf(2.f * s, z1mz, sl_l * omz * omz));
+    const float sr = s * rden;
+    const float fld = kLn2 * lg2_approx(sr * sr * num);
+    if (INV) {
+      ld[u] = -fld;
+    } else {
+      out[u] = fmaf(h * fmaf(s, sq_z, sl_l * z1mz), rden, yl[u]);
+      ld[u] = fld;
+    }
+  }
+  // linear tails outside [lo, hi] (rare: one branch for the pair)
+  if (v[0] <= lo || v[0] >= hi || v[1] <= lo || v[1] >= hi) {
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (v[u] <= lo) {
+        float s0 = rqs_slope(p[u][2 * K]);
+        out[u] = INV ? (v[u] - lo) / s0 + lo : fmaf(v[u] - lo, s0, lo);
+        ld[u] = INV ? -logf(s0) : logf(s0);
+      } else if (v[u] >= hi) {
+        float sK = rqs_slope(p[u][3 * K]);
+        out[u] = INV ? (v[u] - hi) / sK + hi : fmaf(v[u] - hi, sK, hi);
+        ld[u] = INV ? -logf(sK) : logf(sK);
+      }
+    }
+  }
+}
+
 // Independent(Normal(0,1)) / Independent(Uniform(0,1)) contribution of one coordinate.
 __device__ __forceinline__ float base_term(int base, float z) {
   if (base == FLOWCUDA_BASE_NORMAL) return fmaf(-0.5f * z, z, -kHalfLog2Pi);
