@@ -9,10 +9,9 @@
  * on the reference side would bind.
  *
  * Conventions
- *   - every pointer is a DEVICE pointer unless the parameter name ends in `_host`;
+ *   - every pointer is a DEVICE pointer;
  *   - `stream` is a `cudaStream_t` passed as `void*`; all work is enqueued on it, the
- *     library never synchronises, allocates, frees or retains pointers
- *     (exception: the `*_host` convenience entry points, which own their staging buffers);
+ *     library never synchronises, allocates, frees or retains pointers;
  *   - arrays are dense row-major float32 unless stated; sample index is the slowest axis;
  *   - return value: 0 on success, negative `FLOWCUDA_E*` on error; the message is
  *     available (thread-local) from `flowcuda_last_error()`; no C++ exception crosses;
@@ -341,24 +340,6 @@ int flowcuda_sgd_step(float* p, const float* g, int64_t count, float lr, float g
  * all-reduce). */
 int flowcuda_adam_step(float* p, const float* g, float* m, float* v, int64_t count, int64_t step,
                        float lr, float b1, float b2, float eps, float grad_scale, void* stream);
-
-/* ------------------------------------------------------------------------------------
- * Diagnostics — one 128-row tile through every tensor-core primitive the flow kernels use
- * (tile-image staging, TMA bulk copy, tcgen05.mma kind::tf32 / kind::f16 in 1- and 3-pass
- * form, tcgen05.commit, tcgen05.ld at aligned and unaligned columns).
- *   d[128,n] = a[128,k] @ w[k,n];  mode 0 tf32x3, 1 bf16x3, 2 tf32, 3 bf16.
- * d_unaligned (optional, [128,n]) receives columns [0, 25*(n/25)) re-read in 25-column
- * groups at unaligned TMEM offsets.
- * ---------------------------------------------------------------------------------- */
-size_t flowcuda_selftest_umma_workspace_bytes(int n, int k);
-int flowcuda_selftest_umma(const float* a, const float* w, float* d, float* d_unaligned, int n, int k,
-                           int mode, void* workspace, size_t workspace_bytes, void* stream);
-
-/* Microbenchmark: device cycles of chains of small tcgen05.mma (M128, K8, tf32) for several N,
- * 1-3 independent accumulators, A from TMEM or shared memory.  out_device: int64 records
- * {N, nacc*1000 + n_mma (+100000: A from smem), issue cycles, cycles until the commit arrives},
- * terminated by -1. */
-int flowcuda_selftest_mma_timing(long long* out_device, int capacity, void* stream);
 
 #ifdef __cplusplus
 }

@@ -103,12 +103,34 @@ SIGNATURES = {
     "flowcuda_sum_scaled": (_i, [_p, _i64, _d, _p, _p, _p]),
     "flowcuda_sgd_step": (_i, [_p, _p, _i64, _f, _f, _p]),
     "flowcuda_adam_step": (_i, [_p, _p, _p, _p, _i64, _i64, _f, _f, _f, _f, _f, _p]),
+}
+
+# include/flowcuda_selftest.h — diagnostics of the tcgen05 primitives, in a separate TEST library
+SELFTEST_LIB_PATH = os.path.join(PKG, "libflowcuda_selftest.so")
+SELFTEST_SIGNATURES = {
+    "flowcuda_selftest_last_error": (C.c_char_p, []),
     "flowcuda_selftest_umma_workspace_bytes": (_sz, [_i, _i]),
     "flowcuda_selftest_mma_timing": (_i, [_p, _i, _p]),
     "flowcuda_selftest_umma": (_i, [_p, _p, _p, _p, _i, _i, _i, _p, _sz, _p]),
 }
 
 _lib = None
+_selftest = None
+
+
+def load_selftest() -> C.CDLL:
+    """The diagnostics library (tests/ and tools/ only)."""
+    global _selftest
+    if _selftest is None:
+        if not os.path.exists(SELFTEST_LIB_PATH):
+            raise FlowCudaError(f"{SELFTEST_LIB_PATH} is missing: build it with `python -m normalizing_flows_b200.build`")
+        lib = C.CDLL(SELFTEST_LIB_PATH)
+        for name, (res, args) in SELFTEST_SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype = res
+            fn.argtypes = args
+        _selftest = lib
+    return _selftest
 
 
 def load() -> C.CDLL:

@@ -18,6 +18,9 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 OBJ = os.path.join(CSRC, "_obj")
 LIB = os.path.join(PKG, "libflowcuda.so")
+# diagnostics of the tcgen05 primitives (include/flowcuda_selftest.h): a separate TEST library, not part of the product .so
+SELFTEST_LIB = os.path.join(PKG, "libflowcuda_selftest.so")
+SELFTEST_SOURCES = ("tc_selftest.cu",)
 INCLUDE = os.path.join(os.path.dirname(PKG), "include")
 
 NVCC_FLAGS = [
@@ -43,6 +46,7 @@ def sources():
 def _deps_mtime() -> float:
     hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
     hdrs.append(os.path.join(INCLUDE, "flowcuda.h"))
+    hdrs.append(os.path.join(INCLUDE, "flowcuda_selftest.h"))
     hdrs.append(os.path.abspath(__file__))
     return max(os.path.getmtime(h) for h in hdrs)
 
@@ -74,9 +78,13 @@ def build(force: bool = False, verbose: bool = False) -> str:
             for out in ex.map(run, jobs):
                 if verbose and out:
                     print(out, file=sys.stderr)
-    need_link = bool(jobs) or not os.path.exists(LIB) or any(os.path.getmtime(o) > os.path.getmtime(LIB) for o in objs)
-    if need_link:
-        run([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB, *objs])
+    test_objs = [o for o in objs if os.path.basename(o)[:-2] + ".cu" in SELFTEST_SOURCES]
+    prod_objs = [o for o in objs if o not in test_objs]
+    core_obj = os.path.join(OBJ, "core.o")
+    for lib, members in ((LIB, prod_objs), (SELFTEST_LIB, test_objs + [core_obj])):
+        need_link = bool(jobs) or not os.path.exists(lib) or any(os.path.getmtime(o) > os.path.getmtime(lib) for o in members)
+        if need_link:
+            run([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", lib, *members])
     return LIB
 
 

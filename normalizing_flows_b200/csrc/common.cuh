@@ -38,6 +38,22 @@ int sm_count();
     if (e__ != cudaSuccess) return flowcuda::cuda_fail(e__, name);  \
   } while (0)
 
+// Opt a kernel in to `bytes` of dynamic shared memory ONCE per device (and again only if a later call needs more):
+// cudaFuncSetAttribute is a driver round trip that does not belong on the per-launch path ("no global
+// mutable state except one-time cudaFuncSetAttribute").  The cache is per call site (= per kernel instantiation)
+// and per device; racing first calls both set the same value.
+#define FC_ENSURE_SMEM(kern, bytes)                                                                              \
+  do {                                                                                                           \
+    static int fc_smem_set__[32] = {0};                                                                          \
+    int fc_dev__ = 0;                                                                                            \
+    FC_CUDA(cudaGetDevice(&fc_dev__));                                                                           \
+    const int fc_need__ = (int)(bytes);                                                                          \
+    if (fc_dev__ < 0 || fc_dev__ >= 32 || fc_need__ > fc_smem_set__[fc_dev__]) {                                 \
+      FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, fc_need__));               \
+      if (fc_dev__ >= 0 && fc_dev__ < 32) fc_smem_set__[fc_dev__] = fc_need__;                                   \
+    }                                                                                                            \
+  } while (0)
+
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 constexpr float kHalfLog2Pi = 0.9189385332046727f;  // 0.5*log(2*pi)

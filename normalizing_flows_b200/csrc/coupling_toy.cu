@@ -186,7 +186,7 @@ static int toy_launch(const ToyArgs& a, cudaStream_t s) {
   using I = ToyImage<OP>;
   size_t smem = (((size_t)I::total + 3) & ~(size_t)3) * 4 + (size_t)kToyH * kToyThreads * 4;
   auto kern = coupling_toy_kernel<TR, KT, OP, INV>;
-  FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  FC_ENSURE_SMEM(kern, smem);
   int64_t need = (a.n + (int64_t)kToyThreads * kToyS - 1) / ((int64_t)kToyThreads * kToyS);
   int64_t cap = (int64_t)sm_count() * 2;  // 2 CTAs resident per SM
   int grid = (int)(need < 1 ? 1 : (need < cap ? need : cap));

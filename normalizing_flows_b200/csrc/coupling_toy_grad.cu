@@ -329,7 +329,7 @@ static int tg_grid(int64_t n) {
 template <int TR, int KT, int OP, int T>
 static int tg_launch_t(TgArgs a, size_t fl, cudaStream_t s) {
   auto kern = coupling_toy_grad_kernel<TR, KT, OP, T>;
-  FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(fl * 4)));
+  FC_ENSURE_SMEM(kern, fl * 4);
   const int64_t tiles = (a.n + T - 1) / T;
   const int grid = (int)(tiles < sm_count() ? tiles : sm_count());  // never more rows than tg_grid(n) zeroed
   kern<<<grid, T, fl * 4, s>>>(a);

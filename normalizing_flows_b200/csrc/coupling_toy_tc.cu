@@ -479,7 +479,7 @@ static int toy_tc_launch(const flowcuda_coupling_spec* sp, const float* params, 
   }
   a.T = T;
   auto kern = coupling_toy_tc_kernel<TR, KT, INV>;
-  FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  FC_ENSURE_SMEM(kern, smem);
   const int64_t nchunks = (a.n + (int64_t)T * 512 - 1) / ((int64_t)T * 512);
   const int grid = (int)(nchunks < sms ? nchunks : sms);
   kern<<<grid, kTcThreads, smem, s>>>(a);

@@ -525,11 +525,7 @@ template <int EPI, bool INV, bool WIDE>
 static int dt_launch_gemm_w(const DtGemm& g, int64_t MT, int NT, cudaStream_t s) {
   auto kern = dense_tc_gemm_kernel<EPI, INV, WIDE>;
   constexpr size_t kSmem = DtCfg<EPI, WIDE>::kSmem;
-  static bool configured = false;  // one-time per template instance
-  if (!configured) {
-    FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
-    configured = true;
-  }
+  FC_ENSURE_SMEM(kern, kSmem);
   const int64_t tiles = MT * NT;
   const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
   kern<<<grid, DtCfg<EPI, WIDE>::kThreads, kSmem, s>>>(g, (int)MT, NT);
@@ -541,11 +537,7 @@ template <int EPI, bool INV>
 static int dt_launch_gemm_nh(const DtGemm& g, int64_t MT, int NT, cudaStream_t s) {
   auto kern = dense_tc_gemm_kernel<EPI, INV, false, true>;
   constexpr size_t kSmem = DtCfg<EPI, false>::kSmem;
-  static bool configured = false;
-  if (!configured) {
-    FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
-    configured = true;
-  }
+  FC_ENSURE_SMEM(kern, kSmem);
   const int64_t tiles = MT * NT * 2;
   const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
   kern<<<grid, DtCfg<EPI, false>::kThreads, kSmem, s>>>(g, (int)MT, NT);

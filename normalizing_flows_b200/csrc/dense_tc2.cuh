@@ -415,9 +415,9 @@ static int dt2_launch_w(const DtGemm& g, const Dt2Launch& L, int64_t MT, int NT,
   auto kern = dense_tc2_gemm_kernel<EPI, INV, WIDE, CL>;
   // one-time per template instance: the shared-memory opt-in and how many clusters the device really keeps
   // resident (GPC sizes can strand SMs for 4-CTA clusters; a persistent walk must not launch more than fit)
+  FC_ENSURE_SMEM(kern, Cfg::kSmem);
   static int resident = 0;
   if (resident == 0) {
-    FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::kSmem));
     cudaLaunchConfig_t qc = {};
     qc.gridDim = dim3((unsigned)(sm_count() / CL * CL));
     qc.blockDim = dim3(Cfg::kThreads);

@@ -489,7 +489,7 @@ static int made_sample_run(const flowcuda_made_spec* sp, const float* params, co
   a.D = D; a.H1 = H1; a.H2 = H2; a.L = sp->num_layers;
   const size_t smem = ((size_t)(D + H1 + H2) * kMsS + (size_t)kMsRing * (2 * 1 + 2 * 2) * kMsT + 2 * (size_t)(D + 2)) * sizeof(float);
   auto kern = made_sample_kernel<kMsS, kMsT, 1, 2>;
-  FC_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  FC_ENSURE_SMEM(kern, smem);
   const int64_t blocks = (n + kMsS - 1) / kMsS;
   kern<<<(unsigned)blocks, kMsT, smem, s>>>(a);
   FC_LAUNCH_CHECK("made_sample_kernel");

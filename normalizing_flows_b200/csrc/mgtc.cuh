@@ -408,7 +408,7 @@ static int mgtc_launch(MgGemm g, const MgTcScratch& sc, cudaStream_t s) {
   g.splits = a.S;
   g.part = a.S > 1 ? sc.part : nullptr;
   a.g = g;
-  FC_CUDA(cudaFuncSetAttribute(mgtc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMgTcSmem));
+  FC_ENSURE_SMEM(mgtc_gemm_kernel, kMgTcSmem);
   const int items = a.MT * a.NT * a.S;
   const int grid = items < sm_count() ? items : sm_count();
   mgtc_gemm_kernel<<<grid, kMgTcThreads, kMgTcSmem, s>>>(a);

@@ -182,7 +182,7 @@ static int launch_chain(const float* params, int L, int H, uint64_t flip_mask, c
     realnvp_chain_kernel<4, MODE><<<grid, kNvpThreads, smem, s>>>(params, L, H, flip_mask, in, out_v, out_lp, out_ls, n);
   } else {
     if (smem > 48 * 1024)
-      FC_CUDA(cudaFuncSetAttribute(realnvp_chain_kernel<0, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      FC_ENSURE_SMEM((realnvp_chain_kernel<0, MODE>), smem);
     int grid = grid_resident(realnvp_chain_kernel<0, MODE>, kNvpThreads, smem, work, kNvpThreads);
     realnvp_chain_kernel<0, MODE><<<grid, kNvpThreads, smem, s>>>(params, L, H, flip_mask, in, out_v, out_lp, out_ls, n);
   }

@@ -209,7 +209,7 @@ int flowcuda_realnvp_nll_grad(const float* params, int n_layers, int hidden, uin
     realnvp_grad_stage1<4><<<grid, kGradThreads, smem, s>>>(params, n_layers, hidden, flip_mask, y, n, (float*)workspace);
   } else {
     if (smem > 48 * 1024)
-      FC_CUDA(cudaFuncSetAttribute(realnvp_grad_stage1<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      FC_ENSURE_SMEM(realnvp_grad_stage1<0>, smem);
     realnvp_grad_stage1<0><<<grid, kGradThreads, smem, s>>>(params, n_layers, hidden, flip_mask, y, n, (float*)workspace);
   }
   FC_LAUNCH_CHECK("realnvp_grad_stage1");

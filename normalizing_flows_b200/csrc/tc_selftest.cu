@@ -4,6 +4,7 @@
 // mbarrier, tcgen05.ld at aligned and unaligned column offsets.  tests/test_gpu_tc.py compares
 // the result with a float64 matmul.
 #include "tc.cuh"
+#include "../../include/flowcuda_selftest.h"
 
 namespace flowcuda {
 
@@ -187,12 +188,12 @@ int flowcuda_selftest_umma(const float* a, const float* w, float* d, float* d_un
   if (bf16) {
     pack_b_image_kernel<true><<<8, 256, 0, s>>>(w, k, n, n, hi, lo);
     FC_LAUNCH_CHECK("pack_b_image_kernel");
-    FC_CUDA(cudaFuncSetAttribute(tc_selftest_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    FC_ENSURE_SMEM(tc_selftest_kernel<true>, smem);
     tc_selftest_kernel<true><<<1, 128, smem, s>>>(a, hi, lo, d, d_unaligned, n, k, mode < 2 || a_tmem, a_tmem, cols);
   } else {
     pack_b_image_kernel<false><<<8, 256, 0, s>>>(w, k, n, n, hi, lo);
     FC_LAUNCH_CHECK("pack_b_image_kernel");
-    FC_CUDA(cudaFuncSetAttribute(tc_selftest_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    FC_ENSURE_SMEM(tc_selftest_kernel<false>, smem);
     tc_selftest_kernel<false><<<1, 128, smem, s>>>(a, hi, lo, d, d_unaligned, n, k, mode < 2 || a_tmem, a_tmem, cols);
   }
   FC_LAUNCH_CHECK("tc_selftest_kernel");
@@ -332,8 +333,11 @@ __global__ void __launch_bounds__(128) tc_mma_timing_kernel(volatile long long* 
 extern "C" int flowcuda_selftest_mma_timing(long long* out_device, int capacity, void* stream) {
   FC_REQUIRE(out_device && capacity >= 4 * 64, "selftest_mma_timing: need room for 64 records");
   const size_t smem = 160 * 1024 + 64;
-  FC_CUDA(cudaFuncSetAttribute(flowcuda::tc_mma_timing_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  FC_ENSURE_SMEM(flowcuda::tc_mma_timing_kernel, smem);
   flowcuda::tc_mma_timing_kernel<<<1, 128, smem, (cudaStream_t)stream>>>(out_device);
   FC_LAUNCH_CHECK("tc_mma_timing_kernel");
   return FLOWCUDA_OK;
 }
+
+// this test library links its own copy of core.cu's error plumbing
+extern "C" const char* flowcuda_selftest_last_error(void) { return flowcuda_last_error(); }

@@ -496,11 +496,12 @@ def selftest_umma(a: torch.Tensor, w: torch.Tensor, mode: int, want_unaligned: b
     a, w = _f32(a), _f32(w)
     _dev_check(a, w)
     k, n = w.shape
-    lib = _lib.load()
+    lib = _lib.load_selftest()
     need = lib.flowcuda_selftest_umma_workspace_bytes(n, k)
     ws = torch.empty((need + 3) // 4, device=a.device, dtype=torch.float32)
     d = torch.zeros(128, n, device=a.device, dtype=torch.float32)
     d2 = torch.zeros(128, n, device=a.device, dtype=torch.float32) if want_unaligned else None
-    check(lib.flowcuda_selftest_umma(_ptr(a), _ptr(w), _ptr(d), _ptr(d2), n, k, mode, _ptr(ws), ws.numel() * 4,
-                                     _stream()), "selftest_umma")
+    rc = lib.flowcuda_selftest_umma(_ptr(a), _ptr(w), _ptr(d), _ptr(d2), n, k, mode, _ptr(ws), ws.numel() * 4, _stream())
+    if rc != 0:
+        raise _lib.FlowCudaError(f"selftest_umma failed with code {rc}: {lib.flowcuda_selftest_last_error().decode()}")
     return (d, d2) if want_unaligned else d

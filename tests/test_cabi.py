@@ -28,6 +28,14 @@ def test_header_symbols_exported(lib):
     for name in declared:
         assert hasattr(raw, name), name
     assert lib.flowcuda_version() == 100
+    # diagnostics live in their own test library with their own header; the product library does not export them
+    hdr2 = open(os.path.join(ROOT, "include", "flowcuda_selftest.h")).read()
+    declared2 = set(re.findall(r"\b(flowcuda_[a-z0-9_]+)\s*\(", hdr2))
+    assert declared2 == set(_lib.SELFTEST_SIGNATURES), declared2 ^ set(_lib.SELFTEST_SIGNATURES)
+    raw2 = ctypes.CDLL(_lib.SELFTEST_LIB_PATH)
+    for name in declared2:
+        assert hasattr(raw2, name), name
+        assert not hasattr(raw, name) or name == "flowcuda_last_error", f"{name} must not ship in libflowcuda.so"
 
 
 def test_spec_struct_matches_header():

@@ -3,7 +3,7 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import ctypes as C, torch
 from normalizing_flows_b200 import _lib
-lib = _lib.load()
+lib = _lib.load_selftest()
 out = torch.zeros(4 * 80, dtype=torch.int64, device="cuda")
 for rep in range(2):
     _lib.check(lib.flowcuda_selftest_mma_timing(C.c_void_p(out.data_ptr()), out.numel(), None))
