@@ -341,6 +341,32 @@ int flowcuda_sgd_step(float* p, const float* g, int64_t count, float lr, float g
 int flowcuda_adam_step(float* p, const float* g, float* m, float* v, int64_t count, int64_t step,
                        float lr, float b1, float b2, float eps, float grad_scale, void* stream);
 
+/* ------------------------------------------------------------------------------------
+ * Scalar bijectors and base densities as stand-alone elementwise kernels — what the host mirror's
+ * `distrax.ScalarAffine`, `tfb.Scale`, `tfb.Shift`, `tfb.SoftClip`, `distrax.RationalQuadraticSpline`,
+ * `Normal` / `Uniform` / `Independent.log_prob` run when a user composes them by hand
+ * (real_nvp_toy_densities.py:84-86, maf_toy_densities.py:86-87, bflow.py:28-34,44,82-88,133-142).
+ * Element i of the flattened input uses parameter row (i / inner) % rows: `inner` trailing elements
+ * share a row ([N,1] parameters broadcast over D), rows repeat along the leading axes ([D] parameters).
+ * Outputs y / ld may be NULL when not wanted.
+ * ---------------------------------------------------------------------------------- */
+/* y = x*scale + shift, ld = log|scale|; inverse: x = (y - shift)/scale, ld = -log|scale|.  `scale` holds
+ * log-scales when scale_is_log != 0.  NULL shift = 0; NULL scale = 1. */
+int flowcuda_affine_elementwise(const float* x, const float* shift, const float* scale, int scale_is_log, int inverse,
+                                float* y, float* ld, int64_t n, int64_t rows, int64_t inner, void* stream);
+/* tfb.SoftClip(low, high, hinge_softness). */
+int flowcuda_softclip_elementwise(const float* x, float low, float high, float hinge_softness, int inverse, float* y,
+                                  float* ld, int64_t n, void* stream);
+/* distrax.RationalQuadraticSpline(params[rows, 3*num_bins+1], range_min, range_max). */
+int flowcuda_rqs_elementwise(const float* x, const float* params, int num_bins, float range_min, float range_max,
+                             int inverse, float* y, float* ld, int64_t n, int64_t rows, int64_t inner, void* stream);
+/* kind 0: Normal(loc=a, scale=b).log_prob; kind 1: Uniform(low=a, high=b).log_prob (-inf outside [low, high]);
+ * NULL a / b = 0 / 1. */
+int flowcuda_base_log_prob(const float* x, const float* a, const float* b, int kind, float* out, int64_t n,
+                           int64_t rows, int64_t inner, void* stream);
+/* out[r] = sum_c x[r, c], fixed summation order (distrax.Independent / Block: sum over the event dims). */
+int flowcuda_sum_last(const float* x, float* out, int64_t rows, int64_t cols, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -103,6 +103,11 @@ SIGNATURES = {
     "flowcuda_sum_scaled": (_i, [_p, _i64, _d, _p, _p, _p]),
     "flowcuda_sgd_step": (_i, [_p, _p, _i64, _f, _f, _p]),
     "flowcuda_adam_step": (_i, [_p, _p, _p, _p, _i64, _i64, _f, _f, _f, _f, _f, _p]),
+    "flowcuda_affine_elementwise": (_i, [_p, _p, _p, _i, _i, _p, _p, _i64, _i64, _i64, _p]),
+    "flowcuda_softclip_elementwise": (_i, [_p, _f, _f, _f, _i, _p, _p, _i64, _p]),
+    "flowcuda_rqs_elementwise": (_i, [_p, _p, _i, _f, _f, _i, _p, _p, _i64, _i64, _i64, _p]),
+    "flowcuda_base_log_prob": (_i, [_p, _p, _p, _i, _p, _i64, _i64, _i64, _p]),
+    "flowcuda_sum_last": (_i, [_p, _p, _i64, _i64, _p]),
 }
 
 # include/flowcuda_selftest.h — diagnostics of the tcgen05 primitives, in a separate TEST library
