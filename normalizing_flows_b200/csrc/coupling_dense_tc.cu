@@ -9,7 +9,8 @@
 //   A image  [m_tile][k_stage][hi|lo][4 chunks][128 rows][16 B]   (activations, 32 K per stage)
 //   B image  [n_tile][k_stage][hi|lo][4 chunks][256 rows][16 B]   (weights, packed per call;
 //            masks folded in: the first Linear keeps only the visible dims' rows, the last only
-//            the transformed dims' columns, 10 dims x 25 spline params (+6 pad) per 256 tile)
+//            the transformed dims' columns; a 256-column tile is two self-contained halves of 5 dims x 25 spline
+//            params (+3 pad) each, so that the tail of the tile list can be split into half tiles)
 // CTA = loader warp + MMA warp + 4 epilogue warps, 2 CTAs per SM so that one CTA's epilogue
 // overlaps the other's MMAs.  Epilogues (thread = sample row = TMEM lane):
 //   hidden: +bias, relu, bf16 hi/lo split, written straight into the next Linear's A image;
@@ -50,9 +51,11 @@ __global__ void __launch_bounds__(256) dense_tc_pack_w_kernel(DtPackW a) {
       col = nt * kDtBN + n;
       if (col >= a.n_out) col = -1;
     } else {
-      const int di = n / a.ppd, pp = n - di * a.ppd;
-      const int dim = nt * a.dpt + di;
-      if (di < a.dpt && dim < ndims) col = (tp + 2 * dim) * a.ppd + pp;
+      int di, pp;  // tile column -> (dim of the tile, parameter): two self-contained 128-column halves (dt_col_to_dim)
+      if (dt_col_to_dim(n, a.dpt, a.ppd, di, pp)) {
+        const int dim = nt * a.dpt + di;
+        if (dim < ndims) col = (tp + 2 * dim) * a.ppd + pp;
+      }
     }
     float f[8];
 #pragma unroll

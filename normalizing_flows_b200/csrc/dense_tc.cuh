@@ -80,10 +80,28 @@ struct DtGemm {
 
 constexpr int kEpiHidden = 0, kEpiRqs8 = 1, kEpiAffine = 2;
 
+// Column layout of a transform tile (last Linear): the 256 columns are two halves of 128; half g holds the
+// dpt/2 dims [g*dpt/2, (g+1)*dpt/2) of the tile, ppd consecutive parameters each (affine: 64 dims x 2 = 128 columns;
+// RQS with 8 bins: 5 dims x 25 = 125 columns + 3 pad).  Halves are self-contained so that a CTA can compute ONE half
+// of a tile (128-column MMA) when the tail of the tile list is split (dense_tc_gemm_kernel, TS).
+__host__ __device__ __forceinline__ bool dt_col_to_dim(int n, int dpt, int ppd, int& di, int& pp) {
+  const int dph = dpt >> 1, r = n & 127;
+  const int q = r / ppd;
+  di = (n >> 7) * dph + q;
+  pp = r - q * ppd;
+  return q < dph;
+}
+__host__ __device__ __forceinline__ int dt_dim_to_col(int di, int dpt, int ppd) {
+  const int dph = dpt >> 1;
+  return ((di / dph) << 7) + (di % dph) * ppd;
+}
+
 // bias index of tile column n (transform epilogues)
 __device__ __forceinline__ float dt_tile_bias(const DtGemm& a, int nt, int n) {
-  const int di = n / a.ppd, pp = n - di * a.ppd, dim = nt * a.dpt + di;
-  if (di >= a.dpt || dim >= a.ndims) return 0.f;
+  int di, pp;
+  if (!dt_col_to_dim(n, a.dpt, a.ppd, di, pp)) return 0.f;
+  const int dim = nt * a.dpt + di;
+  if (dim >= a.ndims) return 0.f;
   if (a.made) {
     const int q = a.rev ? a.D - 1 - dim : dim;
     return a.bias[pp * a.D + q];
@@ -124,31 +142,6 @@ __device__ __forceinline__ void dt_epilogue(const DtGemm& a, int mt, int nt, uin
         }
       }
     }
-  } else if (EPI == kEpiRqs8) {
-    float ldsum = 0.f;
-#pragma unroll 1
-    for (int di = 5 * half; di < 5 * half + 5; ++di) {
-      const int dim = nt * 10 + di;
-      if (dim >= a.ndims) break;  // uniform across the CTA
-      uint32_t vv[25];
-      tc::tmem_ld_x16(tb + (uint32_t)(25 * di), vv);
-      tc::tmem_ld_x8(tb + (uint32_t)(25 * di + 16), vv + 16);
-      tc::tmem_ld_x1(tb + (uint32_t)(25 * di + 24), vv + 24);
-      tc::tmem_ld_wait();
-      if (grow < a.N) {
-        float o[25];
-#pragma unroll
-        for (int i = 0; i < 25; ++i)
-          o[i] = i < 16 ? fmaf(__uint_as_float(vv[i]), kLog2e, sbias[25 * di + i]) : __uint_as_float(vv[i]) + sbias[25 * di + i];
-        const int d = a.tp + a.dstride * dim;
-        const float xin = a.v[grow * a.D + d];
-        float nv, l1;
-        rqs_apply_mufu<INV, 8>([&](int i) { return o[i]; }, a.koff, a.lo, a.hi, xin, nv, l1);
-        a.v[grow * a.D + d] = nv;
-        ldsum += l1;
-      }
-    }
-    if (grow < a.N) a.ldp[grow * a.tiles + 2 * nt + half] = ldsum;
   } else {
     // Affine epilogue.  The accumulator comes out of TMEM as thread = sample row, but the state v[N, D]
     // is row-major: a thread-per-row access touches 32 cache lines per request.  Each warp therefore
@@ -247,35 +240,59 @@ __device__ __forceinline__ void dt_epilogue(const DtGemm& a, int mt, int nt, uin
   }
 }
 
-// RQS epilogue of a whole 128 x 256 tile by one warp per TMEM lane quarter (thread = sample row, 10 dims x 25 spline
-// parameters): dims (di, di + 5) are evaluated as a pair of independent splines (rqs_apply_mufu_x2), their 2 x 25
-// accumulator columns fetched together; `xin` holds the row's 10 state values, loaded BEFORE the accumulator was
-// waited for (they do not depend on it) — the thread-per-row state access touches 32 cache lines per warp request and
-// its latency used to sit inside every spline.  Log-det partials keep the two-per-tile layout and summation order of the
-// half-tile form (dims 0-4 | 5-9), so results are bit-identical to it.
+// RQS epilogue by one warp per TMEM lane quarter (thread = sample row; 25 spline parameters per dim, 5 dims per
+// 128-column half).  `part` = -1: a whole 128 x 256 tile, dims paired (di, di + 5) — one from each half; `part` = h:
+// only half h of the tile (the accumulator then holds that half at TMEM columns 0..127), dims paired (0,1), (2,3), (4).
+// A pair is evaluated as two independent splines in lockstep (rqs_apply_mufu_x2), their 2 x 25 accumulator columns
+// fetched together.  The row's state values are loaded BEFORE the accumulator is waited for (dt_rqs_load_x): they do not
+// depend on it, and the thread-per-row access (32 cache lines per warp request) used to sit inside every spline.
+struct DtRqsX {
+  float xa[5], xb[5];  // first / second member of pair j = 0..4
+};
+__device__ __forceinline__ void dt_rqs_pair(int part, int j, int& d0, int& d1) {
+  if (part < 0) {
+    d0 = j;
+    d1 = j + 5;
+  } else {
+    d0 = 5 * part + 2 * j;
+    d1 = (2 * j + 1 < 5) ? d0 + 1 : -1;
+  }
+}
+__device__ __forceinline__ void dt_rqs_load_x(const DtGemm& a, int mt, int nt, int part, int warp, int lane, DtRqsX& x) {
+  const int64_t grow = (int64_t)mt * 128 + (warp & 3) * 32 + lane;
+#pragma unroll
+  for (int j = 0; j < 5; ++j) {
+    int d0, d1;
+    dt_rqs_pair(part, j, d0, d1);
+    const bool live = part < 0 || j < 3;
+    const int dim0 = nt * 10 + d0, dim1 = nt * 10 + d1;
+    x.xa[j] = (live && grow < a.N && dim0 < a.ndims) ? a.v[grow * a.D + a.tp + a.dstride * dim0] : 0.f;
+    x.xb[j] = (live && d1 >= 0 && grow < a.N && dim1 < a.ndims) ? a.v[grow * a.D + a.tp + a.dstride * dim1] : 0.f;
+  }
+}
+
 template <bool INV>
-__device__ __forceinline__ void dt_epilogue_rqs_tile(const DtGemm& a, int mt, int nt, uint32_t tb, const float* __restrict__ sbias,
-                                                     int warp, int lane, const float (&xin)[10]) {
+__device__ __forceinline__ void dt_epilogue_rqs_tile(const DtGemm& a, int mt, int nt, int part, uint32_t tb,
+                                                     const float* __restrict__ sbias, int warp, int lane, DtRqsX& x) {
   const int row = (warp & 3) * 32 + lane;
   const int64_t grow = (int64_t)mt * 128 + row;
   float ldsum[2] = {0.f, 0.f};
-  // the loop below is not unrolled (one copy of the spline code), so the state values are consumed from the head of two
-  // register queues that shift by one per iteration — a runtime index would put the array in local memory
-  float xa[5], xb[5];
-#pragma unroll
-  for (int i = 0; i < 5; ++i) {
-    xa[i] = xin[i];
-    xb[i] = xin[i + 5];
-  }
+  const int npair = part < 0 ? 5 : 3;
+  const int cshift = part < 0 ? 0 : 128 * part;  // accumulator column = tile column - cshift
+  // the loop is not unrolled (one copy of the spline code): the state values are consumed from the head of two
+  // register queues that shift by one per iteration — a runtime index would put the arrays in local memory
 #pragma unroll 1
-  for (int di = 0; di < 5; ++di) {
-    const int dim0 = nt * 10 + di, dim1 = dim0 + 5;
+  for (int j = 0; j < npair; ++j) {
+    int d0, d1;
+    dt_rqs_pair(part, j, d0, d1);
+    const int dim0 = nt * 10 + d0, dim1 = nt * 10 + d1;
     if (dim0 >= a.ndims) break;  // uniform across the CTA
-    const bool two = dim1 < a.ndims;
+    const bool two = d1 >= 0 && dim1 < a.ndims;
+    const int c0 = dt_dim_to_col(d0, 10, 25), c1 = dt_dim_to_col(two ? d1 : d0, 10, 25);
     uint32_t vv[2][25];
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
-      const uint32_t c = (uint32_t)(25 * (di + 5 * u));
+      const uint32_t c = (uint32_t)((u ? c1 : c0) - cshift);
       tc::tmem_ld_x16(tb + c, vv[u]);
       tc::tmem_ld_x8(tb + c + 16, vv[u] + 16);
       tc::tmem_ld_x1(tb + c + 24, vv[u] + 24);
@@ -285,12 +302,12 @@ __device__ __forceinline__ void dt_epilogue_rqs_tile(const DtGemm& a, int mt, in
       float o[2][25];
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
-        const float* sb = sbias + 25 * (di + 5 * u);
+        const float* sb = sbias + (u ? c1 : c0);
 #pragma unroll
         for (int i = 0; i < 25; ++i)
           o[u][i] = i < 16 ? fmaf(__uint_as_float(vv[u][i]), kLog2e, sb[i]) : __uint_as_float(vv[u][i]) + sb[i];
       }
-      const float v2[2] = {xa[0], two ? xb[0] : 0.5f * (a.lo + a.hi)};
+      const float v2[2] = {x.xa[0], two ? x.xb[0] : 0.5f * (a.lo + a.hi)};
       float nv[2], l2[2];
       rqs_apply_mufu_x2<INV, 8>(o[0], o[1], a.koff, a.lo, a.hi, v2, nv, l2);
       a.v[grow * a.D + a.tp + a.dstride * dim0] = nv[0];
@@ -302,23 +319,17 @@ __device__ __forceinline__ void dt_epilogue_rqs_tile(const DtGemm& a, int mt, in
     }
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-      xa[i] = xa[i + 1];
-      xb[i] = xb[i + 1];
+      x.xa[i] = x.xa[i + 1];
+      x.xb[i] = x.xb[i + 1];
     }
   }
   if (grow < a.N) {
-    a.ldp[grow * a.tiles + 2 * nt] = ldsum[0];
-    a.ldp[grow * a.tiles + 2 * nt + 1] = ldsum[1];
-  }
-}
-
-// the row's 10 state values of tile nt (issued before the accumulator wait)
-__device__ __forceinline__ void dt_rqs_load_x(const DtGemm& a, int mt, int nt, int warp, int lane, float (&xin)[10]) {
-  const int64_t grow = (int64_t)mt * 128 + (warp & 3) * 32 + lane;
-#pragma unroll
-  for (int i = 0; i < 10; ++i) {
-    const int dim = nt * 10 + i;
-    xin[i] = (grow < a.N && dim < a.ndims) ? a.v[grow * a.D + a.tp + a.dstride * dim] : 0.f;
+    if (part < 0) {
+      a.ldp[grow * a.tiles + 2 * nt] = ldsum[0];      // dims 0-4 of the tile
+      a.ldp[grow * a.tiles + 2 * nt + 1] = ldsum[1];  // dims 5-9
+    } else {
+      a.ldp[grow * a.tiles + 2 * nt + part] = ldsum[0] + ldsum[1];
+    }
   }
 }
 
@@ -339,17 +350,60 @@ template <int EPI, bool WIDE> struct DtCfg {
   static constexpr size_t kSmem = (size_t)kStages * kDtStageBytes + kScratch * 4 + 2 * kDtBN * 4 + (2 * kStages + 4) * 8 + 16;
 };
 
-// Persistent kernel: one CTA per SM walks the (m tile, n tile) list; a TMA ring feeds the MMA warp across
-// tile boundaries, and the two 256-column TMEM accumulators alternate between two epilogue warpgroups, so
-// an epilogue may take twice the MMA time of a tile before it stalls the tensor pipe.
-// NH ("n halves", hidden epilogue only): a CTA computes 128 x 128 — one half of an n tile — so that a launch with few
-// tiles (the 512-wide hidden Linears at batch 4096: 64 tiles for 148 SMs, each a latency-bound serial chain of 16 K
-// stages) becomes twice as many CTAs of half the MMA time; the tile's B half is eight 2 KB runs of the weight image.
+// Work items of a persistent CTA.  A full item is one 128 x 256 tile; a half item (`part` = 0 / 1) is the 128 x 128 half
+// of a tile whose B operand is the eight 2 KB runs [rows 128*part, +128) of the tile's weight image (MMA with N = 128).
+//   * NH (hidden epilogue): EVERY tile is split — a launch with fewer tiles than SMs (the 512-wide hidden Linears at
+//     batch 4096: 64 tiles, each a latency-bound chain of 16 K stages) becomes twice as many CTAs of half the MMA time;
+//   * TS (RQS epilogue): only the tiles of the last, PARTIAL wave are split — 1248 tiles on 148 CTAs are 8 full waves
+//     plus 64 tiles; unsplit, 84 CTAs idle through the ninth tile and the kernel ends with a whole tile's epilogue;
+//     split, every CTA ends with at most half a tile (MMAs 9 -> 8.5 tile times, final epilogue halved).
+struct DtItem {
+  int mt, nt, part;  // part < 0: the whole tile
+};
+template <bool NH, bool TS>
+__device__ __forceinline__ bool dt_item(int w, int MT, int NT, DtItem& it) {
+  const int grid = (int)gridDim.x, cta = (int)blockIdx.x;
+  if (NH) {
+    const int t = cta + w * grid;
+    if (t >= MT * NT * 2) return false;
+    it.mt = t / (2 * NT);
+    const int c = t - it.mt * 2 * NT;
+    it.nt = c >> 1;
+    it.part = c & 1;
+    return true;
+  }
+  const int ntiles = MT * NT;
+  int t = cta + w * grid;
+  it.part = -1;
+  if (TS) {
+    const int nfull = ntiles / grid, rem = ntiles - nfull * grid;
+    if (w > nfull) return false;
+    if (w == nfull) {
+      if (rem == 0) return false;
+      if (2 * rem <= grid) {  // split the tail: half `cta & 1` of tail tile `cta >> 1`
+        if (cta >= 2 * rem) return false;
+        t = nfull * grid + (cta >> 1);
+        it.part = cta & 1;
+      } else if (cta >= rem) {
+        return false;
+      }
+    }
+  } else if (t >= ntiles) {
+    return false;
+  }
+  it.mt = t / NT;
+  it.nt = t - it.mt * NT;
+  return true;
+}
+
+// Persistent kernel: one CTA per SM walks its work items; a TMA ring feeds the MMA warp across item boundaries, and the
+// two 256-column TMEM accumulators alternate between two epilogue warpgroups, so an epilogue may take twice the MMA time
+// of a tile before it stalls the tensor pipe.
 template <int EPI, bool INV, bool WIDE, bool NH = false>
 __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_kernel(DtGemm a, int MT, int NT) {
   using Cfg = DtCfg<EPI, WIDE>;
   static_assert(!NH || (EPI == kEpiHidden && !WIDE), "n-half tiles exist for the hidden epilogue with 4-warp groups");
-  constexpr int BNC = NH ? kDtBN / 2 : kDtBN;  // accumulator columns of a CTA tile
+  constexpr bool TS = EPI == kEpiRqs8;  // split the tiles of the partial last wave
   constexpr int kDtStages = Cfg::kStages;
   constexpr int EW = Cfg::kEpiWarps;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -362,8 +416,6 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
   uint64_t* acc_empty = acc_full + 2;                                              // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int NTH = NH ? 2 * NT : NT;  // tile columns (n tile, half)
-  const int ntiles = MT * NTH;
 
   if (warp == 1) tc::tmem_alloc(tmem_slot, 2 * kDtBN);
   if (tid == 0) {
@@ -385,9 +437,9 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
   if (warp == 0) {
     if (lane == 0) {  // ===== TMA loader
       uint32_t it = 0;
-      for (int t = blockIdx.x; t < ntiles; t += gridDim.x) {
-        const int mt = t / NTH, ntc = t - mt * NTH;
-        const int nt = NH ? ntc >> 1 : ntc, hh = NH ? ntc & 1 : 0;
+      DtItem wi;
+      for (int w = 0; dt_item<NH, TS>(w, MT, NT, wi); ++w) {
+        const int mt = wi.mt, nt = wi.nt;
         int KS = a.KS;
         if (nt < kDtMaxKsTiles && a.ks_tile[nt] != 0) KS = a.ks_tile[nt];
         const uint8_t* ag = a.a_img + (int64_t)mt * a.KS * 2 * kDtABytes;
@@ -396,11 +448,11 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
           const uint32_t st = it % kDtStages, ph = (it / kDtStages) & 1u;
           tc::mbar_wait(&empty[st], ph ^ 1u);  // passes at once on a fresh barrier
           uint8_t* dst = stages + st * kDtStageBytes;
-          if (NH) {
+          if ((NH || TS) && wi.part >= 0) {
             tc::mbar_arrive_expect_tx(&full[st], 4 * kDtABytes);
             tc::tma_bulk_g2s(dst, ag + (int64_t)ks * 2 * kDtABytes, 2 * kDtABytes, &full[st]);
-            // rows 128 hh .. 128 hh + 127 of each of the 2 x 4 K chunks: 2 KB runs, 4 KB apart in the image
-            const uint8_t* bs = bg + (int64_t)ks * 2 * kDtBBytes + hh * 2048;
+            // rows [128 part, +128) of each of the 2 x 4 K chunks: 2 KB runs, 4 KB apart in the image
+            const uint8_t* bs = bg + (int64_t)ks * 2 * kDtBBytes + wi.part * 2048;
 #pragma unroll
             for (int c = 0; c < 8; ++c) tc::tma_bulk_g2s(dst + 2 * kDtABytes + c * 2048, bs + c * 4096, 2048, &full[st]);
           } else {
@@ -413,15 +465,18 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
     }
   } else if (warp == 1) {
     if (lane == 0) {  // ===== MMA issuer: 3 passes x 2 K steps per stage
-      constexpr uint32_t idesc = tc::make_idesc(tc::kFmtBF16, 128, BNC);
-      constexpr uint32_t lbo_a = 16u * 128u, lbo_b = (uint32_t)(BNC >> 3) * 128u;
-      constexpr uint32_t kBLo = NH ? kDtABytes : kDtBBytes;  // offset of the lo image inside the staged B
-      uint32_t it = 0, tl = 0;
-      for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tl) {
-        const int nt = NH ? (t % NTH) >> 1 : t % NT;
+      constexpr uint32_t lbo_a = 16u * 128u;
+      uint32_t it = 0;
+      DtItem wi;
+      for (int w = 0; dt_item<NH, TS>(w, MT, NT, wi); ++w) {
+        const int nt = wi.nt;
+        const bool halfn = (NH || TS) && wi.part >= 0;
+        const uint32_t idesc = halfn ? tc::make_idesc(tc::kFmtBF16, 128, kDtBN / 2) : tc::make_idesc(tc::kFmtBF16, 128, kDtBN);
+        const uint32_t lbo_b = halfn ? 16u * 128u : 32u * 128u;       // rows / 8 * 128 of the staged B image
+        const uint32_t b_lo = halfn ? (uint32_t)kDtABytes : (uint32_t)kDtBBytes;  // offset of its lo part
         int KS = a.KS;
         if (nt < kDtMaxKsTiles && a.ks_tile[nt] != 0) KS = a.ks_tile[nt];
-        const uint32_t slot = tl & 1u, aph = (tl >> 1) & 1u;
+        const uint32_t slot = (uint32_t)w & 1u, aph = ((uint32_t)w >> 1) & 1u;
         tc::mbar_wait(&acc_empty[slot], aph ^ 1u);  // the epilogue has drained this accumulator
         tc::tc_fence_after();
         const uint32_t dtm = tmem + slot * (uint32_t)kDtBN;
@@ -433,7 +488,7 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
           const uint32_t sa = tc::smem_u32(stages + st * kDtStageBytes), sb = sa + 2 * kDtABytes;
 #pragma unroll
           for (int pass = 0; pass < 3; ++pass) {
-            const uint32_t ab = sa + (pass == 2 ? kDtABytes : 0), bb = sb + (pass == 1 ? kBLo : 0);
+            const uint32_t ab = sa + (pass == 2 ? kDtABytes : 0), bb = sb + (pass == 1 ? b_lo : 0);
 #pragma unroll
             for (int s = 0; s < kDtBK / 16; ++s) {
               tc::mma_ss<tc::kFmtBF16>(dtm, tc::make_smem_desc(ab + s * 2u * lbo_a, lbo_a, 128u),
@@ -447,7 +502,7 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
       }
     }
   } else {
-    // ===== epilogue warps: group 0 (warps 2-9) takes the even tiles of this CTA, group 1 (warps 10-17) the odd;
+    // ===== epilogue warps: group 0 (warps 2-9) takes the even items of this CTA, group 1 (warps 10-17) the odd;
     // inside a group, warps 0-3 take the tile's columns 0-127 and warps 4-7 columns 128-255 (two warps per TMEM
     // lane quarter).  With only four warps per tile the epilogues were bound by single-warp issue.
     const uint32_t group = (uint32_t)(warp - 2) / EW;
@@ -458,12 +513,11 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
       else asm volatile("bar.sync 2, %0;" ::"n"(EW * 32) : "memory");
     };
     float* sbias = sbias2 + group * kDtBN;
-    uint32_t tl = 0;
-    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, ++tl) {
-      if ((tl & 1u) != group) continue;
-      const int mt = t / NTH, ntc = t - mt * NTH;
-      const int nt = NH ? ntc >> 1 : ntc, hh = NH ? ntc & 1 : 0;
-      const uint32_t slot = group, aph = (tl >> 1) & 1u;
+    DtItem wi;
+    for (int w = 0; dt_item<NH, TS>(w, MT, NT, wi); ++w) {
+      if (((uint32_t)w & 1u) != group) continue;
+      const int mt = wi.mt, nt = wi.nt;
+      const uint32_t slot = group, aph = ((uint32_t)w >> 1) & 1u;
       for (int n = et; n < kDtBN; n += EW * 32) {  // bias of this tile's columns
         float b = 0.f;
         if (EPI == kEpiHidden) {
@@ -472,13 +526,13 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
         } else {
           b = dt_tile_bias(a, nt, n);
           // RQS: the 16 bin logits of a dimension reach the spline in log2 units (rqs_apply_mufu)
-          if (EPI == kEpiRqs8 && n % 25 < 16) b *= kLog2e;
+          if (EPI == kEpiRqs8 && (n & 127) % 25 < 16) b *= kLog2e;
         }
         sbias[n] = b;
       }
       group_sync();
-      float xin[10];
-      if (EPI == kEpiRqs8) dt_rqs_load_x(a, mt, nt, warp, lane, xin);
+      DtRqsX xin;
+      if (EPI == kEpiRqs8) dt_rqs_load_x(a, mt, nt, wi.part, warp, lane, xin);
       if (EPI == kEpiAffine && (EW == 4 || half == 0)) {
         // the bijector reads this tile's slice of the state v (it left L2 while the Linears streamed their
         // images): pull the thread's row of the slice into L2 now, under the tile's MMAs
@@ -495,10 +549,10 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
       tc::tc_fence_after();
       const uint32_t tb = tmem + slot * (uint32_t)kDtBN + ((uint32_t)((warp & 3) * 32) << 16);
       if (EPI == kEpiRqs8) {
-        dt_epilogue_rqs_tile<INV>(a, mt, nt, tb, sbias, warp, lane, xin);
+        dt_epilogue_rqs_tile<INV>(a, mt, nt, wi.part, tb, sbias, warp, lane, xin);
       } else if (NH) {
-        // the accumulator holds columns [128 hh, 128 hh + 128) of the n tile at TMEM columns 0..127
-        dt_epilogue<EPI, INV>(a, mt, nt, tb - (uint32_t)(hh * (kDtBN / 2)), sbias, Tbase, warp, lane, hh);
+        // the accumulator holds columns [128 part, +128) of the n tile at TMEM columns 0..127
+        dt_epilogue<EPI, INV>(a, mt, nt, tb - (uint32_t)(wi.part * (kDtBN / 2)), sbias, Tbase, warp, lane, wi.part);
       } else if (EW == 8) {
         dt_epilogue<EPI, INV>(a, mt, nt, tb, sbias, Tbase + group * kDtTileScratchFloats, warp, lane, half);
       } else {

@@ -295,14 +295,14 @@ dense_tc2_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             if (col < a.n_out) b = a.bias[col];
           } else {
             b = dt_tile_bias(a, nt, n);
-            if (EPI == kEpiRqs8 && n % 25 < 16) b *= kLog2e;  // bin logits reach the spline in log2 units
+            if (EPI == kEpiRqs8 && (n & 127) % 25 < 16) b *= kLog2e;  // bin logits reach the spline in log2 units
           }
           sbias[n] = b;
         }
       }
       group_sync();
-      float xin[10];
-      if (EPI == kEpiRqs8 && tl.live) dt_rqs_load_x(a, mt, nt, warp, lane, xin);
+      DtRqsX xin;
+      if (EPI == kEpiRqs8 && tl.live) dt_rqs_load_x(a, mt, nt, -1, warp, lane, xin);
       if (tl.live && EPI == kEpiAffine && (EW == 4 || half == 0)) {
         // pull this thread's row of the tile's state slice into L2 under the tile's MMAs
         const int64_t prow = (int64_t)mt * 128 + (warp & 3) * 32 + lane;
@@ -318,7 +318,7 @@ dense_tc2_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       if (tl.live) {
         const uint32_t tb = tmem + slot * (uint32_t)kDtBN + ((uint32_t)((warp & 3) * 32) << 16);
         if (EPI == kEpiRqs8) {
-          dt_epilogue_rqs_tile<INV>(a, mt, nt, tb, sbias, warp, lane, xin);
+          dt_epilogue_rqs_tile<INV>(a, mt, nt, -1, tb, sbias, warp, lane, xin);
         } else if (EW == 8) {
           dt_epilogue<EPI, INV>(a, mt, nt, tb, sbias, Tbase + group * kDtTileScratchFloats, warp, lane, half);
         } else {
