@@ -54,6 +54,34 @@ int sm_count();
     }                                                                                                            \
   } while (0)
 
+// ---- programmatic dependent launch (PDL) ---------------------------------------------------------------------------
+// The D=784 paths are chains of 40-100 short kernels, each depending on the one before.  Launched with
+// cudaLaunchAttributeProgrammaticStreamSerialization, kernel k+1 is scheduled while kernel k is still running: its CTAs
+// run their prologue (barrier init, TMEM allocation, descriptor prefetch) on SMs as they free up and then block in
+// pdl_wait() until kernel k has COMPLETED and its writes are visible.  Rules kept by every kernel launched this way:
+// nothing before pdl_wait() reads or writes global memory another kernel of the chain touches, and
+// pdl_launch_dependents() comes after pdl_wait(), so at most one successor is ever resident early.
+// FLOWCUDA_PDL=0 launches the same kernels with plain stream order (the waits are then no-ops).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool pdl_enabled();  // core.cu
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_chain(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 constexpr float kHalfLog2Pi = 0.9189385332046727f;  // 0.5*log(2*pi)

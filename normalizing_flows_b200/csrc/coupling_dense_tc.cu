@@ -121,7 +121,8 @@ static bool dt_layout(const flowcuda_coupling_spec* sp, int64_t n, DtLayout& L) 
   }
   L.off_v = off; off = dt_al256(off + (size_t)n * D * 4);
   L.off_ld = off; off = dt_al256(off + (size_t)n * 4);
-  L.off_ldp = off; off = dt_al256(off + (size_t)n * L.tiles * 2 * 4);  // two partials per (row, tile)
+  // two log-det partials per (row, tile), one slab per flow layer (summed once, by the finish kernel)
+  L.off_ldp = off; off = dt_al256(off + (size_t)sp->num_layers * n * L.tiles * 2 * 4);
   L.off_x = off; off = dt_al256(off + (size_t)L.MT * L.KS[0] * 2 * kDtABytes);
   int ksh = 1;
   for (int i = 1; i < L.nlin; ++i) ksh = L.KS[i] > ksh ? L.KS[i] : ksh;
@@ -174,6 +175,10 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
   }
   if (mode == 2) return FLOWCUDA_OK;
   const int nl = layer_end - layer_begin;
+  // the finish kernel sums every slot of the processed layers' slabs; tiles a layer does not use (odd event sizes: the
+  // two parities differ by one dim) must read as zero
+  if (nl > 0) FC_CUDA(cudaMemsetAsync(ldp, 0, (size_t)nl * n * 2 * L.tiles * sizeof(float), s));
+  int used2 = 0;
   for (int it = 0; it < nl; ++it) {
     const int l = inverse ? layer_begin + it : layer_end - 1 - it;
     const int vis = (l & 1) ? 0 : 1, tp = 1 - vis;
@@ -182,8 +187,8 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
     {
       int64_t total = L.MT * 128 * L.KS[0] * 4;
       int blocks = (int)((total + 255) / 256);
-      dense_tc_pack_x_kernel<<<blocks, 256, 0, s>>>(v, n, D, vis, 2, nvis, L.KS[0], ws + L.off_x);
-      FC_LAUNCH_CHECK("dense_tc_pack_x_kernel");
+      FC_CUDA(launch_chain(dense_tc_pack_x_kernel, dim3(blocks), dim3(256), 0, s, (const float*)v, n, D, vis, 2, nvis, L.KS[0],
+                           ws + L.off_x));
     }
     const uint8_t* aimg = ws + L.off_x;
     for (int i = 0; i < L.nlin; ++i) {
@@ -194,7 +199,7 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
       g.KS = L.KS[i];
       g.n_out = L.sizes[i + 1];
       g.out_img = nullptr; g.out_KS = 0;
-      g.v = v; g.ldp = ldp; g.N = n; g.D = D; g.tp = tp; g.dstride = 2; g.ndims = ndims; g.dpt = L.dpt; g.ppd = L.ppd;
+      g.v = v; g.ldp = ldp + (size_t)it * n * 2 * L.tiles; g.N = n; g.D = D; g.tp = tp; g.dstride = 2; g.ndims = ndims; g.dpt = L.dpt; g.ppd = L.ppd;
       g.tiles = 2 * L.tiles; g.lo = sp->range_min; g.hi = sp->range_max;
       for (int i = 0; i < 9; ++i) g.koff[i] = sp->range_min + (float)i * kRqsMinBin;
       int rc;
@@ -211,18 +216,17 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
         else
           rc = inverse ? dt2_launch_gemm<kEpiAffine, true>(g, dl, L.MT, used, s) : dt2_launch_gemm<kEpiAffine, false>(g, dl, L.MT, used, s);
         if (rc) return rc;
-        dense_tc_ld_accum_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, s>>>(ldp, 2 * L.tiles, 2 * used, ld, n, it == 0);
-        FC_LAUNCH_CHECK("dense_tc_ld_accum_kernel");
+        used2 = 2 * L.tiles;
       }
       if (rc) return rc;
     }
   }
-  if (nl == 0) FC_CUDA(cudaMemsetAsync(ld, 0, (size_t)n * sizeof(float), s));
-  if (out_v) FC_CUDA(cudaMemcpyAsync(out_v, v, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  (void)ld;
   if (out_lp || out_ld) {
-    dense_tc_finish_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, s>>>(v, ld, n, D, with_base, sp->base, out_lp, out_ld);
-    FC_LAUNCH_CHECK("dense_tc_finish_kernel");
+    FC_CUDA(launch_chain(dense_tc_finish_kernel, dim3((unsigned)((n * 32 + 255) / 256)), dim3(256), 0, s, (const float*)v,
+                         (const float*)ldp, nl, 2 * L.tiles, used2, n, D, with_base, (int)sp->base, out_lp, out_ld));
   }
+  if (out_v) FC_CUDA(cudaMemcpyAsync(out_v, v, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToDevice, s));
   return FLOWCUDA_OK;
 }
 

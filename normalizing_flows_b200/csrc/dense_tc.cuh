@@ -35,6 +35,8 @@ constexpr int kDtMaxKsTiles = 48;
 static __global__ void __launch_bounds__(256) dense_tc_pack_x_kernel(const float* __restrict__ v, int64_t N, int D,
                                                                     int off, int stride, int nk, int KS,
                                                                     uint8_t* __restrict__ img) {
+  pdl_wait();  // v is written by the previous kernel of the chain
+  pdl_launch_dependents();
   const int64_t rows = (N + 255) / 256 * 256;  // whole CTA-pair tiles (dense_tc2.cuh): MT is always even
   const int64_t total = rows * (KS * 4);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -433,6 +435,10 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  // everything above touched only this CTA's shared memory and TMEM: from here on the kernel reads what the previous
+  // kernel of the chain wrote (activation images, the state v) and writes what it may still be reading
+  pdl_wait();
+  pdl_launch_dependents();
 
   if (warp == 0) {
     if (lane == 0) {  // ===== TMA loader
@@ -582,8 +588,7 @@ static int dt_launch_gemm_w(const DtGemm& g, int64_t MT, int NT, cudaStream_t s)
   FC_ENSURE_SMEM(kern, kSmem);
   const int64_t tiles = MT * NT;
   const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
-  kern<<<grid, DtCfg<EPI, WIDE>::kThreads, kSmem, s>>>(g, (int)MT, NT);
-  FC_LAUNCH_CHECK("dense_tc_gemm_kernel");
+  FC_CUDA(launch_chain(kern, dim3(grid), dim3(DtCfg<EPI, WIDE>::kThreads), kSmem, s, g, (int)MT, NT));
   return FLOWCUDA_OK;
 }
 
@@ -594,8 +599,7 @@ static int dt_launch_gemm_nh(const DtGemm& g, int64_t MT, int NT, cudaStream_t s
   FC_ENSURE_SMEM(kern, kSmem);
   const int64_t tiles = MT * NT * 2;
   const int grid = (int)(tiles < sm_count() ? tiles : sm_count());
-  kern<<<grid, DtCfg<EPI, false>::kThreads, kSmem, s>>>(g, (int)MT, NT);
-  FC_LAUNCH_CHECK("dense_tc_gemm_kernel(n halves)");
+  FC_CUDA(launch_chain(kern, dim3(grid), dim3(DtCfg<EPI, false>::kThreads), kSmem, s, g, (int)MT, NT));
   return FLOWCUDA_OK;
 }
 
@@ -610,31 +614,31 @@ static int dt_launch_gemm(const DtGemm& g, int64_t MT, int NT, cudaStream_t s) {
 }
 
 // ---- log-det bookkeeping (fixed summation order: deterministic) ----------------------------------
-static __global__ void __launch_bounds__(256) dense_tc_ld_accum_kernel(const float* __restrict__ ldp, int tiles, int used,
-                                                                      float* __restrict__ ld, int64_t N, int first) {
-  // one warp per row: coalesced reads of the row's partials, fixed lane order + fixed shuffle tree
-  const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (r >= N) return;
-  float s = 0.f;
-  for (int t = lane; t < used; t += 32) s += ldp[r * tiles + t];
-  s = warp_sum(s);
-  if (lane == 0) ld[r] = first ? s : ld[r] + s;
-}
-
-static __global__ void __launch_bounds__(256) dense_tc_finish_kernel(const float* __restrict__ v, const float* __restrict__ ld,
-                                                                    int64_t N, int D, int with_base, int base,
-                                                                    float* __restrict__ out_lp, float* __restrict__ out_ld) {
+// Every transform GEMM leaves two log-det partials per (row, tile) in ITS layer's slab of ldp
+// ([layers processed][N][tiles]); one kernel at the end of the chain sums a row's `nslabs * used` partials in a
+// fixed order (lane-strided, then the shuffle tree), adds the base log-density and writes the outputs.
+static __global__ void __launch_bounds__(256) dense_tc_finish_kernel(const float* __restrict__ v, const float* __restrict__ ldp,
+                                                                    int nslabs, int tiles, int used, int64_t N, int D,
+                                                                    int with_base, int base, float* __restrict__ out_lp,
+                                                                    float* __restrict__ out_ld) {
+  pdl_wait();
   int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;  // one warp per row
   int lane = threadIdx.x & 31;
   if (r >= N) return;
+  float ld = 0.f;
+  for (int sl = 0; sl < nslabs; ++sl) {
+    const float* p = ldp + ((int64_t)sl * N + r) * tiles;
+    float s = 0.f;
+    for (int t = lane; t < used; t += 32) s += p[t];
+    ld += warp_sum(s);
+  }
   float s = 0.f;
   if (with_base)
     for (int d = lane; d < D; d += 32) s += base_term(base, v[r * D + d]);
   s = warp_sum(s);
   if (lane == 0) {
-    if (out_ld) out_ld[r] = ld[r];
-    if (out_lp) out_lp[r] = ld[r] + s;
+    if (out_ld) out_ld[r] = ld;
+    if (out_lp) out_lp[r] = ld + s;
   }
 }
 

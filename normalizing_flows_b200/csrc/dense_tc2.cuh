@@ -207,6 +207,8 @@ dense_tc2_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   tc::cluster_sync_all();  // every CTA's barriers exist before any remote arrive / multicast can reach them
   tc::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  pdl_wait();  // from here on: operands written by the previous kernel of the chain (common.cuh, PDL)
+  pdl_launch_dependents();
 
   if (warp == 0) {
     if (lane == 0) {  // ===== TMA producer (every CTA)
@@ -450,13 +452,15 @@ static int dt2_launch_w(const DtGemm& g, const Dt2Launch& L, int64_t MT, int NT,
   cfg.blockDim = dim3(Cfg::kThreads);
   cfg.dynamicSmemBytes = Cfg::kSmem;
   cfg.stream = s;
-  cudaLaunchAttribute at[1];
+  cudaLaunchAttribute at[2];
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = CL;
   at[0].val.clusterDim.y = 1;
   at[0].val.clusterDim.z = 1;
+  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = pdl_enabled() ? 2 : 1;
   FC_CUDA(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, g, MTP, NT, (int)(L.b_tile0 * g.KS * 8)));
   return FLOWCUDA_OK;
 }

@@ -72,7 +72,8 @@ static bool made_layout(const flowcuda_made_spec* sp, int64_t n, MadeLayout& L) 
   }
   L.off_v = off; off = dt_al256(off + (size_t)n * D * 4);
   L.off_ld = off; off = dt_al256(off + (size_t)n * 4);
-  L.off_ldp = off; off = dt_al256(off + (size_t)n * L.tiles * 2 * 4);  // two partials per (row, tile)
+  // two log-det partials per (row, tile), one slab per flow layer (summed once, by the finish kernel)
+  L.off_ldp = off; off = dt_al256(off + (size_t)sp->num_layers * n * L.tiles * 2 * 4);
   L.off_x = off; off = dt_al256(off + (size_t)L.MT * L.KS[0] * 2 * kDtABytes);
   int ksh = 1;
   for (int i = 1; i < L.nlin; ++i) ksh = L.KS[i] > ksh ? L.KS[i] : ksh;
@@ -209,8 +210,8 @@ static int made_log_prob_run(const flowcuda_made_spec* sp, const float* params, 
     if (it == 0 || !fuse_x) {
       int64_t total = L.MT * 128 * L.KS[0] * 4;
       int blocks = (int)((total + 255) / 256);
-      dense_tc_pack_x_kernel<<<blocks, 256, 0, s>>>(v, n, D, rev ? D - 1 : 0, rev ? -1 : 1, D, L.KS[0], ws + L.off_x);
-      FC_LAUNCH_CHECK("dense_tc_pack_x_kernel");
+      FC_CUDA(launch_chain(dense_tc_pack_x_kernel, dim3(blocks), dim3(256), 0, s, (const float*)v, n, D, rev ? D - 1 : 0,
+                           rev ? -1 : 1, D, L.KS[0], ws + L.off_x));
     }
     const uint8_t* aimg = ws + L.off_x;
     for (int i = 0; i < L.nlin; ++i) {
@@ -220,7 +221,7 @@ static int made_log_prob_run(const flowcuda_made_spec* sp, const float* params, 
       g.bias = lp + L.b_off[i];
       g.KS = L.KS[i];
       g.n_out = L.sizes[i + 1];
-      g.v = v; g.ldp = ldp; g.N = n; g.D = D; g.tp = 0; g.dstride = 1; g.ndims = D; g.dpt = 128; g.ppd = 2;
+      g.v = v; g.ldp = ldp + (size_t)it * n * 2 * L.tiles; g.N = n; g.D = D; g.tp = 0; g.dstride = 1; g.ndims = D; g.dpt = 128; g.ppd = 2;
       g.tiles = 2 * L.tiles; g.made = 1; g.rev = rev ? 1 : 0;
       for (int t = 0; t < L.NT[i] && t < kDtMaxKsTiles; ++t) g.ks_tile[t] = (unsigned char)made_ks_needed(L, i, t, rev);
       int rc;
@@ -238,17 +239,17 @@ static int made_log_prob_run(const flowcuda_made_spec* sp, const float* params, 
         }
         rc = dt2_launch_gemm<kEpiAffine, true>(g, dl, L.MT, L.tiles, s);
         if (rc) return rc;
-        dense_tc_ld_accum_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, s>>>(ldp, 2 * L.tiles, 2 * L.tiles, ld, n, it == 0);
-        FC_LAUNCH_CHECK("dense_tc_ld_accum_kernel");
       }
       if (rc) return rc;
     }
   }
-  if (out_u) FC_CUDA(cudaMemcpyAsync(out_u, v, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  (void)ld;
   if (out_lp || out_ld) {
-    dense_tc_finish_kernel<<<(int)((n * 32 + 255) / 256), 256, 0, s>>>(v, ld, n, D, with_base, sp->base, out_lp, out_ld);
-    FC_LAUNCH_CHECK("dense_tc_finish_kernel");
+    FC_CUDA(launch_chain(dense_tc_finish_kernel, dim3((unsigned)((n * 32 + 255) / 256)), dim3(256), 0, s, (const float*)v,
+                         (const float*)ldp, (int)sp->num_layers, 2 * L.tiles, 2 * L.tiles, n, D, with_base, (int)sp->base, out_lp,
+                         out_ld));
   }
+  if (out_u) FC_CUDA(cudaMemcpyAsync(out_u, v, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToDevice, s));
   return FLOWCUDA_OK;
 }
 
