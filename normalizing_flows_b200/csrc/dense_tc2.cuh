@@ -21,6 +21,8 @@
 // and (leader CTA of a pair) MMA issuer, then two epilogue groups alternating over the two 256-column TMEM
 // accumulators — the epilogues are dense_tc.cuh's (hidden / RQS / affine), unchanged: thread = sample row.
 #pragma once
+#include <stdlib.h>
+
 #include <cuda.h>  // CUtensorMap (types only; the encoder is fetched through the runtime, no -lcuda)
 
 #include "dense_tc.cuh"
@@ -465,17 +467,18 @@ static int dt2_launch_w(const DtGemm& g, const Dt2Launch& L, int64_t MT, int NT,
   return FLOWCUDA_OK;
 }
 
-// which kernel a launch takes: FLOWCUDA_DENSE_TC = "1cta" forces the round-1 single-CTA kernel, "pair" the 2-CTA
-// clusters; default: 4-CTA clusters (two pairs, multicast A) when the launch has at least two n tiles, pairs otherwise.
+// Which kernel a launch takes.  Default: the single-CTA kernel (dense_tc.cuh) — measured on B200 (profiles/r02/
+// gemm_modes_*.log, ncu_mnist_{1cta,pair}) the D=784 GEMMs were never operand-feed bound (L2 throughput 41 % with the
+// tensor pipe 68 % active; the spline epilogue and the launch-latency chain of the hidden Linears were the limits), and
+// pairing CTAs couples two epilogues to one MMA stream: the pair kernel runs the maf_mnist step in 1.12 ms, the 4-CTA
+// multicast clusters in 1.16 ms, the single-CTA kernel in 1.03 ms.  FLOWCUDA_DENSE_TC = "pair" / "quad" selects the
+// CTA-pair kernels (tests/test_gpu_tc.py runs the parity cases through both).
 static inline int dt2_mode() {
-  static int mode = -1;
-  if (mode < 0) {
-    const char* e = getenv("FLOWCUDA_DENSE_TC");
-    mode = 4;
-    if (e && e[0] == '1') mode = 1;
-    else if (e && e[0] == 'p') mode = 2;
-  }
-  return mode;
+  // read on every call (a getenv is nothing next to a launch) so that tests can switch kernels in-process
+  const char* e = getenv("FLOWCUDA_DENSE_TC");
+  if (e && e[0] == 'p') return 2;
+  if (e && e[0] == 'q') return 4;
+  return 1;
 }
 
 template <int EPI, bool INV>

@@ -130,6 +130,32 @@ def test_dense_coupling_bf16x3_parity(case, n):
     close(xsamp, O.coupling_flow_sample(ospec, params, x64).numpy(), tol=2e-4, what="sample")
 
 
+@pytest.mark.parametrize("mode", ["pair", "quad"])
+@pytest.mark.parametrize("case", ["rqs_d40_uniform", "affine_d300", "rqs_d50_wide"])
+def test_dense_coupling_cta_pair_kernels(case, mode, monkeypatch):
+    """The same flows through the CTA-pair GEMM (tcgen05 cta_group::2, tensor-map TMA; `quad`: 4-CTA clusters with the A
+    operand multicast) — csrc/dense_tc2.cuh; FLOWCUDA_DENSE_TC selects it per call."""
+    from normalizing_flows_b200 import _lib, ops
+
+    monkeypatch.setenv("FLOWCUDA_DENSE_TC", mode)
+    ospec, scale, xs = DENSE_TC[case]
+    params = O.init_coupling_params(ospec, seed=11, scale=scale)
+    flat = O.flatten_layers(params)
+    spec = _spec_pair(ops, ospec, precision=_lib.PRECISION_BF16X3)
+    n = 700  # three pair tiles, the last one ragged
+    gen = torch.Generator().manual_seed(n)
+    x = (torch.rand(n, ospec.event_dim, generator=gen, dtype=torch.float64) if xs is None
+         else torch.randn(n, ospec.event_dim, generator=gen, dtype=torch.float64) * xs).float()
+    lp, z, ld = ops.coupling_log_prob(spec, G(flat), x.cuda(), want_z=True, want_log_det=True)
+    zref, ldref = O.coupling_flow_to_base(ospec, params, x.double())
+    close(lp, O.coupling_flow_log_prob(ospec, params, x.double()).numpy(), tol=2e-4, what="log_prob", nonfinite="equal")
+    close(z, zref.numpy(), tol=2e-4, what="z")
+    close(ld, ldref.numpy(), tol=2e-4, what="log_det")
+    monkeypatch.delenv("FLOWCUDA_DENSE_TC")
+    lp1, _, _ = ops.coupling_log_prob(spec, G(flat), x.cuda())
+    assert (lp1 - lp).abs().max().item() <= 1e-5 * max(1.0, lp.abs().max().item())  # same arithmetic, other tiling
+
+
 def test_dense_coupling_bf16x3_mnist_shape():
     """maf_mnist.py:28-31 conditioner 784->512->512->512->19600, 8 bins, Uniform base (2 flow layers to
     bound the CPU oracle's time): |log_prob - float64 oracle| <= 1e-3 absolute (north_star)."""
