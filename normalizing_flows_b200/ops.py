@@ -13,6 +13,7 @@ from ._lib import CouplingSpec, check
 
 
 def _dev_check(*ts):
+    dev = None
     for t in ts:
         if t is None:
             continue
@@ -22,6 +23,30 @@ def _dev_check(*ts):
             raise _lib.FlowCudaError(f"flowcuda ops are float32; got {t.dtype}")
         if not t.is_contiguous():
             raise _lib.FlowCudaError("flowcuda ops need contiguous tensors")
+        if dev is None:
+            dev = t.device
+        elif t.device != dev:
+            raise _lib.FlowCudaError(f"flowcuda ops need all tensors on one device; got {dev} and {t.device}")
+
+
+def _on_tensor_device(fn):
+    """Run an op in the device context (and on the current stream) of its first CUDA tensor argument: the kernels launch
+    in the CURRENT context, which in a process driving several GPUs need not be the tensors' device."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapped(*args, **kwargs):
+        dev = None
+        for a in list(args) + list(kwargs.values()):
+            if isinstance(a, torch.Tensor) and a.is_cuda:
+                dev = a.device
+                break
+        if dev is None or dev.index is None or dev.index == torch.cuda.current_device():
+            return fn(*args, **kwargs)
+        with torch.cuda.device(dev):
+            return fn(*args, **kwargs)
+
+    return wrapped
 
 
 def _f32(t: torch.Tensor) -> torch.Tensor:
@@ -33,6 +58,7 @@ def _ptr(t: Optional[torch.Tensor]):
 
 
 def _stream():
+    # current stream of the current device; _dev_check has made the tensors' device current
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
@@ -45,6 +71,7 @@ def flip_mask_of(flips: Sequence[bool]) -> int:
 
 
 # ---------------------------------------------------------------------------- row #1
+@_on_tensor_device
 def realnvp_log_prob(params: torch.Tensor, n_layers: int, hidden: int, flip_mask: int, y: torch.Tensor,
                      want_z: bool = False):
     y = _f32(y)
@@ -57,6 +84,7 @@ def realnvp_log_prob(params: torch.Tensor, n_layers: int, hidden: int, flip_mask
     return (lp, z) if want_z else lp
 
 
+@_on_tensor_device
 def realnvp_sample(params: torch.Tensor, n_layers: int, hidden: int, flip_mask: int, z: torch.Tensor) -> torch.Tensor:
     z = _f32(z)
     _dev_check(params, z)
@@ -66,6 +94,7 @@ def realnvp_sample(params: torch.Tensor, n_layers: int, hidden: int, flip_mask: 
     return x
 
 
+@_on_tensor_device
 def realnvp_forward(layer_params: torch.Tensor, hidden: int, flip: bool, x: torch.Tensor) -> torch.Tensor:
     x = _f32(x)
     _dev_check(layer_params, x)
@@ -75,6 +104,7 @@ def realnvp_forward(layer_params: torch.Tensor, hidden: int, flip: bool, x: torc
     return y
 
 
+@_on_tensor_device
 def realnvp_inverse(layer_params: torch.Tensor, hidden: int, flip: bool, y: torch.Tensor):
     y = _f32(y)
     _dev_check(layer_params, y)
@@ -85,6 +115,7 @@ def realnvp_inverse(layer_params: torch.Tensor, hidden: int, flip: bool, y: torc
     return x, ls
 
 
+@_on_tensor_device
 def realnvp_nll_grad(params: torch.Tensor, n_layers: int, hidden: int, flip_mask: int, y: torch.Tensor,
                      lr: float = 0.0, params_out: Optional[torch.Tensor] = None,
                      workspace: Optional[torch.Tensor] = None):
@@ -105,6 +136,7 @@ def realnvp_nll_grad(params: torch.Tensor, n_layers: int, hidden: int, flip_mask
 
 
 # ---------------------------------------------------------------------------- row #5
+@_on_tensor_device
 def bernstein_constrain_thetas(theta_raw: torch.Tensor) -> torch.Tensor:
     t = _f32(theta_raw)
     _dev_check(t)
@@ -115,6 +147,7 @@ def bernstein_constrain_thetas(theta_raw: torch.Tensor) -> torch.Tensor:
     return out
 
 
+@_on_tensor_device
 def bernstein_forward_and_log_det(theta: torch.Tensor, x: torch.Tensor, want_y: bool = True, want_ld: bool = True):
     """theta [M] (shared) or [*x.shape, M] (one row per element); x any shape."""
     theta, x = _f32(theta), _f32(x)
@@ -133,6 +166,7 @@ def bernstein_forward_and_log_det(theta: torch.Tensor, x: torch.Tensor, want_y: 
     return y, ld
 
 
+@_on_tensor_device
 def bernstein_forward_and_log_det_vjp(theta: torch.Tensor, x: torch.Tensor, ybar=None, ldbar=None,
                                       want_xbar: bool = True, want_thetabar: bool = True):
     """Reverse mode of bernstein_forward_and_log_det (csrc/bernstein_grad.cu): cotangents ybar / ldbar (shape of
@@ -161,6 +195,7 @@ def bernstein_forward_and_log_det_vjp(theta: torch.Tensor, x: torch.Tensor, ybar
     return xbar, tbar
 
 
+@_on_tensor_device
 def bernstein_constrain_thetas_vjp(theta_raw: torch.Tensor, thetabar: torch.Tensor) -> torch.Tensor:
     t, tb = _f32(theta_raw), _f32(thetabar)
     _dev_check(t, tb)
@@ -173,6 +208,7 @@ def bernstein_constrain_thetas_vjp(theta_raw: torch.Tensor, thetabar: torch.Tens
     return out
 
 
+@_on_tensor_device
 def bernstein_inverse(theta: torch.Tensor, y: torch.Tensor, n_points: int = 200) -> torch.Tensor:
     """theta [E,M] (or [M] with E=1), y [N,E] -> x [E,N] (the reference's vmap output layout)."""
     theta, y = _f32(theta), _f32(y)
@@ -190,6 +226,7 @@ def bernstein_inverse(theta: torch.Tensor, y: torch.Tensor, n_points: int = 200)
     return x
 
 
+@_on_tensor_device
 def bernstein_flow_log_prob(theta: torch.Tensor, scal: torch.Tensor, x: torch.Tensor) -> torch.Tensor:
     theta, scal, x = _f32(theta), _f32(scal), _f32(x)
     _dev_check(theta, scal, x)
@@ -244,6 +281,7 @@ class PackedWeights:
         return self.workspace.numel() * self.workspace.element_size()
 
 
+@_on_tensor_device
 def coupling_pack_weights(spec: CouplingSpec, params: torch.Tensor, max_batch: int) -> PackedWeights:
     _dev_check(params)
     lib = _lib.load()
@@ -254,6 +292,7 @@ def coupling_pack_weights(spec: CouplingSpec, params: torch.Tensor, max_batch: i
     return PackedWeights(ws, max_batch, "coupling")
 
 
+@_on_tensor_device
 def made_pack_weights(spec: "_lib.MadeSpec", params: torch.Tensor, max_batch: int) -> PackedWeights:
     _dev_check(params)
     lib = _lib.load()
@@ -274,6 +313,7 @@ def _use_packed(packed: Optional[PackedWeights], kind: str, n: int) -> bool:
     return True
 
 
+@_on_tensor_device
 def coupling_log_prob(spec: CouplingSpec, params: torch.Tensor, x: torch.Tensor, want_z: bool = False,
                       want_log_det: bool = False, want_log_prob: bool = True, layers: Optional[Tuple[int, int]] = None,
                       with_base: bool = True, packed: Optional[PackedWeights] = None):
@@ -297,6 +337,7 @@ def coupling_log_prob(spec: CouplingSpec, params: torch.Tensor, x: torch.Tensor,
     return lp, z, ld
 
 
+@_on_tensor_device
 def coupling_sample(spec: CouplingSpec, params: torch.Tensor, z: torch.Tensor, want_log_det: bool = False,
                     layers: Optional[Tuple[int, int]] = None, packed: Optional[PackedWeights] = None):
     """Base -> data direction (Transformed.sample with the noise given).  Returns (x, log_det)."""
@@ -317,6 +358,7 @@ def coupling_sample(spec: CouplingSpec, params: torch.Tensor, z: torch.Tensor, w
     return x, ld
 
 
+@_on_tensor_device
 def coupling_nll_grad(spec: CouplingSpec, params: torch.Tensor, x: torch.Tensor):
     """(loss[1], grad[param_count]) of -mean(log_prob(x)) — jax.value_and_grad(loss_fn) of the toy scripts."""
     x = _f32(x).reshape(x.shape[0], -1)
@@ -354,6 +396,7 @@ def made_param_count(spec: _lib.MadeSpec) -> int:
     return n
 
 
+@_on_tensor_device
 def made_log_prob(spec: _lib.MadeSpec, params: torch.Tensor, x: torch.Tensor, want_u: bool = False,
                   want_log_det: bool = False, want_log_prob: bool = True, with_base: bool = True,
                   workspace: Optional[torch.Tensor] = None, packed: Optional[PackedWeights] = None):
@@ -379,6 +422,7 @@ def made_log_prob(spec: _lib.MadeSpec, params: torch.Tensor, x: torch.Tensor, wa
     return lp, u, ld
 
 
+@_on_tensor_device
 def made_sample(spec: _lib.MadeSpec, params: torch.Tensor, z: torch.Tensor) -> torch.Tensor:
     """MAF sampling with the base noise given (base -> data), sequential over dimensions."""
     z = _f32(z).reshape(z.shape[0], spec.event_dim)
@@ -389,6 +433,7 @@ def made_sample(spec: _lib.MadeSpec, params: torch.Tensor, z: torch.Tensor) -> t
     return x
 
 
+@_on_tensor_device
 def made_nll_grad(spec: _lib.MadeSpec, params: torch.Tensor, x: torch.Tensor, workspace: Optional[torch.Tensor] = None):
     """(loss[1], grad[param_count]) of -mean(log_prob(x)) for the MADE flow — jax.value_and_grad(loss_fn)."""
     x = _f32(x).reshape(x.shape[0], spec.event_dim)
@@ -408,6 +453,7 @@ def made_nll_grad(spec: _lib.MadeSpec, params: torch.Tensor, x: torch.Tensor, wo
 
 
 # ---------------------------------------------------------------------------- rows #7, #9
+@_on_tensor_device
 def sum_scaled(v: torch.Tensor, scale: float) -> torch.Tensor:
     v = _f32(v).reshape(-1)
     _dev_check(v)
@@ -417,16 +463,19 @@ def sum_scaled(v: torch.Tensor, scale: float) -> torch.Tensor:
     return out
 
 
+@_on_tensor_device
 def nll(log_prob: torch.Tensor) -> torch.Tensor:
     """-jnp.mean(log_prob) (real_nvp.py:293)."""
     return sum_scaled(log_prob, -1.0 / max(1, log_prob.numel()))
 
 
+@_on_tensor_device
 def sgd_step(p: torch.Tensor, g: torch.Tensor, lr: float, grad_scale: float = 1.0) -> None:
     _dev_check(p, g)
     check(_lib.load().flowcuda_sgd_step(_ptr(p), _ptr(g), p.numel(), float(lr), float(grad_scale), _stream()), "sgd_step")
 
 
+@_on_tensor_device
 def adam_step(p: torch.Tensor, g: torch.Tensor, m: torch.Tensor, v: torch.Tensor, step: int, lr: float,
               b1: float = 0.9, b2: float = 0.999, eps: float = 1e-8, grad_scale: float = 1.0) -> None:
     _dev_check(p, g, m, v)
@@ -453,6 +502,7 @@ def density_sample(kind, seed: int, n: int, offset: int = 0, num_blobs: int = 8,
     return out
 
 
+@_on_tensor_device
 def dequantize_u8(bytes_: torch.Tensor, seed: int, offset: int = 0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """(uint8 + U[0,1)) / 256 on the device (prepare_data, src/maf_mnist.py:101-106)."""
     if not bytes_.is_cuda or bytes_.dtype != torch.uint8 or not bytes_.is_contiguous():
@@ -478,6 +528,7 @@ def base_noise(shape, seed: int, uniform: bool = False, offset: int = 0, device=
     return out
 
 
+@_on_tensor_device
 def rotate2d(x: torch.Tensor, cos_theta: float, sin_theta: float, inverse: bool = False) -> torch.Tensor:
     """y = x @ R (R = [[c,-s],[s,c]]^T) or x @ R^T, x[...,2] (src/rotation_flow.py:23-27)."""
     if x.shape[-1] != 2:
@@ -490,7 +541,136 @@ def rotate2d(x: torch.Tensor, cos_theta: float, sin_theta: float, inverse: bool 
     return y
 
 
+# ---------------------------------------------------------------------------- elementwise bijectors / base densities
+def _rows_inner(x_shape, p_shape):
+    """Broadcast pattern of parameters of shape `p_shape` against data of shape `x_shape` as (rows, inner) of the
+    kernels' index rule row = (i / inner) % rows; None when the pattern is neither leading- nor trailing-broadcast."""
+    xs, ps = tuple(x_shape), tuple(p_shape)
+    pn = 1
+    for d in ps:
+        pn *= d
+    if pn == 1:
+        return 1, 1
+    ps = (1,) * (len(xs) - len(ps)) + ps if len(ps) <= len(xs) else None
+    if ps is None:
+        return None
+    # strip leading 1s (leading broadcast: rows repeat) and trailing 1s (trailing broadcast: `inner` elements share a row)
+    lead = 0
+    while lead < len(ps) and ps[lead] == 1:
+        lead += 1
+    trail = len(ps)
+    while trail > lead and ps[trail - 1] == 1:
+        trail -= 1
+    if ps[lead:trail] != xs[lead:trail]:
+        return None
+    inner = 1
+    for d in xs[trail:]:
+        inner *= d
+    return pn, inner
+
+
+def _bcast_params(x, *ps):
+    """(rows, inner, params...) with the parameters contiguous float32 on x's device; falls back to materialising the
+    broadcast when the pattern is irregular."""
+    ps = [None if p is None else _f32(torch.as_tensor(p)).to(x.device) for p in ps]
+    live = [p for p in ps if p is not None]
+    if not live:
+        return 1, 1, ps
+    shape = torch.broadcast_shapes(*[p.shape for p in live])
+    ri = _rows_inner(x.shape, shape)
+    if ri is None:
+        shape = torch.broadcast_shapes(shape, x.shape)
+        ri = (int(x.numel()), 1) if tuple(shape) == tuple(x.shape) else None
+        if ri is None:
+            raise ValueError(f"parameters of shape {tuple(shape)} do not broadcast against data of shape {tuple(x.shape)}")
+    ps = [None if p is None else p.expand(shape).contiguous() for p in ps]
+    return ri[0], ri[1], ps
+
+
+@_on_tensor_device
+def affine_elementwise(x, shift=None, scale=None, log_scale=None, inverse=False, want_y=True, want_ld=True):
+    """distrax.ScalarAffine / tfb.Scale / tfb.Shift: (y, log_det) elementwise, parameters broadcast."""
+    x = _f32(x)
+    _dev_check(x)
+    sc, is_log = (log_scale, 1) if log_scale is not None else (scale, 0)
+    rows, inner, (sh, sc) = _bcast_params(x, shift, sc)
+    y = torch.empty_like(x) if want_y else None
+    ld = torch.empty_like(x) if want_ld else None
+    check(_lib.load().flowcuda_affine_elementwise(_ptr(x), _ptr(sh), _ptr(sc), is_log, int(inverse), _ptr(y), _ptr(ld), x.numel(),
+                                                  rows, inner, _stream()), "affine_elementwise")
+    return y, ld
+
+
+def add_elementwise(a, b):
+    """a + b on the device (log-det bookkeeping of Chain / Transformed): the affine kernel with shift = b."""
+    a = _f32(a)
+    b = _f32(torch.as_tensor(b)).to(a.device)
+    if b.shape != a.shape:
+        b = b.expand(a.shape).contiguous()
+    return affine_elementwise(a, shift=b, want_ld=False)[0]
+
+
+@_on_tensor_device
+def softclip_elementwise(x, low, high, hinge_softness, inverse=False):
+    x = _f32(x)
+    _dev_check(x)
+    y, ld = torch.empty_like(x), torch.empty_like(x)
+    check(_lib.load().flowcuda_softclip_elementwise(_ptr(x), float(low), float(high), float(hinge_softness), int(inverse), _ptr(y),
+                                                    _ptr(ld), x.numel(), _stream()), "softclip_elementwise")
+    return y, ld
+
+
+@_on_tensor_device
+def rqs_elementwise(x, params, range_min, range_max, inverse=False):
+    """distrax.RationalQuadraticSpline(params[..., 3K+1], range_min, range_max) applied to x[...]."""
+    x = _f32(x)
+    _dev_check(x)
+    params = _f32(torch.as_tensor(params)).to(x.device)
+    P = params.shape[-1]
+    ri = _rows_inner(x.shape, params.shape[:-1])
+    if ri is None:
+        shape = torch.broadcast_shapes(params.shape[:-1], x.shape)
+        if tuple(shape) != tuple(x.shape):
+            raise ValueError(f"spline parameters {tuple(params.shape)} do not broadcast against data {tuple(x.shape)}")
+        params = params.expand(*shape, P).contiguous()
+        ri = (int(x.numel()), 1)
+    y, ld = torch.empty_like(x), torch.empty_like(x)
+    check(_lib.load().flowcuda_rqs_elementwise(_ptr(x), _ptr(params), (P - 1) // 3, float(range_min), float(range_max), int(inverse),
+                                               _ptr(y), _ptr(ld), x.numel(), ri[0], ri[1], _stream()), "rqs_elementwise")
+    return y, ld
+
+
+@_on_tensor_device
+def base_log_prob(x, a=None, b=None, uniform=False):
+    """Normal(loc=a, scale=b).log_prob(x) / Uniform(low=a, high=b).log_prob(x), elementwise."""
+    x = _f32(x)
+    _dev_check(x)
+    rows, inner, (a, b) = _bcast_params(x, a, b)
+    out = torch.empty_like(x)
+    check(_lib.load().flowcuda_base_log_prob(_ptr(x), _ptr(a), _ptr(b), int(uniform), _ptr(out), x.numel(), rows, inner, _stream()),
+          "base_log_prob")
+    return out
+
+
+@_on_tensor_device
+def sum_last(x, ndims):
+    """Sum over the last `ndims` axes in a fixed order (distrax.Independent / Block)."""
+    if ndims == 0:
+        return x
+    x = _f32(x)
+    _dev_check(x)
+    batch = x.shape[: x.dim() - ndims]
+    cols = 1
+    for d in x.shape[x.dim() - ndims:]:
+        cols *= d
+    rows = x.numel() // max(cols, 1)
+    out = torch.empty(rows, device=x.device, dtype=torch.float32)
+    check(_lib.load().flowcuda_sum_last(_ptr(x), _ptr(out), rows, cols, _stream()), "sum_last")
+    return out.reshape(batch)
+
+
 # ---------------------------------------------------------------------------- diagnostics
+@_on_tensor_device
 def selftest_umma(a: torch.Tensor, w: torch.Tensor, mode: int, want_unaligned: bool = False):
     """d[128,n] = a[128,k] @ w[k,n] through the tcgen05 primitives (mode 0 tf32x3, 1 bf16x3, 2 tf32, 3 bf16)."""
     a, w = _f32(a), _f32(w)
