@@ -61,8 +61,19 @@ def test_chain_and_masked_coupling_protocol():
     loose._fused = None
     z2, ld2 = loose.forward_and_log_det(x.cuda())
     assert scaled_err(z2, z) < 1e-5 and scaled_err(ld2, ld) < 1e-5
-    with pytest.raises(TypeError):
-        distrax.MaskedCoupling(mask=torch.tensor([False, True]), conditioner=lambda x: x, bijector=distrax.scalar_affine_fn)
+    # a Python conditioner callable + the reference's bijector_fn: composed step by step (conditioner call, bijector_fn(params),
+    # the inner bijector's elementwise kernel, masking) — distrax.MaskedCoupling semantics, SURVEY A.3
+    cond = lambda mx: torch.stack([0.3 * mx.sum(-1), 0.1 * mx.sum(-1)], -1)
+    mc = distrax.MaskedCoupling(mask=torch.tensor([False, True]), conditioner=cond, bijector=distrax.scalar_affine_fn)
+    xg = x.cuda()
+    yg, ldg = mc.forward_and_log_det(xg)
+    shift, ls = 0.3 * x[:, 1].double(), 0.1 * x[:, 1].double()
+    yref = torch.stack([x[:, 0].double() * torch.exp(ls) + shift, x[:, 1].double()], -1)
+    assert scaled_err(yg, yref) < 1e-5 and scaled_err(ldg, ls) < 1e-6
+    xb, ldb = mc.inverse_and_log_det(yg)
+    assert scaled_err(xb, x) < 1e-5 and scaled_err(ldb, -ls) < 1e-6
+    with pytest.raises(ValueError):
+        distrax.MaskedCoupling(mask=torch.tensor([0, 1]), conditioner=cond, bijector=distrax.scalar_affine_fn)  # mask must be bool
 
 
 def test_real_nvp_functional_api():
