@@ -224,6 +224,135 @@ bern_shared_kernel(const float* __restrict__ theta, int M, const float* __restri
   }
 }
 
+// Small orders (M <= 16: the reference's own M = 9, bflow.py:24, and M = 8, maf_mwe.py:103) — HBM-bound work that the
+// general kernel above ran latency-bound: its eight-coefficient folding carries 94 registers (two CTAs per SM, 22 % of
+// the warps) to save FMAs that at these orders are not the limit (ncu r01: M = 9 at 31 % of the HBM roof).  Here the
+// order is a template parameter, the plain recurrences  y <- y·v + a_j·u^j  (j <= n) and  J <- J·v + d_j·u^j  (j <= n-1:
+// no padding factor to divide out) are fully unrolled on packed pairs, and the kernel keeps < 52 registers so that
+// five CTAs (40 warps) per SM hide the load latency; 37 packed operations per element pair at M = 9.
+template <int M, int MODE>
+__global__ void __launch_bounds__(kBernThreads, 5)
+bern_small_kernel(const float* __restrict__ theta, const float* __restrict__ scal, const float* __restrict__ x,
+                  float* __restrict__ out_y, float* __restrict__ out_ld, int64_t n) {
+  constexpr int deg = M - 1;
+  __shared__ __align__(16) float2 ta[M], td[M];
+  if (threadIdx.x < M) {
+    const int j = threadIdx.x;
+    const float a = (float)((double)theta[j] * bern_binom(deg, j));
+    float d = 0.f;
+    if (j < deg) d = (float)((double)deg * ((double)theta[j + 1] - (double)theta[j]) * bern_binom(deg - 1, j));
+    ta[j] = make_float2(a, a);
+    td[j] = make_float2(d, d);
+  }
+  __syncthreads();
+  float s1 = 1.f, b1 = 0.f, s4 = 1.f, b4 = 0.f, lconst = 0.f, kk = 1.f, logk = 0.f;
+  if (MODE == 1) {
+    s1 = softplus_f(scal[0]);
+    b1 = scal[1];
+    s4 = softplus_f(scal[2]);
+    b4 = scal[3];
+    kk = 1.f / (1.5f * softplus_f(1.f / 1.5f));
+    logk = logf(kk);
+    lconst = logf(s1) + logf(s4) - kHalfLog2Pi;
+  }
+  const f2_t one = f2_splat(1.f), neg1 = f2_splat(-1.f);
+  const int64_t nquads = n >> 2;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q < nquads; q += stride) {
+    const float4 xv = ld_stream_f4(reinterpret_cast<const float4*>(x) + q);
+    float xs[4] = {xv.x, xv.y, xv.z, xv.w};
+    float pre_ld[4] = {0.f, 0.f, 0.f, 0.f};
+    if (MODE == 1) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) softclip01(s1 * (xs[i] + b1), 1.5f, kk, logk, xs[i], pre_ld[i]);
+    }
+    f2_t u[2] = {f2_pack(bern_clip(xs[0]), bern_clip(xs[1])), f2_pack(bern_clip(xs[2]), bern_clip(xs[3]))};
+    f2_t v[2], ry[2], rj[2], pw[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      v[h] = f2_fma(u[h], neg1, one);
+      ry[h] = *reinterpret_cast<const f2_t*>(&ta[0]);
+      rj[h] = *reinterpret_cast<const f2_t*>(&td[0]);
+      pw[h] = u[h];
+    }
+#pragma unroll
+    for (int j = 1; j <= deg; ++j) {
+      const f2_t a = *reinterpret_cast<const f2_t*>(&ta[j]), d = *reinterpret_cast<const f2_t*>(&td[j]);
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        ry[h] = f2_fma(ry[h], v[h], f2_mul(a, pw[h]));
+        if (j < deg) {
+          rj[h] = f2_fma(rj[h], v[h], f2_mul(d, pw[h]));
+          pw[h] = f2_mul(pw[h], u[h]);
+        }
+      }
+    }
+    float ys[4], jj[4];
+    f2_unpack(ry[0], ys[0], ys[1]);
+    f2_unpack(ry[1], ys[2], ys[3]);
+    f2_unpack(rj[0], jj[0], jj[1]);
+    f2_unpack(rj[1], jj[2], jj[3]);
+    const float ld[4] = {__logf(jj[0]), __logf(jj[1]), __logf(jj[2]), __logf(jj[3])};
+    if (MODE == 0) {
+      if (out_y) st_stream_f4(reinterpret_cast<float4*>(out_y) + q, make_float4(ys[0], ys[1], ys[2], ys[3]));
+      if (out_ld) st_stream_f4(reinterpret_cast<float4*>(out_ld) + q, make_float4(ld[0], ld[1], ld[2], ld[3]));
+    } else {
+      float lp[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float z = s4 * (ys[i] + b4);
+        lp[i] = fmaf(-0.5f * z, z, lconst + pre_ld[i] + ld[i]);
+      }
+      st_stream_f4(reinterpret_cast<float4*>(out_ld) + q, make_float4(lp[0], lp[1], lp[2], lp[3]));
+    }
+  }
+  // tail (n % 4 elements), scalar
+  const int64_t t = (nquads << 2) + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n) {
+    float xi = x[t], pl = 0.f;
+    if (MODE == 1) softclip01(s1 * (xi + b1), 1.5f, kk, logk, xi, pl);
+    const float uu = bern_clip(xi), vv = 1.f - uu;
+    float y = ta[0].x, J = td[0].x, p = uu;
+#pragma unroll
+    for (int j = 1; j <= deg; ++j) {
+      y = fmaf(y, vv, ta[j].x * p);
+      if (j < deg) {
+        J = fmaf(J, vv, td[j].x * p);
+        p *= uu;
+      }
+    }
+    if (MODE == 0) {
+      if (out_y) out_y[t] = y;
+      if (out_ld) out_ld[t] = logf(J);
+    } else {
+      const float z = s4 * (y + b4);
+      out_ld[t] = fmaf(-0.5f * z, z, lconst + pl + logf(J));
+    }
+  }
+}
+
+template <int MODE>
+static int bern_small_launch(int M, const float* theta, const float* scal, const float* x, float* y, float* ld, int64_t n,
+                             cudaStream_t s) {
+#define FC_BERN_CASE(K)                                                                                        \
+  case K: {                                                                                                    \
+    const int grid = grid_resident(bern_small_kernel<K, MODE>, kBernThreads, 0, (n + 3) / 4, kBernThreads);    \
+    bern_small_kernel<K, MODE><<<grid, kBernThreads, 0, s>>>(theta, scal, x, y, ld, n);                        \
+    break;                                                                                                     \
+  }
+  switch (M) {
+    FC_BERN_CASE(2) FC_BERN_CASE(3) FC_BERN_CASE(4) FC_BERN_CASE(5) FC_BERN_CASE(6) FC_BERN_CASE(7) FC_BERN_CASE(8)
+    FC_BERN_CASE(9) FC_BERN_CASE(10) FC_BERN_CASE(11) FC_BERN_CASE(12) FC_BERN_CASE(13) FC_BERN_CASE(14) FC_BERN_CASE(15)
+    FC_BERN_CASE(16)
+    default:
+      return 1;  // not a small order
+  }
+#undef FC_BERN_CASE
+  FC_LAUNCH_CHECK("bern_small_kernel");
+  return FLOWCUDA_OK;
+}
+constexpr int kBernSmallMax = 16;
+
 // Per-element theta rows (maf_mwe.py:103-107): theta[n, M], x[n].  Binomials are uniform.
 __global__ void __launch_bounds__(kBernThreads)
 bern_rows_kernel(const float* __restrict__ theta, int M, int64_t theta_stride, const float* __restrict__ x,
@@ -351,6 +480,7 @@ int flowcuda_bernstein_forward_and_log_det(const float* theta, int order, int64_
   cudaStream_t s = (cudaStream_t)stream;
   if (theta_stride == 0) {
     FC_REQUIRE((((uintptr_t)x | (uintptr_t)y | (uintptr_t)log_det) & 15) == 0, "bernstein_forward: buffers must be 16-byte aligned");
+    if (order <= kBernSmallMax) return bern_small_launch<0>(order, theta, nullptr, x, y, log_det, n, s);
     int grid = grid_resident(bern_shared_kernel<0>, kBernThreads, 0, (n + 3) / 4, kBernThreads);
     bern_shared_kernel<0><<<grid, kBernThreads, 0, s>>>(theta, order, nullptr, x, y, log_det, n);
   } else {
@@ -368,6 +498,7 @@ int flowcuda_bernstein_flow_log_prob(const float* theta, int order, const float*
   FC_REQUIRE((((uintptr_t)x | (uintptr_t)log_prob) & 15) == 0, "bernstein_flow_log_prob: buffers must be 16-byte aligned");
   FC_REQUIRE(n >= 0, "bernstein_flow_log_prob: negative n");
   if (n == 0) return FLOWCUDA_OK;
+  if (order <= kBernSmallMax) return bern_small_launch<1>(order, theta, scal, x, nullptr, log_prob, n, (cudaStream_t)stream);
   int grid = grid_resident(bern_shared_kernel<1>, kBernThreads, 0, (n + 3) / 4, kBernThreads);
   bern_shared_kernel<1><<<grid, kBernThreads, 0, (cudaStream_t)stream>>>(theta, order, scal, x, nullptr, log_prob, n);
   FC_LAUNCH_CHECK("bern_shared_kernel<1>");
