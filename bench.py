@@ -408,6 +408,13 @@ class Bernstein(Workload):
     flops_per_sample = 2 * 32 + 10
     bound = "hbm"
     cpu_sample = 1 << 20
+    # order 32: two polynomials x 32 coefficients at 1.25 packed operations per coefficient + setup = ~83 FP32 operations per
+    # 12-byte element; ncu (profiles/r01/final/ncu_bern_summary.txt) puts the sustained packed-FMA rate of this mix at
+    # ~76 operations/cycle/SM => 65 us per 2^24 elements against the 31 us HBM floor
+    ceiling = 0.47
+    ceiling_why = ("FMA-bound, not HBM-bound, at order 32: ~83 FP32 operations per 12-byte element at the measured ~76 "
+                   "operations/cycle/SM is 65 us per 2^24 elements against the 31 us HBM floor; the reference's own order "
+                   "(M = 9, bernstein_m9) IS HBM-bound and runs at 0.68 of the roof")
 
     def make_inputs(self, gen, n):
         return torch.rand(n, generator=gen)
@@ -434,6 +441,8 @@ class Bernstein9(Bernstein):
     desc = "configs[2] at the reference's own order: BernsteinBijector forward_and_log_det, M=9 shared theta (src/bflow.py:24); U(0,1), 2^24 elements/GPU"
     order = 9
     flops_per_sample = 2 * 9 + 10
+    ceiling = 1.0
+    ceiling_why = ""
 
 
 WORKLOADS = {w.name: w for w in (MafMnist, RealNvpToy, MafToy, MafMade, Deep16Nvp, Deep16Made, RealNvpHand, Bernstein, Bernstein9)}
