@@ -184,7 +184,11 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
     const int vis = (l & 1) ? 0 : 1, tp = 1 - vis;
     const int ndims = (D - tp + 1) / 2, nvis = (D - vis + 1) / 2;
     const float* lp = params + L.per_layer * l;
-    {
+    // the first layer's activation image comes from the state; every later one is written by the previous layer's
+    // transform epilogue (its transformed dims are this layer's visible dims).  Odd event sizes: the two parities
+    // differ by one dim, whose column the epilogue never writes - keep the packing pass there.
+    const bool fuse_x = (D % 2) == 0;
+    if (it == 0 || !fuse_x) {
       int64_t total = L.MT * 128 * L.KS[0] * 4;
       int blocks = (int)((total + 255) / 256);
       FC_CUDA(launch_chain(dense_tc_pack_x_kernel, dim3(blocks), dim3(256), 0, s, (const float*)v, n, D, vis, 2, nvis, L.KS[0],
@@ -211,6 +215,11 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
         aimg = g.out_img;
       } else {
         const int used = (ndims + L.dpt - 1) / L.dpt;
+        if (fuse_x && it + 1 < nl) {
+          g.out_img = ws + L.off_x;
+          g.out_KS = L.KS[0];
+          g.next_rev = 0;
+        }
         if (sp->transform == FLOWCUDA_TRANSFORM_RQS)
           rc = inverse ? dt2_launch_gemm<kEpiRqs8, true>(g, dl, L.MT, used, s) : dt2_launch_gemm<kEpiRqs8, false>(g, dl, L.MT, used, s);
         else

@@ -232,6 +232,7 @@ __device__ __forceinline__ void dt_epilogue(const DtGemm& a, int mt, int nt, uin
           }
 #pragma unroll
           for (int q = 0; q < 2; ++q) {
+            if (ck + q < 0 || ck + q >= a.out_KS * 4) continue;  // beyond the next Linear's K range (its padding stays zero)
             uint8_t* st = og + (int64_t)((ck + q) >> 2) * 2 * kDtABytes + tc::img_off(128, row, (ck + q) & 3);
             *reinterpret_cast<uint4*>(st) = make_uint4(h[4 * q], h[4 * q + 1], h[4 * q + 2], h[4 * q + 3]);
             *reinterpret_cast<uint4*>(st + kDtABytes) = make_uint4(l[4 * q], l[4 * q + 1], l[4 * q + 2], l[4 * q + 3]);
@@ -319,6 +320,21 @@ __device__ __forceinline__ void dt_epilogue_rqs_tile(const DtGemm& a, int mt, in
       if (two) {
         a.v[grow * a.D + a.tp + a.dstride * dim1] = nv[1];
         ldsum[1] += l2[1];
+      }
+      if (a.out_img != nullptr) {
+        // the dims this layer transforms are exactly the dims the NEXT layer's conditioner sees (the masks alternate):
+        // write the new values straight into its activation image (K index = dim index, bf16 hi/lo), so that no
+        // packing pass re-reads v between the layers
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          if (u == 1 && !two) break;
+          const int j = u ? dim1 : dim0;
+          const __nv_bfloat16 h = __float2bfloat16_rn(nv[u]);
+          const __nv_bfloat16 l = __float2bfloat16_rn(nv[u] - __bfloat162float(h));
+          uint8_t* st = a.out_img + ((int64_t)mt * a.out_KS + (j >> 5)) * 2 * kDtABytes + tc::img_off(128, row, (j >> 3) & 3) + (j & 7) * 2;
+          *reinterpret_cast<__nv_bfloat16*>(st) = h;
+          *reinterpret_cast<__nv_bfloat16*>(st + kDtABytes) = l;
+        }
       }
     }
 #pragma unroll
