@@ -121,8 +121,8 @@ static bool dt_layout(const flowcuda_coupling_spec* sp, int64_t n, DtLayout& L) 
   }
   L.off_v = off; off = dt_al256(off + (size_t)n * D * 4);
   L.off_ld = off; off = dt_al256(off + (size_t)n * 4);
-  // two log-det partials per (row, tile), one slab per flow layer (summed once, by the finish kernel)
-  L.off_ldp = off; off = dt_al256(off + (size_t)sp->num_layers * n * L.tiles * 2 * 4);
+  // four log-det partials per (row, tile) — one per 64-column quarter — and one slab per flow layer (summed once, by the finish kernel)
+  L.off_ldp = off; off = dt_al256(off + (size_t)sp->num_layers * n * L.tiles * 4 * 4);
   L.off_x = off; off = dt_al256(off + (size_t)L.MT * L.KS[0] * 2 * kDtABytes);
   int ksh = 1;
   for (int i = 1; i < L.nlin; ++i) ksh = L.KS[i] > ksh ? L.KS[i] : ksh;
@@ -177,7 +177,7 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
   const int nl = layer_end - layer_begin;
   // the finish kernel sums every slot of the processed layers' slabs; tiles a layer does not use (odd event sizes: the
   // two parities differ by one dim) must read as zero
-  if (nl > 0) FC_CUDA(cudaMemsetAsync(ldp, 0, (size_t)nl * n * 2 * L.tiles * sizeof(float), s));
+  if (nl > 0) FC_CUDA(cudaMemsetAsync(ldp, 0, (size_t)nl * n * 4 * L.tiles * sizeof(float), s));
   int used2 = 0;
   for (int it = 0; it < nl; ++it) {
     const int l = inverse ? layer_begin + it : layer_end - 1 - it;
@@ -203,8 +203,8 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
       g.KS = L.KS[i];
       g.n_out = L.sizes[i + 1];
       g.out_img = nullptr; g.out_KS = 0;
-      g.v = v; g.ldp = ldp + (size_t)it * n * 2 * L.tiles; g.N = n; g.D = D; g.tp = tp; g.dstride = 2; g.ndims = ndims; g.dpt = L.dpt; g.ppd = L.ppd;
-      g.tiles = 2 * L.tiles; g.lo = sp->range_min; g.hi = sp->range_max;
+      g.v = v; g.ldp = ldp + (size_t)it * n * 4 * L.tiles; g.N = n; g.D = D; g.tp = tp; g.dstride = 2; g.ndims = ndims; g.dpt = L.dpt; g.ppd = L.ppd;
+      g.tiles = 4 * L.tiles; g.lo = sp->range_min; g.hi = sp->range_max;
       for (int i = 0; i < 9; ++i) g.koff[i] = sp->range_min + (float)i * kRqsMinBin;
       int rc;
       const Dt2Launch dl = {L.MT, (int64_t)sp->num_layers * L.NT[i], (int64_t)l * L.NT[i]};
@@ -225,7 +225,7 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
         else
           rc = inverse ? dt2_launch_gemm<kEpiAffine, true>(g, dl, L.MT, used, s) : dt2_launch_gemm<kEpiAffine, false>(g, dl, L.MT, used, s);
         if (rc) return rc;
-        used2 = 2 * L.tiles;
+        used2 = 4 * L.tiles;
       }
       if (rc) return rc;
     }
@@ -233,7 +233,7 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
   (void)ld;
   if (out_lp || out_ld) {
     FC_CUDA(launch_chain(dense_tc_finish_kernel, dim3((unsigned)((n * 32 + 255) / 256)), dim3(256), 0, s, (const float*)v,
-                         (const float*)ldp, nl, 2 * L.tiles, used2, n, D, with_base, (int)sp->base, out_lp, out_ld));
+                         (const float*)ldp, nl, 4 * L.tiles, used2, n, D, with_base, (int)sp->base, out_lp, out_ld));
   }
   if (out_v) FC_CUDA(cudaMemcpyAsync(out_v, v, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToDevice, s));
   return FLOWCUDA_OK;

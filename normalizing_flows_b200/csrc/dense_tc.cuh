@@ -100,6 +100,18 @@ __host__ __device__ __forceinline__ int dt_dim_to_col(int di, int dpt, int ppd) 
   return ((di / dph) << 7) + (di % dph) * ppd;
 }
 
+// accumulator columns n tile `nt` really needs (a multiple of 16, the MMA N granularity): all 256 except for the last,
+// ragged tile of a transform Linear, whose unused columns hold zero weights — a narrower MMA skips them
+__device__ __forceinline__ int dt_tile_cols(const DtGemm& a, int nt) {
+  if (a.dpt <= 0) return kDtBN;
+  const int vd = a.ndims - nt * a.dpt;  // valid dims of this tile
+  if (vd >= a.dpt) return kDtBN;
+  const int dph = a.dpt >> 1;
+  const int cols = vd <= dph ? vd * a.ppd : 128 + (vd - dph) * a.ppd;
+  const int n16 = (cols + 15) & ~15;
+  return n16 < 16 ? 16 : n16;
+}
+
 // bias index of tile column n (transform epilogues)
 __device__ __forceinline__ float dt_tile_bias(const DtGemm& a, int nt, int n) {
   int di, pp;
@@ -113,15 +125,16 @@ __device__ __forceinline__ float dt_tile_bias(const DtGemm& a, int nt, int n) {
   return a.bias[(a.tp + a.dstride * dim) * a.ppd + pp];
 }
 
-// One 128 x 256 accumulator tile -> its epilogue (thread = sample row = TMEM lane).  `tb` is the TMEM
-// address of this warp's lane quarter of the accumulator, `Tbase` the CTA's transposition scratch.
-// Eight warps share a tile: `half` selects columns [128*half, 128*half + 128) (two warps per TMEM lane quarter).
+// Epilogue of tile columns [c_lo, c_hi) of an accumulator (thread = sample row = TMEM lane).  `tb` is the TMEM address
+// of this warp's lane quarter of the accumulator, whose column 0 holds tile column `cshift` (0, or 128 for the second
+// half of a tile computed as a half item); `T` is this warp's 32 x 36-float transposition scratch (affine).  Column
+// ranges are multiples of 16 (hidden) / 32 (affine); a warp's log-det partial goes to slot 4*nt + c_lo/64 of its row.
 template <int EPI, bool INV>
 __device__ __forceinline__ void dt_epilogue(const DtGemm& a, int mt, int nt, uint32_t tb, const float* __restrict__ sbias,
-                                            float* Tbase, int warp, int lane, int half) {
+                                            float* T, int warp, int lane, int c_lo, int c_hi, int cshift) {
   const int row = (warp & 3) * 32 + lane;
   const int64_t grow = (int64_t)mt * 128 + row;
-  const int c_lo = half * (kDtBN / 2), c_hi = c_lo + kDtBN / 2;
+  tb -= (uint32_t)cshift;
   if (EPI == kEpiHidden) {
     uint8_t* og = a.out_img + (int64_t)mt * a.out_KS * 2 * kDtABytes;
 #pragma unroll 1
@@ -154,7 +167,6 @@ __device__ __forceinline__ void dt_epilogue(const DtGemm& a, int mt, int nt, uin
     // a third phase (thread = row again) sums the log-det and, for MADE stacks, writes the NEXT
     // layer's activation image directly (bf16 hi/lo), so no separate packing pass re-reads v.
     constexpr int TS = 36;  // row stride of the transposition tile in floats (16-byte aligned rows)
-    float* T = Tbase + (half * 4 + (warp & 3)) * 32 * TS;
     const int r0 = (warp & 3) * 32;
     const int k = lane & 15, hp = lane >> 4;
     uint8_t* og = a.out_img ? a.out_img + (int64_t)mt * a.out_KS * 2 * kDtABytes : nullptr;
@@ -241,16 +253,17 @@ __device__ __forceinline__ void dt_epilogue(const DtGemm& a, int mt, int nt, uin
       }
       __syncwarp();
     }
-    if (grow < a.N) a.ldp[grow * a.tiles + 2 * nt + half] = ldsum;
+    if (grow < a.N) a.ldp[grow * a.tiles + 4 * nt + (c_lo >> 6)] = ldsum;
   }
 }
 
 // RQS epilogue by one warp per TMEM lane quarter (thread = sample row; 25 spline parameters per dim, 5 dims per
-// 128-column half).  `part` = -1: a whole 128 x 256 tile, dims paired (di, di + 5) — one from each half; `part` = h:
-// only half h of the tile (the accumulator then holds that half at TMEM columns 0..127), dims paired (0,1), (2,3), (4).
+// 128-column half).  `part` = h: the 5 dims of half h of the tile, paired (0,1), (2,3), (4); `part` = -1: the whole
+// tile, dims paired (j, j + 5).  `cshift` = tile column held at accumulator column 0 (128 for a half item of half 1).
 // A pair is evaluated as two independent splines in lockstep (rqs_apply_mufu_x2), their 2 x 25 accumulator columns
 // fetched together.  The row's state values are loaded BEFORE the accumulator is waited for (dt_rqs_load_x): they do not
 // depend on it, and the thread-per-row access (32 cache lines per warp request) used to sit inside every spline.
+// Log-det partials: slot 4*nt + 2*h of the row for the dims of half h.
 struct DtRqsX {
   float xa[5], xb[5];  // first / second member of pair j = 0..4
 };
@@ -277,13 +290,12 @@ __device__ __forceinline__ void dt_rqs_load_x(const DtGemm& a, int mt, int nt, i
 }
 
 template <bool INV>
-__device__ __forceinline__ void dt_epilogue_rqs_tile(const DtGemm& a, int mt, int nt, int part, uint32_t tb,
+__device__ __forceinline__ void dt_epilogue_rqs_tile(const DtGemm& a, int mt, int nt, int part, int cshift, uint32_t tb,
                                                      const float* __restrict__ sbias, int warp, int lane, DtRqsX& x) {
   const int row = (warp & 3) * 32 + lane;
   const int64_t grow = (int64_t)mt * 128 + row;
   float ldsum[2] = {0.f, 0.f};
   const int npair = part < 0 ? 5 : 3;
-  const int cshift = part < 0 ? 0 : 128 * part;  // accumulator column = tile column - cshift
   // the loop is not unrolled (one copy of the spline code): the state values are consumed from the head of two
   // register queues that shift by one per iteration — a runtime index would put the arrays in local memory
 #pragma unroll 1
@@ -328,10 +340,10 @@ __device__ __forceinline__ void dt_epilogue_rqs_tile(const DtGemm& a, int mt, in
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
           if (u == 1 && !two) break;
-          const int j = u ? dim1 : dim0;
+          const int jj = u ? dim1 : dim0;
           const __nv_bfloat16 h = __float2bfloat16_rn(nv[u]);
           const __nv_bfloat16 l = __float2bfloat16_rn(nv[u] - __bfloat162float(h));
-          uint8_t* st = a.out_img + ((int64_t)mt * a.out_KS + (j >> 5)) * 2 * kDtABytes + tc::img_off(128, row, (j >> 3) & 3) + (j & 7) * 2;
+          uint8_t* st = a.out_img + ((int64_t)mt * a.out_KS + (jj >> 5)) * 2 * kDtABytes + tc::img_off(128, row, (jj >> 3) & 3) + (jj & 7) * 2;
           *reinterpret_cast<__nv_bfloat16*>(st) = h;
           *reinterpret_cast<__nv_bfloat16*>(st + kDtABytes) = l;
         }
@@ -345,10 +357,10 @@ __device__ __forceinline__ void dt_epilogue_rqs_tile(const DtGemm& a, int mt, in
   }
   if (grow < a.N) {
     if (part < 0) {
-      a.ldp[grow * a.tiles + 2 * nt] = ldsum[0];      // dims 0-4 of the tile
-      a.ldp[grow * a.tiles + 2 * nt + 1] = ldsum[1];  // dims 5-9
+      a.ldp[grow * a.tiles + 4 * nt] = ldsum[0];      // dims 0-4 of the tile
+      a.ldp[grow * a.tiles + 4 * nt + 2] = ldsum[1];  // dims 5-9
     } else {
-      a.ldp[grow * a.tiles + 2 * nt + part] = ldsum[0] + ldsum[1];
+      a.ldp[grow * a.tiles + 4 * nt + 2 * part] = ldsum[0] + ldsum[1];
     }
   }
 }
@@ -423,7 +435,7 @@ template <int EPI, bool INV, bool WIDE, bool NH = false>
 __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_kernel(DtGemm a, int MT, int NT) {
   using Cfg = DtCfg<EPI, WIDE>;
   static_assert(!NH || (EPI == kEpiHidden && !WIDE), "n-half tiles exist for the hidden epilogue with 4-warp groups");
-  constexpr bool TS = EPI == kEpiRqs8;  // split the tiles of the partial last wave
+  constexpr bool TS = EPI != kEpiHidden;  // transform Linears: split the tiles of the partial last wave
   constexpr int kDtStages = Cfg::kStages;
   constexpr int EW = Cfg::kEpiWarps;
   extern __shared__ __align__(128) uint8_t smem[];
@@ -445,7 +457,7 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
     }
     for (int s = 0; s < 2; ++s) {
       tc::mbar_init(&acc_full[s], 1);
-      tc::mbar_init(&acc_empty[s], EW);  // one arrival per epilogue warp of the group
+      tc::mbar_init(&acc_empty[s], 2 * EW);  // one arrival per epilogue warp: both groups drain every accumulator
     }
     tc::fence_mbar_init();
   }
@@ -495,7 +507,15 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
       for (int w = 0; dt_item<NH, TS>(w, MT, NT, wi); ++w) {
         const int nt = wi.nt;
         const bool halfn = (NH || TS) && wi.part >= 0;
-        const uint32_t idesc = halfn ? tc::make_idesc(tc::kFmtBF16, 128, kDtBN / 2) : tc::make_idesc(tc::kFmtBF16, 128, kDtBN);
+        // MMA width: the half / the whole tile, narrowed to the columns a ragged last tile of a transform Linear needs
+        int ncols = kDtBN;
+        if (EPI != kEpiHidden) {
+          ncols = dt_tile_cols(a, nt);
+          if (halfn) ncols = wi.part == 0 ? min(ncols, kDtBN / 2) : max(ncols - kDtBN / 2, 16);
+        } else if (halfn) {
+          ncols = kDtBN / 2;
+        }
+        const uint32_t idesc = tc::make_idesc(tc::kFmtBF16, 128, ncols);
         const uint32_t lbo_b = halfn ? 16u * 128u : 32u * 128u;       // rows / 8 * 128 of the staged B image
         const uint32_t b_lo = halfn ? (uint32_t)kDtABytes : (uint32_t)kDtBBytes;  // offset of its lo part
         int KS = a.KS;
@@ -526,22 +546,37 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
       }
     }
   } else {
-    // ===== epilogue warps: group 0 (warps 2-9) takes the even items of this CTA, group 1 (warps 10-17) the odd;
-    // inside a group, warps 0-3 take the tile's columns 0-127 and warps 4-7 columns 128-255 (two warps per TMEM
-    // lane quarter).  With only four warps per tile the epilogues were bound by single-warp issue.
+    // ===== epilogue warps.  BOTH groups work on EVERY item, each on its half of the accumulator's columns: with the
+    // two accumulators alternating between items, the MMAs of item i+1 then run under the epilogue of item i and a
+    // group never waits for "its" accumulator to be refilled — per-item time max(MMA, epilogue/2).  (Round 1 gave
+    // whole items to alternating groups; a group's accumulator could only be refilled after the group had drained
+    // it, so the per-item time was (MMA + epilogue)/2: tensor pipe 76 % at best on the RQS Linear.)
+    // Inside a group of eight warps, two warps share a TMEM lane quarter and split the group's columns again.
     const uint32_t group = (uint32_t)(warp - 2) / EW;
-    const int half = ((warp - 2) >> 2) & 1;  // EW == 8 only
+    const int sub = ((warp - 2) >> 2) & 1;  // EW == 8 only: which half of the group's column range
     const int et = (tid - 64) % (EW * 32);
     auto group_sync = [&]() {  // this epilogue group only
       if (group == 0) asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory");
       else asm volatile("bar.sync 2, %0;" ::"n"(EW * 32) : "memory");
     };
     float* sbias = sbias2 + group * kDtBN;
+    float* Tw = Tbase + ((int)group * EW + (warp - 2) % EW) * 32 * 36;  // this warp's transposition scratch (affine)
     DtItem wi;
     for (int w = 0; dt_item<NH, TS>(w, MT, NT, wi); ++w) {
-      if (((uint32_t)w & 1u) != group) continue;
       const int mt = wi.mt, nt = wi.nt;
-      const uint32_t slot = group, aph = ((uint32_t)w >> 1) & 1u;
+      const uint32_t slot = (uint32_t)w & 1u, aph = ((uint32_t)w >> 1) & 1u;
+      const bool halfitem = (NH || TS) && wi.part >= 0;
+      const int cshift = halfitem ? wi.part * (kDtBN / 2) : 0;
+      // this warp's columns of the tile: the group's half of what the accumulator holds, halved again by `sub` in
+      // eight-warp groups (64-column quarters: the granularity of the log-det partial slots); of a half item's 128
+      // columns each group takes 64, which only the `sub` = 0 warps of an eight-warp group work on
+      const bool split8 = EW == 8 && !halfitem;
+      const bool colwork = EW == 4 || !halfitem || sub == 0;
+      const int span = halfitem ? 64 : (split8 ? 64 : 128);
+      const int c_lo = cshift + ((int)group * (split8 ? 2 : 1) + (split8 ? sub : 0)) * span, c_hi = c_lo + span;
+      // RQS: a group takes the 5 dims of one half; a half item is one half -> group 0 alone
+      const int rpart = halfitem ? wi.part : (int)group;
+      const bool rqs_work = EPI == kEpiRqs8 && (!halfitem || group == 0);
       for (int n = et; n < kDtBN; n += EW * 32) {  // bias of this tile's columns
         float b = 0.f;
         if (EPI == kEpiHidden) {
@@ -556,12 +591,12 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
       }
       group_sync();
       DtRqsX xin;
-      if (EPI == kEpiRqs8) dt_rqs_load_x(a, mt, nt, wi.part, warp, lane, xin);
-      if (EPI == kEpiAffine && (EW == 4 || half == 0)) {
-        // the bijector reads this tile's slice of the state v (it left L2 while the Linears streamed their
+      if (rqs_work) dt_rqs_load_x(a, mt, nt, rpart, warp, lane, xin);
+      if (EPI == kEpiAffine) {
+        // the bijector reads this warp's slice of the state v (it left L2 while the Linears streamed their
         // images): pull the thread's row of the slice into L2 now, under the tile's MMAs
         const int64_t prow = (int64_t)mt * 128 + (warp & 3) * 32 + lane;
-        const int dlo = nt * a.dpt, nd = min(a.dpt, a.ndims - dlo);
+        const int dlo = nt * a.dpt + c_lo / a.ppd, nd = min(span / a.ppd, a.ndims - dlo);
         if (prow < a.N && nd > 0) {
           const float* p0 = a.v + prow * a.D + a.tp + a.dstride * dlo;
           const uintptr_t q1 = (uintptr_t)(p0 + a.dstride * (nd - 1));
@@ -573,21 +608,14 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
       tc::tc_fence_after();
       const uint32_t tb = tmem + slot * (uint32_t)kDtBN + ((uint32_t)((warp & 3) * 32) << 16);
       if (EPI == kEpiRqs8) {
-        dt_epilogue_rqs_tile<INV>(a, mt, nt, wi.part, tb, sbias, warp, lane, xin);
-      } else if (NH) {
-        // the accumulator holds columns [128 part, +128) of the n tile at TMEM columns 0..127
-        dt_epilogue<EPI, INV>(a, mt, nt, tb - (uint32_t)(wi.part * (kDtBN / 2)), sbias, Tbase, warp, lane, wi.part);
-      } else if (EW == 8) {
-        dt_epilogue<EPI, INV>(a, mt, nt, tb, sbias, Tbase + group * kDtTileScratchFloats, warp, lane, half);
-      } else {
-#pragma unroll 1  // one copy of the epilogue code
-        for (int h = 0; h < 2; ++h)
-          dt_epilogue<EPI, INV>(a, mt, nt, tb, sbias, Tbase + group * kDtTileScratchFloats, warp, lane, h);
+        if (rqs_work) dt_epilogue_rqs_tile<INV>(a, mt, nt, rpart, cshift, tb, sbias, warp, lane, xin);
+      } else if (colwork) {
+        dt_epilogue<EPI, INV>(a, mt, nt, tb, sbias, Tw, warp, lane, c_lo, c_hi, cshift);
       }
       tc::tc_fence_before();
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(&acc_empty[slot]);
-      // every warp of the group must be done with sbias before the group's next tile overwrites it
+      // every warp of the group must be done with sbias before the group's next item overwrites it
       group_sync();
     }
   }

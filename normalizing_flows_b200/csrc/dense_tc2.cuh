@@ -199,7 +199,7 @@ dense_tc2_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     }
     for (int s = 0; s < 2; ++s) {
       tc::mbar_init(&acc_full[s], 1);
-      tc::mbar_init(&acc_empty[s], 2 * EW);  // the epilogue warps of BOTH CTAs of the pair
+      tc::mbar_init(&acc_empty[s], 4 * EW);  // both epilogue groups of BOTH CTAs of the pair drain every accumulator
     }
     tc::fence_mbar_init();
   }
@@ -275,22 +275,26 @@ dense_tc2_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       }
     }
   } else {
-    // ===== epilogue warps (every CTA): group 0 takes the even tiles of this CTA's walk, group 1 the odd ones
+    // ===== epilogue warps (every CTA).  As in dense_tc.cuh both groups work on EVERY tile, each on its half of the
+    // accumulator's columns (an eight-warp group splits its half again), so that the MMAs of tile i+1 run under the
+    // epilogue of tile i: per-tile time max(MMA, epilogue/2).
     const uint32_t group = (uint32_t)(warp - 2) / EW;
-    const int half = ((warp - 2) >> 2) & 1;  // EW == 8 only
+    const int sub = ((warp - 2) >> 2) & 1;  // EW == 8 only
     const int et = (tid - 64) % (EW * 32);
     auto group_sync = [&]() {
       if (group == 0) asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory");
       else asm volatile("bar.sync 2, %0;" ::"n"(EW * 32) : "memory");
     };
     float* sbias = sbias2 + group * kDtBN;
+    float* Tw = Tbase + ((int)group * EW + (warp - 2) % EW) * 32 * 36;
+    const int span = EW == 8 ? 64 : 128;
+    const int c_lo = ((int)group * (EW == 8 ? 2 : 1) + (EW == 8 ? sub : 0)) * span, c_hi = c_lo + span;
     const uint32_t acc_empty_leader0 = tc::mapa_u32(tc::smem_u32(&acc_empty[0]), leader);
     uint32_t tl_i = 0;
     for (int q = q0; q < nq; q += qstep, ++tl_i) {
-      if ((tl_i & 1u) != group) continue;
       const Dt2Tile tl = dt2_tile<CL>(a, q, NT, (int)pair);
       const int mt = 2 * tl.mtp + (int)prank, nt = tl.nt;
-      const uint32_t slot = group, aph = (tl_i >> 1) & 1u;
+      const uint32_t slot = tl_i & 1u, aph = (tl_i >> 1) & 1u;
       if (tl.live) {
         for (int n = et; n < kDtBN; n += EW * 32) {  // bias of this tile's columns
           float b = 0.f;
@@ -306,11 +310,11 @@ dense_tc2_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       }
       group_sync();
       DtRqsX xin;
-      if (EPI == kEpiRqs8 && tl.live) dt_rqs_load_x(a, mt, nt, -1, warp, lane, xin);
-      if (tl.live && EPI == kEpiAffine && (EW == 4 || half == 0)) {
-        // pull this thread's row of the tile's state slice into L2 under the tile's MMAs
+      if (EPI == kEpiRqs8 && tl.live) dt_rqs_load_x(a, mt, nt, (int)group, warp, lane, xin);
+      if (tl.live && EPI == kEpiAffine) {
+        // pull this thread's row of the warp's state slice into L2 under the tile's MMAs
         const int64_t prow = (int64_t)mt * 128 + (warp & 3) * 32 + lane;
-        const int dlo = nt * a.dpt, nd = min(a.dpt, a.ndims - dlo);
+        const int dlo = nt * a.dpt + c_lo / a.ppd, nd = min(span / a.ppd, a.ndims - dlo);
         if (prow < a.N && nd > 0) {
           const float* p0 = a.v + prow * a.D + a.tp + a.dstride * dlo;
           const uintptr_t q1 = (uintptr_t)(p0 + a.dstride * (nd - 1));
@@ -321,14 +325,8 @@ dense_tc2_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       tc::tc_fence_after();
       if (tl.live) {
         const uint32_t tb = tmem + slot * (uint32_t)kDtBN + ((uint32_t)((warp & 3) * 32) << 16);
-        if (EPI == kEpiRqs8) {
-          dt_epilogue_rqs_tile<INV>(a, mt, nt, -1, tb, sbias, warp, lane, xin);
-        } else if (EW == 8) {
-          dt_epilogue<EPI, INV>(a, mt, nt, tb, sbias, Tbase + group * kDtTileScratchFloats, warp, lane, half);
-        } else {
-#pragma unroll 1
-          for (int h = 0; h < 2; ++h) dt_epilogue<EPI, INV>(a, mt, nt, tb, sbias, Tbase + group * kDtTileScratchFloats, warp, lane, h);
-        }
+        if (EPI == kEpiRqs8) dt_epilogue_rqs_tile<INV>(a, mt, nt, (int)group, 0, tb, sbias, warp, lane, xin);
+        else dt_epilogue<EPI, INV>(a, mt, nt, tb, sbias, Tw, warp, lane, c_lo, c_hi, 0);
       }
       tc::tc_fence_before();
       __syncwarp();

@@ -72,8 +72,8 @@ static bool made_layout(const flowcuda_made_spec* sp, int64_t n, MadeLayout& L) 
   }
   L.off_v = off; off = dt_al256(off + (size_t)n * D * 4);
   L.off_ld = off; off = dt_al256(off + (size_t)n * 4);
-  // two log-det partials per (row, tile), one slab per flow layer (summed once, by the finish kernel)
-  L.off_ldp = off; off = dt_al256(off + (size_t)sp->num_layers * n * L.tiles * 2 * 4);
+  // four log-det partials per (row, tile) — one per 64-column quarter — and one slab per flow layer (summed once, by the finish kernel)
+  L.off_ldp = off; off = dt_al256(off + (size_t)sp->num_layers * n * L.tiles * 4 * 4);
   L.off_x = off; off = dt_al256(off + (size_t)L.MT * L.KS[0] * 2 * kDtABytes);
   int ksh = 1;
   for (int i = 1; i < L.nlin; ++i) ksh = L.KS[i] > ksh ? L.KS[i] : ksh;
@@ -201,6 +201,9 @@ static int made_log_prob_run(const flowcuda_made_spec* sp, const float* params, 
     FC_LAUNCH_CHECK("made_tc_pack_w_kernel");
   }
   if (mode == 2) return FLOWCUDA_OK;
+  // the finish kernel sums every partial slot of every layer's slab; four-warp epilogue groups fill only two of a
+  // tile's four quarter slots
+  FC_CUDA(cudaMemsetAsync(ldp, 0, (size_t)sp->num_layers * n * 4 * L.tiles * sizeof(float), s));
   for (int it = 0; it < sp->num_layers; ++it) {
     const int l = sp->num_layers - 1 - it;  // data -> base: last layer first
     const bool rev = (l & 1) != 0;
@@ -221,8 +224,8 @@ static int made_log_prob_run(const flowcuda_made_spec* sp, const float* params, 
       g.bias = lp + L.b_off[i];
       g.KS = L.KS[i];
       g.n_out = L.sizes[i + 1];
-      g.v = v; g.ldp = ldp + (size_t)it * n * 2 * L.tiles; g.N = n; g.D = D; g.tp = 0; g.dstride = 1; g.ndims = D; g.dpt = 128; g.ppd = 2;
-      g.tiles = 2 * L.tiles; g.made = 1; g.rev = rev ? 1 : 0;
+      g.v = v; g.ldp = ldp + (size_t)it * n * 4 * L.tiles; g.N = n; g.D = D; g.tp = 0; g.dstride = 1; g.ndims = D; g.dpt = 128; g.ppd = 2;
+      g.tiles = 4 * L.tiles; g.made = 1; g.rev = rev ? 1 : 0;
       for (int t = 0; t < L.NT[i] && t < kDtMaxKsTiles; ++t) g.ks_tile[t] = (unsigned char)made_ks_needed(L, i, t, rev);
       int rc;
       const Dt2Launch dl = {L.MT, (int64_t)sp->num_layers * L.NT[i], (int64_t)l * L.NT[i]};
@@ -246,7 +249,7 @@ static int made_log_prob_run(const flowcuda_made_spec* sp, const float* params, 
   (void)ld;
   if (out_lp || out_ld) {
     FC_CUDA(launch_chain(dense_tc_finish_kernel, dim3((unsigned)((n * 32 + 255) / 256)), dim3(256), 0, s, (const float*)v,
-                         (const float*)ldp, (int)sp->num_layers, 2 * L.tiles, 2 * L.tiles, n, D, with_base, (int)sp->base, out_lp,
+                         (const float*)ldp, (int)sp->num_layers, 4 * L.tiles, 4 * L.tiles, n, D, with_base, (int)sp->base, out_lp,
                          out_ld));
   }
   if (out_u) FC_CUDA(cudaMemcpyAsync(out_u, v, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToDevice, s));
