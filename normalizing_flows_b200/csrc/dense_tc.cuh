@@ -257,54 +257,41 @@ __device__ __forceinline__ void dt_epilogue(const DtGemm& a, int mt, int nt, uin
   }
 }
 
-// RQS epilogue by one warp per TMEM lane quarter (thread = sample row; 25 spline parameters per dim, 5 dims per
-// 128-column half).  `part` = h: the 5 dims of half h of the tile, paired (0,1), (2,3), (4); `part` = -1: the whole
-// tile, dims paired (j, j + 5).  `cshift` = tile column held at accumulator column 0 (128 for a half item of half 1).
-// A pair is evaluated as two independent splines in lockstep (rqs_apply_mufu_x2), their 2 x 25 accumulator columns
-// fetched together.  The row's state values are loaded BEFORE the accumulator is waited for (dt_rqs_load_x): they do not
-// depend on it, and the thread-per-row access (32 cache lines per warp request) used to sit inside every spline.
-// Log-det partials: slot 4*nt + 2*h of the row for the dims of half h.
+// RQS epilogue by one warp per TMEM lane quarter (thread = sample row; 25 spline parameters per dim, two 128-column
+// halves of 5 dims per tile).  The warp takes the tile's dims [d_lo, d_hi) (at most 6), paired (d, d + 1): a pair is
+// evaluated as two independent splines in lockstep (rqs_apply_mufu_x2), their 2 x 25 accumulator columns fetched
+// together.  `cshift` = tile column held at accumulator column 0 (128 for a half item of half 1).  The row's state
+// values are loaded BEFORE the accumulator is waited for (dt_rqs_load_x): they do not depend on it, and the
+// thread-per-row access (32 cache lines per warp request) used to sit inside every spline.  The log-det partial of the
+// warp's dims goes to slot `ldslot` of the row's four slots of tile nt.
 struct DtRqsX {
-  float xa[5], xb[5];  // first / second member of pair j = 0..4
+  float xa[3], xb[3];  // first / second member of pair j = 0..2
 };
-__device__ __forceinline__ void dt_rqs_pair(int part, int j, int& d0, int& d1) {
-  if (part < 0) {
-    d0 = j;
-    d1 = j + 5;
-  } else {
-    d0 = 5 * part + 2 * j;
-    d1 = (2 * j + 1 < 5) ? d0 + 1 : -1;
-  }
-}
-__device__ __forceinline__ void dt_rqs_load_x(const DtGemm& a, int mt, int nt, int part, int warp, int lane, DtRqsX& x) {
+__device__ __forceinline__ void dt_rqs_load_x(const DtGemm& a, int mt, int nt, int d_lo, int d_hi, int warp, int lane, DtRqsX& x) {
   const int64_t grow = (int64_t)mt * 128 + (warp & 3) * 32 + lane;
 #pragma unroll
-  for (int j = 0; j < 5; ++j) {
-    int d0, d1;
-    dt_rqs_pair(part, j, d0, d1);
-    const bool live = part < 0 || j < 3;
+  for (int j = 0; j < 3; ++j) {
+    const int d0 = d_lo + 2 * j, d1 = d0 + 1;
     const int dim0 = nt * 10 + d0, dim1 = nt * 10 + d1;
-    x.xa[j] = (live && grow < a.N && dim0 < a.ndims) ? a.v[grow * a.D + a.tp + a.dstride * dim0] : 0.f;
-    x.xb[j] = (live && d1 >= 0 && grow < a.N && dim1 < a.ndims) ? a.v[grow * a.D + a.tp + a.dstride * dim1] : 0.f;
+    x.xa[j] = (d0 < d_hi && grow < a.N && dim0 < a.ndims) ? a.v[grow * a.D + a.tp + a.dstride * dim0] : 0.f;
+    x.xb[j] = (d1 < d_hi && grow < a.N && dim1 < a.ndims) ? a.v[grow * a.D + a.tp + a.dstride * dim1] : 0.f;
   }
 }
 
 template <bool INV>
-__device__ __forceinline__ void dt_epilogue_rqs_tile(const DtGemm& a, int mt, int nt, int part, int cshift, uint32_t tb,
-                                                     const float* __restrict__ sbias, int warp, int lane, DtRqsX& x) {
+__device__ __forceinline__ void dt_epilogue_rqs_tile(const DtGemm& a, int mt, int nt, int d_lo, int d_hi, int ldslot, int cshift,
+                                                     uint32_t tb, const float* __restrict__ sbias, int warp, int lane, DtRqsX& x) {
   const int row = (warp & 3) * 32 + lane;
   const int64_t grow = (int64_t)mt * 128 + row;
   float ldsum[2] = {0.f, 0.f};
-  const int npair = part < 0 ? 5 : 3;
   // the loop is not unrolled (one copy of the spline code): the state values are consumed from the head of two
   // register queues that shift by one per iteration — a runtime index would put the arrays in local memory
 #pragma unroll 1
-  for (int j = 0; j < npair; ++j) {
-    int d0, d1;
-    dt_rqs_pair(part, j, d0, d1);
+  for (int d0 = d_lo; d0 < d_hi; d0 += 2) {
+    const int d1 = d0 + 1;
     const int dim0 = nt * 10 + d0, dim1 = nt * 10 + d1;
     if (dim0 >= a.ndims) break;  // uniform across the CTA
-    const bool two = d1 >= 0 && dim1 < a.ndims;
+    const bool two = d1 < d_hi && dim1 < a.ndims;
     const int c0 = dt_dim_to_col(d0, 10, 25), c1 = dt_dim_to_col(two ? d1 : d0, 10, 25);
     uint32_t vv[2][25];
 #pragma unroll
@@ -349,20 +336,21 @@ __device__ __forceinline__ void dt_epilogue_rqs_tile(const DtGemm& a, int mt, in
         }
       }
     }
-#pragma unroll
-    for (int i = 0; i < 4; ++i) {
-      x.xa[i] = x.xa[i + 1];
-      x.xb[i] = x.xb[i + 1];
-    }
+    x.xa[0] = x.xa[1];
+    x.xa[1] = x.xa[2];
+    x.xb[0] = x.xb[1];
+    x.xb[1] = x.xb[2];
   }
-  if (grow < a.N) {
-    if (part < 0) {
-      a.ldp[grow * a.tiles + 4 * nt] = ldsum[0];      // dims 0-4 of the tile
-      a.ldp[grow * a.tiles + 4 * nt + 2] = ldsum[1];  // dims 5-9
-    } else {
-      a.ldp[grow * a.tiles + 4 * nt + 2 * part] = ldsum[0] + ldsum[1];
-    }
-  }
+  if (grow < a.N) a.ldp[grow * a.tiles + 4 * nt + ldslot] = ldsum[0] + ldsum[1];
+}
+
+// dims of a whole RQS tile that epilogue group `g` takes on the CTA's w-th item: 10 dims = 5 pairs for two groups — three
+// pairs and two, alternating between the groups from item to item so that each averages 2.5 (the accumulators' double
+// buffering absorbs the one-pair difference)
+__device__ __forceinline__ void dt_rqs_group_dims(int w, int g, int& d_lo, int& d_hi) {
+  const int cut = (w & 1) ? 4 : 6;
+  d_lo = g == 0 ? 0 : cut;
+  d_hi = g == 0 ? cut : 10;
 }
 
 constexpr int kDtTileScratchFloats = 8 * 32 * 36;  // per-warp 32 x 36 transposition tiles of one epilogue group (affine)
@@ -438,6 +426,11 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
   constexpr bool TS = EPI != kEpiHidden;  // transform Linears: split the tiles of the partial last wave
   constexpr int kDtStages = Cfg::kStages;
   constexpr int EW = Cfg::kEpiWarps;
+  // Warp roles: the epilogue warps come FIRST (warp w reads TMEM lane quarter w % 4), the TMA producer and the MMA issuer
+  // LAST.  The schedulers pick the highest eligible warp id first: with the issuer at warp 1 every one of its ~30
+  // instructions per MMA queued behind four busy epilogue warps of its scheduler, and the tensor pipe idled between
+  // MMAs (36-41 % active on the affine Linears with the issuer never waiting on a barrier).
+  constexpr int kLoadWarp = 2 * EW, kMmaWarp = 2 * EW + 1;
   extern __shared__ __align__(128) uint8_t smem[];
   uint8_t* stages = smem;                                                          // [stages][48 KB]
   float* Tbase = reinterpret_cast<float*>(smem + kDtStages * kDtStageBytes);       // epilogue scratch
@@ -449,8 +442,8 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
-  if (warp == 1) tc::tmem_alloc(tmem_slot, 2 * kDtBN);
-  if (tid == 0) {
+  if (warp == kMmaWarp) tc::tmem_alloc(tmem_slot, 2 * kDtBN);
+  if (tid == kLoadWarp * 32) {
     for (int s = 0; s < kDtStages; ++s) {
       tc::mbar_init(&full[s], 1);
       tc::mbar_init(&empty[s], 1);
@@ -470,7 +463,7 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
   pdl_wait();
   pdl_launch_dependents();
 
-  if (warp == 0) {
+  if (warp == kLoadWarp) {
     if (lane == 0) {  // ===== TMA loader
       uint32_t it = 0;
       DtItem wi;
@@ -499,7 +492,7 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == kMmaWarp) {
     if (lane == 0) {  // ===== MMA issuer: 3 passes x 2 K steps per stage
       constexpr uint32_t lbo_a = 16u * 128u;
       uint32_t it = 0;
@@ -552,15 +545,15 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
     // whole items to alternating groups; a group's accumulator could only be refilled after the group had drained
     // it, so the per-item time was (MMA + epilogue)/2: tensor pipe 76 % at best on the RQS Linear.)
     // Inside a group of eight warps, two warps share a TMEM lane quarter and split the group's columns again.
-    const uint32_t group = (uint32_t)(warp - 2) / EW;
-    const int sub = ((warp - 2) >> 2) & 1;  // EW == 8 only: which half of the group's column range
-    const int et = (tid - 64) % (EW * 32);
+    const uint32_t group = (uint32_t)warp / EW;
+    const int sub = (warp >> 2) & 1;  // EW == 8 only: which half of the group's column range
+    const int et = tid % (EW * 32);
     auto group_sync = [&]() {  // this epilogue group only
       if (group == 0) asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory");
       else asm volatile("bar.sync 2, %0;" ::"n"(EW * 32) : "memory");
     };
     float* sbias = sbias2 + group * kDtBN;
-    float* Tw = Tbase + ((int)group * EW + (warp - 2) % EW) * 32 * 36;  // this warp's transposition scratch (affine)
+    float* Tw = Tbase + ((int)group * EW + warp % EW) * 32 * 36;  // this warp's transposition scratch (affine)
     DtItem wi;
     for (int w = 0; dt_item<NH, TS>(w, MT, NT, wi); ++w) {
       const int mt = wi.mt, nt = wi.nt;
@@ -574,9 +567,16 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
       const bool colwork = EW == 4 || !halfitem || sub == 0;
       const int span = halfitem ? 64 : (split8 ? 64 : 128);
       const int c_lo = cshift + ((int)group * (split8 ? 2 : 1) + (split8 ? sub : 0)) * span, c_hi = c_lo + span;
-      // RQS: a group takes the 5 dims of one half; a half item is one half -> group 0 alone
-      const int rpart = halfitem ? wi.part : (int)group;
-      const bool rqs_work = EPI == kEpiRqs8 && (!halfitem || group == 0);
+      // RQS: the groups share a whole tile's 10 dims (dt_rqs_group_dims); a half item's 5 dims go 3 + 2
+      int rd_lo = 0, rd_hi = 0;
+      if (EPI == kEpiRqs8) {
+        if (halfitem) {
+          rd_lo = 5 * wi.part + (group == 0 ? 0 : 3);
+          rd_hi = 5 * wi.part + (group == 0 ? 3 : 5);
+        } else {
+          dt_rqs_group_dims(w, (int)group, rd_lo, rd_hi);
+        }
+      }
       for (int n = et; n < kDtBN; n += EW * 32) {  // bias of this tile's columns
         float b = 0.f;
         if (EPI == kEpiHidden) {
@@ -591,7 +591,7 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
       }
       group_sync();
       DtRqsX xin;
-      if (rqs_work) dt_rqs_load_x(a, mt, nt, rpart, warp, lane, xin);
+      if (EPI == kEpiRqs8) dt_rqs_load_x(a, mt, nt, rd_lo, rd_hi, warp, lane, xin);
       if (EPI == kEpiAffine) {
         // the bijector reads this warp's slice of the state v (it left L2 while the Linears streamed their
         // images): pull the thread's row of the slice into L2 now, under the tile's MMAs
@@ -608,7 +608,9 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
       tc::tc_fence_after();
       const uint32_t tb = tmem + slot * (uint32_t)kDtBN + ((uint32_t)((warp & 3) * 32) << 16);
       if (EPI == kEpiRqs8) {
-        if (rqs_work) dt_epilogue_rqs_tile<INV>(a, mt, nt, rpart, cshift, tb, sbias, warp, lane, xin);
+        // log-det slots: a whole tile's groups use slots 0 / 2, a half item's groups the two slots of its half
+        dt_epilogue_rqs_tile<INV>(a, mt, nt, rd_lo, rd_hi, halfitem ? 2 * wi.part + (int)group : 2 * (int)group, cshift, tb, sbias,
+                                  warp, lane, xin);
       } else if (colwork) {
         dt_epilogue<EPI, INV>(a, mt, nt, tb, sbias, Tw, warp, lane, c_lo, c_hi, cshift);
       }
@@ -621,7 +623,7 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
   }
   tc::tc_fence_before();
   __syncthreads();
-  if (warp == 1) {
+  if (warp == kMmaWarp) {
     __syncwarp();
     tc::tmem_dealloc(tmem, 2 * kDtBN);
   }

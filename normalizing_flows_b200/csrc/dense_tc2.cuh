@@ -171,6 +171,7 @@ dense_tc2_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   using Cfg = Dt2Cfg<EPI, WIDE, CL>;
   constexpr int S = Cfg::kStages;
   constexpr int EW = Cfg::kEpiWarps;
+  constexpr int kLoadWarp = 2 * EW, kMmaWarp = 2 * EW + 1;  // issuer and producer at the highest warp ids (dense_tc.cuh)
   extern __shared__ uint8_t smem_raw[];
   // the dynamic window is only 16-byte aligned by contract: TMA destinations want 128 B, keep 1 KB
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -190,7 +191,7 @@ dense_tc2_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   const int nq = CL == 2 ? MTP * NT : MTP * ((NT + 1) >> 1);
   const int q0 = (int)tc::cluster_id_x(), qstep = (int)tc::nclusters_x();
 
-  if (tid == 0) {
+  if (tid == kLoadWarp * 32) {
     tc::tma_prefetch_desc(&tmA);
     tc::tma_prefetch_desc(&tmB);
     for (int s = 0; s < S; ++s) {
@@ -203,7 +204,7 @@ dense_tc2_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     }
     tc::fence_mbar_init();
   }
-  if (warp == 1) tc::tmem_alloc2(tmem_slot, 2 * kDtBN);
+  if (warp == kMmaWarp) tc::tmem_alloc2(tmem_slot, 2 * kDtBN);
   tc::tc_fence_before();
   __syncthreads();
   tc::cluster_sync_all();  // every CTA's barriers exist before any remote arrive / multicast can reach them
@@ -212,7 +213,7 @@ dense_tc2_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   pdl_wait();  // from here on: operands written by the previous kernel of the chain (common.cuh, PDL)
   pdl_launch_dependents();
 
-  if (warp == 0) {
+  if (warp == kLoadWarp) {
     if (lane == 0) {  // ===== TMA producer (every CTA)
       const uint32_t full_leader0 = tc::mapa_u32(tc::smem_u32(&full[0]), leader);
       uint32_t it = 0;
@@ -239,7 +240,7 @@ dense_tc2_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == kMmaWarp) {
     if (lane == 0 && prank == 0) {  // ===== MMA issuer (pair leader): 3 passes x 2 K steps per stage, M = 256 over the pair
       constexpr uint32_t idesc = tc::make_idesc(tc::kFmtBF16, 256, kDtBN);
       constexpr uint32_t lbo = 16u * 128u;  // both operands are 128-row images in each CTA
@@ -278,15 +279,15 @@ dense_tc2_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     // ===== epilogue warps (every CTA).  As in dense_tc.cuh both groups work on EVERY tile, each on its half of the
     // accumulator's columns (an eight-warp group splits its half again), so that the MMAs of tile i+1 run under the
     // epilogue of tile i: per-tile time max(MMA, epilogue/2).
-    const uint32_t group = (uint32_t)(warp - 2) / EW;
-    const int sub = ((warp - 2) >> 2) & 1;  // EW == 8 only
-    const int et = (tid - 64) % (EW * 32);
+    const uint32_t group = (uint32_t)warp / EW;
+    const int sub = (warp >> 2) & 1;  // EW == 8 only
+    const int et = tid % (EW * 32);
     auto group_sync = [&]() {
       if (group == 0) asm volatile("bar.sync 1, %0;" ::"n"(EW * 32) : "memory");
       else asm volatile("bar.sync 2, %0;" ::"n"(EW * 32) : "memory");
     };
     float* sbias = sbias2 + group * kDtBN;
-    float* Tw = Tbase + ((int)group * EW + (warp - 2) % EW) * 32 * 36;
+    float* Tw = Tbase + ((int)group * EW + warp % EW) * 32 * 36;
     const int span = EW == 8 ? 64 : 128;
     const int c_lo = ((int)group * (EW == 8 ? 2 : 1) + (EW == 8 ? sub : 0)) * span, c_hi = c_lo + span;
     const uint32_t acc_empty_leader0 = tc::mapa_u32(tc::smem_u32(&acc_empty[0]), leader);
@@ -310,7 +311,9 @@ dense_tc2_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       }
       group_sync();
       DtRqsX xin;
-      if (EPI == kEpiRqs8 && tl.live) dt_rqs_load_x(a, mt, nt, (int)group, warp, lane, xin);
+      int rd_lo = 0, rd_hi = 0;
+      if (EPI == kEpiRqs8) dt_rqs_group_dims((int)tl_i, (int)group, rd_lo, rd_hi);
+      if (EPI == kEpiRqs8 && tl.live) dt_rqs_load_x(a, mt, nt, rd_lo, rd_hi, warp, lane, xin);
       if (tl.live && EPI == kEpiAffine) {
         // pull this thread's row of the warp's state slice into L2 under the tile's MMAs
         const int64_t prow = (int64_t)mt * 128 + (warp & 3) * 32 + lane;
@@ -325,7 +328,7 @@ dense_tc2_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       tc::tc_fence_after();
       if (tl.live) {
         const uint32_t tb = tmem + slot * (uint32_t)kDtBN + ((uint32_t)((warp & 3) * 32) << 16);
-        if (EPI == kEpiRqs8) dt_epilogue_rqs_tile<INV>(a, mt, nt, (int)group, 0, tb, sbias, warp, lane, xin);
+        if (EPI == kEpiRqs8) dt_epilogue_rqs_tile<INV>(a, mt, nt, rd_lo, rd_hi, 2 * (int)group, 0, tb, sbias, warp, lane, xin);
         else dt_epilogue<EPI, INV>(a, mt, nt, tb, sbias, Tw, warp, lane, c_lo, c_hi, 0);
       }
       tc::tc_fence_before();
@@ -337,7 +340,7 @@ dense_tc2_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
   tc::tc_fence_before();
   __syncthreads();
   tc::cluster_sync_all();  // no CTA leaves (or frees TMEM) while a peer can still signal its barriers or read its operands
-  if (warp == 1) {
+  if (warp == kMmaWarp) {
     __syncwarp();
     tc::tmem_dealloc2(tmem, 2 * kDtBN);
   }
