@@ -54,6 +54,10 @@ def _deps_mtime() -> float:
 def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(OBJ, exist_ok=True)
     nvcc = _nvcc()
+    flags = list(NVCC_FLAGS)
+    if os.environ.get("FLOWCUDA_BUILD_TRACE") == "1":  # diagnostics build (tools/dt_trace.py); never the shipped library
+        flags.append("-DFLOWCUDA_TRACE")
+        force = True
     hdr_m = _deps_mtime()
     jobs = []
     objs = []
@@ -62,7 +66,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         o = os.path.join(OBJ, src[:-3] + ".o")
         objs.append(o)
         if force or not os.path.exists(o) or os.path.getmtime(o) < max(os.path.getmtime(s), hdr_m):
-            cmd = [nvcc, *NVCC_FLAGS, "-c", s, "-o", o]
+            cmd = [nvcc, *flags, "-c", s, "-o", o]
             if verbose:
                 cmd.insert(1, "-Xptxas=-v")
             jobs.append(cmd)

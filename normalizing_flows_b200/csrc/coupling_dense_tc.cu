@@ -240,3 +240,11 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
 }
 
 }  // namespace flowcuda
+
+#ifdef FLOWCUDA_TRACE
+// diagnostics build only (tools/dt_trace.py): point the GEMM kernels of this translation unit at a device buffer of
+// 8 counters per CTA
+extern "C" int flowcuda_debug_set_dt_trace(unsigned long long* device_buf) {
+  return cudaMemcpyToSymbol(flowcuda::g_dt_trace, &device_buf, sizeof(device_buf)) == cudaSuccess ? 0 : -2;
+}
+#endif

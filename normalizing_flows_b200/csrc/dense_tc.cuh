@@ -84,6 +84,19 @@ struct DtGemm {
 
 constexpr int kEpiHidden = 0, kEpiRqs8 = 1, kEpiAffine = 2;
 
+// Diagnostics (tools/dt_trace.py; compiled only into a -DFLOWCUDA_TRACE build, never into the shipped library): where the
+// single-thread roles of dense_tc_gemm_kernel spend their cycles.  Per CTA 8 counters: kernel cycles, issuer waiting for
+// a free accumulator / for operands, producer waiting for a free stage, epilogue warp 0 / warp EW waiting for an accumulator,
+// and their item counts.
+#ifdef FLOWCUDA_TRACE
+__device__ unsigned long long* g_dt_trace = nullptr;
+#define DT_TRACE_T0(var) const long long var = clock64()
+#define DT_TRACE_ADD(acc, var) acc += clock64() - var
+#else
+#define DT_TRACE_T0(var)
+#define DT_TRACE_ADD(acc, var)
+#endif
+
 // Column layout of a transform tile (last Linear): the 256 columns are two halves of 128; half g holds the
 // dpt/2 dims [g*dpt/2, (g+1)*dpt/2) of the tile, ppd consecutive parameters each (affine: 64 dims x 2 = 128 columns;
 // RQS with 8 bins: 5 dims x 25 = 125 columns + 3 pad).  Halves are self-contained so that a CTA can compute ONE half
@@ -380,14 +393,25 @@ template <int EPI, bool WIDE> struct DtCfg {
 struct DtItem {
   int mt, nt, part;  // part < 0: the whole tile
 };
+// Tile order.  Coupling Linears: m-tile major (concurrent CTAs spread over the n tiles; n-tile major order put 128 CTAs
+// on the same weight stages at once and the issuer's operand waits grew from 14 K to 21 K cycles on the deep16 stack).
+// MADE Linears (`desc`): n-tile major, DESCENDING — the masks leave n tile 0 the fewest K stages, so the expensive tiles
+// go first and the tail of the walk is cheap (slowest issuer of the affine Linear 85 K -> 80 K cycles, tools/dt_trace.py).
 template <bool NH, bool TS>
-__device__ __forceinline__ bool dt_item(int w, int MT, int NT, DtItem& it) {
+__device__ __forceinline__ bool dt_item(int w, int MT, int NT, bool desc, DtItem& it) {
   const int grid = (int)gridDim.x, cta = (int)blockIdx.x;
   if (NH) {
     const int t = cta + w * grid;
     if (t >= MT * NT * 2) return false;
-    it.mt = t / (2 * NT);
-    const int c = t - it.mt * 2 * NT;
+    int c;
+    if (desc) {
+      c = t / MT;
+      it.mt = t - c * MT;
+      c = 2 * NT - 1 - c;
+    } else {
+      it.mt = t / (2 * NT);
+      c = t - it.mt * 2 * NT;
+    }
     it.nt = c >> 1;
     it.part = c & 1;
     return true;
@@ -411,8 +435,14 @@ __device__ __forceinline__ bool dt_item(int w, int MT, int NT, DtItem& it) {
   } else if (t >= ntiles) {
     return false;
   }
-  it.mt = t / NT;
-  it.nt = t - it.mt * NT;
+  if (desc) {
+    it.nt = t / MT;
+    it.mt = t - it.nt * MT;
+    it.nt = NT - 1 - it.nt;
+  } else {
+    it.mt = t / NT;
+    it.nt = t - it.mt * NT;
+  }
   return true;
 }
 
@@ -467,7 +497,10 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
     if (lane == 0) {  // ===== TMA loader
       uint32_t it = 0;
       DtItem wi;
-      for (int w = 0; dt_item<NH, TS>(w, MT, NT, wi); ++w) {
+#ifdef FLOWCUDA_TRACE
+      long long tr_wait = 0;
+#endif
+      for (int w = 0; dt_item<NH, TS>(w, MT, NT, a.made != 0, wi); ++w) {
         const int mt = wi.mt, nt = wi.nt;
         int KS = a.KS;
         if (nt < kDtMaxKsTiles && a.ks_tile[nt] != 0) KS = a.ks_tile[nt];
@@ -475,7 +508,9 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
         const uint8_t* bg = a.b_img + (int64_t)nt * a.KS * 2 * kDtBBytes;
         for (int ks = 0; ks < KS; ++ks, ++it) {
           const uint32_t st = it % kDtStages, ph = (it / kDtStages) & 1u;
+          DT_TRACE_T0(t0);
           tc::mbar_wait(&empty[st], ph ^ 1u);  // passes at once on a fresh barrier
+          DT_TRACE_ADD(tr_wait, t0);
           uint8_t* dst = stages + st * kDtStageBytes;
           if ((NH || TS) && wi.part >= 0) {
             tc::mbar_arrive_expect_tx(&full[st], 4 * kDtABytes);
@@ -491,13 +526,20 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
           }
         }
       }
+#ifdef FLOWCUDA_TRACE
+      if (g_dt_trace) g_dt_trace[blockIdx.x * 8 + 3] = (unsigned long long)tr_wait;
+#endif
     }
   } else if (warp == kMmaWarp) {
     if (lane == 0) {  // ===== MMA issuer: 3 passes x 2 K steps per stage
       constexpr uint32_t lbo_a = 16u * 128u;
       uint32_t it = 0;
       DtItem wi;
-      for (int w = 0; dt_item<NH, TS>(w, MT, NT, wi); ++w) {
+#ifdef FLOWCUDA_TRACE
+      long long tr_acc = 0, tr_full = 0, tr_items = 0;
+      const long long tr_start = clock64();
+#endif
+      for (int w = 0; dt_item<NH, TS>(w, MT, NT, a.made != 0, wi); ++w) {
         const int nt = wi.nt;
         const bool halfn = (NH || TS) && wi.part >= 0;
         // MMA width: the half / the whole tile, narrowed to the columns a ragged last tile of a transform Linear needs
@@ -514,13 +556,20 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
         int KS = a.KS;
         if (nt < kDtMaxKsTiles && a.ks_tile[nt] != 0) KS = a.ks_tile[nt];
         const uint32_t slot = (uint32_t)w & 1u, aph = ((uint32_t)w >> 1) & 1u;
+        DT_TRACE_T0(t0);
         tc::mbar_wait(&acc_empty[slot], aph ^ 1u);  // the epilogue has drained this accumulator
+        DT_TRACE_ADD(tr_acc, t0);
+#ifdef FLOWCUDA_TRACE
+        ++tr_items;
+#endif
         tc::tc_fence_after();
         const uint32_t dtm = tmem + slot * (uint32_t)kDtBN;
         uint32_t acc = 0;
         for (int ks = 0; ks < KS; ++ks, ++it) {
           const uint32_t st = it % kDtStages, ph = (it / kDtStages) & 1u;
+          DT_TRACE_T0(t1);
           tc::mbar_wait(&full[st], ph);
+          DT_TRACE_ADD(tr_full, t1);
           tc::tc_fence_after();
           const uint32_t sa = tc::smem_u32(stages + st * kDtStageBytes), sb = sa + 2 * kDtABytes;
 #pragma unroll
@@ -537,6 +586,15 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
         }
         tc::mma_commit(&acc_full[slot]);
       }
+#ifdef FLOWCUDA_TRACE
+      if (g_dt_trace) {
+        g_dt_trace[blockIdx.x * 8 + 0] = (unsigned long long)(clock64() - tr_start);
+        g_dt_trace[blockIdx.x * 8 + 1] = (unsigned long long)tr_acc;
+        g_dt_trace[blockIdx.x * 8 + 2] = (unsigned long long)tr_full;
+        g_dt_trace[blockIdx.x * 8 + 6] = (unsigned long long)tr_items;
+        g_dt_trace[blockIdx.x * 8 + 7] = (unsigned long long)it;
+      }
+#endif
     }
   } else {
     // ===== epilogue warps.  BOTH groups work on EVERY item, each on its half of the accumulator's columns: with the
@@ -555,7 +613,10 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
     float* sbias = sbias2 + group * kDtBN;
     float* Tw = Tbase + ((int)group * EW + warp % EW) * 32 * 36;  // this warp's transposition scratch (affine)
     DtItem wi;
-    for (int w = 0; dt_item<NH, TS>(w, MT, NT, wi); ++w) {
+#ifdef FLOWCUDA_TRACE
+    long long tr_wait = 0;
+#endif
+    for (int w = 0; dt_item<NH, TS>(w, MT, NT, a.made != 0, wi); ++w) {
       const int mt = wi.mt, nt = wi.nt;
       const uint32_t slot = (uint32_t)w & 1u, aph = ((uint32_t)w >> 1) & 1u;
       const bool halfitem = (NH || TS) && wi.part >= 0;
@@ -604,7 +665,9 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
             asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
         }
       }
+      DT_TRACE_T0(t0);
       tc::mbar_wait(&acc_full[slot], aph);
+      DT_TRACE_ADD(tr_wait, t0);
       tc::tc_fence_after();
       const uint32_t tb = tmem + slot * (uint32_t)kDtBN + ((uint32_t)((warp & 3) * 32) << 16);
       if (EPI == kEpiRqs8) {
@@ -620,6 +683,9 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
       // every warp of the group must be done with sbias before the group's next item overwrites it
       group_sync();
     }
+#ifdef FLOWCUDA_TRACE
+    if (g_dt_trace && lane == 0 && (warp == 0 || warp == EW)) g_dt_trace[blockIdx.x * 8 + (warp == 0 ? 4 : 5)] = (unsigned long long)tr_wait;
+#endif
   }
   tc::tc_fence_before();
   __syncthreads();

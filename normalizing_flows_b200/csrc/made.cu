@@ -566,3 +566,9 @@ int flowcuda_made_sample(const flowcuda_made_spec* spec, const float* params, co
 }
 
 }  // extern "C"
+
+#ifdef FLOWCUDA_TRACE
+extern "C" int flowcuda_debug_set_dt_trace_made(unsigned long long* device_buf) {
+  return cudaMemcpyToSymbol(flowcuda::g_dt_trace, &device_buf, sizeof(device_buf)) == cudaSuccess ? 0 : -2;
+}
+#endif
