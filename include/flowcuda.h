@@ -332,6 +332,19 @@ int flowcuda_rotate2d(const float* x, float cos_theta, float sin_theta, int inve
 int flowcuda_sum_scaled(const float* v, int64_t n, double scale, float* out, void* workspace,
                         void* stream);
 
+/* flowcuda_sum_scaled with NO workspace argument and NO allocation.  This entry point has no
+ * counterpart in the reference.  Same kernels,
+ * same grid rule and therefore the same bits as flowcuda_sum_scaled, but the 1024 stage-1 partials
+ * (8 KB) live in a file-scope `static __device__ __align__(256)` array of the library, whose device
+ * address is resolved once per device (cudaGetSymbolAddress, that device current) and cached.  It calls
+ * no cudaMalloc / cudaFree / allocating library routine.  v, out: caller's device buffers.
+ * Limit: n <= 2^26 elements (67 108 864 floats, 256 MB of input); larger n returns
+ * FLOWCUDA_EINVAL with a message naming the limit — use flowcuda_sum_scaled there.
+ * The array is shared by every call on a device and keeps the last call's partials (the slots a call
+ * uses are cleared first): calls that overlap on one device (two streams, two host threads) RACE on it;
+ * serialise them on one stream or with an event. */
+int flowcuda_sum_scaled_static(const float* v, int64_t n, double scale, float* out, void* stream);
+
 /* p <- p - lr*g (real_nvp.py:298). */
 int flowcuda_sgd_step(float* p, const float* g, int64_t count, float lr, float grad_scale, void* stream);
 

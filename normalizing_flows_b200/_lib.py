@@ -101,6 +101,7 @@ SIGNATURES = {
     "flowcuda_base_noise": (_i, [_i, _u64, _u64, _p, _i64, _p]),
     "flowcuda_rotate2d": (_i, [_p, _f, _f, _i, _p, _i64, _p]),
     "flowcuda_sum_scaled": (_i, [_p, _i64, _d, _p, _p, _p]),
+    "flowcuda_sum_scaled_static": (_i, [_p, _i64, _d, _p, _p]),
     "flowcuda_sgd_step": (_i, [_p, _p, _i64, _f, _f, _p]),
     "flowcuda_adam_step": (_i, [_p, _p, _p, _p, _i64, _i64, _f, _f, _f, _f, _f, _p]),
     "flowcuda_affine_elementwise": (_i, [_p, _p, _p, _i, _i, _p, _p, _i64, _i64, _i64, _p]),

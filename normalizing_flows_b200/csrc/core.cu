@@ -168,6 +168,58 @@ int flowcuda_sum_scaled(const float* v, int64_t n, double scale, float* out, voi
   return FLOWCUDA_OK;
 }
 
+// ---- flowcuda_sum_scaled without a caller workspace and without any allocation ----------------------------
+// The stage-1 partials live in a file-scope device array instead of caller memory.  kSumBlocks doubles = 8 KB per
+// device, part of the module image: nothing here (or below it) calls cudaMalloc/cudaFree or an allocating library.
+// The array is ONE per device and per loaded library: it keeps the previous call's partials, and two calls that
+// overlap on the same device (different streams, or different host threads) race on it — callers serialise them
+// (same stream, or an event between them) or use flowcuda_sum_scaled with their own workspaces.
+static __device__ __align__(256) double g_sum_static_scratch[kSumBlocks];
+constexpr int64_t kSumStaticMaxN = (int64_t)1 << 26;  // 64 Mi floats (256 MB of input): stated limit of the entry point
+constexpr int kSumStaticMaxDevices = 64;
+
+// Device address of the scratch array on the CURRENT device.  The host-side symbol is a handle, not a device
+// address: it is resolved once per device with that device current, and the result is cached.
+static int sum_static_scratch(double** out) {
+  static double* cached[kSumStaticMaxDevices] = {nullptr};
+  int dev = -1;
+  FC_CUDA(cudaGetDevice(&dev));
+  FC_REQUIRE(dev >= 0 && dev < kSumStaticMaxDevices, "sum_scaled_static: device ordinal %d outside [0, %d)", dev,
+             kSumStaticMaxDevices);
+  double* p = __atomic_load_n(&cached[dev], __ATOMIC_ACQUIRE);
+  if (!p) {
+    void* sym = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&sym, g_sum_static_scratch);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_sum_static_scratch)");
+    FC_REQUIRE(sym != nullptr && ((uintptr_t)sym & 255) == 0, "sum_scaled_static: scratch symbol resolved to %p", sym);
+    p = (double*)sym;
+    __atomic_store_n(&cached[dev], p, __ATOMIC_RELEASE);  // every thread resolves the same address: benign if repeated
+  }
+  *out = p;
+  return FLOWCUDA_OK;
+}
+
+int flowcuda_sum_scaled_static(const float* v, int64_t n, double scale, float* out, void* stream) {
+  FC_REQUIRE(out && n >= 0 && (v || n == 0), "sum_scaled_static: NULL pointer or negative n");
+  FC_REQUIRE(n <= kSumStaticMaxN, "sum_scaled_static: n = %lld exceeds the limit of %lld elements of this entry point "
+             "(use flowcuda_sum_scaled with a caller workspace)", (long long)n, (long long)kSumStaticMaxN);
+  double* scratch = nullptr;
+  int rc = sum_static_scratch(&scratch);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  int nb = (int)((n + 4095) / 4096);  // same grid rule as flowcuda_sum_scaled -> same summation order, same bits
+  if (nb < 1) nb = 1;
+  if (nb > kSumBlocks) nb = kSumBlocks;
+  // Stage 1 overwrites every partial stage 2 reads, so nothing has to start at zero for a correct result; the slots
+  // are cleared all the same so that a stale partial of an earlier (larger) call can never be summed by mistake.
+  FC_CUDA(cudaMemsetAsync(scratch, 0, (size_t)nb * sizeof(double), s));
+  sum_stage1<<<nb, kSumThreads, 0, s>>>(v, n, scratch);
+  FC_LAUNCH_CHECK("sum_stage1 (static scratch)");
+  sum_stage2<<<1, kSumThreads, 0, s>>>(scratch, nb, scale, out);
+  FC_LAUNCH_CHECK("sum_stage2 (static scratch)");
+  return FLOWCUDA_OK;
+}
+
 int flowcuda_rotate2d(const float* x, float cos_theta, float sin_theta, int inverse, float* y, int64_t n, void* stream) {
   FC_REQUIRE(n >= 0 && ((x && y) || n == 0), "rotate2d: NULL pointer or negative n");
   FC_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)y & 15) == 0, "rotate2d: buffers must be 16-byte aligned");
