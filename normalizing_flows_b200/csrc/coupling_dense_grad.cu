@@ -21,7 +21,10 @@ struct CgLayout {
   int hmax;
   int tc;  // tensor-core engine (spec->precision == BF16X3)
   size_t off_aimg, off_bimg, a_bytes, b_bytes, part_floats;
+  int img;  // tensor-core engine + spline transform: the bijector adjoint writes dO as operand images (no fp32 dO)
+  size_t off_dOa, off_dOb, off_colp, dOa_bytes, dOb_bytes;
 };
+constexpr int kCgColSlices = 64;  // row slices of cg_transform_bwd_img_kernel = partial column sums per column
 
 static size_t cg_al(size_t x) { return (x + 255) & ~(size_t)255; }
 
@@ -60,7 +63,19 @@ static bool cg_layout(const flowcuda_coupling_spec* sp, int64_t n, CgLayout& L) 
   L.off_tmp2 = off; off = cg_al(off + (size_t)n * L.D * 4);
   L.off_ld = off; off = cg_al(off + (size_t)n * 4);
   L.off_lp = off; off = cg_al(off + (size_t)n * 4);
-  L.off_dO = off; off = cg_al(off + (size_t)n * L.D * L.P * 4);
+  L.tc = sp->precision == FLOWCUDA_PRECISION_BF16X3;
+  L.img = L.tc && sp->transform == FLOWCUDA_TRANSFORM_RQS;
+  L.off_dO = off;
+  if (!L.img) off = cg_al(off + (size_t)n * L.D * L.P * 4);
+  L.off_dOa = L.off_dOb = L.off_colp = off; L.dOa_bytes = L.dOb_bytes = 0;
+  if (L.img) {
+    const int64_t ncmax = (int64_t)((L.D + 1) / 2) * L.P;
+    L.dOa_bytes = mgtc_a_bytes(n, ncmax);
+    L.dOb_bytes = mgtc_b_bytes(ncmax, n);
+    L.off_dOa = off; off = cg_al(off + L.dOa_bytes);
+    L.off_dOb = off; off = cg_al(off + L.dOb_bytes);
+    L.off_colp = off; off = cg_al(off + (size_t)kCgColSlices * ncmax * sizeof(double));
+  }
   for (int j = 0; j < 2; ++j) { L.off_dh[j] = off; off = cg_al(off + (size_t)n * L.hmax * 4); }
   L.off_sum = off; off = cg_al(off + 1024 * 8);
   size_t mx = 0;
@@ -68,7 +83,6 @@ static bool cg_layout(const flowcuda_coupling_spec* sp, int64_t n, CgLayout& L) 
     const size_t e = (size_t)L.sizes[i] * L.sizes[i + 1];
     if (e > mx) mx = e;
   }
-  L.tc = sp->precision == FLOWCUDA_PRECISION_BF16X3;
   L.part_floats = mx * (L.tc ? kMgTcSplits : kMgSplits);
   {
     size_t wmax = 0;  // the column sums borrow the buffer: kMgColSlices doubles per column
@@ -261,6 +275,154 @@ __global__ void __launch_bounds__(128) cg_transform_bwd_compact_kernel(const flo
   }
 }
 
+// The tensor-core training step's form of that adjoint (spline transforms): dO never exists as an fp32 matrix.
+// The kernel writes it straight into the two operand images the reverse-mode GEMMs consume —
+//   A image  [m tile of 128 rows][k stage of 32 columns][hi|lo]   for  d h = dO · Wᵀ        (K = conditioner columns)
+//   B image  [n tile of 256 columns][k stage of 32 rows][hi|lo]   for  dW  = hᵀ · dO        (K = batch)
+// (the bf16 hi/lo split mgtc_pack_kernel would have made of the same values: bit-identical operands, two HBM passes
+// over dO fewer per flow layer) — and sums its columns for the bias gradient on the way (fixed order: eight rows in
+// float, then a double per (CTA, column) across the CTA's row blocks, then the slices in order in stage 2).
+// CTA = 8 rows x 32 dims (thread = one (sample, transformed dim) item, as above); the block's 8 x 32·PP values are
+// staged in shared memory, so that both images are written in full 128-byte runs: eight consecutive rows of one
+// 8-column chunk (A), eight consecutive columns of one 8-row chunk (B).  Row stride = 4 (mod 32) words: the A
+// pass's 128-bit reads of eight rows are conflict-free.  Pads (rows up to the next multiple of 128, columns up to
+// the next image tile) are written as zeros by the same passes, so no memset of the images is needed.
+struct CgBwdImg {
+  const float* v; const float* o; const float* g; float* gin;
+  int64_t N, ldo;
+  int D, tp, nd, ncomp;   // nd transformed dims, ncomp = nd * PP conditioner columns
+  int opad;               // 0: o holds the dims back to back (column k*PP); else dims per 128-column half of a GEMM tile
+  float lo, hi;
+  uint8_t* a_img; int KSa;
+  uint8_t* b_img; int KSb, NTb;
+  double* colpart;        // [gridDim.y][ncomp]
+  int rblocks;            // 8-row blocks, pads included
+};
+
+template <int K>
+__global__ void __launch_bounds__(256) cg_transform_bwd_img_kernel(CgBwdImg a) {
+  constexpr int PP = 3 * K + 1, CW = 32 * PP, RS = CW + 36 - (CW % 32), NJ = (CW + 255) / 256;
+  static_assert(CW % 8 == 0 && RS % 32 == 4, "chunk alignment / bank layout");
+  __shared__ __align__(16) float buf[8][RS];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int c = blockIdx.x, k0 = c * 32, k = k0 + lane;
+  const int per = (a.rblocks + gridDim.y - 1) / gridDim.y;
+  const int rb0 = blockIdx.y * per, rb1 = min(a.rblocks, rb0 + per);
+  const float ldbar = -1.f / (float)a.N;
+  const int64_t cb = (int64_t)c * CW;  // first conditioner column of this task
+  auto ocol = [&](int kk) { return a.opad ? (kk / a.opad) * 128 + (kk % a.opad) * PP : kk * PP; };
+  double csum[NJ];
+#pragma unroll
+  for (int j = 0; j < NJ; ++j) csum[j] = 0.0;
+  // the task's columns inside a row of o: one contiguous run [q0, q1) (pads of the tile layout included)
+  const int klast = min(k0 + 31, a.nd - 1);
+  const int q0 = k0 < a.nd ? ocol(k0) : 0, q1 = k0 < a.nd ? ocol(klast) + PP : 0;
+  const int cq0 = a.opad ? (q0 >> 7) * (a.opad * PP) + (q0 & 127) : q0;  // q0 as a back-to-back column
+  constexpr int NL = (CW + 31 + 3 * 8) / 32;  // loads per lane that cover the run
+  for (int rb = rb0; rb < rb1; ++rb) {
+    const int64_t r = (int64_t)rb * 8 + warp;
+    float* row = buf[warp];
+    const bool valid = r < a.N && k < a.nd;
+    float xv = 0.f, gv = 0.f, gp = 0.f;
+    if (valid) {  // issued before the staging loads complete
+      const int64_t xi = r * a.D + a.tp + 2 * k;
+      xv = a.v[xi];
+      gv = a.g[xi];
+      if (((a.tp + 2 * k) ^ 1) < a.D) gp = a.g[r * a.D + ((a.tp + 2 * k) ^ 1)];
+    }
+    if (r < a.N) {
+      const float* __restrict__ src = a.o + r * a.ldo + q0;
+      float t[NL];
+#pragma unroll
+      for (int i = 0; i < NL; ++i) {  // all loads first: one round trip per row block, not one per dim
+        const int e = lane + 32 * i;
+        t[i] = e < q1 - q0 ? src[e] : 0.f;
+      }
+#pragma unroll
+      for (int i = 0; i < NL; ++i) {
+        const int e = lane + 32 * i;
+        if (e >= q1 - q0) continue;
+        const int q = q0 + e;
+        if (a.opad) {
+          if ((q & 127) < a.opad * PP) row[(q >> 7) * (a.opad * PP) + (q & 127) - cq0] = t[i];
+        } else {
+          row[e] = t[i];
+        }
+      }
+    }
+    __syncwarp();
+    float obar[PP];
+    if (valid) {
+      const int d = a.tp + 2 * k;
+      const int64_t xi = r * a.D + d;
+      float ov[PP];
+#pragma unroll
+      for (int p = 0; p < PP; ++p) ov[p] = row[lane * PP + p];
+      float y, l1, xbar;
+      rqs_fwd_bwd<K>(ov, a.lo, a.hi, xv, gv, ldbar, y, l1, xbar, obar);
+      a.gin[xi] = xbar;
+      if ((d ^ 1) < a.D) a.gin[r * a.D + (d ^ 1)] = gp;  // the pass-through neighbour
+      if (a.tp == 1 && (a.D & 1) && k == a.nd - 1) a.gin[r * a.D + a.D - 1] = a.g[r * a.D + a.D - 1];
+    } else {
+#pragma unroll
+      for (int p = 0; p < PP; ++p) obar[p] = 0.f;
+    }
+    __syncwarp();
+#pragma unroll
+    for (int p = 0; p < PP; ++p) row[lane * PP + p] = obar[p];
+    __syncthreads();
+    // A image: (8-column chunk, row) items, the eight rows of a chunk adjacent
+    {
+      const int64_t r0 = (int64_t)rb * 8;
+      const int64_t mt = r0 >> 7;
+      for (int idx = tid; idx < CW; idx += 256) {
+        const int row8 = idx & 7, cc = idx >> 3;
+        const int64_t gc = (cb >> 3) + cc;  // global chunk of 8 columns
+        if (gc >= (int64_t)a.KSa * 4) continue;
+        const float4 f0 = *reinterpret_cast<const float4*>(&buf[row8][cc * 8]);
+        const float4 f1 = *reinterpret_cast<const float4*>(&buf[row8][cc * 8 + 4]);
+        uint32_t h[4], l[4];
+        tc::split_bf16x2(f0.x, f0.y, h[0], l[0]);
+        tc::split_bf16x2(f0.z, f0.w, h[1], l[1]);
+        tc::split_bf16x2(f1.x, f1.y, h[2], l[2]);
+        tc::split_bf16x2(f1.z, f1.w, h[3], l[3]);
+        uint8_t* st = a.a_img + ((mt * a.KSa + (gc >> 2)) * 2) * (int64_t)kDtABytes +
+                      tc::img_off(128, (int)((r0 + row8) & 127), (int)(gc & 3));
+        *reinterpret_cast<uint4*>(st) = make_uint4(h[0], h[1], h[2], h[3]);
+        *reinterpret_cast<uint4*>(st + kDtABytes) = make_uint4(l[0], l[1], l[2], l[3]);
+      }
+      // B image + column sums: one column per item, its eight rows are one 8-element K chunk
+      const bool brow = r0 < (int64_t)a.KSb * 32;
+      const int ks = (int)(r0 >> 5), c4 = (int)((r0 & 31) >> 3);
+#pragma unroll
+      for (int j = 0; j < NJ; ++j) {
+        const int jj = tid + 256 * j;
+        if (jj >= CW) break;
+        const int64_t col = cb + jj;
+        if (col >= (int64_t)a.NTb * kDtBN) continue;
+        float f[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) f[e] = buf[e][jj];
+        csum[j] += (double)(((f[0] + f[1]) + (f[2] + f[3])) + ((f[4] + f[5]) + (f[6] + f[7])));
+        if (!brow) continue;
+        uint32_t h[4], l[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) tc::split_bf16x2(f[2 * e], f[2 * e + 1], h[e], l[e]);
+        uint8_t* st = a.b_img + (((col >> 8) * a.KSb + ks) * 2) * (int64_t)kDtBBytes + tc::img_off(kDtBN, (int)(col & 255), c4);
+        *reinterpret_cast<uint4*>(st) = make_uint4(h[0], h[1], h[2], h[3]);
+        *reinterpret_cast<uint4*>(st + kDtBBytes) = make_uint4(l[0], l[1], l[2], l[3]);
+      }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int j = 0; j < NJ; ++j) {
+    const int jj = tid + 256 * j;
+    const int64_t col = cb + jj;
+    if (jj < CW && col < a.ncomp) a.colpart[(int64_t)blockIdx.y * a.ncomp + col] = csum[j];
+  }
+}
+
 // gin[:, visible dims] += dmx[:, visible dims]
 __global__ void __launch_bounds__(256) cg_add_visible_kernel(const float* __restrict__ dmx, float* __restrict__ gin, int64_t N,
                                                             int D, int tp) {
@@ -324,7 +486,25 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
     const int ncomp = ((D - tp + 1) / 2) * P;
     const int64_t ldo = L.tc ? ncomp : 0;
     const MgColMap cm = {0, P, 2 * P, tp * P};
-    if (ldo)
+    const int nd = ncomp / P;
+    const int KSa = (ncomp + kDtBK - 1) / kDtBK, KSb = (int)((n + kDtBK - 1) / kDtBK), NTb = (ncomp + kDtBN - 1) / kDtBN;
+    int cslices = 1;
+    if constexpr (K > 0) {
+      if (L.img) {
+        CgBwdImg bi = {};
+        bi.v = V(l); bi.o = H(l, nh); bi.g = G; bi.gin = S; bi.N = n; bi.ldo = ldo; bi.D = D; bi.tp = tp; bi.nd = nd;
+        bi.ncomp = ncomp; bi.opad = 0; bi.lo = sp->range_min; bi.hi = sp->range_max;
+        bi.a_img = ws + L.off_dOa; bi.KSa = KSa; bi.b_img = ws + L.off_dOb; bi.KSb = KSb; bi.NTb = NTb;
+        bi.colpart = (double*)(ws + L.off_colp);
+        bi.rblocks = (int)(((n + 127) / 128) * 16);
+        cslices = bi.rblocks < kCgColSlices ? bi.rblocks : kCgColSlices;
+        constexpr int CW = 32 * (3 * K + 1);
+        const int64_t cols = (int64_t)KSa * kDtBK > (int64_t)NTb * kDtBN ? (int64_t)KSa * kDtBK : (int64_t)NTb * kDtBN;
+        cg_transform_bwd_img_kernel<K><<<dim3((unsigned)((cols + CW - 1) / CW), cslices), 256, 0, s>>>(bi);
+      }
+    }
+    if (L.img) {
+    } else if (ldo)
       cg_transform_bwd_compact_kernel<K><<<grid_for(((int64_t)n * (ncomp / P) + 31) / 32, 4, 16), 128, 0, s>>>(
           V(l), H(l, nh), G, S, dO, n, D, tp, sp->range_min, sp->range_max);
     else
@@ -335,23 +515,30 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
     const float* dout = dO;
     for (int i = nh; i >= 0; --i) {
       const bool last = i == nh && L.tc;  // compact dO: the other columns' gradients are exactly zero
+      const bool pre = last && L.img;     // ... and it exists only as the two operand images
       const int kin = L.sizes[i], nfull = L.sizes[i + 1], nout = last ? ncomp : nfull;
       const float* in = i == 0 ? MX : H(l, i - 1);
       // dW_i = inᵀ · dout (split-K, fixed-order reduce), db_i = column sums
       if (last) FC_CUDA(cudaMemsetAsync(Gl + L.w_off[i], 0, ((size_t)kin * nfull + nfull) * sizeof(float), s));
+      MgColMap bm = cm;
+      bm.mode = last ? 3 : 0;
+      if (pre) {  // the partial column sums came with the images; add the slices before `part` is reused
+        mg_colsum_stage2<<<(nout + 255) / 256, 256, 0, s>>>((const double*)(ws + L.off_colp), cslices, nout, Gl + L.b_off[i], bm);
+        FC_LAUNCH_CHECK("mg_colsum_stage2");
+      }
       MgGemm g = mg_gemm(in, 1, kin, dout, nout, 1, Gl + L.w_off[i], nfull, kin, nout, n);
       g.splits = splits; g.part = part;
       if (last) { g.map = cm; g.map.mode = 3; }
-      if ((rc = mg_launch(g, s))) return rc;
-      MgColMap bm = cm;
-      bm.mode = last ? 3 : 0;
-      if ((rc = mg_colsum(dout, n, nout, Gl + L.b_off[i], part, s, bm))) return rc;
+      if (pre) { if ((rc = mgtc_launch(g, sc, s, MgTcPre{nullptr, ws + L.off_dOb}))) return rc; }
+      else if ((rc = mg_launch(g, s))) return rc;
+      if (!pre && (rc = mg_colsum(dout, n, nout, Gl + L.b_off[i], part, s, bm))) return rc;
       // d in = dout · W_iᵀ (relu gate of the stored activation; the masked input has no gate)
       float* din = i == 0 ? DMX : dH[i & 1];
       g = mg_gemm(dout, nout, 1, Pl + L.w_off[i], 1, nfull, din, kin, N, kin, nout);
       if (last) { g.map = cm; g.map.mode = 2; }
       if (i > 0) { g.gate = H(l, i - 1); g.ldg = kin; }
-      if ((rc = mg_launch(g, s))) return rc;
+      if (pre) { if ((rc = mgtc_launch(g, sc, s, MgTcPre{ws + L.off_dOa, nullptr}))) return rc; }
+      else if ((rc = mg_launch(g, s))) return rc;
       dout = din;
     }
     cg_add_visible_kernel<<<eb, 256, 0, s>>>(DMX, S, n, D, tp);

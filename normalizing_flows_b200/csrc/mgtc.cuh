@@ -348,8 +348,14 @@ static inline size_t mgtc_b_bytes(int64_t N, int64_t K) {
   return (size_t)((N + kDtBN - 1) / kDtBN) * (size_t)((K + kDtBK - 1) / kDtBK) * 2 * kDtBBytes;
 }
 
+// Operand images some other kernel has already written in the engine's format (NULL: pack op(A) / op(B) here).
+struct MgTcPre {
+  const uint8_t* a_img;
+  const uint8_t* b_img;
+};
+
 // Same contract as mg_launch; the engine itself decides whether and how far to split K.
-static int mgtc_launch(MgGemm g, const MgTcScratch& sc, cudaStream_t s) {
+static int mgtc_launch(MgGemm g, const MgTcScratch& sc, cudaStream_t s, MgTcPre pre = MgTcPre{nullptr, nullptr}) {
   MgTcArgs a = {};
   a.MT = (g.M + 127) / 128;
   a.NT = (g.N + kDtBN - 1) / kDtBN;
@@ -377,12 +383,12 @@ static int mgtc_launch(MgGemm g, const MgTcScratch& sc, cudaStream_t s) {
   a.ks_chunk = (a.KS + a.S - 1) / a.S;
   a.S = (a.KS + a.ks_chunk - 1) / a.ks_chunk;
   const size_t ab = mgtc_a_bytes(g.M, g.K), bb = mgtc_b_bytes(g.N, g.K);
-  if (ab > sc.a_bytes || bb > sc.b_bytes) {
+  if ((!pre.a_img && ab > sc.a_bytes) || (!pre.b_img && bb > sc.b_bytes)) {
     set_error("mgtc_launch: operand images (%zu, %zu bytes) exceed the scratch (%zu, %zu)", ab, bb, sc.a_bytes, sc.b_bytes);
     return FLOWCUDA_EWORKSPACE;
   }
   const MgMask none = {};
-  {
+  if (!pre.a_img) {
     const int64_t total = (int64_t)a.MT * 128 * a.KS * 4;
     const int gr = grid_for(total, 256, 8);
     if (g.acs == 1)
@@ -391,7 +397,7 @@ static int mgtc_launch(MgGemm g, const MgTcScratch& sc, cudaStream_t s) {
       mgtc_pack_kernel<128, false><<<gr, 256, 0, s>>>(g.A, g.ars, g.acs, g.M, g.K, a.KS, a.MT, none, 0, MgColMap{}, sc.a_img);
     FC_LAUNCH_CHECK("mgtc_pack_kernel<A>");
   }
-  {
+  if (!pre.b_img) {
     const int64_t total = (int64_t)a.NT * kDtBN * a.KS * 4;
     // B(k, j) = B[k*brs + j*bcs]: image row j, K index k
     const int gr = grid_for(total, 256, 8);
@@ -403,8 +409,8 @@ static int mgtc_launch(MgGemm g, const MgTcScratch& sc, cudaStream_t s) {
       mgtc_pack_kernel<kDtBN, false><<<gr, 256, 0, s>>>(g.B, g.bcs, g.brs, g.N, g.K, a.KS, a.NT, g.mask, mm, bm, sc.b_img);
     FC_LAUNCH_CHECK("mgtc_pack_kernel<B>");
   }
-  a.a_img = sc.a_img;
-  a.b_img = sc.b_img;
+  a.a_img = pre.a_img ? pre.a_img : sc.a_img;
+  a.b_img = pre.b_img ? pre.b_img : sc.b_img;
   g.splits = a.S;
   g.part = a.S > 1 ? sc.part : nullptr;
   a.g = g;
