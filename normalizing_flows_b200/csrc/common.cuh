@@ -224,4 +224,30 @@ inline int grid_for(int64_t work_items, int per_block, int waves_cap = 8) {
   return (int)(need < cap ? need : cap);
 }
 
+// one 256-bit store (sm_100: STG.256): eight 32-bit words to a 32-byte aligned address
+__device__ __forceinline__ void st_global_v8(float* p, const uint32_t* w) {
+  asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]),
+               "r"(w[5]), "r"(w[6]), "r"(w[7])
+               : "memory");
+}
+
+// Training forward through the density path's GEMMs (coupling_dense_tc.cu) — what coupling_dense_grad.cu asks the
+// epilogues to keep for the reverse mode.  Per flow layer l one activation block of `per_layer_act` floats:
+//   [0, N*D)            the layer's input state v
+//   act_h[i], i < nh    relu(h_{i+1}) as fp32 [N, hidden_i]
+//   act_h[nh]           the last Linear's RAW accumulators (no bias) in tile-column order, fp32 [N, ldo]
+struct DtTrainStores {
+  float* act;
+  size_t per_layer_act;
+  size_t act_h[FLOWCUDA_MAX_HIDDEN_LAYERS + 1];
+  int64_t ldo;
+};
+bool coupling_dense_tc_supported(const flowcuda_coupling_spec* sp);
+size_t coupling_dense_tc_workspace_bytes(const flowcuda_coupling_spec* sp, int64_t n);
+int64_t coupling_dense_tc_store_ldo(const flowcuda_coupling_spec* sp);
+// data -> base pass over all layers with the stores above; out_z [N, D] and out_ld [N] (sum of the log-dets)
+int coupling_dense_tc_train_forward(const flowcuda_coupling_spec* sp, const float* params, const float* x, int64_t n,
+                                    const DtTrainStores& tr, float* out_z, float* out_ld, void* workspace,
+                                    size_t workspace_bytes, cudaStream_t s);
+
 }  // namespace flowcuda

@@ -22,6 +22,9 @@ struct CgLayout {
   int tc;  // tensor-core engine (spec->precision == BF16X3)
   size_t off_aimg, off_bimg, a_bytes, b_bytes, part_floats;
   int img;  // tensor-core engine + spline transform: the bijector adjoint writes dO as operand images (no fp32 dO)
+  int fwd_dt;  // ... and the forward pass runs on the density path's GEMMs with fused epilogues (coupling_dense_tc.cu)
+  int64_t ldo_dt;
+  size_t off_dt, dt_bytes;
   size_t off_dOa, off_dOb, off_colp, dOa_bytes, dOb_bytes;
 };
 constexpr int kCgColSlices = 64;  // row slices of cg_transform_bwd_img_kernel = partial column sums per column
@@ -53,8 +56,17 @@ static bool cg_layout(const flowcuda_coupling_spec* sp, int64_t n, CgLayout& L) 
     L.b_off[i] = o; o += L.sizes[i + 1];
   }
   L.per_layer = o;
-  size_t a = (size_t)n * L.D;  // v
-  for (int i = 0; i < L.nlin; ++i) { L.act_h[i] = a; a += (size_t)n * L.sizes[i + 1]; }
+  L.tc = sp->precision == FLOWCUDA_PRECISION_BF16X3;
+  L.img = L.tc && sp->transform == FLOWCUDA_TRANSFORM_RQS;
+  L.fwd_dt = L.img && sp->num_bins == 8 && coupling_dense_tc_supported(sp);
+  L.ldo_dt = L.fwd_dt ? coupling_dense_tc_store_ldo(sp) : 0;
+  auto al64 = [](size_t x) { return (x + 63) & ~(size_t)63; };  // 256-byte aligned blocks: the epilogues store 16-byte vectors
+  size_t a = al64((size_t)n * L.D);  // v
+  for (int i = 0; i < L.nlin; ++i) {
+    size_t w = L.sizes[i + 1];
+    if (i == L.nh && L.fwd_dt && (size_t)L.ldo_dt > w) w = L.ldo_dt;
+    L.act_h[i] = a; a = al64(a + (size_t)n * w);
+  }
   L.per_layer_act = a;
   size_t off = 0;
   L.off_state = off; off = cg_al(off + (size_t)n * L.D * 4);
@@ -63,8 +75,6 @@ static bool cg_layout(const flowcuda_coupling_spec* sp, int64_t n, CgLayout& L) 
   L.off_tmp2 = off; off = cg_al(off + (size_t)n * L.D * 4);
   L.off_ld = off; off = cg_al(off + (size_t)n * 4);
   L.off_lp = off; off = cg_al(off + (size_t)n * 4);
-  L.tc = sp->precision == FLOWCUDA_PRECISION_BF16X3;
-  L.img = L.tc && sp->transform == FLOWCUDA_TRANSFORM_RQS;
   L.off_dO = off;
   if (!L.img) off = cg_al(off + (size_t)n * L.D * L.P * 4);
   L.off_dOa = L.off_dOb = L.off_colp = off; L.dOa_bytes = L.dOb_bytes = 0;
@@ -104,6 +114,8 @@ static bool cg_layout(const flowcuda_coupling_spec* sp, int64_t n, CgLayout& L) 
     L.off_aimg = off; off = cg_al(off + L.a_bytes);
     L.off_bimg = off; off = cg_al(off + L.b_bytes);
   }
+  L.off_dt = off; L.dt_bytes = 0;
+  if (L.fwd_dt) { L.dt_bytes = coupling_dense_tc_workspace_bytes(sp, n) + 256; off = cg_al(off + L.dt_bytes); }
   L.off_act = off; off = cg_al(off + L.per_layer_act * 4 * (size_t)L.L);
   L.total = off + 256;
   return true;
@@ -297,6 +309,7 @@ struct CgBwdImg {
   uint8_t* b_img; int KSb, NTb;
   double* colpart;        // [gridDim.y][ncomp]
   int rblocks;            // 8-row blocks, pads included
+  const float* bias;      // o holds raw accumulators: + bias[(tp + 2k)*PP + p] (the last Linear's full bias); NULL: o is final
 };
 
 template <int K>
@@ -304,8 +317,14 @@ __global__ void __launch_bounds__(256) cg_transform_bwd_img_kernel(CgBwdImg a) {
   constexpr int PP = 3 * K + 1, CW = 32 * PP, RS = CW + 36 - (CW % 32), NJ = (CW + 255) / 256;
   static_assert(CW % 8 == 0 && RS % 32 == 4, "chunk alignment / bank layout");
   __shared__ __align__(16) float buf[8][RS];
+  __shared__ float sbias[CW];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int c = blockIdx.x, k0 = c * 32, k = k0 + lane;
+  for (int e = tid; e < CW; e += 256) {
+    const int kk = k0 + e / PP;
+    sbias[e] = (a.bias != nullptr && kk < a.nd) ? a.bias[(a.tp + 2 * kk) * PP + e % PP] : 0.f;
+  }
+  __syncthreads();
   const int per = (a.rblocks + gridDim.y - 1) / gridDim.y;
   const int rb0 = blockIdx.y * per, rb1 = min(a.rblocks, rb0 + per);
   const float ldbar = -1.f / (float)a.N;
@@ -357,7 +376,7 @@ __global__ void __launch_bounds__(256) cg_transform_bwd_img_kernel(CgBwdImg a) {
       const int64_t xi = r * a.D + d;
       float ov[PP];
 #pragma unroll
-      for (int p = 0; p < PP; ++p) ov[p] = row[lane * PP + p];
+      for (int p = 0; p < PP; ++p) ov[p] = row[lane * PP + p] + sbias[lane * PP + p];
       float y, l1, xbar;
       rqs_fwd_bwd<K>(ov, a.lo, a.hi, xv, gv, ldbar, y, l1, xbar, obar);
       a.gin[xi] = xbar;
@@ -453,6 +472,14 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
   int rc;
   const MgTcScratch sc = {ws + L.off_aimg, L.a_bytes, ws + L.off_bimg, L.b_bytes, part, L.part_floats};
   auto mg_launch = [&](const MgGemm& g, cudaStream_t st) { return L.tc ? mgtc_launch(g, sc, st) : flowcuda::mg_launch(g, st); };
+  if (L.fwd_dt) {
+    // forward on the density path: per layer four GEMMs whose epilogues apply relu / the spline, write the next
+    // operand image AND leave the reverse mode's operands behind (fp32 h_i, raw conditioner accumulators, layer inputs)
+    DtTrainStores tr = {};
+    tr.act = act; tr.per_layer_act = L.per_layer_act; tr.ldo = L.ldo_dt;
+    for (int i = 0; i < L.nlin; ++i) tr.act_h[i] = L.act_h[i];
+    if ((rc = coupling_dense_tc_train_forward(sp, params, x, n, tr, S, LD, ws + L.off_dt, L.dt_bytes, s))) return rc;
+  } else {
   FC_CUDA(cudaMemcpyAsync(S, x, (size_t)n * D * 4, cudaMemcpyDeviceToDevice, s));
   for (int it = 0; it < L.L; ++it) {  // data -> base: layer L-1 first (Inverse(Chain(layers)))
     const int l = L.L - 1 - it, tp = l & 1;
@@ -476,6 +503,7 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
     cg_transform_fwd_kernel<K><<<rb, 256, 0, s>>>(V(l), H(l, nh), S, LD, n, D, P, tp, sp->range_min, sp->range_max, it == 0, ldo);
     FC_LAUNCH_CHECK("coupling_nll_grad forward");
   }
+  }
   cg_finish_kernel<<<rb, 256, 0, s>>>(S, LD, LP, G, n, D, sp->base);
   FC_LAUNCH_CHECK("cg_finish_kernel");
   if ((rc = flowcuda_sum_scaled(LP, n, -1.0 / (double)n, loss, ws + L.off_sum, s))) return rc;
@@ -494,6 +522,7 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
         CgBwdImg bi = {};
         bi.v = V(l); bi.o = H(l, nh); bi.g = G; bi.gin = S; bi.N = n; bi.ldo = ldo; bi.D = D; bi.tp = tp; bi.nd = nd;
         bi.ncomp = ncomp; bi.opad = 0; bi.lo = sp->range_min; bi.hi = sp->range_max;
+        if (L.fwd_dt) { bi.opad = 5; bi.ldo = L.ldo_dt; bi.bias = Pl + L.b_off[nh]; }
         bi.a_img = ws + L.off_dOa; bi.KSa = KSa; bi.b_img = ws + L.off_dOb; bi.KSb = KSb; bi.NTb = NTb;
         bi.colpart = (double*)(ws + L.off_colp);
         bi.rblocks = (int)(((n + 127) / 128) * 16);

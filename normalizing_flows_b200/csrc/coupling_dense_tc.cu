@@ -142,9 +142,9 @@ size_t coupling_dense_tc_workspace_bytes(const flowcuda_coupling_spec* sp, int64
   return L.total;
 }
 
-int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params, const float* in, float* out_v,
-                          float* out_lp, float* out_ld, int64_t n, int layer_begin, int layer_end, int with_base,
-                          bool inverse, void* workspace, size_t workspace_bytes, cudaStream_t s, int mode) {
+static int dt_run(const flowcuda_coupling_spec* sp, const float* params, const float* in, float* out_v,
+                  float* out_lp, float* out_ld, int64_t n, int layer_begin, int layer_end, int with_base,
+                  bool inverse, void* workspace, size_t workspace_bytes, cudaStream_t s, int mode, const DtTrainStores* tr) {
   // mode 0: pack the weights, then run; 1: the workspace already holds this flow's weight images; 2: pack only
   DtLayout L;
   if (!dt_layout(sp, n, L)) {
@@ -188,6 +188,7 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
     // transform epilogue (its transformed dims are this layer's visible dims).  Odd event sizes: the two parities
     // differ by one dim, whose column the epilogue never writes - keep the packing pass there.
     const bool fuse_x = (D % 2) == 0;
+    if (tr) FC_CUDA(cudaMemcpyAsync(tr->act + (size_t)l * tr->per_layer_act, v, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToDevice, s));
     if (it == 0 || !fuse_x) {
       int64_t total = L.MT * 128 * L.KS[0] * 4;
       int blocks = (int)((total + 255) / 256);
@@ -208,6 +209,11 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
       for (int i = 0; i < 9; ++i) g.koff[i] = sp->range_min + (float)i * kRqsMinBin;
       int rc;
       const Dt2Launch dl = {L.MT, (int64_t)sp->num_layers * L.NT[i], (int64_t)l * L.NT[i]};
+      if (tr) {
+        float* blk = tr->act + (size_t)l * tr->per_layer_act + tr->act_h[i];
+        if (i < nh) { g.store_h = blk; g.store_ld = L.sizes[i + 1]; }
+        else { g.store_o = blk; g.store_ldo = tr->ldo; }
+      }
       if (i < nh) {
         g.out_img = ws + L.off_h[i & 1];
         g.out_KS = L.KS[i + 1];
@@ -237,6 +243,25 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
   }
   if (out_v) FC_CUDA(cudaMemcpyAsync(out_v, v, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToDevice, s));
   return FLOWCUDA_OK;
+}
+
+int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params, const float* in, float* out_v,
+                          float* out_lp, float* out_ld, int64_t n, int layer_begin, int layer_end, int with_base,
+                          bool inverse, void* workspace, size_t workspace_bytes, cudaStream_t s, int mode) {
+  return dt_run(sp, params, in, out_v, out_lp, out_ld, n, layer_begin, layer_end, with_base, inverse, workspace,
+                workspace_bytes, s, mode, nullptr);
+}
+
+int64_t coupling_dense_tc_store_ldo(const flowcuda_coupling_spec* sp) {
+  DtLayout L;
+  if (!dt_layout(sp, 128, L)) return 0;
+  return (int64_t)L.tiles * kDtBN;
+}
+
+int coupling_dense_tc_train_forward(const flowcuda_coupling_spec* sp, const float* params, const float* x, int64_t n,
+                                    const DtTrainStores& tr, float* out_z, float* out_ld, void* workspace,
+                                    size_t workspace_bytes, cudaStream_t s) {
+  return dt_run(sp, params, x, out_z, nullptr, out_ld, n, 0, sp->num_layers, 0, false, workspace, workspace_bytes, s, 0, &tr);
 }
 
 }  // namespace flowcuda

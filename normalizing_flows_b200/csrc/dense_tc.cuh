@@ -80,6 +80,11 @@ struct DtGemm {
   float lo, hi;
   float koff[9];         // RQS epilogue: lo + i * min_bin_size (constant-bank operands of rqs_apply_mufu)
   unsigned char ks_tile[kDtMaxKsTiles];  // K stages n tile nt really needs (0 = all KS)
+  // Training forward (coupling_dense_grad.cu): what the reverse mode reads back, stored by the same epilogues.
+  float* store_h;        // hidden epilogue: relu(A·W + b) as fp32 [N, store_ld] (NULL: not stored)
+  int64_t store_ld;
+  float* store_o;        // RQS epilogue: the RAW accumulator (A·W, no bias) in tile-column order, fp32 [N, store_ldo]:
+  int64_t store_ldo;     //   column nt*256 + c of a row = tile column c of n tile nt (dt_dim_to_col; 3 pad columns per half)
 };
 
 constexpr int kEpiHidden = 0, kEpiRqs8 = 1, kEpiAffine = 2;
@@ -156,11 +161,23 @@ __device__ __forceinline__ void dt_epilogue(const DtGemm& a, int mt, int nt, uin
       tc::tmem_ld_x16(tb + (uint32_t)c, vv);
       tc::tmem_ld_wait();
       uint32_t h[8], l[8];
+      float fv[16];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const float f0 = fmaxf(__uint_as_float(vv[2 * e]) + sbias[c + 2 * e], 0.f);
-        const float f1 = fmaxf(__uint_as_float(vv[2 * e + 1]) + sbias[c + 2 * e + 1], 0.f);
-        tc::split_bf16x2(f0, f1, h[e], l[e]);
+      for (int e = 0; e < 16; ++e) fv[e] = fmaxf(__uint_as_float(vv[e]) + sbias[c + e], 0.f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) tc::split_bf16x2(fv[2 * e], fv[2 * e + 1], h[e], l[e]);
+      if (a.store_h != nullptr && grow < a.N) {  // training: the reverse mode's relu gate and weight-gradient operand
+        const int col = nt * kDtBN + c;
+        float* dst = a.store_h + grow * a.store_ld + col;
+        if (col + 16 <= a.n_out && ((uintptr_t)dst & 15) == 0) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q)
+            reinterpret_cast<float4*>(dst)[q] = make_float4(fv[4 * q], fv[4 * q + 1], fv[4 * q + 2], fv[4 * q + 3]);
+        } else {
+#pragma unroll
+          for (int e = 0; e < 16; ++e)
+            if (col + e < a.n_out) dst[e] = fv[e];
+        }
       }
 #pragma unroll
       for (int q = 0; q < 2; ++q) {
@@ -297,6 +314,33 @@ __device__ __forceinline__ void dt_epilogue_rqs_tile(const DtGemm& a, int mt, in
   const int row = (warp & 3) * 32 + lane;
   const int64_t grow = (int64_t)mt * 128 + row;
   float ldsum[2] = {0.f, 0.f};
+  if (a.store_o != nullptr) {
+    // training: the conditioner output is read back by the spline adjoint.  The accumulator columns of this warp's
+    // dims go out as they sit in TMEM (16-column groups, 64 contiguous bytes per row and group) — the bias is added
+    // by the reader, and the 25-column runs of a dim would not be 16-byte aligned
+    const int dv = min(d_hi, a.ndims - nt * 10);  // valid dims end
+    if (dv > d_lo) {
+      const int cA = dt_dim_to_col(d_lo, 10, 25) & ~31, cB = (dt_dim_to_col(dv - 1, 10, 25) + 25 + 31) & ~31;
+      float* dst = a.store_o + grow * a.store_ldo + (int64_t)nt * kDtBN;
+      // 64 columns per TMEM round trip, 256-bit stores: a thread writes whole 32-byte sectors of its row
+#pragma unroll 1
+      for (int c = cA; c < cB; c += 64) {
+        uint32_t v0[32], v1[32];
+        const bool two = c + 32 < cB;  // uniform
+        tc::tmem_ld_x32(tb + (uint32_t)(c - cshift), v0);
+        if (two) tc::tmem_ld_x32(tb + (uint32_t)(c + 32 - cshift), v1);
+        tc::tmem_ld_wait();
+        if (grow < a.N) {
+#pragma unroll
+          for (int q = 0; q < 4; ++q) st_global_v8(dst + c + 8 * q, v0 + 8 * q);
+          if (two) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) st_global_v8(dst + c + 32 + 8 * q, v1 + 8 * q);
+          }
+        }
+      }
+    }
+  }
   // the loop is not unrolled (one copy of the spline code): the state values are consumed from the head of two
   // register queues that shift by one per iteration — a runtime index would put the arrays in local memory
 #pragma unroll 1
