@@ -317,14 +317,11 @@ __global__ void __launch_bounds__(256) cg_transform_bwd_img_kernel(CgBwdImg a) {
   constexpr int PP = 3 * K + 1, CW = 32 * PP, RS = CW + 36 - (CW % 32), NJ = (CW + 255) / 256;
   static_assert(CW % 8 == 0 && RS % 32 == 4, "chunk alignment / bank layout");
   __shared__ __align__(16) float buf[8][RS];
-  __shared__ float sbias[CW];
+  constexpr int NL = (CW + 31 + 3 * 8) / 32;  // loads per lane that cover a row's run of this task's columns
+  __shared__ float sbe[NL * 32];               // bias of run element e (0 where o already holds the final values)
+  __shared__ unsigned short sdst[NL * 32];     // run element e -> column inside the task (0xffff: pad of the tile layout)
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int c = blockIdx.x, k0 = c * 32, k = k0 + lane;
-  for (int e = tid; e < CW; e += 256) {
-    const int kk = k0 + e / PP;
-    sbias[e] = (a.bias != nullptr && kk < a.nd) ? a.bias[(a.tp + 2 * kk) * PP + e % PP] : 0.f;
-  }
-  __syncthreads();
   const int per = (a.rblocks + gridDim.y - 1) / gridDim.y;
   const int rb0 = blockIdx.y * per, rb1 = min(a.rblocks, rb0 + per);
   const float ldbar = -1.f / (float)a.N;
@@ -333,11 +330,23 @@ __global__ void __launch_bounds__(256) cg_transform_bwd_img_kernel(CgBwdImg a) {
   double csum[NJ];
 #pragma unroll
   for (int j = 0; j < NJ; ++j) csum[j] = 0.0;
-  // the task's columns inside a row of o: one contiguous run [q0, q1) (pads of the tile layout included)
+  // the task's columns inside a row of o: one contiguous run [q0, q1) (pads of the tile layout included); where each
+  // element of the run goes, and its bias, is the same for every row: tabulated once
   const int klast = min(k0 + 31, a.nd - 1);
   const int q0 = k0 < a.nd ? ocol(k0) : 0, q1 = k0 < a.nd ? ocol(klast) + PP : 0;
-  const int cq0 = a.opad ? (q0 >> 7) * (a.opad * PP) + (q0 & 127) : q0;  // q0 as a back-to-back column
-  constexpr int NL = (CW + 31 + 3 * 8) / 32;  // loads per lane that cover the run
+  for (int e = tid; e < NL * 32; e += 256) {
+    int d = 0xffff;
+    float b = 0.f;
+    if (e < q1 - q0) {
+      const int q = q0 + e;
+      if (!a.opad) d = e;
+      else if ((q & 127) < a.opad * PP) d = (q >> 7) * (a.opad * PP) + (q & 127) - (int)cb;
+      if (d != 0xffff && a.bias != nullptr) b = a.bias[(a.tp + 2 * (k0 + d / PP)) * PP + d % PP];
+    }
+    sdst[e] = (unsigned short)d;
+    sbe[e] = b;
+  }
+  __syncthreads();
   for (int rb = rb0; rb < rb1; ++rb) {
     const int64_t r = (int64_t)rb * 8 + warp;
     float* row = buf[warp];
@@ -357,17 +366,15 @@ __global__ void __launch_bounds__(256) cg_transform_bwd_img_kernel(CgBwdImg a) {
         const int e = lane + 32 * i;
         t[i] = e < q1 - q0 ? src[e] : 0.f;
       }
+      int dd[NL];  // table reads first: behind the stores below they would be ordered one by one (same address space)
 #pragma unroll
       for (int i = 0; i < NL; ++i) {
-        const int e = lane + 32 * i;
-        if (e >= q1 - q0) continue;
-        const int q = q0 + e;
-        if (a.opad) {
-          if ((q & 127) < a.opad * PP) row[(q >> 7) * (a.opad * PP) + (q & 127) - cq0] = t[i];
-        } else {
-          row[e] = t[i];
-        }
+        dd[i] = sdst[lane + 32 * i];
+        t[i] += sbe[lane + 32 * i];
       }
+#pragma unroll
+      for (int i = 0; i < NL; ++i)
+        if (dd[i] != 0xffff) row[dd[i]] = t[i];
     }
     __syncwarp();
     float obar[PP];
@@ -376,7 +383,7 @@ __global__ void __launch_bounds__(256) cg_transform_bwd_img_kernel(CgBwdImg a) {
       const int64_t xi = r * a.D + d;
       float ov[PP];
 #pragma unroll
-      for (int p = 0; p < PP; ++p) ov[p] = row[lane * PP + p] + sbias[lane * PP + p];
+      for (int p = 0; p < PP; ++p) ov[p] = row[lane * PP + p];
       float y, l1, xbar;
       rqs_fwd_bwd<K>(ov, a.lo, a.hi, xv, gv, ldbar, y, l1, xbar, obar);
       a.gin[xi] = xbar;
