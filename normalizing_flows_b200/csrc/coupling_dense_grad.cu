@@ -9,6 +9,7 @@
 //   pass through get dL/do = 0 and receive the conditioner's input gradient instead.
 #include "mgtc.cuh"
 #include "rqs_grad.cuh"
+#include <mutex>
 
 namespace flowcuda {
 
@@ -22,6 +23,10 @@ struct CgLayout {
   int tc;  // tensor-core engine (spec->precision == BF16X3)
   size_t off_aimg, off_bimg, a_bytes, b_bytes, part_floats;
   int img;  // tensor-core engine + spline transform: the bijector adjoint writes dO as operand images (no fp32 dO)
+  // Tensor-core engine: the weight-gradient jobs (dW_i, db_i — nothing downstream of them inside the step) run on an
+  // internal side stream next to the input-gradient chain.  They get their own operand/partial scratch, and the buffers
+  // both streams touch are doubled by flow-layer parity (masked input, one dH per Linear).
+  size_t off_mx2, off_dhx[2][FLOWCUDA_MAX_HIDDEN_LAYERS + 1], off_aimg2, off_bimg2, off_part2, a2_bytes, b2_bytes;
   int fwd_dt;  // ... and the forward pass runs on the density path's GEMMs with fused epilogues (coupling_dense_tc.cu)
   int64_t ldo_dt;
   size_t off_dt, dt_bytes;
@@ -113,6 +118,24 @@ static bool cg_layout(const flowcuda_coupling_spec* sp, int64_t n, CgLayout& L) 
     }
     L.off_aimg = off; off = cg_al(off + L.a_bytes);
     L.off_bimg = off; off = cg_al(off + L.b_bytes);
+  }
+  L.off_mx2 = L.off_tmp; L.off_aimg2 = L.off_aimg; L.off_bimg2 = L.off_bimg; L.off_part2 = L.off_part;
+  L.a2_bytes = L.a_bytes; L.b2_bytes = L.b_bytes;
+  for (int p = 0; p < 2; ++p)
+    for (int i = 0; i <= L.nh; ++i) L.off_dhx[p][i] = L.off_dh[i & 1];
+  if (L.tc) {
+    L.off_mx2 = off; off = cg_al(off + (size_t)n * L.D * 4);
+    for (int p = 0; p < 2; ++p)
+      for (int i = 1; i <= L.nh; ++i) { L.off_dhx[p][i] = off; off = cg_al(off + (size_t)n * L.sizes[i] * 4); }
+    L.a2_bytes = L.b2_bytes = 0;
+    for (int i = 0; i < L.nlin; ++i) {  // the side stream only runs dW_i = in_iᵀ · dout_i (K = batch)
+      const size_t ab = mgtc_a_bytes(L.sizes[i], n), bb = mgtc_b_bytes(L.sizes[i + 1], n);
+      if (ab > L.a2_bytes) L.a2_bytes = ab;
+      if (!(L.img && i == L.nh) && bb > L.b2_bytes) L.b2_bytes = bb;
+    }
+    L.off_aimg2 = off; off = cg_al(off + L.a2_bytes);
+    L.off_bimg2 = off; off = cg_al(off + L.b2_bytes);
+    L.off_part2 = off; off = cg_al(off + L.part_floats * 4);
   }
   L.off_dt = off; L.dt_bytes = 0;
   if (L.fwd_dt) { L.dt_bytes = coupling_dense_tc_workspace_bytes(sp, n) + 256; off = cg_al(off + L.dt_bytes); }
@@ -458,6 +481,40 @@ __global__ void __launch_bounds__(256) cg_add_visible_kernel(const float* __rest
 }
 
 
+// One internal non-blocking stream and three events per device, created on first use and kept for the life of the
+// process (the library creates nothing else).  FLOWCUDA_TRAIN_OVERLAP=0 keeps the whole step on the caller's stream.
+struct CgSide {
+  cudaStream_t q;
+  cudaEvent_t ev_m, ev_last, ev_s[2];
+};
+static std::mutex g_cg_side_mutex;  // the events are reused from call to call: one enqueuing host thread at a time
+static bool cg_overlap_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("FLOWCUDA_TRAIN_OVERLAP");
+    on = (e && e[0] == '0') ? 0 : 1;
+  }
+  return on != 0;
+}
+static int cg_side_get(CgSide** out) {
+  static CgSide tab[64] = {};
+  int dev = -1;
+  FC_CUDA(cudaGetDevice(&dev));
+  FC_REQUIRE(dev >= 0 && dev < 64, "coupling_nll_grad: device ordinal %d outside [0, 64)", dev);
+  CgSide& sd = tab[dev];
+  if (!sd.q) {
+    cudaStream_t q;
+    FC_CUDA(cudaStreamCreateWithFlags(&q, cudaStreamNonBlocking));
+    FC_CUDA(cudaEventCreateWithFlags(&sd.ev_m, cudaEventDisableTiming));
+    FC_CUDA(cudaEventCreateWithFlags(&sd.ev_last, cudaEventDisableTiming));
+    FC_CUDA(cudaEventCreateWithFlags(&sd.ev_s[0], cudaEventDisableTiming));
+    FC_CUDA(cudaEventCreateWithFlags(&sd.ev_s[1], cudaEventDisableTiming));
+    sd.q = q;
+  }
+  *out = &sd;
+  return FLOWCUDA_OK;
+}
+
 template <int K>
 static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const float* params, const float* x, int64_t n,
                   float* loss, float* grad, uint8_t* ws, cudaStream_t s) {
@@ -469,7 +526,6 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
   float* LD = (float*)(ws + L.off_ld);
   float* LP = (float*)(ws + L.off_lp);
   float* dO = (float*)(ws + L.off_dO);
-  float* dH[2] = {(float*)(ws + L.off_dh[0]), (float*)(ws + L.off_dh[1])};
   float* part = (float*)(ws + L.off_part);
   float* act = (float*)(ws + L.off_act);
   const int splits = n >= 1024 ? kMgSplits : 1;
@@ -514,8 +570,23 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
   cg_finish_kernel<<<rb, 256, 0, s>>>(S, LD, LP, G, n, D, sp->base);
   FC_LAUNCH_CHECK("cg_finish_kernel");
   if ((rc = flowcuda_sum_scaled(LP, n, -1.0 / (double)n, loss, ws + L.off_sum, s))) return rc;
-  for (int l = 0; l < L.L; ++l) {  // backward: the layer applied last first
-    const int tp = l & 1;
+  // Backward.  Main stream: bijector adjoint -> input-gradient GEMMs (the dependency chain).  Side stream: per Linear the
+  // weight gradient (operand packs, split-K GEMM, fixed-order reduce) and the bias gradient — off the chain, so they fill
+  // the SMs the chain's small GEMMs (64 CTAs) leave idle.  Same kernels, same arguments, same summation orders as the
+  // single-stream schedule: the results are bit-identical.
+  CgSide* sd = nullptr;
+  const bool overlap = L.tc && cg_overlap_enabled();
+  std::unique_lock<std::mutex> side_lock(g_cg_side_mutex, std::defer_lock);
+  if (overlap) {
+    side_lock.lock();
+    if ((rc = cg_side_get(&sd))) return rc;
+  }
+  cudaStream_t q = overlap ? sd->q : s;
+  const MgTcScratch sc2 = {ws + L.off_aimg2, L.a2_bytes, ws + L.off_bimg2, L.b2_bytes, (float*)(ws + L.off_part2), L.part_floats};
+  float* part_q = overlap ? (float*)(ws + L.off_part2) : part;
+  float* MXp[2] = {MX, overlap ? (float*)(ws + L.off_mx2) : MX};
+  for (int l = 0; l < L.L; ++l) {  // the layer applied last first
+    const int tp = l & 1, lp = l & 1;
     const float* Pl = params + L.per_layer * l;
     float* Gl = grad + L.per_layer * l;
     const int ncomp = ((D - tp + 1) / 2) * P;
@@ -524,6 +595,13 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
     const int nd = ncomp / P;
     const int KSa = (ncomp + kDtBK - 1) / kDtBK, KSb = (int)((n + kDtBK - 1) / kDtBK), NTb = (ncomp + kDtBN - 1) / kDtBN;
     int cslices = 1;
+    float* MXl = MXp[lp];
+    if (overlap) {
+      // parity-lp buffers (masked input, dH) were last read by the side jobs of layer l-2; dO / its column sums by the
+      // last-Linear job of layer l-1
+      if (l >= 2) FC_CUDA(cudaStreamWaitEvent(s, sd->ev_s[lp], 0));
+      if (l >= 1) FC_CUDA(cudaStreamWaitEvent(s, sd->ev_last, 0));
+    }
     if constexpr (K > 0) {
       if (L.img) {
         CgBwdImg bi = {};
@@ -547,29 +625,34 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
       cg_transform_bwd_kernel<K><<<grid_for((int64_t)n * D, 128, 32), 128, 0, s>>>(V(l), H(l, nh), G, S, dO, n, D, P, tp,
                                                                                   sp->range_min, sp->range_max, ldo);
     FC_LAUNCH_CHECK("cg_transform_bwd_kernel");
-    cg_mask_input_kernel<<<eb, 256, 0, s>>>(V(l), MX, n, D, tp);
+    cg_mask_input_kernel<<<eb, 256, 0, s>>>(V(l), MXl, n, D, tp);
     const float* dout = dO;
     for (int i = nh; i >= 0; --i) {
       const bool last = i == nh && L.tc;  // compact dO: the other columns' gradients are exactly zero
       const bool pre = last && L.img;     // ... and it exists only as the two operand images
       const int kin = L.sizes[i], nfull = L.sizes[i + 1], nout = last ? ncomp : nfull;
-      const float* in = i == 0 ? MX : H(l, i - 1);
-      // dW_i = inᵀ · dout (split-K, fixed-order reduce), db_i = column sums
-      if (last) FC_CUDA(cudaMemsetAsync(Gl + L.w_off[i], 0, ((size_t)kin * nfull + nfull) * sizeof(float), s));
+      const float* in = i == 0 ? MXl : H(l, i - 1);
+      if (overlap) {  // dout (and, for i = nh, the masked input) is now enqueued on the main stream
+        FC_CUDA(cudaEventRecord(sd->ev_m, s));
+        FC_CUDA(cudaStreamWaitEvent(q, sd->ev_m, 0));
+      }
+      // dW_i = inᵀ · dout (split-K, fixed-order reduce), db_i = column sums                                [side stream]
+      if (last) FC_CUDA(cudaMemsetAsync(Gl + L.w_off[i], 0, ((size_t)kin * nfull + nfull) * sizeof(float), q));
       MgColMap bm = cm;
       bm.mode = last ? 3 : 0;
-      if (pre) {  // the partial column sums came with the images; add the slices before `part` is reused
-        mg_colsum_stage2<<<(nout + 255) / 256, 256, 0, s>>>((const double*)(ws + L.off_colp), cslices, nout, Gl + L.b_off[i], bm);
+      if (pre) {  // the partial column sums came with the images
+        mg_colsum_stage2<<<(nout + 255) / 256, 256, 0, q>>>((const double*)(ws + L.off_colp), cslices, nout, Gl + L.b_off[i], bm);
         FC_LAUNCH_CHECK("mg_colsum_stage2");
       }
       MgGemm g = mg_gemm(in, 1, kin, dout, nout, 1, Gl + L.w_off[i], nfull, kin, nout, n);
-      g.splits = splits; g.part = part;
+      g.splits = splits; g.part = part_q;
       if (last) { g.map = cm; g.map.mode = 3; }
-      if (pre) { if ((rc = mgtc_launch(g, sc, s, MgTcPre{nullptr, ws + L.off_dOb}))) return rc; }
-      else if ((rc = mg_launch(g, s))) return rc;
-      if (!pre && (rc = mg_colsum(dout, n, nout, Gl + L.b_off[i], part, s, bm))) return rc;
-      // d in = dout · W_iᵀ (relu gate of the stored activation; the masked input has no gate)
-      float* din = i == 0 ? DMX : dH[i & 1];
+      if (L.tc) { if ((rc = mgtc_launch(g, overlap ? sc2 : sc, q, MgTcPre{nullptr, pre ? ws + L.off_dOb : nullptr}))) return rc; }
+      else if ((rc = flowcuda::mg_launch(g, q))) return rc;
+      if (!pre && (rc = mg_colsum(dout, n, nout, Gl + L.b_off[i], part_q, q, bm))) return rc;
+      if (overlap && i == nh) FC_CUDA(cudaEventRecord(sd->ev_last, q));
+      // d in = dout · W_iᵀ (relu gate of the stored activation; the masked input has no gate)             [main stream]
+      float* din = i == 0 ? DMX : (float*)(ws + L.off_dhx[overlap ? lp : 0][i]);
       g = mg_gemm(dout, nout, 1, Pl + L.w_off[i], 1, nfull, din, kin, N, kin, nout);
       if (last) { g.map = cm; g.map.mode = 2; }
       if (i > 0) { g.gate = H(l, i - 1); g.ldg = kin; }
@@ -577,9 +660,14 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
       else if ((rc = mg_launch(g, s))) return rc;
       dout = din;
     }
+    if (overlap) FC_CUDA(cudaEventRecord(sd->ev_s[lp], q));
     cg_add_visible_kernel<<<eb, 256, 0, s>>>(DMX, S, n, D, tp);
     FC_LAUNCH_CHECK("coupling_nll_grad backward");
     float* t = G; G = S; S = t;  // S held dL/d(layer input): it is the next layer's output gradient
+  }
+  if (overlap) {  // join: everything the side stream did is ordered before whatever the caller enqueues next
+    FC_CUDA(cudaEventRecord(sd->ev_m, q));
+    FC_CUDA(cudaStreamWaitEvent(s, sd->ev_m, 0));
   }
   return FLOWCUDA_OK;
 }
