@@ -227,11 +227,33 @@ int flowcuda_coupling_sample_packed(const flowcuda_coupling_spec* spec, const fl
  *   event_dim 2, two hidden layers <= 64 (the toy flows): one fused FP32 kernel pair;
  *   any other shape with TRANSFORM_AFFINE / TRANSFORM_RQS (8 or 12 bins) — the
  *   maf_mnist.py:134-166 step: stored-activation reverse mode whose GEMMs run on FP32 CUDA
- *   cores (spec->precision = FP32) or on tcgen05 bf16x3 (spec->precision = BF16X3). */
+ *   cores (spec->precision = FP32) or on tcgen05 bf16x3 (spec->precision = BF16X3).  The bf16x3 engine runs
+ *   the weight-gradient GEMMs on ONE internal non-blocking stream per device (created on first use, with four
+ *   events, kept for the life of the process; joined back into `stream` before the call returns;
+ *   FLOWCUDA_TRAIN_OVERLAP=0 disables it).  Concurrent calls from several host threads on one device are
+ *   serialised while they enqueue. */
 size_t flowcuda_coupling_nll_grad_workspace_bytes(const flowcuda_coupling_spec* spec, int64_t n);
 int flowcuda_coupling_nll_grad(const flowcuda_coupling_spec* spec, const float* params, const float* x,
                                int64_t n, float* loss, float* grad, void* workspace,
                                size_t workspace_bytes, void* stream);
+
+/* The same step with a per-flow-layer completion hook, for data-parallel training (the flat
+ * gradient is all-reduced across ranks every step, 351 MB at the maf_mnist shape): the reverse mode finishes
+ * the flow layers one after the other (layer 0 first), and a layer's gradient slice can be reduced while the
+ * remaining layers are still being differentiated.  `on_layer` is called ON THE HOST, from inside this call,
+ * once per flow layer, right after the last piece of work that writes grad[offset, offset + count) has been
+ * ENQUEUED; `stream` is the stream on which that slice is complete in stream order at that moment (the
+ * library's internal side stream when the tensor-core engine overlaps the weight-gradient jobs, else the
+ * caller's stream); at that point of `stream` the call has also finished READING the layer's parameters, so the
+ * callee may update them in place (all-reduce, then the optimiser step of that layer, all under the remaining
+ * layers' differentiation).  The callee typically records an event on `stream` and makes its own stream wait
+ * for it; it must not synchronise or enqueue work that waits for the rest of this call.
+ * on_layer == NULL: identical to flowcuda_coupling_nll_grad.  Results are the same bits either way. */
+typedef void (*flowcuda_layer_grad_fn)(void* user, int layer, int64_t offset, int64_t count, void* stream);
+int flowcuda_coupling_nll_grad_layers(const flowcuda_coupling_spec* spec, const float* params, const float* x,
+                                      int64_t n, float* loss, float* grad, void* workspace,
+                                      size_t workspace_bytes, void* stream, flowcuda_layer_grad_fn on_layer,
+                                      void* user);
 
 /* ------------------------------------------------------------------------------------
  * Row #8 — MADE-conditioned masked autoregressive affine flow (MAF), named by

@@ -58,6 +58,8 @@ _u64 = C.c_uint64
 _f = C.c_float
 _d = C.c_double
 _sz = C.c_size_t
+# flowcuda_layer_grad_fn: void (*)(void* user, int layer, int64_t offset, int64_t count, void* stream)
+LAYER_GRAD_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_void_p)
 _spec = C.POINTER(CouplingSpec)
 _mspec = C.POINTER(MadeSpec)
 
@@ -85,6 +87,7 @@ SIGNATURES = {
     "flowcuda_coupling_sample": (_i, [_spec, _p, _p, _p, _p, _i64, _i, _i, _p, _sz, _p]),
     "flowcuda_coupling_nll_grad_workspace_bytes": (_sz, [_spec, _i64]),
     "flowcuda_coupling_nll_grad": (_i, [_spec, _p, _p, _i64, _p, _p, _p, _sz, _p]),
+    "flowcuda_coupling_nll_grad_layers": (_i, [_spec, _p, _p, _i64, _p, _p, _p, _sz, _p, _p, _p]),
     "flowcuda_made_param_count": (_i64, [_mspec]),
     "flowcuda_made_workspace_bytes": (_sz, [_mspec, _i64]),
     "flowcuda_made_log_prob": (_i, [_mspec, _p, _p, _p, _p, _p, _i64, _i, _p, _sz, _p]),

@@ -517,7 +517,7 @@ static int cg_side_get(CgSide** out) {
 
 template <int K>
 static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const float* params, const float* x, int64_t n,
-                  float* loss, float* grad, uint8_t* ws, cudaStream_t s) {
+                  float* loss, float* grad, uint8_t* ws, cudaStream_t s, flowcuda_layer_grad_fn on_layer, void* user) {
   const int D = L.D, P = L.P, N = (int)n, nh = L.nh;
   float* S = (float*)(ws + L.off_state);
   float* G = (float*)(ws + L.off_g);
@@ -661,6 +661,16 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
       dout = din;
     }
     if (overlap) FC_CUDA(cudaEventRecord(sd->ev_s[lp], q));
+    if (on_layer) {
+      // This layer's gradient slice is complete on q (every dW / db job of the layer has been enqueued there).  q is
+      // also made to follow the layer's input-gradient chain, the last reader of the layer's PARAMETERS in this call:
+      // the callee may update them in place from the hook (optimiser step per layer, under the remaining layers).
+      if (overlap) {
+        FC_CUDA(cudaEventRecord(sd->ev_m, s));
+        FC_CUDA(cudaStreamWaitEvent(q, sd->ev_m, 0));
+      }
+      on_layer(user, l, L.per_layer * l, L.per_layer, (void*)q);
+    }
     cg_add_visible_kernel<<<eb, 256, 0, s>>>(DMX, S, n, D, tp);
     FC_LAUNCH_CHECK("coupling_nll_grad backward");
     float* t = G; G = S; S = t;  // S held dL/d(layer input): it is the next layer's output gradient
@@ -684,7 +694,7 @@ size_t coupling_dense_grad_workspace_bytes(const flowcuda_coupling_spec* sp, int
 }
 
 int coupling_dense_grad_run(const flowcuda_coupling_spec* sp, const float* params, const float* x, int64_t n, float* loss,
-                            float* grad, void* workspace, size_t wsb, cudaStream_t s) {
+                            float* grad, void* workspace, size_t wsb, cudaStream_t s, flowcuda_layer_grad_fn on_layer, void* user) {
   CgLayout L;
   if (!cg_layout(sp, n, L)) {
     set_error("coupling_nll_grad: needs RQS with 8 or 12 bins or the per-dimension affine transform");
@@ -696,9 +706,9 @@ int coupling_dense_grad_run(const flowcuda_coupling_spec* sp, const float* param
   }
   FC_REQUIRE(n < (1ll << 31) / (L.D * L.P > 0 ? 1 : 1), "coupling_nll_grad: n too large");
   uint8_t* ws = (uint8_t*)(((uintptr_t)workspace + 255) & ~(uintptr_t)255);
-  if (sp->transform == FLOWCUDA_TRANSFORM_AFFINE) return cg_run<0>(sp, L, params, x, n, loss, grad, ws, s);
-  if (sp->num_bins == 8) return cg_run<8>(sp, L, params, x, n, loss, grad, ws, s);
-  return cg_run<12>(sp, L, params, x, n, loss, grad, ws, s);
+  if (sp->transform == FLOWCUDA_TRANSFORM_AFFINE) return cg_run<0>(sp, L, params, x, n, loss, grad, ws, s, on_layer, user);
+  if (sp->num_bins == 8) return cg_run<8>(sp, L, params, x, n, loss, grad, ws, s, on_layer, user);
+  return cg_run<12>(sp, L, params, x, n, loss, grad, ws, s, on_layer, user);
 }
 
 }  // namespace flowcuda

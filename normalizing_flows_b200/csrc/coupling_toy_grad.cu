@@ -357,7 +357,7 @@ namespace flowcuda {
 bool coupling_dense_grad_supported(const flowcuda_coupling_spec* sp);
 size_t coupling_dense_grad_workspace_bytes(const flowcuda_coupling_spec* sp, int64_t n);
 int coupling_dense_grad_run(const flowcuda_coupling_spec* sp, const float* params, const float* x, int64_t n, float* loss,
-                            float* grad, void* workspace, size_t wsb, cudaStream_t s);
+                            float* grad, void* workspace, size_t wsb, cudaStream_t s, flowcuda_layer_grad_fn on_layer, void* user);
 }
 
 // The stored-activation engine serves every shape the fused toy kernel does not, and the toy shapes too when
@@ -376,10 +376,16 @@ size_t flowcuda_coupling_nll_grad_workspace_bytes(const flowcuda_coupling_spec* 
 
 int flowcuda_coupling_nll_grad(const flowcuda_coupling_spec* spec, const float* params, const float* x, int64_t n,
                                float* loss, float* grad, void* workspace, size_t workspace_bytes, void* stream) {
+  return flowcuda_coupling_nll_grad_layers(spec, params, x, n, loss, grad, workspace, workspace_bytes, stream, nullptr, nullptr);
+}
+
+int flowcuda_coupling_nll_grad_layers(const flowcuda_coupling_spec* spec, const float* params, const float* x, int64_t n,
+                                      float* loss, float* grad, void* workspace, size_t workspace_bytes, void* stream,
+                                      flowcuda_layer_grad_fn on_layer, void* user) {
   FC_REQUIRE(spec && params && x && workspace, "coupling_nll_grad: NULL pointer");
   if (tg_use_dense(spec)) {  // generic event size: stored-activation reverse mode (coupling_dense_grad.cu)
     FC_REQUIRE(n >= 1 && loss && grad, "coupling_nll_grad: bad arguments");
-    return coupling_dense_grad_run(spec, params, x, n, loss, grad, workspace, workspace_bytes, (cudaStream_t)stream);
+    return coupling_dense_grad_run(spec, params, x, n, loss, grad, workspace, workspace_bytes, (cudaStream_t)stream, on_layer, user);
   }
   FC_REQUIRE(n >= 1, "coupling_nll_grad: n must be >= 1");
   FC_REQUIRE(((uintptr_t)x & 7) == 0, "coupling_nll_grad: x must be 8-byte aligned");
@@ -409,6 +415,8 @@ int flowcuda_coupling_nll_grad(const flowcuda_coupling_spec* spec, const float* 
   if (rc) return rc;
   tg_reduce_kernel<<<(int)((cols + 3) / 4), 128, 0, s>>>(part, grid, cols, 1.0 / (double)n, loss, grad);
   FC_LAUNCH_CHECK("tg_reduce_kernel");
+  if (on_layer)  // one fused kernel pair: every layer's slice is complete at the same point of the caller's stream
+    for (int l = 0; l < spec->num_layers; ++l) on_layer(user, l, (int64_t)tg_pl(spec) * l, (int64_t)tg_pl(spec), stream);
   return FLOWCUDA_OK;
 }
 

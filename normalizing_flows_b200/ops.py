@@ -359,8 +359,13 @@ def coupling_sample(spec: CouplingSpec, params: torch.Tensor, z: torch.Tensor, w
 
 
 @_on_tensor_device
-def coupling_nll_grad(spec: CouplingSpec, params: torch.Tensor, x: torch.Tensor):
-    """(loss[1], grad[param_count]) of -mean(log_prob(x)) — jax.value_and_grad(loss_fn) of the toy scripts."""
+def coupling_nll_grad(spec: CouplingSpec, params: torch.Tensor, x: torch.Tensor, on_layer=None):
+    """(loss[1], grad[param_count]) of -mean(log_prob(x)) — jax.value_and_grad(loss_fn) of the toy scripts.
+
+    on_layer(layer, grad_slice, stream): optional host callback, called from inside the C call once per flow layer
+    as soon as everything that writes that layer's slice of `grad` has been enqueued; `stream` is a
+    torch.cuda.ExternalStream on which the slice is complete in stream order (flowcuda_coupling_nll_grad_layers:
+    the hook of data-parallel training — reduce a layer's gradient while the others are still being computed)."""
     x = _f32(x).reshape(x.shape[0], -1)
     _dev_check(params, x)
     lib = _lib.load()
@@ -369,8 +374,24 @@ def coupling_nll_grad(spec: CouplingSpec, params: torch.Tensor, x: torch.Tensor)
     ws = torch.empty(max(1, (need + 3) // 4), device=x.device, dtype=torch.float32)
     loss = torch.empty(1, device=x.device, dtype=torch.float32)
     grad = torch.empty_like(params)
-    check(lib.flowcuda_coupling_nll_grad(C.byref(spec), _ptr(params), _ptr(x), n, _ptr(loss), _ptr(grad), _ptr(ws),
-                                         ws.numel() * 4, _stream()), "coupling_nll_grad")
+    if on_layer is None:
+        check(lib.flowcuda_coupling_nll_grad(C.byref(spec), _ptr(params), _ptr(x), n, _ptr(loss), _ptr(grad), _ptr(ws),
+                                             ws.numel() * 4, _stream()), "coupling_nll_grad")
+        return loss, grad
+    failure = []
+
+    def _cb(user, layer, offset, count, stream):  # no exception may cross the C frames
+        try:
+            on_layer(int(layer), grad[offset:offset + count], torch.cuda.ExternalStream(int(stream or 0), device=x.device))
+        except BaseException as e:  # noqa: BLE001
+            failure.append(e)
+
+    cb = _lib.LAYER_GRAD_FN(_cb)
+    rc = lib.flowcuda_coupling_nll_grad_layers(C.byref(spec), _ptr(params), _ptr(x), n, _ptr(loss), _ptr(grad), _ptr(ws),
+                                               ws.numel() * 4, _stream(), C.cast(cb, C.c_void_p), None)
+    if failure:
+        raise failure[0]
+    check(rc, "coupling_nll_grad_layers")
     return loss, grad
 
 

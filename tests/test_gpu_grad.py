@@ -137,3 +137,51 @@ def test_toy_rqs_nll_grad_on_the_tensor_core_engine(n):
     assert np.abs(g - gr).max() / scale_g <= 2e-3
     fused, gfused = ops.coupling_nll_grad(_spec_pair(ops, ospec), p, x.cuda())
     assert abs(fused.item() - loss.item()) <= 2e-5 * max(1.0, abs(fused.item()))
+
+
+def test_layer_hook_reports_every_layer_and_changes_nothing():
+    """flowcuda_coupling_nll_grad_layers: the per-flow-layer completion hook of data-parallel training.  One call per
+    layer with that layer's slice of the flat gradient and a stream on which it is complete; loss and gradient are the
+    bits of the plain entry point; both engines (fused toy kernels: all layers at once on the caller's stream)."""
+    from normalizing_flows_b200 import _lib, ops
+    from normalizing_flows_b200.data_parallel import LayerwiseAllReduce
+
+    for case, prec in (("rqs_d40_uniform", _lib.PRECISION_BF16X3), ("rqs_d40_uniform", 0), ("rqs_mnist_shape", _lib.PRECISION_BF16X3)):
+        ospec, scale, xs, n = DENSE_GRAD[case]
+        flat = O.flatten_layers(O.init_coupling_params(ospec, seed=5, scale=scale))
+        x = torch.rand(n, ospec.event_dim, generator=torch.Generator().manual_seed(1), dtype=torch.float64).float().cuda()
+        spec = _spec_pair(ops, ospec, precision=prec)
+        p = G(flat)
+        loss0, grad0 = ops.coupling_nll_grad(spec, p, x)
+        seen, sums = [], []
+
+        def hook(layer, g, stream):
+            assert isinstance(stream, torch.cuda.Stream)
+            seen.append((layer, g.data_ptr(), g.numel()))
+            with torch.cuda.stream(stream):  # ordered after the layer's last gradient kernel
+                sums.append(g.double().sum())
+
+        loss1, grad1 = ops.coupling_nll_grad(spec, p, x, on_layer=hook)
+        torch.cuda.synchronize()
+        per = p.numel() // ospec.num_layers
+        assert [s[0] for s in seen] == list(range(ospec.num_layers))
+        assert all(s[2] == per and s[1] == grad1.data_ptr() + 4 * per * s[0] for s in seen)
+        assert torch.equal(loss0, loss1) and torch.equal(grad0, grad1)
+        for l, sm in enumerate(sums):  # the slice really was complete on the reported stream
+            assert sm.item() == grad1[l * per:(l + 1) * per].double().sum().item()
+        # single process: the all-reduce helper is a no-op and wait() returns at once
+        ar = LayerwiseAllReduce()
+        loss2, grad2 = ops.coupling_nll_grad(spec, p, x, on_layer=ar)
+        ar.wait()
+        assert torch.equal(grad0, grad2)
+
+    def bad(layer, g, stream):
+        raise ValueError("from the hook")
+
+    with pytest.raises(ValueError):
+        ops.coupling_nll_grad(spec, p, x, on_layer=bad)
+    ospec, scale, xs = COUPLING_CASES["rqs_toy"]  # the fused toy kernels report all layers after the one kernel pair
+    flat = O.flatten_layers(O.init_coupling_params(ospec, seed=5, scale=scale))
+    calls = []
+    ops.coupling_nll_grad(_spec_pair(ops, ospec), G(flat), torch.randn(300, 2).cuda(), on_layer=lambda l, g, st: calls.append(l))
+    assert calls == list(range(ospec.num_layers))
