@@ -9,10 +9,23 @@ Pinning status:
     ``tests/golden/*.npz`` — outputs of the reference's own source files executed
     in this container with numpy standing in for ``jax.numpy``
     (``tests/golden/make_golden.py``; tests/test_oracle_golden.py).
-  * rows #2-#4, #6, #9 (distrax / haiku / optax semantics): PARITY UNPINNED — the
-    libraries are absent from /root/reference and from this image; restated from
-    their published definitions, pinned only by the
-    known-answer properties K1-K4 in SURVEY.md §4.
+  * rows #2-#4 and the bflow chain (§8f-1): WIRING PINNED, PRIMITIVES RESTATED.
+    ``tests/golden/make_golden_flows.py`` imports the reference's own scripts
+    (``src/real_nvp_toy_densities.py``, ``src/maf_toy_densities.py``, ``src/maf_mnist.py``) and
+    executes ``src/bflow.py`` lines 1-34 UNMODIFIED, with the numpy stand-ins of
+    ``tests/golden/ref_shim.py`` in place of jax / haiku / distrax / TFP, and commits the
+    outputs (``coupling_toy_golden.npz``, ``coupling_mnist_golden.npz``, ``bflow_golden.npz``).
+    Everything the reference wrote is therefore pinned — ``make_conditioner`` /
+    ``make_flow_model``, the ``arange % 2`` masks and the per-layer ``logical_not``, ``3*n+1``,
+    Flatten / Reshape, the ``bijector_fn`` closures, ``Inverse(Chain(layers))``, the base
+    distributions, the haiku module names and creation order — and this oracle is held to those
+    vectors at 1e-9 ... 1e-12 (tests/test_oracle_golden.py).  What remains restated from the
+    libraries' published definitions, here AND in the shim, are the
+    library primitives: the rational-quadratic spline, ScalarAffine, Linear / MLP, SoftClip,
+    tfd.Beta, the Normal / Uniform densities.  They are additionally held by the
+    known-answer properties K1-K4 of SURVEY.md §4.
+  * row #9 (optax.adam): restated from Kingma & Ba / optax's documented update; SGD is
+    ``real_nvp.py:298`` verbatim.  UNPINNED (optax is absent).
   * row #8 (MADE-affine MAF): PARITY UNPINNED — no reference code exists.
 
 All ``file:line`` citations are into /root/reference/.
