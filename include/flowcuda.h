@@ -160,7 +160,12 @@ int flowcuda_bernstein_constrain_thetas_vjp(const float* theta_raw, const float*
                                      * accuracy of a tf32 split: ~2^-21 relative products, fp32 accumulate).
                                      * Since r01 the event_dim-2 kernel carries the halves as fp16 under
                                      * kind::f16 (same significand as tf32, half the TMEM/smem footprint);
-                                     * the constant keeps its name for ABI stability. */
+                                     * the constant keeps its name for ABI stability.
+                                     * RANGE: hidden activations are converted with saturation
+                                     * (cvt.satfinite): a post-relu activation above 65504 x the layer's
+                                     * power-of-two weight scale is clamped, where the FP32 path would carry
+                                     * it on.  Conditioners of the reference's scale (|h| < 1e3) are far
+                                     * inside; use FP32 for parameters that are not. */
 #define FLOWCUDA_PRECISION_3PASS FLOWCUDA_PRECISION_3XTF32
 #define FLOWCUDA_PRECISION_TF32 2   /* tcgen05 kind::tf32 single pass (reserved) */
 #define FLOWCUDA_PRECISION_BF16X3 3 /* tcgen05 kind::f16 bf16, error-compensated 3-pass split (wide conditioners) */
