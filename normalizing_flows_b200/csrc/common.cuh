@@ -1,5 +1,6 @@
 // common.cuh — shared helpers for libflowcuda (sm_100a only).
 #pragma once
+#include <mutex>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -223,6 +224,22 @@ inline int grid_for(int64_t work_items, int per_block, int waves_cap = 8) {
   if (need < 1) need = 1;
   return (int)(need < cap ? need : cap);
 }
+
+// ---- the library's one internal stream ----------------------------------------------------------------------------
+// Work that nothing downstream in the caller's stream depends on for a while (the weight-gradient jobs of the training
+// step) runs on ONE non-blocking stream per device, forked from and joined back into the caller's stream with events —
+// all created on first use and kept for the life of the process.  The events are reused from call to call, so host
+// threads enqueue such calls one at a time per process (side_mutex()).  FLOWCUDA_TRAIN_OVERLAP=0 keeps everything on
+// the caller's stream.  (Measured and NOT adopted: packing the weight images of the later flow layers of a density
+// call on this stream beside the GEMM chain — maf_mnist 1.019 vs 1.014 ms, deep16_nvp 1.60 vs 1.54 ms: the HBM pass
+// slows the chain it runs beside by as much as it saves.)
+struct SideCtx {
+  cudaStream_t q;
+  cudaEvent_t ev_m, ev_last, ev_s[2];
+};
+int side_ctx_get(SideCtx** out);
+std::recursive_mutex& side_mutex();
+bool side_env_enabled(const char* name);
 
 // one 256-bit store (sm_100: STG.256): eight 32-bit words to a 32-byte aligned address
 __device__ __forceinline__ void st_global_v8(float* p, const uint32_t* w) {

@@ -30,6 +30,36 @@ bool pdl_enabled() {
   return on != 0;
 }
 
+std::recursive_mutex& side_mutex() {
+  static std::recursive_mutex m;
+  return m;
+}
+
+bool side_env_enabled(const char* name) {
+  const char* e = getenv(name);
+  return !(e && e[0] == '0');
+}
+
+int side_ctx_get(SideCtx** out) {
+  static SideCtx tab[64] = {};
+  int dev = -1;
+  FC_CUDA(cudaGetDevice(&dev));
+  FC_REQUIRE(dev >= 0 && dev < 64, "device ordinal %d outside [0, 64)", dev);
+  std::lock_guard<std::recursive_mutex> lock(side_mutex());
+  SideCtx& sd = tab[dev];
+  if (!sd.q) {
+    cudaStream_t q;
+    FC_CUDA(cudaStreamCreateWithFlags(&q, cudaStreamNonBlocking));
+    FC_CUDA(cudaEventCreateWithFlags(&sd.ev_m, cudaEventDisableTiming));
+    FC_CUDA(cudaEventCreateWithFlags(&sd.ev_last, cudaEventDisableTiming));
+    FC_CUDA(cudaEventCreateWithFlags(&sd.ev_s[0], cudaEventDisableTiming));
+    FC_CUDA(cudaEventCreateWithFlags(&sd.ev_s[1], cudaEventDisableTiming));
+    sd.q = q;
+  }
+  *out = &sd;
+  return FLOWCUDA_OK;
+}
+
 int sm_count() {
   static int cached[64] = {0};
   int dev = 0;

@@ -9,7 +9,6 @@
 //   pass through get dL/do = 0 and receive the conditioner's input gradient instead.
 #include "mgtc.cuh"
 #include "rqs_grad.cuh"
-#include <mutex>
 
 namespace flowcuda {
 
@@ -481,40 +480,6 @@ __global__ void __launch_bounds__(256) cg_add_visible_kernel(const float* __rest
 }
 
 
-// One internal non-blocking stream and three events per device, created on first use and kept for the life of the
-// process (the library creates nothing else).  FLOWCUDA_TRAIN_OVERLAP=0 keeps the whole step on the caller's stream.
-struct CgSide {
-  cudaStream_t q;
-  cudaEvent_t ev_m, ev_last, ev_s[2];
-};
-static std::mutex g_cg_side_mutex;  // the events are reused from call to call: one enqueuing host thread at a time
-static bool cg_overlap_enabled() {
-  static int on = -1;
-  if (on < 0) {
-    const char* e = getenv("FLOWCUDA_TRAIN_OVERLAP");
-    on = (e && e[0] == '0') ? 0 : 1;
-  }
-  return on != 0;
-}
-static int cg_side_get(CgSide** out) {
-  static CgSide tab[64] = {};
-  int dev = -1;
-  FC_CUDA(cudaGetDevice(&dev));
-  FC_REQUIRE(dev >= 0 && dev < 64, "coupling_nll_grad: device ordinal %d outside [0, 64)", dev);
-  CgSide& sd = tab[dev];
-  if (!sd.q) {
-    cudaStream_t q;
-    FC_CUDA(cudaStreamCreateWithFlags(&q, cudaStreamNonBlocking));
-    FC_CUDA(cudaEventCreateWithFlags(&sd.ev_m, cudaEventDisableTiming));
-    FC_CUDA(cudaEventCreateWithFlags(&sd.ev_last, cudaEventDisableTiming));
-    FC_CUDA(cudaEventCreateWithFlags(&sd.ev_s[0], cudaEventDisableTiming));
-    FC_CUDA(cudaEventCreateWithFlags(&sd.ev_s[1], cudaEventDisableTiming));
-    sd.q = q;
-  }
-  *out = &sd;
-  return FLOWCUDA_OK;
-}
-
 template <int K>
 static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const float* params, const float* x, int64_t n,
                   float* loss, float* grad, uint8_t* ws, cudaStream_t s, flowcuda_layer_grad_fn on_layer, void* user) {
@@ -574,12 +539,13 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
   // weight gradient (operand packs, split-K GEMM, fixed-order reduce) and the bias gradient — off the chain, so they fill
   // the SMs the chain's small GEMMs (64 CTAs) leave idle.  Same kernels, same arguments, same summation orders as the
   // single-stream schedule: the results are bit-identical.
-  CgSide* sd = nullptr;
-  const bool overlap = L.tc && cg_overlap_enabled();
-  std::unique_lock<std::mutex> side_lock(g_cg_side_mutex, std::defer_lock);
+  SideCtx* sd = nullptr;
+  static const bool overlap_env = side_env_enabled("FLOWCUDA_TRAIN_OVERLAP");
+  const bool overlap = L.tc && overlap_env;
+  std::unique_lock<std::recursive_mutex> side_lock(side_mutex(), std::defer_lock);
   if (overlap) {
     side_lock.lock();
-    if ((rc = cg_side_get(&sd))) return rc;
+    if ((rc = side_ctx_get(&sd))) return rc;
   }
   cudaStream_t q = overlap ? sd->q : s;
   const MgTcScratch sc2 = {ws + L.off_aimg2, L.a2_bytes, ws + L.off_bimg2, L.b2_bytes, (float*)(ws + L.off_part2), L.part_floats};
