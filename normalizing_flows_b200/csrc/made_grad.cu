@@ -96,6 +96,9 @@ struct MgLayout {
   size_t off_state, off_tmp, off_ld, off_lp, off_dO, off_dH2, off_dH1, off_sum, off_deg, off_part, off_act, total;  // bytes
   int tc;                       // tensor-core engine
   size_t off_aimg, off_bimg, a_bytes, b_bytes, part_floats;
+  // tensor-core engine: the weight-gradient jobs run on the library's side stream (common.cuh) with their own scratch;
+  // dO / dH2 / dH1 are doubled by flow-layer parity
+  size_t off_dO2, off_dH2b, off_dH1b, off_aimg2, off_bimg2, off_part2;
 };
 
 static size_t mg_al(size_t x) { return (x + 255) & ~(size_t)255; }
@@ -144,6 +147,16 @@ static bool mg_layout(const flowcuda_made_spec* sp, int64_t n, MgLayout& L) {
     }
     L.off_aimg = off; off = mg_al(off + L.a_bytes);
     L.off_bimg = off; off = mg_al(off + L.b_bytes);
+  }
+  L.off_dO2 = L.off_dO; L.off_dH2b = L.off_dH2; L.off_dH1b = L.off_dH1;
+  L.off_aimg2 = L.off_aimg; L.off_bimg2 = L.off_bimg; L.off_part2 = L.off_part;
+  if (L.tc) {
+    L.off_dO2 = off; off = mg_al(off + (size_t)n * 2 * L.D * 4);
+    L.off_dH2b = off; off = mg_al(off + (size_t)n * L.H2 * 4);
+    L.off_dH1b = off; off = mg_al(off + (size_t)n * L.H1 * 4);
+    L.off_aimg2 = off; off = mg_al(off + L.a_bytes);
+    L.off_bimg2 = off; off = mg_al(off + L.b_bytes);
+    L.off_part2 = off; off = mg_al(off + L.part_floats * 4);
   }
   L.off_act = off; off = mg_al(off + L.per_layer_act * 4 * (size_t)L.L);
   L.total = off + 256;
@@ -212,42 +225,75 @@ static int mg_run(const flowcuda_made_spec* sp, const float* params, const float
   mg_finish_kernel<<<rb, 256, 0, s>>>(S, LD, LP, T, n, D);  // T = d loss / d base point (natural order)
   FC_LAUNCH_CHECK("mg_finish_kernel");
   if ((rc = flowcuda_sum_scaled(LP, n, -1.0 / (double)n, loss, ws + L.off_sum, s))) return rc;
-  // ---- backward: layer 0 first
+  // ---- backward: layer 0 first.  Main stream: affine adjoint -> input-gradient GEMMs (the dependency chain); the
+  // weight / bias gradients — nothing in the step depends on them — go to the side stream (tensor-core engine), as in
+  // coupling_dense_grad.cu: same kernels and summation orders, bit-identical results.
+  SideCtx* sd = nullptr;
+  static const bool overlap_env = side_env_enabled("FLOWCUDA_TRAIN_OVERLAP");
+  const bool overlap = L.tc && overlap_env;
+  std::unique_lock<std::recursive_mutex> side_lock(side_mutex(), std::defer_lock);
+  if (overlap) {
+    side_lock.lock();
+    if ((rc = side_ctx_get(&sd))) return rc;
+  }
+  cudaStream_t q = overlap ? sd->q : s;
+  const MgTcScratch sc2 = {ws + L.off_aimg2, L.a_bytes, ws + L.off_bimg2, L.b_bytes, (float*)(ws + L.off_part2), L.part_floats};
+  float* part_q = overlap ? (float*)(ws + L.off_part2) : part;
+  auto side_launch = [&](const MgGemm& g) { return L.tc ? mgtc_launch(g, overlap ? sc2 : sc, q) : flowcuda::mg_launch(g, q); };
+  auto fork = [&]() -> int {  // what the main stream has enqueued so far is ordered before the next side job
+    if (!overlap) return FLOWCUDA_OK;
+    FC_CUDA(cudaEventRecord(sd->ev_m, s));
+    FC_CUDA(cudaStreamWaitEvent(q, sd->ev_m, 0));
+    return FLOWCUDA_OK;
+  };
   float* const S0 = S; float* const T0 = T;
   for (int l = 0; l < L.L; ++l) {
     const float* P = params + L.per_layer * l;
     float* G = grad + L.per_layer * l;
+    const int lp = l & 1;
+    float* dOl = overlap && lp ? (float*)(ws + L.off_dO2) : dO;
+    float* dH2l = overlap && lp ? (float*)(ws + L.off_dH2b) : dH2;
+    float* dH1l = overlap && lp ? (float*)(ws + L.off_dH1b) : dH1;
+    if (overlap && l >= 2) FC_CUDA(cudaStreamWaitEvent(s, sd->ev_s[lp], 0));  // the side jobs of layer l-2 read these buffers
     // the gradient travels in the ordering of the layer that produced it: T (natural = layer 0's) first, then
     // the two buffers alternate and every layer reads its input gradient reversed
     float* gin = (l & 1) ? S0 : T0;
     float* S = (l & 1) ? T0 : S0;
-    mg_affine_bwd_kernel<<<eb, 256, 0, s>>>(XP(l), OO(l), gin, l > 0, S, dO, n, D);
+    mg_affine_bwd_kernel<<<eb, 256, 0, s>>>(XP(l), OO(l), gin, l > 0, S, dOl, n, D);
     FC_LAUNCH_CHECK("mg_affine_bwd_kernel");
     // output Linear
-    MgGemm g = mg_gemm(HB(l), 1, H2, dO, 2 * D, 1, G + L.w3, 2 * D, H2, 2 * D, n);
-    g.mask = m2; g.splits = splits; g.part = part;
-    if ((rc = mg_launch(g, s))) return rc;
-    if ((rc = mg_colsum(dO, n, 2 * D, G + L.b3, part, s))) return rc;
-    g = mg_gemm(dO, 2 * D, 1, P + L.w3, 1, 2 * D, dH2, H2, N, H2, 2 * D);
+    if ((rc = fork())) return rc;
+    MgGemm g = mg_gemm(HB(l), 1, H2, dOl, 2 * D, 1, G + L.w3, 2 * D, H2, 2 * D, n);
+    g.mask = m2; g.splits = splits; g.part = part_q;
+    if ((rc = side_launch(g))) return rc;
+    if ((rc = mg_colsum(dOl, n, 2 * D, G + L.b3, part_q, q))) return rc;
+    g = mg_gemm(dOl, 2 * D, 1, P + L.w3, 1, 2 * D, dH2l, H2, N, H2, 2 * D);
     g.gate = HB(l); g.ldg = H2; g.mask = m2; g.mask_on_b = 2;
     if ((rc = mg_launch(g, s))) return rc;
     // hidden 2
-    g = mg_gemm(HA(l), 1, H1, dH2, H2, 1, G + L.w2, H2, H1, H2, n);
-    g.mask = m1; g.splits = splits; g.part = part;
-    if ((rc = mg_launch(g, s))) return rc;
-    if ((rc = mg_colsum(dH2, n, H2, G + L.b2, part, s))) return rc;
-    g = mg_gemm(dH2, H2, 1, P + L.w2, 1, H2, dH1, H1, N, H1, H2);
+    if ((rc = fork())) return rc;
+    g = mg_gemm(HA(l), 1, H1, dH2l, H2, 1, G + L.w2, H2, H1, H2, n);
+    g.mask = m1; g.splits = splits; g.part = part_q;
+    if ((rc = side_launch(g))) return rc;
+    if ((rc = mg_colsum(dH2l, n, H2, G + L.b2, part_q, q))) return rc;
+    g = mg_gemm(dH2l, H2, 1, P + L.w2, 1, H2, dH1l, H1, N, H1, H2);
     g.gate = HA(l); g.ldg = H1; g.mask = m1; g.mask_on_b = 2;
     if ((rc = mg_launch(g, s))) return rc;
     // hidden 1
-    g = mg_gemm(XP(l), 1, D, dH1, H1, 1, G + L.w1, H1, D, H1, n);
-    g.mask = m0; g.splits = splits; g.part = part;
-    if ((rc = mg_launch(g, s))) return rc;
-    if ((rc = mg_colsum(dH1, n, H1, G + L.b1, part, s))) return rc;
-    g = mg_gemm(dH1, H1, 1, P + L.w1, 1, H1, S, D, N, D, H1);
+    if ((rc = fork())) return rc;
+    g = mg_gemm(XP(l), 1, D, dH1l, H1, 1, G + L.w1, H1, D, H1, n);
+    g.mask = m0; g.splits = splits; g.part = part_q;
+    if ((rc = side_launch(g))) return rc;
+    if ((rc = mg_colsum(dH1l, n, H1, G + L.b1, part_q, q))) return rc;
+    if (overlap) FC_CUDA(cudaEventRecord(sd->ev_s[lp], q));
+    g = mg_gemm(dH1l, H1, 1, P + L.w1, 1, H1, S, D, N, D, H1);
     g.accumulate = 1; g.mask = m0; g.mask_on_b = 2;
     if ((rc = mg_launch(g, s))) return rc;
     FC_LAUNCH_CHECK("made_nll_grad backward");
+  }
+  if (overlap) {  // join
+    FC_CUDA(cudaEventRecord(sd->ev_m, q));
+    FC_CUDA(cudaStreamWaitEvent(s, sd->ev_m, 0));
   }
   return FLOWCUDA_OK;
 }
