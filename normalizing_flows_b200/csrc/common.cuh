@@ -243,7 +243,8 @@ bool side_env_enabled(const char* name);
 
 // one 256-bit store (sm_100: STG.256): eight 32-bit words to a 32-byte aligned address
 __device__ __forceinline__ void st_global_v8(float* p, const uint32_t* w) {
-  asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]),
+  // streamed: nothing re-reads the line soon, and it must not push the GEMM's L2-resident operand images out
+  asm volatile("st.global.L1::no_allocate.L2::evict_first.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]),
                "r"(w[5]), "r"(w[6]), "r"(w[7])
                : "memory");
 }
@@ -252,7 +253,7 @@ __device__ __forceinline__ void st_global_v8(float* p, const uint32_t* w) {
 // epilogues to keep for the reverse mode.  Per flow layer l one activation block of `per_layer_act` floats:
 //   [0, N*D)            the layer's input state v
 //   act_h[i], i < nh    relu(h_{i+1}) as fp32 [N, hidden_i]
-//   act_h[nh]           the last Linear's RAW accumulators (no bias) in tile-column order, fp32 [N, ldo]
+//   act_h[nh]           the last Linear's RAW accumulators (no bias), 32 floats per transformed dim, fp32 [N, ldo]
 struct DtTrainStores {
   float* act;
   size_t per_layer_act;

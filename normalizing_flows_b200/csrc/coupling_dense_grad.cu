@@ -325,7 +325,7 @@ struct CgBwdImg {
   const float* v; const float* o; const float* g; float* gin;
   int64_t N, ldo;
   int D, tp, nd, ncomp;   // nd transformed dims, ncomp = nd * PP conditioner columns
-  int opad;               // 0: o holds the dims back to back (column k*PP); else dims per 128-column half of a GEMM tile
+  int opad;               // 0: o holds the dims back to back (column k*PP); else log2 of the column stride per dim (5: 32 floats)
   float lo, hi;
   uint8_t* a_img; int KSa;
   uint8_t* b_img; int KSb, NTb;
@@ -339,7 +339,7 @@ __global__ void __launch_bounds__(256) cg_transform_bwd_img_kernel(CgBwdImg a) {
   constexpr int PP = 3 * K + 1, CW = 32 * PP, RS = CW + 36 - (CW % 32), NJ = (CW + 255) / 256;
   static_assert(CW % 8 == 0 && RS % 32 == 4, "chunk alignment / bank layout");
   __shared__ __align__(16) float buf[8][RS];
-  constexpr int NL = (CW + 31 + 3 * 8) / 32;  // loads per lane that cover a row's run of this task's columns
+  constexpr int NL = K == 8 ? 32 : (CW + 31) / 32;  // loads per lane that cover a row's run of this task's columns (K = 8: up to 32 floats per dim)
   __shared__ float sbe[NL * 32];               // bias of run element e (0 where o already holds the final values)
   __shared__ unsigned short sdst[NL * 32];     // run element e -> column inside the task (0xffff: pad of the tile layout)
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -348,7 +348,7 @@ __global__ void __launch_bounds__(256) cg_transform_bwd_img_kernel(CgBwdImg a) {
   const int rb0 = blockIdx.y * per, rb1 = min(a.rblocks, rb0 + per);
   const float ldbar = -1.f / (float)a.N;
   const int64_t cb = (int64_t)c * CW;  // first conditioner column of this task
-  auto ocol = [&](int kk) { return a.opad ? (kk / a.opad) * 128 + (kk % a.opad) * PP : kk * PP; };
+  auto ocol = [&](int kk) { return a.opad ? kk << a.opad : kk * PP; };
   double csum[NJ];
 #pragma unroll
   for (int j = 0; j < NJ; ++j) csum[j] = 0.0;
@@ -362,7 +362,7 @@ __global__ void __launch_bounds__(256) cg_transform_bwd_img_kernel(CgBwdImg a) {
     if (e < q1 - q0) {
       const int q = q0 + e;
       if (!a.opad) d = e;
-      else if ((q & 127) < a.opad * PP) d = (q >> 7) * (a.opad * PP) + (q & 127) - (int)cb;
+      else if ((q & ((1 << a.opad) - 1)) < PP) d = (q >> a.opad) * PP + (q & ((1 << a.opad) - 1)) - (int)cb;
       if (d != 0xffff && a.bias != nullptr) b = a.bias[(a.tp + 2 * (k0 + d / PP)) * PP + d % PP];
     }
     sdst[e] = (unsigned short)d;
@@ -573,7 +573,7 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
         CgBwdImg bi = {};
         bi.v = V(l); bi.o = H(l, nh); bi.g = G; bi.gin = S; bi.N = n; bi.ldo = ldo; bi.D = D; bi.tp = tp; bi.nd = nd;
         bi.ncomp = ncomp; bi.opad = 0; bi.lo = sp->range_min; bi.hi = sp->range_max;
-        if (L.fwd_dt) { bi.opad = 5; bi.ldo = L.ldo_dt; bi.bias = Pl + L.b_off[nh]; }
+        if (L.fwd_dt) { bi.opad = 5; bi.ldo = L.ldo_dt; bi.bias = Pl + L.b_off[nh]; }  // 2^5 floats per dim
         bi.a_img = ws + L.off_dOa; bi.KSa = KSa; bi.b_img = ws + L.off_dOb; bi.KSb = KSb; bi.NTb = NTb;
         bi.colpart = (double*)(ws + L.off_colp);
         bi.rblocks = (int)(((n + 127) / 128) * 16);

@@ -255,7 +255,7 @@ int coupling_dense_tc_run(const flowcuda_coupling_spec* sp, const float* params,
 int64_t coupling_dense_tc_store_ldo(const flowcuda_coupling_spec* sp) {
   DtLayout L;
   if (!dt_layout(sp, 128, L)) return 0;
-  return (int64_t)L.tiles * kDtBN;
+  return (int64_t)((sp->event_dim + 1) / 2) * 32;  // 32 floats per transformed dim (dense_tc.cuh: store_o)
 }
 
 int coupling_dense_tc_train_forward(const flowcuda_coupling_spec* sp, const float* params, const float* x, int64_t n,

@@ -83,8 +83,8 @@ struct DtGemm {
   // Training forward (coupling_dense_grad.cu): what the reverse mode reads back, stored by the same epilogues.
   float* store_h;        // hidden epilogue: relu(A·W + b) as fp32 [N, store_ld] (NULL: not stored)
   int64_t store_ld;
-  float* store_o;        // RQS epilogue: the RAW accumulator (A·W, no bias) in tile-column order, fp32 [N, store_ldo]:
-  int64_t store_ldo;     //   column nt*256 + c of a row = tile column c of n tile nt (dt_dim_to_col; 3 pad columns per half)
+  float* store_o;        // RQS epilogue: the RAW accumulators (A·W, no bias), fp32 [N, store_ldo]: 32 floats per transformed
+  int64_t store_ldo;     //   dim (its 25 spline parameters + 7 zeros), dim k of the layer at column 32*k
 };
 
 constexpr int kEpiHidden = 0, kEpiRqs8 = 1, kEpiAffine = 2;
@@ -314,33 +314,6 @@ __device__ __forceinline__ void dt_epilogue_rqs_tile(const DtGemm& a, int mt, in
   const int row = (warp & 3) * 32 + lane;
   const int64_t grow = (int64_t)mt * 128 + row;
   float ldsum[2] = {0.f, 0.f};
-  if (a.store_o != nullptr) {
-    // training: the conditioner output is read back by the spline adjoint.  The accumulator columns of this warp's
-    // dims go out as they sit in TMEM (16-column groups, 64 contiguous bytes per row and group) — the bias is added
-    // by the reader, and the 25-column runs of a dim would not be 16-byte aligned
-    const int dv = min(d_hi, a.ndims - nt * 10);  // valid dims end
-    if (dv > d_lo) {
-      const int cA = dt_dim_to_col(d_lo, 10, 25) & ~31, cB = (dt_dim_to_col(dv - 1, 10, 25) + 25 + 31) & ~31;
-      float* dst = a.store_o + grow * a.store_ldo + (int64_t)nt * kDtBN;
-      // 64 columns per TMEM round trip, 256-bit stores: a thread writes whole 32-byte sectors of its row
-#pragma unroll 1
-      for (int c = cA; c < cB; c += 64) {
-        uint32_t v0[32], v1[32];
-        const bool two = c + 32 < cB;  // uniform
-        tc::tmem_ld_x32(tb + (uint32_t)(c - cshift), v0);
-        if (two) tc::tmem_ld_x32(tb + (uint32_t)(c + 32 - cshift), v1);
-        tc::tmem_ld_wait();
-        if (grow < a.N) {
-#pragma unroll
-          for (int q = 0; q < 4; ++q) st_global_v8(dst + c + 8 * q, v0 + 8 * q);
-          if (two) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) st_global_v8(dst + c + 32 + 8 * q, v1 + 8 * q);
-          }
-        }
-      }
-    }
-  }
   // the loop is not unrolled (one copy of the spline code): the state values are consumed from the head of two
   // register queues that shift by one per iteration — a runtime index would put the arrays in local memory
 #pragma unroll 1
@@ -360,6 +333,21 @@ __device__ __forceinline__ void dt_epilogue_rqs_tile(const DtGemm& a, int mt, in
     }
     tc::tmem_ld_wait();
     if (grow < a.N) {
+      if (a.store_o != nullptr) {
+        // training: the spline adjoint reads the conditioner output back.  The RAW accumulators of a dim (the reader
+        // adds the bias) go out from the registers the spline is about to consume, 32 floats per (row, dim) — 25
+        // values + 7 zeros — so that every store is a whole, aligned 32-byte sector (STG.256); no second pass over TMEM
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          if (u == 1 && !two) break;
+          float* dst = a.store_o + grow * a.store_ldo + (int64_t)(u ? dim1 : dim0) * 32;
+          const uint32_t tail[8] = {vv[u][24], 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+          st_global_v8(dst, vv[u]);
+          st_global_v8(dst + 8, vv[u] + 8);
+          st_global_v8(dst + 16, vv[u] + 16);
+          st_global_v8(dst + 24, tail);
+        }
+      }
       float o[2][25];
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
