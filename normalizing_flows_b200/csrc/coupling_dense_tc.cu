@@ -226,7 +226,9 @@ static int dt_run(const flowcuda_coupling_spec* sp, const float* params, const f
           g.out_KS = L.KS[0];
           g.next_rev = 0;
         }
-        if (sp->transform == FLOWCUDA_TRANSFORM_RQS)
+        if (sp->transform == FLOWCUDA_TRANSFORM_RQS && tr && !inverse)
+          rc = dt_launch_gemm<kEpiRqs8Store, false>(g, L.MT, used, s);  // training forward: single-CTA kernel with the accumulator store
+        else if (sp->transform == FLOWCUDA_TRANSFORM_RQS)
           rc = inverse ? dt2_launch_gemm<kEpiRqs8, true>(g, dl, L.MT, used, s) : dt2_launch_gemm<kEpiRqs8, false>(g, dl, L.MT, used, s);
         else
           rc = inverse ? dt2_launch_gemm<kEpiAffine, true>(g, dl, L.MT, used, s) : dt2_launch_gemm<kEpiAffine, false>(g, dl, L.MT, used, s);

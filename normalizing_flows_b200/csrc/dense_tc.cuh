@@ -88,6 +88,10 @@ struct DtGemm {
 };
 
 constexpr int kEpiHidden = 0, kEpiRqs8 = 1, kEpiAffine = 2;
+// the RQS epilogue that also stores the conditioner accumulators (training forward).  Its own instantiation: compiled
+// into the density kernel, the store path cost that kernel 50 registers and 5 % of its cycles with the pointer NULL
+constexpr int kEpiRqs8Store = 3;
+__host__ __device__ constexpr bool dt_is_rqs(int epi) { return epi == kEpiRqs8 || epi == kEpiRqs8Store; }
 
 // Diagnostics (tools/dt_trace.py; compiled only into a -DFLOWCUDA_TRACE build, never into the shipped library): where the
 // single-thread roles of dense_tc_gemm_kernel spend their cycles.  Per CTA 8 counters: kernel cycles, issuer waiting for
@@ -308,7 +312,7 @@ __device__ __forceinline__ void dt_rqs_load_x(const DtGemm& a, int mt, int nt, i
   }
 }
 
-template <bool INV>
+template <bool INV, bool STORE = false>
 __device__ __forceinline__ void dt_epilogue_rqs_tile(const DtGemm& a, int mt, int nt, int d_lo, int d_hi, int ldslot, int cshift,
                                                      uint32_t tb, const float* __restrict__ sbias, int warp, int lane, DtRqsX& x) {
   const int row = (warp & 3) * 32 + lane;
@@ -333,7 +337,7 @@ __device__ __forceinline__ void dt_epilogue_rqs_tile(const DtGemm& a, int mt, in
     }
     tc::tmem_ld_wait();
     if (grow < a.N) {
-      if (a.store_o != nullptr) {
+      if (STORE && a.store_o != nullptr) {
         // training: the spline adjoint reads the conditioner output back.  The RAW accumulators of a dim (the reader
         // adds the bias) go out from the registers the spline is about to consume, 32 floats per (row, dim) — 25
         // values + 7 zeros — so that every store is a whole, aligned 32-byte sector (STG.256); no second pass over TMEM
@@ -662,7 +666,7 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
       const int c_lo = cshift + ((int)group * (split8 ? 2 : 1) + (split8 ? sub : 0)) * span, c_hi = c_lo + span;
       // RQS: the groups share a whole tile's 10 dims (dt_rqs_group_dims); a half item's 5 dims go 3 + 2
       int rd_lo = 0, rd_hi = 0;
-      if (EPI == kEpiRqs8) {
+      if (dt_is_rqs(EPI)) {
         if (halfitem) {
           rd_lo = 5 * wi.part + (group == 0 ? 0 : 3);
           rd_hi = 5 * wi.part + (group == 0 ? 3 : 5);
@@ -678,13 +682,13 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
         } else {
           b = dt_tile_bias(a, nt, n);
           // RQS: the 16 bin logits of a dimension reach the spline in log2 units (rqs_apply_mufu)
-          if (EPI == kEpiRqs8 && (n & 127) % 25 < 16) b *= kLog2e;
+          if (dt_is_rqs(EPI) && (n & 127) % 25 < 16) b *= kLog2e;
         }
         sbias[n] = b;
       }
       group_sync();
       DtRqsX xin;
-      if (EPI == kEpiRqs8) dt_rqs_load_x(a, mt, nt, rd_lo, rd_hi, warp, lane, xin);
+      if (dt_is_rqs(EPI)) dt_rqs_load_x(a, mt, nt, rd_lo, rd_hi, warp, lane, xin);
       if (EPI == kEpiAffine) {
         // the bijector reads this warp's slice of the state v (it left L2 while the Linears streamed their
         // images): pull the thread's row of the slice into L2 now, under the tile's MMAs
@@ -702,9 +706,9 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
       DT_TRACE_ADD(tr_wait, t0);
       tc::tc_fence_after();
       const uint32_t tb = tmem + slot * (uint32_t)kDtBN + ((uint32_t)((warp & 3) * 32) << 16);
-      if (EPI == kEpiRqs8) {
+      if (dt_is_rqs(EPI)) {
         // log-det slots: a whole tile's groups use slots 0 / 2, a half item's groups the two slots of its half
-        dt_epilogue_rqs_tile<INV>(a, mt, nt, rd_lo, rd_hi, halfitem ? 2 * wi.part + (int)group : 2 * (int)group, cshift, tb, sbias,
+        dt_epilogue_rqs_tile<INV, EPI == kEpiRqs8Store>(a, mt, nt, rd_lo, rd_hi, halfitem ? 2 * wi.part + (int)group : 2 * (int)group, cshift, tb, sbias,
                                   warp, lane, xin);
       } else if (colwork) {
         dt_epilogue<EPI, INV>(a, mt, nt, tb, sbias, Tw, warp, lane, c_lo, c_hi, cshift);
@@ -755,7 +759,7 @@ static int dt_launch_gemm(const DtGemm& g, int64_t MT, int NT, cudaStream_t s) {
     // fewer tiles than SMs: split every n tile in two (128 x 128 CTA tiles) when that fills more of the device
     if (MT * NT < sm_count() * 3 / 4) return dt_launch_gemm_nh<kEpiHidden, false>(g, MT, NT, s);
   }
-  if (EPI != kEpiRqs8 && MT * NT > sm_count()) return dt_launch_gemm_w<EPI, INV, true>(g, MT, NT, s);
+  if (!dt_is_rqs(EPI) && MT * NT > sm_count()) return dt_launch_gemm_w<EPI, INV, true>(g, MT, NT, s);
   return dt_launch_gemm_w<EPI, INV, false>(g, MT, NT, s);
 }
 
