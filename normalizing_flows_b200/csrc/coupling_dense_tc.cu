@@ -16,7 +16,7 @@
 //   hidden: +bias, relu, bf16 hi/lo split, written straight into the next Linear's A image;
 //   last:   the inner bijector (RQS / affine) on the tile's dims, state updated in place,
 //           log-det partial per (row, tile) — the [N, 19600] conditioner output never exists.
-#include "dense_tc2.cuh"
+#include "dense_tc_chain.cuh"
 
 namespace flowcuda {
 
@@ -30,7 +30,8 @@ struct DtPackW {
   int first;             // 1: first Linear (koff = visible parity of the layer), else koff = 0
   int dpt, ppd, D;       // last Linear: dims per tile, params per dim (dpt = 0: plain columns); D = event dim
   int KS, NT;            // k stages, n tiles
-  uint8_t* img;          // [layer][NT][KS][hi|lo][16 KB]
+  uint8_t* img;          // [layer][NT][KS][hi|lo][tr rows x 64 B]
+  int tr;                // rows per n tile of the image: 256 (dense_tc_gemm_kernel) or 128 (hidden Linears for dense_tc_chain_kernel)
 };
 
 // grid (blocks, NT, layers)
@@ -42,13 +43,15 @@ __global__ void __launch_bounds__(256) dense_tc_pack_w_kernel(DtPackW a) {
   const int koff = a.first ? vis : 0;
   const int ndims = (a.D - tp + 1) / 2;                       // transformed dims of this layer
   const int kvalid = a.first ? (a.D - vis + 1) / 2 : a.kvalid;  // visible dims feed the first Linear
-  uint8_t* base = a.img + ((int64_t)l * a.NT + nt) * a.KS * 2 * (int64_t)kDtBBytes;
-  const int total = a.KS * 4 * kDtBN;
+  const int TR = a.tr;
+  const int64_t half = (int64_t)TR * kDtBK * 2;  // bytes of one of hi/lo of a stage
+  uint8_t* base = a.img + ((int64_t)l * a.NT + nt) * a.KS * 2 * half;
+  const int total = a.KS * 4 * TR;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-    const int n = i % kDtBN, ck = i / kDtBN;
+    const int n = i % TR, ck = i / TR;
     int col = -1;
     if (a.dpt == 0) {
-      col = nt * kDtBN + n;
+      col = nt * TR + n;
       if (col >= a.n_out) col = -1;
     } else {
       int di, pp;  // tile column -> (dim of the tile, parameter): two self-contained 128-column halves (dt_col_to_dim)
@@ -66,9 +69,9 @@ __global__ void __launch_bounds__(256) dense_tc_pack_w_kernel(DtPackW a) {
     uint32_t h[4], lo[4];
 #pragma unroll
     for (int e = 0; e < 4; ++e) tc::split_bf16x2(f[2 * e], f[2 * e + 1], h[e], lo[e]);
-    uint8_t* st = base + (int64_t)(ck >> 2) * 2 * kDtBBytes + tc::img_off(kDtBN, n, ck & 3);
+    uint8_t* st = base + (int64_t)(ck >> 2) * 2 * half + tc::img_off(TR, n, ck & 3);
     *reinterpret_cast<uint4*>(st) = make_uint4(h[0], h[1], h[2], h[3]);
-    *reinterpret_cast<uint4*>(st + kDtBBytes) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    *reinterpret_cast<uint4*>(st + half) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
   }
 }
 
@@ -161,16 +164,22 @@ static int dt_run(const flowcuda_coupling_spec* sp, const float* params, const f
   float* ld = (float*)(ws + L.off_ld);
   float* ldp = (float*)(ws + L.off_ldp);
   if (mode != 2) FC_CUDA(cudaMemcpyAsync(v, in, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  // the hidden Linears as one cluster kernel (dense_tc_chain.cuh) when every one is 512 wide; their weight images are
+  // then packed in 128-row tiles (one contiguous 16 KB stage per CTA).  The choice depends on the spec and the process
+  // environment only, so a workspace packed by flowcuda_coupling_pack_weights matches the later calls.
+  bool chain = dt_chain_enabled() && dt2_mode() == 1 && nh >= 1 && nh <= kDcMaxLinears;
+  for (int i = 0; i < nh && chain; ++i) chain = L.sizes[i + 1] == 512;
   // pack every Linear of every layer (masks folded in)
   for (int i = 0; i < L.nlin && mode != 1; ++i) {
     DtPackW p;
+    p.tr = chain && i < nh ? 128 : kDtBN;
     p.params = params; p.per_layer = L.per_layer; p.w_off = L.w_off[i];
     p.k_in = L.sizes[i]; p.n_out = L.sizes[i + 1];
     p.first = i == 0; p.kstride = i == 0 ? 2 : 1; p.kvalid = L.sizes[i];
     p.dpt = i == nh ? L.dpt : 0; p.ppd = L.ppd; p.D = D;
-    p.KS = L.KS[i]; p.NT = L.NT[i]; p.img = ws + L.off_w[i];
-    int blocks = (L.KS[i] * 4 * kDtBN + 255) / 256;
-    dense_tc_pack_w_kernel<<<dim3(blocks, L.NT[i], sp->num_layers), 256, 0, s>>>(p);
+    p.KS = L.KS[i]; p.NT = L.NT[i] * (kDtBN / p.tr); p.img = ws + L.off_w[i];
+    int blocks = (L.KS[i] * 4 * p.tr + 255) / 256;
+    dense_tc_pack_w_kernel<<<dim3(blocks, p.NT, sp->num_layers), 256, 0, s>>>(p);
     FC_LAUNCH_CHECK("dense_tc_pack_w_kernel");
   }
   if (mode == 2) return FLOWCUDA_OK;
@@ -196,7 +205,24 @@ static int dt_run(const flowcuda_coupling_spec* sp, const float* params, const f
                            ws + L.off_x));
     }
     const uint8_t* aimg = ws + L.off_x;
-    for (int i = 0; i < L.nlin; ++i) {
+    int first_lin = 0;
+    if (chain) {
+      DtChain c = {};
+      c.nlin = nh; c.N = n; c.a_img0 = aimg;
+      for (int i = 0; i < nh; ++i) {
+        c.KS[i] = L.KS[i];
+        c.b_img[i] = ws + L.off_w[i] + (size_t)l * L.NT[i] * L.KS[i] * 2 * kDtBBytes;
+        c.bias[i] = lp + L.b_off[i];
+        c.out_img[i] = ws + L.off_h[i & 1];
+        c.out_KS[i] = L.KS[i + 1];
+        c.store_h[i] = tr ? tr->act + (size_t)l * tr->per_layer_act + tr->act_h[i] : nullptr;
+      }
+      int rc = dt_launch_chain(c, L.MT, s);
+      if (rc) return rc;
+      aimg = c.out_img[nh - 1];
+      first_lin = nh;
+    }
+    for (int i = first_lin; i < L.nlin; ++i) {
       DtGemm g = {};
       g.a_img = aimg;
       g.b_img = ws + L.off_w[i] + (size_t)l * L.NT[i] * L.KS[i] * 2 * kDtBBytes;

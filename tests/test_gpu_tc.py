@@ -156,6 +156,27 @@ def test_dense_coupling_cta_pair_kernels(case, mode, monkeypatch):
     assert (lp1 - lp).abs().max().item() <= 1e-5 * max(1.0, lp.abs().max().item())  # same arithmetic, other tiling
 
 
+def test_hidden_chain_cluster_kernel_matches_per_linear_kernels(monkeypatch):
+    """FLOWCUDA_HIDDEN_CHAIN=1: the three 512-wide hidden Linears of a conditioner as one 4-CTA-cluster kernel with the
+    activation stage multicast and the weight images in 128-row tiles (csrc/dense_tc_chain.cuh) — same products in the
+    same order as the per-Linear kernels, so log_prob, z and the gradient must be the same bits; ragged batch
+    (three m tiles, the last one partial) and the prepared-weights path included."""
+    from normalizing_flows_b200 import _lib, ops
+
+    ospec = O.CouplingSpec(784, 3, [512, 512, 512], "rqs", 8, 0.0, 1.0, "uniform")
+    flat = O.flatten_layers(O.init_coupling_params(ospec, seed=9, scale=0.1))
+    spec = _spec_pair(ops, ospec, precision=_lib.PRECISION_BF16X3)
+    x = torch.rand(300, 784, generator=torch.Generator().manual_seed(4), dtype=torch.float64).float().cuda()
+    p = G(flat)
+    lp0, z0, _ = ops.coupling_log_prob(spec, p, x, want_z=True, want_log_det=True)
+    loss0, grad0 = ops.coupling_nll_grad(spec, p, x)
+    monkeypatch.setenv("FLOWCUDA_HIDDEN_CHAIN", "1")
+    lp1, z1, _ = ops.coupling_log_prob(spec, p, x, want_z=True, want_log_det=True)
+    loss1, grad1 = ops.coupling_nll_grad(spec, p, x)
+    assert torch.equal(lp0, lp1) and torch.equal(z0, z1)
+    assert torch.equal(loss0, loss1) and torch.equal(grad0, grad1)
+
+
 def test_dense_coupling_bf16x3_mnist_shape():
     """maf_mnist.py:28-31 conditioner 784->512->512->512->19600, 8 bins, Uniform base (2 flow layers to
     bound the CPU oracle's time): |log_prob - float64 oracle| <= 1e-3 absolute (north_star)."""
