@@ -407,7 +407,7 @@ __global__ void __launch_bounds__(256) cg_transform_bwd_img_kernel(CgBwdImg a) {
 #pragma unroll
       for (int p = 0; p < PP; ++p) ov[p] = row[lane * PP + p];
       float y, l1, xbar;
-      rqs_fwd_bwd<K>(ov, a.lo, a.hi, xv, gv, ldbar, y, l1, xbar, obar);
+      rqs_fwd_bwd<K, true>(ov, a.lo, a.hi, xv, gv, ldbar, y, l1, xbar, obar);
       a.gin[xi] = xbar;
       if ((d ^ 1) < a.D) a.gin[r * a.D + (d ^ 1)] = gp;  // the pass-through neighbour
       if (a.tp == 1 && (a.D & 1) && k == a.nd - 1) a.gin[r * a.D + a.D - 1] = a.g[r * a.D + a.D - 1];
