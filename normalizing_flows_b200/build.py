@@ -58,6 +58,11 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if os.environ.get("FLOWCUDA_BUILD_TRACE") == "1":  # diagnostics build (tools/dt_trace.py); never the shipped library
         flags.append("-DFLOWCUDA_TRACE")
         force = True
+    # objects built with other flags (a diagnostics build left behind) must not be linked into this library
+    stamp = os.path.join(OBJ, ".flags")
+    want = " ".join(flags)
+    if not os.path.exists(stamp) or open(stamp).read() != want:
+        force = True
     hdr_m = _deps_mtime()
     jobs = []
     objs = []
@@ -82,6 +87,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
             for out in ex.map(run, jobs):
                 if verbose and out:
                     print(out, file=sys.stderr)
+    with open(stamp, "w") as f:
+        f.write(want)
     test_objs = [o for o in objs if os.path.basename(o)[:-2] + ".cu" in SELFTEST_SOURCES]
     prod_objs = [o for o in objs if o not in test_objs]
     core_obj = os.path.join(OBJ, "core.o")

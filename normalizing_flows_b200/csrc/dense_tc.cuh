@@ -96,7 +96,7 @@ __host__ __device__ constexpr bool dt_is_rqs(int epi) { return epi == kEpiRqs8 |
 // Diagnostics (tools/dt_trace.py; compiled only into a -DFLOWCUDA_TRACE build, never into the shipped library): where the
 // single-thread roles of dense_tc_gemm_kernel spend their cycles.  Per CTA 8 counters: kernel cycles, issuer waiting for
 // a free accumulator / for operands, producer waiting for a free stage, epilogue warp 0 / warp EW waiting for an accumulator,
-// and their item counts.
+// and their item counts.  n-half (hidden) launches write a second block of 148 x 8 counters behind the first.
 #ifdef FLOWCUDA_TRACE
 __device__ unsigned long long* g_dt_trace = nullptr;
 #define DT_TRACE_T0(var) const long long var = clock64()
@@ -563,7 +563,7 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
         }
       }
 #ifdef FLOWCUDA_TRACE
-      if (g_dt_trace) g_dt_trace[blockIdx.x * 8 + 3] = (unsigned long long)tr_wait;
+      if (g_dt_trace) g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + 3] = (unsigned long long)tr_wait;
 #endif
     }
   } else if (warp == kMmaWarp) {
@@ -608,13 +608,16 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
           DT_TRACE_ADD(tr_full, t1);
           tc::tc_fence_after();
           const uint32_t sa = tc::smem_u32(stages + st * kDtStageBytes), sb = sa + 2 * kDtABytes;
+          // ONE descriptor pair per stage; the six MMAs add their operand offsets (>> 4) to the start-address field —
+          // rebuilding both descriptors per MMA was ~15 dependent uniform-datapath instructions, more than the 64 tensor
+          // cycles of a 128-column MMA leave (the addresses stay below 2^18, the field cannot carry)
+          const uint64_t da = tc::make_smem_desc(sa, lbo_a, 128u), db = tc::make_smem_desc(sb, lbo_b, 128u);
 #pragma unroll
           for (int pass = 0; pass < 3; ++pass) {
-            const uint32_t ab = sa + (pass == 2 ? kDtABytes : 0), bb = sb + (pass == 1 ? b_lo : 0);
+            const uint32_t ao = pass == 2 ? (uint32_t)kDtABytes : 0u, bo = pass == 1 ? b_lo : 0u;
 #pragma unroll
             for (int s = 0; s < kDtBK / 16; ++s) {
-              tc::mma_ss<tc::kFmtBF16>(dtm, tc::make_smem_desc(ab + s * 2u * lbo_a, lbo_a, 128u),
-                                       tc::make_smem_desc(bb + s * 2u * lbo_b, lbo_b, 128u), idesc, acc);
+              tc::mma_ss<tc::kFmtBF16>(dtm, da + ((ao + s * 2u * lbo_a) >> 4), db + ((bo + s * 2u * lbo_b) >> 4), idesc, acc);
               acc = 1;
             }
           }
@@ -624,11 +627,11 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
       }
 #ifdef FLOWCUDA_TRACE
       if (g_dt_trace) {
-        g_dt_trace[blockIdx.x * 8 + 0] = (unsigned long long)(clock64() - tr_start);
-        g_dt_trace[blockIdx.x * 8 + 1] = (unsigned long long)tr_acc;
-        g_dt_trace[blockIdx.x * 8 + 2] = (unsigned long long)tr_full;
-        g_dt_trace[blockIdx.x * 8 + 6] = (unsigned long long)tr_items;
-        g_dt_trace[blockIdx.x * 8 + 7] = (unsigned long long)it;
+        g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + 0] = (unsigned long long)(clock64() - tr_start);
+        g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + 1] = (unsigned long long)tr_acc;
+        g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + 2] = (unsigned long long)tr_full;
+        g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + 6] = (unsigned long long)tr_items;
+        g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + 7] = (unsigned long long)it;
       }
 #endif
     }
@@ -720,7 +723,7 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
       group_sync();
     }
 #ifdef FLOWCUDA_TRACE
-    if (g_dt_trace && lane == 0 && (warp == 0 || warp == EW)) g_dt_trace[blockIdx.x * 8 + (warp == 0 ? 4 : 5)] = (unsigned long long)tr_wait;
+    if (g_dt_trace && lane == 0 && (warp == 0 || warp == EW)) g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + (warp == 0 ? 4 : 5)] = (unsigned long long)tr_wait;
 #endif
   }
   tc::tc_fence_before();

@@ -179,13 +179,13 @@ static __global__ void __launch_bounds__(kMgTcThreads, 1) mgtc_gemm_kernel(MgTcA
           tc::mbar_wait(&full[st], ph);
           tc::tc_fence_after();
           const uint32_t sa = tc::smem_u32(stages + st * kDtStageBytes), sb = sa + 2 * kDtABytes;
+          const uint64_t da = tc::make_smem_desc(sa, lbo_a, 128u), db = tc::make_smem_desc(sb, lbo_b, 128u);  // per stage; see dense_tc.cuh
 #pragma unroll
           for (int pass = 0; pass < 3; ++pass) {
-            const uint32_t ab = sa + (pass == 2 ? kDtABytes : 0), bb = sb + (pass == 1 ? kDtBBytes : 0);
+            const uint32_t ao = pass == 2 ? (uint32_t)kDtABytes : 0u, bo = pass == 1 ? (uint32_t)kDtBBytes : 0u;
 #pragma unroll
             for (int s = 0; s < kDtBK / 16; ++s) {
-              tc::mma_ss<tc::kFmtBF16>(dtm, tc::make_smem_desc(ab + s * 2u * lbo_a, lbo_a, 128u),
-                                       tc::make_smem_desc(bb + s * 2u * lbo_b, lbo_b, 128u), idesc, acc);
+              tc::mma_ss<tc::kFmtBF16>(dtm, da + ((ao + s * 2u * lbo_a) >> 4), db + ((bo + s * 2u * lbo_b) >> 4), idesc, acc);
               acc = 1;
             }
           }

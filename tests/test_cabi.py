@@ -27,6 +27,8 @@ def test_header_symbols_exported(lib):
     raw = ctypes.CDLL(_lib.LIB_PATH)
     for name in declared:
         assert hasattr(raw, name), name
+    for dbg in ("flowcuda_debug_set_dt_trace", "flowcuda_debug_set_dt_trace_made"):
+        assert not hasattr(raw, dbg), f"{dbg}: a FLOWCUDA_BUILD_TRACE diagnostics build is in place of the product library"
     assert lib.flowcuda_version() == 100
     # diagnostics live in their own test library with their own header; the product library does not export them
     hdr2 = open(os.path.join(ROOT, "include", "flowcuda_selftest.h")).read()

@@ -10,18 +10,19 @@ from oracle import flows_oracle as O
 
 wl = sys.argv[1] if len(sys.argv) > 1 else "maf_mnist"
 lib = C.CDLL(_lib.LIB_PATH)
-buf = torch.zeros(148 * 8, dtype=torch.int64, device="cuda")
+buf = torch.zeros(2 * 148 * 8, dtype=torch.int64, device="cuda")  # [full-tile launches | n-half (hidden) launches]
 names = ["issuer cycles", "issuer waits accumulator", "issuer waits operands", "producer waits stage", "epilogue g0 waits acc",
          "epilogue g1 waits acc", "items", "k stages"]
 
 def report(tag):
     torch.cuda.synchronize()
-    b = buf.cpu().reshape(148, 8).double()
-    live = b[:, 0] > 0
-    if not live.any():
-        print(tag, "no trace"); return
-    b = b[live]
-    print(f"{tag}: CTAs {int(live.sum())}", " | ".join(f"{n} {b[:, i].mean():.0f} (max {b[:, i].max():.0f})" for i, n in enumerate(names)))
+    for half, what in ((0, tag), (1, tag + " -- LAST n-half (hidden) launch")):
+        b = buf.cpu().reshape(2, 148, 8)[half].double()
+        live = b[:, 0] > 0
+        if not live.any():
+            continue
+        b = b[live]
+        print(f"{what}: CTAs {int(live.sum())}", " | ".join(f"{n} {b[:, i].mean():.0f} (max {b[:, i].max():.0f})" for i, n in enumerate(names)))
     buf.zero_()
 
 if wl == "maf_made":
