@@ -64,7 +64,10 @@ def constrain_thetas(theta_unconstrained, range_min=None, range_max=None, fn=Non
 
 
 def get_bernstein_poly(theta):
-    """BernsteinBijector.py:23-36: returns x -> mean_k Beta(k, M-k+1).pdf(x) * theta_k (no clip)."""
+    """BernsteinBijector.py:23-36: returns x -> mean_k Beta(k, M-k+1).pdf(x) * theta_k.
+
+    Deviation: the kernel clips x to [1e-7, 1 - 1e-7] (the clip of `forward`, BernsteinBijector.py:81-84) here too; the
+    reference's bare polynomial does not, and returns 0 / NaN from the Beta pdfs outside (0, 1)."""
     theta = torch.as_tensor(theta, dtype=torch.float32, device="cuda")
 
     def bernstein_poly(x):

@@ -23,12 +23,34 @@ def _check_fn(fn):
         raise TypeError("the fused Real NVP kernels implement real_nvp.shift_and_log_scale_fn only")
 
 
+_PACK_CACHE = {}  # fingerprint of the leaves -> (the leaves themselves, flat CUDA tensor)
+
+
 def pack_params(params) -> torch.Tensor:
-    """[[W1,b1],[W2,b2]] per layer -> flat float32 CUDA tensor (W row-major, then b)."""
+    """[[W1,b1],[W2,b2]] per layer -> flat float32 CUDA tensor (W row-major, then b).
+
+    The reference passes the nested list on every call (`forward_nvp(net_params, ...)`, real_nvp.py:71); packing and
+    copying it each time would put a host round trip in front of a 40 us kernel.  The flat buffer is cached and reused
+    while every leaf is the same tensor object at the same version (torch bumps `_version` on in-place writes; the
+    cache keeps the leaves alive, so an id cannot be recycled under it); numpy leaves are fingerprinted by their bytes
+    (18 floats per layer)."""
     if isinstance(params, torch.Tensor):
         return params.to("cuda", torch.float32).contiguous()
-    chunks = [torch.as_tensor(t, dtype=torch.float32).reshape(-1) for layer in params for (W, b) in layer for t in (W, b)]
-    return torch.cat(chunks).to("cuda").contiguous()
+    leaves = [t for layer in params for (W, b) in layer for t in (W, b)]
+    fp = tuple((id(t), t._version) if isinstance(t, torch.Tensor) else (t.tobytes() if hasattr(t, "tobytes") else repr(t))
+               for t in leaves)
+    hit = _PACK_CACHE.get(fp)
+    if hit is not None:
+        return hit[1]
+    chunks = [torch.as_tensor(t, dtype=torch.float32).reshape(-1) for t in leaves]
+    if all(c.is_cuda for c in chunks):
+        flat = torch.cat(chunks).contiguous()
+    else:
+        flat = torch.cat([c.cpu() for c in chunks]).to("cuda").contiguous()
+    if len(_PACK_CACHE) >= 64:
+        _PACK_CACHE.clear()
+    _PACK_CACHE[fp] = (leaves, flat)
+    return flat
 
 
 def unpack_params(flat: torch.Tensor, n_layers: int, hidden: int = 4):
