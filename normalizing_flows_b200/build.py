@@ -51,6 +51,39 @@ def _deps_mtime() -> float:
     return max(os.path.getmtime(h) for h in hdrs)
 
 
+def _xla_ffi_include():
+    """Directory holding xla/ffi/api/ffi.h, or None (the usual case here: JAX is not installable on either box)."""
+    cand = [os.environ.get("XLA_FFI_INCLUDE")]
+    try:
+        import importlib
+
+        cand.append(importlib.import_module("jax.ffi").include_dir())
+    except Exception:
+        pass
+    for c in cand:
+        if c and os.path.exists(os.path.join(c, "xla", "ffi", "api", "ffi.h")):
+            return c
+    return None
+
+
+def build_xla_ffi_adapter(verbose: bool = False):
+    """integration/flowcuda_xla_ffi.cc -> integration/libflowcuda_xla_ffi.so when the XLA FFI headers exist (UNVERIFIED
+    path: never exercised on this project's machines); returns the library path or None."""
+    inc = _xla_ffi_include()
+    if inc is None:
+        return None
+    root = os.path.dirname(PKG)
+    src = os.path.join(root, "integration", "flowcuda_xla_ffi.cc")
+    out = os.path.join(root, "integration", "libflowcuda_xla_ffi.so")
+    cuda_inc = os.path.join(os.path.dirname(os.path.dirname(_nvcc())), "include")
+    cmd = ["g++", "-std=c++17", "-O2", "-shared", "-fPIC", "-I", inc, "-I", INCLUDE, "-I", cuda_inc, src, "-L", PKG, "-lflowcuda",
+           "-Wl,-rpath," + PKG, "-o", out]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("XLA FFI adapter failed to build: %s\n%s" % (" ".join(cmd), r.stderr))
+    return out
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(OBJ, exist_ok=True)
     nvcc = _nvcc()
@@ -102,3 +135,6 @@ def build(force: bool = False, verbose: bool = False) -> str:
 if __name__ == "__main__":
     path = build(force="--force" in sys.argv, verbose="-v" in sys.argv)
     print(path)
+    adapter = build_xla_ffi_adapter()
+    if adapter:
+        print(adapter)

@@ -73,3 +73,21 @@ def test_product_never_imports_oracle():
         if fn.endswith(".py"):
             src = open(os.path.join(pkg, fn)).read()
             assert "oracle" not in src.replace("(`oracle/`", "").replace("oracle/", ""), fn
+
+
+def test_xla_ffi_adapter_is_inert_without_the_header(tmp_path):
+    """integration/flowcuda_xla_ffi.cc (the jax.ffi handlers a maintainer builds on a machine that has JAX) must
+    preprocess to nothing where xla/ffi/api/ffi.h does not exist — the only state that can be checked here — and the
+    build must not try to compile it then."""
+    import subprocess
+
+    from normalizing_flows_b200 import build
+
+    src = os.path.join(ROOT, "integration", "flowcuda_xla_ffi.cc")
+    obj = str(tmp_path / "adapter.o")
+    r = subprocess.run(["g++", "-std=c++17", "-c", "-I", os.path.join(ROOT, "include"), src, "-o", obj], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    syms = subprocess.run(["nm", obj], capture_output=True, text=True).stdout
+    assert "_ffi" not in syms
+    if build._xla_ffi_include() is None:
+        assert build.build_xla_ffi_adapter() is None
