@@ -292,6 +292,16 @@ int flowcuda_made_log_prob(const flowcuda_made_spec* spec, const float* params, 
                            float* log_prob, float* u, float* log_det, int64_t n, int with_base,
                            void* workspace, size_t workspace_bytes, void* stream);
 
+/* The same density pass with every product in FP32 on the CUDA cores (the engine of
+ * flowcuda_made_nll_grad with precision FP32): the full-precision partner of the tensor-core pass
+ * (|d log_prob| <= 1e-5 relative against the float64 restatement) — ~20x slower, for validation
+ * and for callers whose parameters leave bf16x3's 1e-3 budget.  Normal base, two hidden layers (the
+ * limits of made_nll_grad).  u (optional): base-space point. */
+size_t flowcuda_made_log_prob_fp32_workspace_bytes(const flowcuda_made_spec* spec, int64_t n);
+int flowcuda_made_log_prob_fp32(const flowcuda_made_spec* spec, const float* params, const float* x,
+                                float* log_prob, float* u, int64_t n, void* workspace,
+                                size_t workspace_bytes, void* stream);
+
 /* Sampling with the base noise given, z[N,D] -> x[N,D]: layer 0 first ... layer L-1 last,
  * within a layer x_i = z_i·exp(log_scale_i(x_<i)) + shift_i(x_<i) sequentially over the D
  * positions — one persistent FP32 kernel with incrementally updated pre-activations.

@@ -92,6 +92,8 @@ SIGNATURES = {
     "flowcuda_made_workspace_bytes": (_sz, [_mspec, _i64]),
     "flowcuda_made_log_prob": (_i, [_mspec, _p, _p, _p, _p, _p, _i64, _i, _p, _sz, _p]),
     "flowcuda_made_sample": (_i, [_mspec, _p, _p, _p, _i64, _p]),
+    "flowcuda_made_log_prob_fp32_workspace_bytes": (_sz, [_mspec, _i64]),
+    "flowcuda_made_log_prob_fp32": (_i, [_mspec, _p, _p, _p, _p, _i64, _p, _sz, _p]),
     "flowcuda_made_nll_grad_workspace_bytes": (_sz, [_mspec, _i64]),
     "flowcuda_coupling_pack_weights": (_i, [_spec, _p, _p, _sz, _p]),
     "flowcuda_coupling_log_prob_packed": (_i, [_spec, _p, _p, _p, _p, _p, _i64, _i, _i, _i, _p, _sz, _p]),

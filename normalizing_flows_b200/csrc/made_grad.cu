@@ -164,8 +164,11 @@ static bool mg_layout(const flowcuda_made_spec* sp, int64_t n, MgLayout& L) {
 }
 
 
+// fwd_only: stop after the density pass and copy log_prob[N] (and, if asked, the base-space point u[N, D]) out —
+// flowcuda_made_log_prob_fp32, the FP32 partner of the tensor-core density pass (made.cu)
 static int mg_run(const flowcuda_made_spec* sp, const float* params, const float* x, int64_t n, float* loss, float* grad,
-                  void* workspace, size_t wsb, cudaStream_t s) {
+                  void* workspace, size_t wsb, cudaStream_t s, bool fwd_only = false, float* out_lp = nullptr,
+                  float* out_u = nullptr) {
   MgLayout L;
   if (!mg_layout(sp, n, L)) {
     set_error("made_nll_grad: needs exactly two hidden layers");
@@ -224,6 +227,11 @@ static int mg_run(const flowcuda_made_spec* sp, const float* params, const float
   }
   mg_finish_kernel<<<rb, 256, 0, s>>>(S, LD, LP, T, n, D);  // T = d loss / d base point (natural order)
   FC_LAUNCH_CHECK("mg_finish_kernel");
+  if (fwd_only) {
+    if (out_lp) FC_CUDA(cudaMemcpyAsync(out_lp, LP, (size_t)n * 4, cudaMemcpyDeviceToDevice, s));
+    if (out_u) FC_CUDA(cudaMemcpyAsync(out_u, S, (size_t)n * D * 4, cudaMemcpyDeviceToDevice, s));
+    return FLOWCUDA_OK;
+  }
   if ((rc = flowcuda_sum_scaled(LP, n, -1.0 / (double)n, loss, ws + L.off_sum, s))) return rc;
   // ---- backward: layer 0 first.  Main stream: affine adjoint -> input-gradient GEMMs (the dependency chain); the
   // weight / bias gradients — nothing in the step depends on them — go to the side stream (tensor-core engine), as in
@@ -308,6 +316,24 @@ size_t flowcuda_made_nll_grad_workspace_bytes(const flowcuda_made_spec* spec, in
   MgLayout L;
   if (n < 0 || !mg_layout(spec, n, L)) return 0;
   return L.total;
+}
+
+size_t flowcuda_made_log_prob_fp32_workspace_bytes(const flowcuda_made_spec* spec, int64_t n) {
+  if (!spec) return 0;
+  flowcuda_made_spec sp = *spec;
+  sp.precision = FLOWCUDA_PRECISION_FP32;
+  return flowcuda_made_nll_grad_workspace_bytes(&sp, n);
+}
+
+int flowcuda_made_log_prob_fp32(const flowcuda_made_spec* spec, const float* params, const float* x, float* log_prob, float* u,
+                                int64_t n, void* workspace, size_t workspace_bytes, void* stream) {
+  FC_REQUIRE(spec && params && x && (log_prob || u), "made_log_prob_fp32: NULL pointer or no output requested");
+  FC_REQUIRE(n >= 1 && n < (1ll << 31), "made_log_prob_fp32: n=%lld outside [1, 2^31)", (long long)n);
+  FC_REQUIRE(spec->event_dim >= 1 && spec->num_layers >= 1, "made_log_prob_fp32: bad spec");
+  FC_REQUIRE(spec->base == FLOWCUDA_BASE_NORMAL, "made_log_prob_fp32: Normal base only (as made_nll_grad)");
+  flowcuda_made_spec sp = *spec;
+  sp.precision = FLOWCUDA_PRECISION_FP32;  // every product on the FP32 CUDA-core engine (mg_sgemm.cuh)
+  return mg_run(&sp, params, x, n, nullptr, nullptr, workspace, workspace_bytes, (cudaStream_t)stream, true, log_prob, u);
 }
 
 int flowcuda_made_nll_grad(const flowcuda_made_spec* spec, const float* params, const float* x, int64_t n, float* loss,

@@ -444,6 +444,23 @@ def made_log_prob(spec: _lib.MadeSpec, params: torch.Tensor, x: torch.Tensor, wa
 
 
 @_on_tensor_device
+def made_log_prob_fp32(spec: _lib.MadeSpec, params: torch.Tensor, x: torch.Tensor, want_u: bool = False):
+    """The MAF density pass with every product in FP32 on the CUDA cores (flowcuda_made_log_prob_fp32): the
+    full-precision partner of `made_log_prob`.  Returns (log_prob, u or None)."""
+    x = _f32(x).reshape(x.shape[0], spec.event_dim)
+    _dev_check(params, x)
+    lib = _lib.load()
+    n = x.shape[0]
+    lp = torch.empty(n, device=x.device, dtype=torch.float32)
+    u = torch.empty_like(x) if want_u else None
+    need = lib.flowcuda_made_log_prob_fp32_workspace_bytes(C.byref(spec), n)
+    ws = torch.empty(max(1, (need + 3) // 4), device=x.device, dtype=torch.float32)
+    check(lib.flowcuda_made_log_prob_fp32(C.byref(spec), _ptr(params), _ptr(x), _ptr(lp), _ptr(u), n, _ptr(ws), ws.numel() * 4,
+                                          _stream()), "made_log_prob_fp32")
+    return lp, u
+
+
+@_on_tensor_device
 def made_sample(spec: _lib.MadeSpec, params: torch.Tensor, z: torch.Tensor) -> torch.Tensor:
     """MAF sampling with the base noise given (base -> data), sequential over dimensions."""
     z = _f32(z).reshape(z.shape[0], spec.event_dim)

@@ -182,6 +182,8 @@ def test_maf_made_all_8_layers_vs_oracle():
     ref = O.maf_log_prob(ospec, p64, x.double())
     lp, _, _ = ops.made_log_prob(ops.make_made_spec(784, 8, [512, 512]), flat, x.cuda())
     hold("maf_made_L8_log_prob_bf16x3", lp, ref, 1e-3, absolute=True, kind="d784")
+    lp32, _ = ops.made_log_prob_fp32(ops.make_made_spec(784, 8, [512, 512]), flat, x.cuda())
+    hold("maf_made_L8_log_prob_fp32", lp32, ref, 1e-3, absolute=True, kind="d784")
 
 
 @pytest.mark.parametrize("name,ospec_name", [("maf_toy", "RQS_TOY"), ("realnvp_toy", "REAL_NVP_TOY")])

@@ -47,6 +47,26 @@ def test_made_log_prob_parity(case, n):
     close(ld, ldref.numpy(), tol=2e-4, what="log_det")
 
 
+@pytest.mark.parametrize("case", sorted(CASES))
+def test_made_log_prob_fp32_partner(case):
+    """flowcuda_made_log_prob_fp32: the density pass with every product in FP32 (CUDA cores) against the float64 oracle
+    at the FP32 tolerance (1e-5 scaled), and the tensor-core pass against IT inside its 1e-3 budget."""
+    from normalizing_flows_b200 import ops
+    from parity_util import hold
+
+    ospec, scale = CASES[case]
+    params = O.init_made_params(ospec, seed=3, scale=scale)
+    flat = G(O.flatten_layers(params))
+    spec = _spec(ops, ospec)
+    n = 300
+    x = torch.randn(n, ospec.event_dim, generator=torch.Generator().manual_seed(n), dtype=torch.float64).float()
+    lp32, u32 = ops.made_log_prob_fp32(spec, flat, x.cuda(), want_u=True)
+    hold(f"made_fp32_{case}_log_prob", lp32, O.maf_log_prob(ospec, params, x.double()), 1e-5, kind="toy")
+    hold(f"made_fp32_{case}_u", u32, _oracle_u(ospec, params, x.double()), 1e-5, kind="toy")
+    lp, _, _ = ops.made_log_prob(spec, flat, x.cuda())
+    assert (lp - lp32).abs().max().item() <= 1e-3
+
+
 def _oracle_u(ospec, params, x):
     v = x
     for l in reversed(range(ospec.num_layers)):
