@@ -382,7 +382,10 @@ def coupling_nll_grad(spec: CouplingSpec, params: torch.Tensor, x: torch.Tensor,
 
     def _cb(user, layer, offset, count, stream):  # no exception may cross the C frames
         try:
-            on_layer(int(layer), grad[offset:offset + count], torch.cuda.ExternalStream(int(stream or 0), device=x.device))
+            # a NULL handle is the legacy default stream = torch's default stream; torch.cuda.ExternalStream(0) does NOT
+            # denote it (its work was seen to run unordered), so it is mapped by hand
+            st = torch.cuda.ExternalStream(int(stream), device=x.device) if stream else torch.cuda.default_stream(x.device)
+            on_layer(int(layer), grad[offset:offset + count], st)
         except BaseException as e:  # noqa: BLE001
             failure.append(e)
 
