@@ -246,8 +246,10 @@ int flowcuda_coupling_nll_grad(const flowcuda_coupling_spec* spec, const float* 
  * gradient is all-reduced across ranks every step, 351 MB at the maf_mnist shape): the reverse mode finishes
  * the flow layers one after the other (layer 0 first), and a layer's gradient slice can be reduced while the
  * remaining layers are still being differentiated.  `on_layer` is called ON THE HOST, from inside this call,
- * once per flow layer, right after the last piece of work that writes grad[offset, offset + count) has been
- * ENQUEUED; `stream` is the stream on which that slice is complete in stream order at that moment (the
+ * one or more times per flow layer — with disjoint slices that together cover the layer's parameters (the
+ * stored-activation engine reports a layer's last Linear, nine tenths of it, as soon as that Linear is done,
+ * and the hidden Linears at the end of the layer) — each time right after the last piece of work that writes
+ * grad[offset, offset + count) has been ENQUEUED; `stream` is the stream on which that slice is complete in stream order at that moment (the
  * library's internal side stream when the tensor-core engine overlaps the weight-gradient jobs, else the
  * caller's stream); at that point of `stream` the call has also finished READING the layer's parameters, so the
  * callee may update them in place (all-reduce, then the optimiser step of that layer, all under the remaining

@@ -541,6 +541,7 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
   // single-stream schedule: the results are bit-identical.
   SideCtx* sd = nullptr;
   static const bool overlap_env = side_env_enabled("FLOWCUDA_TRAIN_OVERLAP");
+  static const bool hook_split = side_env_enabled("FLOWCUDA_HOOK_SPLIT");  // 0: one report per flow layer
   const bool overlap = L.tc && overlap_env;
   std::unique_lock<std::recursive_mutex> side_lock(side_mutex(), std::defer_lock);
   if (overlap) {
@@ -602,6 +603,13 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
         FC_CUDA(cudaEventRecord(sd->ev_m, s));
         FC_CUDA(cudaStreamWaitEvent(q, sd->ev_m, 0));
       }
+      if (on_layer && hook_split && i == nh - 1) {
+        // The last Linear's weights and bias — nine tenths of the layer's parameters — are final on q here: its
+        // gradient jobs were enqueued first, and q has just been ordered behind the input-gradient GEMM that was the
+        // last reader of its weights.  Reported now, its all-reduce / update runs under the rest of the layer instead
+        // of after it (the last layer's bucket is otherwise the exposed tail of the whole step).
+        on_layer(user, l, L.per_layer * l + L.w_off[nh], L.per_layer - L.w_off[nh], (void*)q);
+      }
       // dW_i = inᵀ · dout (split-K, fixed-order reduce), db_i = column sums                                [side stream]
       if (last) FC_CUDA(cudaMemsetAsync(Gl + L.w_off[i], 0, ((size_t)kin * nfull + nfull) * sizeof(float), q));
       MgColMap bm = cm;
@@ -628,14 +636,15 @@ static int cg_run(const flowcuda_coupling_spec* sp, const CgLayout& L, const flo
     }
     if (overlap) FC_CUDA(cudaEventRecord(sd->ev_s[lp], q));
     if (on_layer) {
-      // This layer's gradient slice is complete on q (every dW / db job of the layer has been enqueued there).  q is
+      // The rest of this layer's gradient slice is complete on q (every dW / db job of the layer has been enqueued there).  q is
       // also made to follow the layer's input-gradient chain, the last reader of the layer's PARAMETERS in this call:
       // the callee may update them in place from the hook (optimiser step per layer, under the remaining layers).
       if (overlap) {
         FC_CUDA(cudaEventRecord(sd->ev_m, s));
         FC_CUDA(cudaStreamWaitEvent(q, sd->ev_m, 0));
       }
-      on_layer(user, l, L.per_layer * l, L.per_layer, (void*)q);
+      if (hook_split) on_layer(user, l, L.per_layer * l, L.w_off[nh], (void*)q);  // the hidden Linears' slice; the last Linear's went out above
+      else on_layer(user, l, L.per_layer * l, L.per_layer, (void*)q);
     }
     cg_add_visible_kernel<<<eb, 256, 0, s>>>(DMX, S, n, D, tp);
     FC_LAUNCH_CHECK("coupling_nll_grad backward");

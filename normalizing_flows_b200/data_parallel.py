@@ -63,7 +63,8 @@ class DataParallelTrainer:
 
 
 class LayerwiseAllReduce:
-    """Sum all-reduce of the flat gradient, one bucket per flow layer, issued while the reverse mode is still working
+    """Sum all-reduce of the flat gradient in the buckets the reverse mode reports (per flow layer: its last Linear as
+    soon as that is done, then its hidden Linears), issued while the reverse mode is still working
     on the remaining layers (351 MB per step at the maf_mnist shape) — and, optionally, that layer's
     optimiser step right behind it.  Use as the `on_layer` hook of ops.coupling_nll_grad, then `wait()`:
 
@@ -81,7 +82,6 @@ class LayerwiseAllReduce:
         self.after = after
         self.works = []
         self.comm = None
-        self._base = None
 
     def __call__(self, layer, grad_slice, stream):
         multi = dist.is_initialized() and dist.get_world_size(self.group) > 1
@@ -89,8 +89,6 @@ class LayerwiseAllReduce:
             return
         if self.comm is None:
             self.comm = torch.cuda.Stream(device=grad_slice.device)
-        if self._base is None:  # the hook is called for layer 0 first: its slice starts the flat gradient
-            self._base = grad_slice.data_ptr() - layer * grad_slice.numel() * grad_slice.element_size()
         ev = torch.cuda.Event()
         ev.record(stream)
         self.comm.wait_event(ev)
@@ -102,7 +100,7 @@ class LayerwiseAllReduce:
                 else:
                     w.wait()  # the communication stream (not the host) waits for the collective
             if self.after is not None:
-                lo = (grad_slice.data_ptr() - self._base) // grad_slice.element_size()
+                lo = grad_slice.storage_offset()  # the slice is a view of the flat gradient
                 self.after(layer, lo, lo + grad_slice.numel(), grad_slice)
 
     def wait(self):
@@ -111,7 +109,6 @@ class LayerwiseAllReduce:
         self.works = []
         if self.comm is not None:
             torch.cuda.current_stream().wait_stream(self.comm)
-        self._base = None
 
 
 def cuda_grad_fn(spec):

@@ -362,8 +362,9 @@ def coupling_sample(spec: CouplingSpec, params: torch.Tensor, z: torch.Tensor, w
 def coupling_nll_grad(spec: CouplingSpec, params: torch.Tensor, x: torch.Tensor, on_layer=None):
     """(loss[1], grad[param_count]) of -mean(log_prob(x)) — jax.value_and_grad(loss_fn) of the toy scripts.
 
-    on_layer(layer, grad_slice, stream): optional host callback, called from inside the C call once per flow layer
-    as soon as everything that writes that layer's slice of `grad` has been enqueued; `stream` is a
+    on_layer(layer, grad_slice, stream): optional host callback, called from inside the C call one or more times per
+    flow layer (disjoint views of `grad` that together cover the layer) as soon as everything that writes the slice has
+    been enqueued; `stream` is a
     torch.cuda.ExternalStream on which the slice is complete in stream order (flowcuda_coupling_nll_grad_layers:
     the hook of data-parallel training — reduce a layer's gradient while the others are still being computed)."""
     x = _f32(x).reshape(x.shape[0], -1)
