@@ -97,3 +97,35 @@ def test_density_generators_shard_the_stream_by_rank(monkeypatch):
     assert all(c[0] == "gaussian_blobs" and c[4] == {"num_blobs": 5, "r": 1.5} for c in calls)
     with pytest.raises(ValueError):
         list(densities.make_dataset_banana(1, batch_size=10, world_size=4))
+
+
+def test_real_nvp_pack_params_cache(monkeypatch):
+    """real_nvp.pack_params keeps the flat device buffer of a nested [[W1,b1],[W2,b2]] list while its leaves are
+    unchanged (the reference passes the nested list on every forward_nvp / inverse_nvp call, real_nvp.py:71-134) and
+    rebuilds it when a leaf is written in place or replaced.  CPU-only: the device copy is stubbed."""
+    import numpy as np
+    import torch
+
+    from normalizing_flows_b200 import real_nvp as r
+
+    copies = []
+    monkeypatch.setattr(torch.Tensor, "to", lambda self, *a, **k: (copies.append(1) or self))
+    r._PACK_CACHE.clear()
+    p = r.init_mlp()
+    f1 = r.pack_params([p])
+    f2 = r.pack_params([p])  # a NEW outer list around the same leaves, as forward_nvp builds it
+    assert f1 is f2 and len(copies) == 1
+    p[0][0].add_(1.0)  # in-place write bumps the tensor's version
+    f3 = r.pack_params([p])
+    assert f3 is not f1 and abs(float(f3[0]) - (float(f1[0]) + 1.0)) < 1e-6
+    p[1][1] = torch.ones(2)  # a replaced leaf
+    f4 = r.pack_params([p])
+    assert f4 is not f3 and float(f4[-1]) == 1.0
+    q = [[np.ones((1, 4), np.float32), np.zeros(4, np.float32)], [np.ones((4, 2), np.float32), np.zeros(2, np.float32)]]
+    g1 = r.pack_params([q])
+    q[0][0][0, 0] = 5.0  # numpy leaves are fingerprinted by content
+    g2 = r.pack_params([q])
+    assert g2 is not g1 and float(g2[0]) == 5.0
+    for _ in range(80):  # bounded
+        r.pack_params([r.init_mlp()])
+    assert len(r._PACK_CACHE) <= 64
