@@ -507,6 +507,9 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
   uint64_t* acc_empty = acc_full + 2;                                              // [2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+#ifdef FLOWCUDA_TRACE
+  const long long tr_entry = clock64();
+#endif
 
   if (warp == kMmaWarp) tc::tmem_alloc(tmem_slot, 2 * kDtBN);
   if (tid == kLoadWarp * 32) {
@@ -563,7 +566,7 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
         }
       }
 #ifdef FLOWCUDA_TRACE
-      if (g_dt_trace) g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + 3] = (unsigned long long)tr_wait;
+      (void)tr_wait;
 #endif
     }
   } else if (warp == kMmaWarp) {
@@ -628,6 +631,7 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
 #ifdef FLOWCUDA_TRACE
       if (g_dt_trace) {
         g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + 0] = (unsigned long long)(clock64() - tr_start);
+        g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + 3] = (unsigned long long)(tr_start - tr_entry);  // kernel entry -> issuer loop
         g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + 1] = (unsigned long long)tr_acc;
         g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + 2] = (unsigned long long)tr_full;
         g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + 6] = (unsigned long long)tr_items;
@@ -723,7 +727,7 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
       group_sync();
     }
 #ifdef FLOWCUDA_TRACE
-    if (g_dt_trace && lane == 0 && (warp == 0 || warp == EW)) g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + (warp == 0 ? 4 : 5)] = (unsigned long long)tr_wait;
+    if (g_dt_trace && lane == 0 && warp == 0) g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + 4] = (unsigned long long)tr_wait;
 #endif
   }
   tc::tc_fence_before();
@@ -731,6 +735,9 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
   if (warp == kMmaWarp) {
     __syncwarp();
     tc::tmem_dealloc(tmem, 2 * kDtBN);
+#ifdef FLOWCUDA_TRACE
+    if (g_dt_trace && lane == 0) g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + 5] = (unsigned long long)(clock64() - tr_entry);  // whole CTA
+#endif
   }
 }
 

@@ -11,8 +11,8 @@ from oracle import flows_oracle as O
 wl = sys.argv[1] if len(sys.argv) > 1 else "maf_mnist"
 lib = C.CDLL(_lib.LIB_PATH)
 buf = torch.zeros(2 * 148 * 8, dtype=torch.int64, device="cuda")  # [full-tile launches | n-half (hidden) launches]
-names = ["issuer cycles", "issuer waits accumulator", "issuer waits operands", "producer waits stage", "epilogue g0 waits acc",
-         "epilogue g1 waits acc", "items", "k stages"]
+names = ["issuer cycles", "issuer waits accumulator", "issuer waits operands", "entry -> issuer loop", "epilogue g0 waits acc",
+         "whole CTA (entry -> exit)", "items", "k stages"]
 
 def report(tag):
     torch.cuda.synchronize()
