@@ -282,6 +282,42 @@ __global__ void __launch_bounds__(128) tc_mma_timing_kernel(volatile long long* 
         ++rec;
       }
     }
+    // bf16 kind::f16 SS MMAs (K = 16) exactly as the D=784 GEMMs issue them: one descriptor pair per 32-K stage, six MMAs
+    // per stage (3 passes x 2 K steps) over three stage buffers, one accumulator; code 7000 + n_mma, N = 128 / 256
+    for (int ni = 0; ni < 2; ++ni) {
+      const int N = ni == 0 ? 128 : 256;
+      const uint32_t idesc = tc::make_idesc(tc::kFmtBF16, 128, N);
+      const uint32_t lbo_a = 16u * 128u, lbo_b = (uint32_t)(N >> 3) * 128u;
+      const uint32_t half_b = (uint32_t)N * 32u * 2u;  // bytes of one of hi/lo of a B stage
+      const uint32_t stage = 2u * 8192u + 2u * half_b;
+      for (int nm = 96; nm <= 192; nm += 96) {
+        uint32_t acc = 0;
+        long long t0 = clock64();
+        for (int m = 0; m < nm; m += 6) {
+          const uint32_t sa = tc::smem_u32(smem) + (uint32_t)((m / 6) % 3) * stage, sb = sa + 2u * 8192u;
+          const uint64_t da = tc::make_smem_desc(sa, lbo_a, 128u), db = tc::make_smem_desc(sb, lbo_b, 128u);
+#pragma unroll
+          for (int pass = 0; pass < 3; ++pass) {
+            const uint32_t ao = pass == 2 ? 8192u : 0u, bo = pass == 1 ? half_b : 0u;
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+              tc::mma_ss<tc::kFmtBF16>(tmem + 128u, da + ((ao + k * 2u * lbo_a) >> 4), db + ((bo + k * 2u * lbo_b) >> 4), idesc, acc);
+              acc = 1;
+            }
+          }
+        }
+        long long t1 = clock64();
+        tc::mma_commit(bar);
+        tc::mbar_wait(bar, phase);
+        phase ^= 1;
+        long long t2 = clock64();
+        out[4 * rec + 0] = N;
+        out[4 * rec + 1] = 7000 + nm;
+        out[4 * rec + 2] = t1 - t0;
+        out[4 * rec + 3] = t2 - t0;
+        ++rec;
+      }
+    }
     out[4 * rec] = -1;
   }
   __syncthreads();

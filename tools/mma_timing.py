@@ -14,5 +14,7 @@ i = 0
 while o[4 * i] != -1:
     N, code, ti, tt = o[4 * i:4 * i + 4]
     a = "smem" if code >= 100000 else "tmem"; code %= 100000
+    if code // 1000 == 7:
+        a = "bf16 SS as the D=784 GEMMs issue them (nacc column = 7)"
     print(f"{a}  {N:4d}  {code // 1000}  {code % 1000:4d}  {ti:7d}  {tt:7d}  {tt / (code % 1000):7.1f}")
     i += 1
