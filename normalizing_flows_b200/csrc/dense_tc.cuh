@@ -570,7 +570,11 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
 #endif
     }
   } else if (warp == kMmaWarp) {
-    if (lane == 0) {  // ===== MMA issuer: 3 passes x 2 K steps per stage
+    {  // ===== MMA issuer: 3 passes x 2 K steps per stage.  The WHOLE warp runs this loop, converged; the MMAs and commits
+       // are issued by its elected lane (tc::mma_ss_warp).  Inside `if (lane == 0)` the compiler wraps every tcgen05.mma —
+       // an instruction with uniform-register operands — in an ELECT / BRA.U.ANY loop and cannot keep the descriptors in
+       // uniform registers across it: the single thread then needs ~95 cycles per MMA (tools/mma_timing.py), more than
+       // the 64 tensor cycles of a 128-column MMA.
       constexpr uint32_t lbo_a = 16u * 128u;
       uint32_t it = 0;
       DtItem wi;
@@ -620,16 +624,16 @@ __global__ void __launch_bounds__(DtCfg<EPI, WIDE>::kThreads, 1) dense_tc_gemm_k
             const uint32_t ao = pass == 2 ? (uint32_t)kDtABytes : 0u, bo = pass == 1 ? b_lo : 0u;
 #pragma unroll
             for (int s = 0; s < kDtBK / 16; ++s) {
-              tc::mma_ss<tc::kFmtBF16>(dtm, da + ((ao + s * 2u * lbo_a) >> 4), db + ((bo + s * 2u * lbo_b) >> 4), idesc, acc);
+              tc::mma_ss_warp<tc::kFmtBF16>(dtm, da + ((ao + s * 2u * lbo_a) >> 4), db + ((bo + s * 2u * lbo_b) >> 4), idesc, acc);
               acc = 1;
             }
           }
-          tc::mma_commit(&empty[st]);
+          tc::mma_commit_warp(&empty[st]);
         }
-        tc::mma_commit(&acc_full[slot]);
+        tc::mma_commit_warp(&acc_full[slot]);
       }
 #ifdef FLOWCUDA_TRACE
-      if (g_dt_trace) {
+      if (g_dt_trace && lane == 0) {
         g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + 0] = (unsigned long long)(clock64() - tr_start);
         g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + 3] = (unsigned long long)(tr_start - tr_entry);  // kernel entry -> issuer loop
         g_dt_trace[(NH ? 148 * 8 : 0) + blockIdx.x * 8 + 1] = (unsigned long long)tr_acc;

@@ -163,6 +163,16 @@ __device__ __forceinline__ void mma_ts_warp(uint32_t d_tmem, uint32_t a_tmem, ui
         : "memory");
   }
 }
+// SS form of the same: executed by the WHOLE (converged) warp, issued by its elected lane
+template <uint32_t FMT>
+__device__ __forceinline__ void mma_ss_warp(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  static_assert(FMT == kFmtBF16, "bf16 / fp16 operands");
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\telect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 __device__ __forceinline__ void mma_commit_warp(uint64_t* bar) {
   asm volatile(
       "{\n\t.reg .pred q;\n\telect.sync _|q, 0xffffffff;\n\t"

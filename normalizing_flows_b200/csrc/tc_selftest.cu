@@ -214,6 +214,7 @@ __global__ void __launch_bounds__(128) tc_mma_timing_kernel(volatile long long* 
   if (warp == 0) tc::tmem_alloc(slot, 512);
   if (tid == 0) {
     tc::mbar_init(bar, 1);
+    tc::mbar_init(bar + 2, 1);
     tc::fence_mbar_init();
   }
   tc::fence_async_smem();
@@ -290,10 +291,13 @@ __global__ void __launch_bounds__(128) tc_mma_timing_kernel(volatile long long* 
       const uint32_t lbo_a = 16u * 128u, lbo_b = (uint32_t)(N >> 3) * 128u;
       const uint32_t half_b = (uint32_t)N * 32u * 2u;  // bytes of one of hi/lo of a B stage
       const uint32_t stage = 2u * 8192u + 2u * half_b;
+      for (int var = 0; var < 3; ++var)  // 0: MMAs only; 1: + tcgen05 fence and a commit per stage (to a second barrier); 2: + a satisfied try_wait per stage
       for (int nm = 96; nm <= 192; nm += 96) {
         uint32_t acc = 0;
         long long t0 = clock64();
         for (int m = 0; m < nm; m += 6) {
+          if (var >= 2) tc::mbar_wait(bar, phase ^ 1u);  // the previous phase: passes at once, costs the probe
+          if (var >= 1) tc::tc_fence_after();
           const uint32_t sa = tc::smem_u32(smem) + (uint32_t)((m / 6) % 3) * stage, sb = sa + 2u * 8192u;
           const uint64_t da = tc::make_smem_desc(sa, lbo_a, 128u), db = tc::make_smem_desc(sb, lbo_b, 128u);
 #pragma unroll
@@ -305,6 +309,7 @@ __global__ void __launch_bounds__(128) tc_mma_timing_kernel(volatile long long* 
               acc = 1;
             }
           }
+          if (var >= 1) tc::mma_commit(bar + 2);  // a barrier nobody waits on (count 1: phases just roll over)
         }
         long long t1 = clock64();
         tc::mma_commit(bar);
@@ -312,7 +317,7 @@ __global__ void __launch_bounds__(128) tc_mma_timing_kernel(volatile long long* 
         phase ^= 1;
         long long t2 = clock64();
         out[4 * rec + 0] = N;
-        out[4 * rec + 1] = 7000 + nm;
+        out[4 * rec + 1] = 7000 - 1000 * var + nm;
         out[4 * rec + 2] = t1 - t0;
         out[4 * rec + 3] = t2 - t0;
         ++rec;
