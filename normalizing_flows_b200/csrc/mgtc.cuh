@@ -159,7 +159,7 @@ static __global__ void __launch_bounds__(kMgTcThreads, 1) mgtc_gemm_kernel(MgTcA
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {  // ===== MMA issuer
+    {  // ===== MMA issuer: the whole warp runs the loop converged, its elected lane issues (dense_tc.cuh)
       constexpr uint32_t idesc = tc::make_idesc(tc::kFmtBF16, 128, kDtBN);
       constexpr uint32_t lbo_a = 16u * 128u, lbo_b = (uint32_t)(kDtBN >> 3) * 128u;
       uint32_t it = 0, tl = 0;
@@ -185,13 +185,13 @@ static __global__ void __launch_bounds__(kMgTcThreads, 1) mgtc_gemm_kernel(MgTcA
             const uint32_t ao = pass == 2 ? (uint32_t)kDtABytes : 0u, bo = pass == 1 ? (uint32_t)kDtBBytes : 0u;
 #pragma unroll
             for (int s = 0; s < kDtBK / 16; ++s) {
-              tc::mma_ss<tc::kFmtBF16>(dtm, da + ((ao + s * 2u * lbo_a) >> 4), db + ((bo + s * 2u * lbo_b) >> 4), idesc, acc);
+              tc::mma_ss_warp<tc::kFmtBF16>(dtm, da + ((ao + s * 2u * lbo_a) >> 4), db + ((bo + s * 2u * lbo_b) >> 4), idesc, acc);
               acc = 1;
             }
           }
-          tc::mma_commit(&empty[st]);
+          tc::mma_commit_warp(&empty[st]);
         }
-        tc::mma_commit(&acc_full[slot]);
+        tc::mma_commit_warp(&acc_full[slot]);
       }
     }
   } else {
