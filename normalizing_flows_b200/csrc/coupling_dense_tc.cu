@@ -83,6 +83,8 @@ struct DtLayout {
   int KS[FLOWCUDA_MAX_HIDDEN_LAYERS + 1], NT[FLOWCUDA_MAX_HIDDEN_LAYERS + 1];
   int64_t MT;
   size_t off_v, off_ld, off_ldp, off_x, off_h[2], off_w[FLOWCUDA_MAX_HIDDEN_LAYERS + 1], total;
+  size_t off_wc[FLOWCUDA_MAX_HIDDEN_LAYERS + 1];  // hidden Linears once more, in 128-row tiles (dense_tc_chain.cuh)
+  int chain_ok;                                   // every hidden Linear is 512 wide: the chain kernel can run
 };
 
 static bool dt_layout(const flowcuda_coupling_spec* sp, int64_t n, DtLayout& L) {
@@ -121,6 +123,14 @@ static bool dt_layout(const flowcuda_coupling_spec* sp, int64_t n, DtLayout& L) 
   for (int i = 0; i < L.nlin; ++i) {
     L.off_w[i] = off;
     off = dt_al256(off + (size_t)sp->num_layers * L.NT[i] * L.KS[i] * 2 * kDtBBytes);
+  }
+  // the hidden Linears' weights (3 MB per flow layer at the maf_mnist shape) are kept in BOTH tile heights, so that a
+  // workspace packed once serves calls of any batch size, whichever kernel they pick
+  L.chain_ok = nh >= 1 && nh <= kDcMaxLinears;
+  for (int i = 0; i < nh && L.chain_ok; ++i) L.chain_ok = L.sizes[i + 1] == 512;
+  for (int i = 0; i < L.nlin; ++i) {
+    L.off_wc[i] = off;
+    if (L.chain_ok && i < nh) off = dt_al256(off + (size_t)sp->num_layers * L.NT[i] * L.KS[i] * 2 * kDtBBytes);
   }
   L.off_v = off; off = dt_al256(off + (size_t)n * D * 4);
   L.off_ld = off; off = dt_al256(off + (size_t)n * 4);
@@ -164,23 +174,25 @@ static int dt_run(const flowcuda_coupling_spec* sp, const float* params, const f
   float* ld = (float*)(ws + L.off_ld);
   float* ldp = (float*)(ws + L.off_ldp);
   if (mode != 2) FC_CUDA(cudaMemcpyAsync(v, in, (size_t)n * D * sizeof(float), cudaMemcpyDeviceToDevice, s));
-  // the hidden Linears as one cluster kernel (dense_tc_chain.cuh) when every one is 512 wide; their weight images are
-  // then packed in 128-row tiles (one contiguous 16 KB stage per CTA).  The choice depends on the spec and the process
-  // environment only, so a workspace packed by flowcuda_coupling_pack_weights matches the later calls.
-  bool chain = dt_chain_enabled() && dt2_mode() == 1 && nh >= 1 && nh <= kDcMaxLinears;
-  for (int i = 0; i < nh && chain; ++i) chain = L.sizes[i + 1] == 512;
+  // the hidden Linears as one cluster kernel (dense_tc_chain.cuh) when every one is 512 wide and the batch is one wave
+  // of clusters; its weight images (128-row tiles) are packed beside the 256-row ones whenever the shapes allow it
+  const bool chain_pack = L.chain_ok && dt_chain_possible() && dt2_mode() == 1;
+  const bool chain = chain_pack && dt_chain_wanted(L.MT);
   // pack every Linear of every layer (masks folded in)
   for (int i = 0; i < L.nlin && mode != 1; ++i) {
-    DtPackW p;
-    p.tr = chain && i < nh ? 128 : kDtBN;
-    p.params = params; p.per_layer = L.per_layer; p.w_off = L.w_off[i];
-    p.k_in = L.sizes[i]; p.n_out = L.sizes[i + 1];
-    p.first = i == 0; p.kstride = i == 0 ? 2 : 1; p.kvalid = L.sizes[i];
-    p.dpt = i == nh ? L.dpt : 0; p.ppd = L.ppd; p.D = D;
-    p.KS = L.KS[i]; p.NT = L.NT[i] * (kDtBN / p.tr); p.img = ws + L.off_w[i];
-    int blocks = (L.KS[i] * 4 * p.tr + 255) / 256;
-    dense_tc_pack_w_kernel<<<dim3(blocks, p.NT, sp->num_layers), 256, 0, s>>>(p);
-    FC_LAUNCH_CHECK("dense_tc_pack_w_kernel");
+    for (int tr = kDtBN; tr >= 128; tr -= 128) {
+      if (tr == 128 && !(chain_pack && i < nh)) continue;
+      DtPackW p;
+      p.tr = tr;
+      p.params = params; p.per_layer = L.per_layer; p.w_off = L.w_off[i];
+      p.k_in = L.sizes[i]; p.n_out = L.sizes[i + 1];
+      p.first = i == 0; p.kstride = i == 0 ? 2 : 1; p.kvalid = L.sizes[i];
+      p.dpt = i == nh ? L.dpt : 0; p.ppd = L.ppd; p.D = D;
+      p.KS = L.KS[i]; p.NT = L.NT[i] * (kDtBN / p.tr); p.img = ws + (tr == 128 ? L.off_wc[i] : L.off_w[i]);
+      int blocks = (L.KS[i] * 4 * p.tr + 255) / 256;
+      dense_tc_pack_w_kernel<<<dim3(blocks, p.NT, sp->num_layers), 256, 0, s>>>(p);
+      FC_LAUNCH_CHECK("dense_tc_pack_w_kernel");
+    }
   }
   if (mode == 2) return FLOWCUDA_OK;
   const int nl = layer_end - layer_begin;
@@ -211,7 +223,7 @@ static int dt_run(const flowcuda_coupling_spec* sp, const float* params, const f
       c.nlin = nh; c.N = n; c.a_img0 = aimg;
       for (int i = 0; i < nh; ++i) {
         c.KS[i] = L.KS[i];
-        c.b_img[i] = ws + L.off_w[i] + (size_t)l * L.NT[i] * L.KS[i] * 2 * kDtBBytes;
+        c.b_img[i] = ws + L.off_wc[i] + (size_t)l * L.NT[i] * L.KS[i] * 2 * kDtBBytes;
         c.bias[i] = lp + L.b_off[i];
         c.out_img[i] = ws + L.off_h[i & 1];
         c.out_KS[i] = L.KS[i + 1];

@@ -37,6 +37,13 @@ __device__ __forceinline__ void mma_commit_mc(uint64_t* bar, uint16_t mask) {
                "h"(mask)
                : "memory");
 }
+__device__ __forceinline__ void mma_commit_mc_warp(uint64_t* bar, uint16_t mask) {  // whole warp executes, the elected lane commits
+  asm volatile(
+      "{\n\t.reg .pred q;\n\telect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}" ::"r"(smem_u32(bar)),
+      "h"(mask)
+      : "memory");
+}
 }  // namespace tc
 
 constexpr int kDcMaxLinears = FLOWCUDA_MAX_HIDDEN_LAYERS;
@@ -113,7 +120,7 @@ static __global__ void __launch_bounds__(kDcThreads, 1) dense_tc_chain_kernel(Dt
       }
       __syncwarp();
     } else if (warp == kMmaWarp) {
-      if (lane == 0) {  // ===== MMA issuer: 3 passes x 2 K steps per stage, N = 128
+      {  // ===== MMA issuer: 3 passes x 2 K steps per stage, N = 128; whole warp converged, the elected lane issues (dense_tc.cuh)
         tc::tc_fence_after();
         constexpr uint32_t idesc = tc::make_idesc(tc::kFmtBF16, 128, 128);
         constexpr uint32_t lbo = 16u * 128u;
@@ -129,13 +136,13 @@ static __global__ void __launch_bounds__(kDcThreads, 1) dense_tc_chain_kernel(Dt
             const uint32_t ao = pass == 2 ? (uint32_t)kDtABytes : 0u, bo = pass == 1 ? (uint32_t)kDtABytes : 0u;
 #pragma unroll
             for (int s = 0; s < kDtBK / 16; ++s) {
-              tc::mma_ss<tc::kFmtBF16>(tmem, da + ((ao + s * 2u * lbo) >> 4), db + ((bo + s * 2u * lbo) >> 4), idesc, acc);
+              tc::mma_ss_warp<tc::kFmtBF16>(tmem, da + ((ao + s * 2u * lbo) >> 4), db + ((bo + s * 2u * lbo) >> 4), idesc, acc);
               acc = 1;
             }
           }
-          tc::mma_commit_mc(&empty[st], (uint16_t)((1u << kDcCluster) - 1u));
+          tc::mma_commit_mc_warp(&empty[st], (uint16_t)((1u << kDcCluster) - 1u));
         }
-        tc::mma_commit(&acc_full[0]);
+        tc::mma_commit_warp(&acc_full[0]);
       }
       __syncwarp();
     } else {
@@ -168,16 +175,24 @@ static __global__ void __launch_bounds__(kDcThreads, 1) dense_tc_chain_kernel(Dt
   }
 }
 
-// Opt-in (FLOWCUDA_HIDDEN_CHAIN=1; read on every call so that tests can switch in-process).  Measured on B200 at the
-// maf_mnist shape (profiles/r02/README.md): the chain kernel takes 33 us against 3 x 13 us for the per-Linear kernels
-// in isolation, but under graph replay with programmatic dependent launch the step only moves 0.998 -> 0.990 ms, and at
-// batch 16384 (512 non-persistent CTAs in 4-CTA clusters) deep16_nvp goes 1.54 -> 2.06 ms.  Neither the nine bulk
-// copies per stage of the half-tile fetch (now one) nor L2 bandwidth (12 % in the capture; the multicast changes
-// nothing) is what bounds a hidden Linear: it is the dependent chain itself — first-stage latency, epilogue, barrier —
-// about 10 K cycles per Linear around 5 K cycles of MMAs.
-static bool dt_chain_enabled() {
+// When the chain kernel runs (FLOWCUDA_HIDDEN_CHAIN, read on every call so that tests can switch in-process:
+// unset = by batch size, "1" = whenever the shapes allow, "0" = never).  Measured on B200 (profiles/r02/README.md):
+// at the maf_mnist bench shape (batch 4096: 32 clusters, one wave) the step goes 0.998 -> 0.953 ms; at batch 16384 /
+// 32768 the grid is several waves of non-persistent clusters and the per-Linear kernels, throughput-bound there, win
+// (deep16_nvp 1.54 -> 1.84 ms, maf_mnist_b32768 6.93 -> 7.38 ms).  Default: one wave only.
+// History worth keeping: with the MMAs issued from single-thread code (~95 cycles per narrow MMA, issue-bound) this
+// kernel was no faster than the three launches it replaces; the multicast and the single-copy weight stage only paid
+// once the issue loop ran warp-converged (tc::mma_ss_warp).
+static int dt_chain_mode() {
   const char* e = getenv("FLOWCUDA_HIDDEN_CHAIN");
-  return e && e[0] == '1';
+  if (e && e[0] == '1') return 1;
+  if (e && e[0] == '0') return 0;
+  return -1;
+}
+static bool dt_chain_possible() { return dt_chain_mode() != 0; }  // are the 128-row weight images packed at all
+static bool dt_chain_wanted(int64_t MT) {
+  const int m = dt_chain_mode();
+  return m == 1 || (m < 0 && MT * kDcCluster <= sm_count());
 }
 
 static int dt_launch_chain(const DtChain& c, int64_t MT, cudaStream_t s) {

@@ -157,7 +157,8 @@ def test_dense_coupling_cta_pair_kernels(case, mode, monkeypatch):
 
 
 def test_hidden_chain_cluster_kernel_matches_per_linear_kernels(monkeypatch):
-    """FLOWCUDA_HIDDEN_CHAIN=1: the three 512-wide hidden Linears of a conditioner as one 4-CTA-cluster kernel with the
+    """The three 512-wide hidden Linears of a conditioner as one 4-CTA-cluster kernel (default at batches of one wave of
+    clusters; FLOWCUDA_HIDDEN_CHAIN = 0 / 1 forces never / always) with the
     activation stage multicast and the weight images in 128-row tiles (csrc/dense_tc_chain.cuh) — same products in the
     same order as the per-Linear kernels, so log_prob, z and the gradient must be the same bits; ragged batch
     (three m tiles, the last one partial) and the prepared-weights path included."""
@@ -168,6 +169,7 @@ def test_hidden_chain_cluster_kernel_matches_per_linear_kernels(monkeypatch):
     spec = _spec_pair(ops, ospec, precision=_lib.PRECISION_BF16X3)
     x = torch.rand(300, 784, generator=torch.Generator().manual_seed(4), dtype=torch.float64).float().cuda()
     p = G(flat)
+    monkeypatch.setenv("FLOWCUDA_HIDDEN_CHAIN", "0")  # per-Linear kernels (the default above one wave of clusters)
     lp0, z0, _ = ops.coupling_log_prob(spec, p, x, want_z=True, want_log_det=True)
     loss0, grad0 = ops.coupling_nll_grad(spec, p, x)
     monkeypatch.setenv("FLOWCUDA_HIDDEN_CHAIN", "1")
@@ -175,6 +177,14 @@ def test_hidden_chain_cluster_kernel_matches_per_linear_kernels(monkeypatch):
     loss1, grad1 = ops.coupling_nll_grad(spec, p, x)
     assert torch.equal(lp0, lp1) and torch.equal(z0, z1)
     assert torch.equal(loss0, loss1) and torch.equal(grad0, grad1)
+    monkeypatch.delenv("FLOWCUDA_HIDDEN_CHAIN")  # default: by batch size — a workspace prepared once serves both kernels
+    model_p = ops.coupling_pack_weights(spec, p, max_batch=20000) if hasattr(ops, "coupling_pack_weights") else None
+    if model_p is not None:
+        for n in (300, 20000):  # one wave of clusters -> chain kernel; 157 m tiles -> per-Linear kernels
+            xb = torch.rand(n, 784, generator=torch.Generator().manual_seed(n), dtype=torch.float64).float().cuda()
+            a, _, _ = ops.coupling_log_prob(spec, p, xb, packed=model_p)
+            b, _, _ = ops.coupling_log_prob(spec, p, xb)
+            assert torch.equal(a, b)
 
 
 def test_dense_coupling_bf16x3_mnist_shape():
