@@ -16,7 +16,7 @@
 // consumed it: the MMA completion is multicast to the `empty` barrier of every CTA (count 4).
 //
 // Cross-proxy ordering: the image quarters are written with generic-proxy stores and read back by cp.async.bulk (async
-// proxy) of ALL four CTAs — every writer issues fence.proxy.async before it arrives at the cluster barrier
+// proxy) of ALL four CTAs — every writer issues fence.proxy.async.global (the unqualified form adds a CTA-wide membar: 8 % of the kernel) before it arrives at the cluster barrier
 // (arrive.release / wait.acquire), and the producer thread issues it again after the wait.
 #pragma once
 #include "dense_tc2.cuh"
@@ -101,7 +101,7 @@ static __global__ void __launch_bounds__(kDcThreads, 1) dense_tc_chain_kernel(Dt
     const int KS = a.KS[l];
     if (warp == kLoadWarp) {
       if (lane == 0) {  // ===== TMA producer
-        if (l > 0) asm volatile("fence.proxy.async;" ::: "memory");
+        if (l > 0) asm volatile("fence.proxy.async.global;" ::: "memory");
         const uint8_t* ag = (l == 0 ? a.a_img0 : a.out_img[l - 1]) + (int64_t)mt * KS * 2 * kDtABytes;
         const uint8_t* bg = a.b_img[l] + (int64_t)part * KS * kDtBBytes;  // this CTA's 128-row tile: 16 KB (hi|lo) per stage
         uint32_t p = it;
@@ -162,7 +162,7 @@ static __global__ void __launch_bounds__(kDcThreads, 1) dense_tc_chain_kernel(Dt
       const int c_lo = cshift + (warp >> 2) * 64;
       dt_epilogue<kEpiHidden, false>(g, mt, nt, tb, sbias, nullptr, warp, lane, c_lo, c_lo + 64, cshift);
       tc::tc_fence_before();
-      asm volatile("fence.proxy.async;" ::: "memory");  // the image quarter is read back through the async proxy
+      asm volatile("fence.proxy.async.global;" ::: "memory");  // the image quarter (global memory) is read back through the async proxy
     }
     it += (uint32_t)KS;
     if (l + 1 < a.nlin) tc::cluster_sync_all();  // all four quarters of the next operand image are in place
