@@ -206,7 +206,9 @@ class MafMnist(CouplingWorkload):
     bound = "tensor"
     launches_per_step = 8 * 5 + 1
     tc_precision = 3          # FLOWCUDA_PRECISION_BF16X3
-    tc_launches = 4 + 1 + 8 * 4 + 1  # weight packs + first activation pack + per layer 4 GEMMs (fused epilogues) + finish
+    # weight packs + first activation pack + per layer the hidden chain kernel and the transform GEMM (one wave of
+    # clusters at this batch) + finish
+    tc_launches = 4 + 1 + 8 * 2 + 1
     tc_dtype = "bf16x3 (fp32 accumulate)"
     cpu_sample = 256
 
@@ -218,6 +220,7 @@ class MafMnistLarge(MafMnist):
     name = "maf_mnist_b32768"
     desc = MafMnist.desc.replace("4096 samples/GPU", "32768 samples/GPU")
     n = 32768
+    tc_launches = 4 + 1 + 8 * 4 + 1  # above one wave of clusters the hidden Linears run as three GEMM launches per layer
 
 
 class Deep16Nvp(CouplingWorkload):

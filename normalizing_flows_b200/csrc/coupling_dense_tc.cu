@@ -31,7 +31,8 @@ struct DtPackW {
   int dpt, ppd, D;       // last Linear: dims per tile, params per dim (dpt = 0: plain columns); D = event dim
   int KS, NT;            // k stages, n tiles
   uint8_t* img;          // [layer][NT][KS][hi|lo][tr rows x 64 B]
-  int tr;                // rows per n tile of the image: 256 (dense_tc_gemm_kernel) or 128 (hidden Linears for dense_tc_chain_kernel)
+  int tr;                // rows per n tile of the image: 256 (dense_tc_gemm_kernel)
+  uint8_t* img128;       // hidden Linears: the same weights once more in 128-row tiles (dense_tc_chain_kernel), or NULL
 };
 
 // grid (blocks, NT, layers)
@@ -72,6 +73,12 @@ __global__ void __launch_bounds__(256) dense_tc_pack_w_kernel(DtPackW a) {
     uint8_t* st = base + (int64_t)(ck >> 2) * 2 * half + tc::img_off(TR, n, ck & 3);
     *reinterpret_cast<uint4*>(st) = make_uint4(h[0], h[1], h[2], h[3]);
     *reinterpret_cast<uint4*>(st + half) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    if (a.img128 != nullptr) {  // tile (2 nt + n / 128) of twice as many 128-row tiles, same K chunk
+      const int64_t half2 = (int64_t)128 * kDtBK * 2;
+      uint8_t* s2 = a.img128 + (((int64_t)l * 2 * a.NT + 2 * nt + (n >> 7)) * a.KS + (ck >> 2)) * 2 * half2 + tc::img_off(128, n & 127, ck & 3);
+      *reinterpret_cast<uint4*>(s2) = make_uint4(h[0], h[1], h[2], h[3]);
+      *reinterpret_cast<uint4*>(s2 + half2) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+    }
   }
 }
 
@@ -180,19 +187,17 @@ static int dt_run(const flowcuda_coupling_spec* sp, const float* params, const f
   const bool chain = chain_pack && dt_chain_wanted(L.MT);
   // pack every Linear of every layer (masks folded in)
   for (int i = 0; i < L.nlin && mode != 1; ++i) {
-    for (int tr = kDtBN; tr >= 128; tr -= 128) {
-      if (tr == 128 && !(chain_pack && i < nh)) continue;
-      DtPackW p;
-      p.tr = tr;
-      p.params = params; p.per_layer = L.per_layer; p.w_off = L.w_off[i];
-      p.k_in = L.sizes[i]; p.n_out = L.sizes[i + 1];
-      p.first = i == 0; p.kstride = i == 0 ? 2 : 1; p.kvalid = L.sizes[i];
-      p.dpt = i == nh ? L.dpt : 0; p.ppd = L.ppd; p.D = D;
-      p.KS = L.KS[i]; p.NT = L.NT[i] * (kDtBN / p.tr); p.img = ws + (tr == 128 ? L.off_wc[i] : L.off_w[i]);
-      int blocks = (L.KS[i] * 4 * p.tr + 255) / 256;
-      dense_tc_pack_w_kernel<<<dim3(blocks, p.NT, sp->num_layers), 256, 0, s>>>(p);
-      FC_LAUNCH_CHECK("dense_tc_pack_w_kernel");
-    }
+    DtPackW p;
+    p.tr = kDtBN;
+    p.params = params; p.per_layer = L.per_layer; p.w_off = L.w_off[i];
+    p.k_in = L.sizes[i]; p.n_out = L.sizes[i + 1];
+    p.first = i == 0; p.kstride = i == 0 ? 2 : 1; p.kvalid = L.sizes[i];
+    p.dpt = i == nh ? L.dpt : 0; p.ppd = L.ppd; p.D = D;
+    p.KS = L.KS[i]; p.NT = L.NT[i]; p.img = ws + L.off_w[i];
+    p.img128 = chain_pack && i < nh ? ws + L.off_wc[i] : nullptr;  // both tile heights from the one pass over the weights
+    int blocks = (L.KS[i] * 4 * kDtBN + 255) / 256;
+    dense_tc_pack_w_kernel<<<dim3(blocks, L.NT[i], sp->num_layers), 256, 0, s>>>(p);
+    FC_LAUNCH_CHECK("dense_tc_pack_w_kernel");
   }
   if (mode == 2) return FLOWCUDA_OK;
   const int nl = layer_end - layer_begin;
