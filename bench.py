@@ -1017,8 +1017,42 @@ def time_train(w, dev, rank, world, dist, ops, K=5, batch=1 << 18):
         t = torch.tensor([ms], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = t.item()
+    final_loss = float(loss.item())
+    # one GPU, wide flows: the same step with value_and_grad replayed from a CUDA graph (one per distinct batch; the C
+    # call is capturable, tests/test_gpu_grad.py) and Adam launched after it — reported beside the eager figure, which
+    # stays `value` because the multi-GPU step (host callbacks per layer) cannot be replayed
+    replay_ms = None
+    if dist is None and tc:
+        try:
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            caps = []
+            for x in xs:
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=side):
+                    lg = ops.coupling_nll_grad(spec, p, x)
+                caps.append((g, lg))
+            torch.cuda.current_stream().wait_stream(side)
+
+            def rstep(i):
+                g, (_, grad) = caps[i % len(caps)]
+                g.replay()
+                ops.adam_step(p, grad, m, v, i + 1, 1e-4, grad_scale=1.0)
+
+            for i in range(2):
+                rstep(2 + K + i)
+            torch.cuda.synchronize()
+            e0.record()
+            for i in range(K):
+                rstep(4 + K + i)
+            e1.record()
+            torch.cuda.synchronize()
+            replay_ms = e0.elapsed_time(e1) / K
+        except Exception as e:  # noqa: BLE001 - the eager figure stands on its own
+            replay_ms = None
+            print("train graph replay not measured: %r" % (e,), file=sys.stderr)
     return {"value": batch * world * K / (ms * 1e-3), "unit": "samples/s", "batch_per_gpu": batch, "steps": K,
-            "ms_per_step": ms / K, "final_loss": float(loss.item()), "optimizer": "adam(1e-4)",
+            "ms_per_step": ms / K, "graph_replay_ms_per_step": replay_ms, "final_loss": final_loss, "optimizer": "adam(1e-4)",
             "grad_allreduce_bytes": int(p.numel() * 4) if dist is not None else 0,
             "grad_allreduce": ("one NCCL sum all-reduce per flow layer (%d buckets), each followed by that layer's Adam update, overlapped with the reverse mode" % sp.num_layers)
             if dist is not None else None,

@@ -193,3 +193,40 @@ def test_layer_hook_reports_every_layer_and_changes_nothing():
     calls = []
     ops.coupling_nll_grad(_spec_pair(ops, ospec), G(flat), torch.randn(300, 2).cuda(), on_layer=lambda l, g, st: calls.append(l))
     assert calls == list(range(ospec.num_layers))
+
+
+def test_nll_grad_can_be_captured_in_a_cuda_graph():
+    """flowcuda_coupling_nll_grad forks its weight-gradient jobs onto an internal stream and joins them by events, keeps
+    no host state between calls and allocates nothing: a caller may capture it (torch.cuda.graph here, an XLA command
+    buffer behind the FFI adapter) and replay it.  The replayed loss and gradient are the eager call's bits, also after
+    the parameters have been updated in place between replays (tools/train_graph.py times the replayed step)."""
+    from normalizing_flows_b200 import _lib, ops
+
+    for case, prec in (("rqs_mnist_shape", _lib.PRECISION_BF16X3), ("rqs_d40_uniform", _lib.PRECISION_BF16X3), ("rqs_d7_k8", 0)):
+        ospec, scale, xs, n = DENSE_GRAD[case]
+        flat = O.flatten_layers(O.init_coupling_params(ospec, seed=5, scale=scale))
+        g = torch.Generator().manual_seed(3)
+        if ospec.base == "uniform":
+            x = torch.rand(n, ospec.event_dim, generator=g, dtype=torch.float64).float().cuda()
+        else:
+            x = (torch.randn(n, ospec.event_dim, generator=g, dtype=torch.float64) * xs).float().cuda()
+        spec = _spec_pair(ops, ospec, precision=prec)
+        p = G(flat)
+        loss0, grad0 = ops.coupling_nll_grad(spec, p, x)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            loss1, grad1 = ops.coupling_nll_grad(spec, p, x)
+        torch.cuda.current_stream().wait_stream(side)
+        for _ in range(2):
+            grad1.zero_()
+            graph.replay()
+            torch.cuda.synchronize()
+            assert torch.equal(loss0, loss1) and torch.equal(grad0, grad1), case
+        p.add_(grad0, alpha=-1e-3)  # the graph reads the parameters where they live
+        loss2, grad2 = ops.coupling_nll_grad(spec, p, x)
+        graph.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(loss2, loss1) and torch.equal(grad2, grad1), case
+        assert not torch.equal(grad0, grad1)
