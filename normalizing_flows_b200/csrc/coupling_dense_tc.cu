@@ -251,7 +251,11 @@ static int dt_run(const flowcuda_coupling_spec* sp, const float* params, const f
       g.tiles = 4 * L.tiles; g.lo = sp->range_min; g.hi = sp->range_max;
       for (int i = 0; i < 9; ++i) g.koff[i] = sp->range_min + (float)i * kRqsMinBin;
       int rc;
-      const Dt2Launch dl = {L.MT, (int64_t)sp->num_layers * L.NT[i], (int64_t)l * L.NT[i]};
+      // CTA pairs for the RQS transform Linear (its single-CTA form outruns the L2 feed) and for hidden Linears of
+      // batches beyond the chain kernel's one wave (density / sampling passes; the training forward keeps the kernels
+      // it was measured with); single CTAs for the affine output Linear (dense_tc2.cuh, dt2_mode)
+      const bool pairs = i == nh ? sp->transform == FLOWCUDA_TRANSFORM_RQS : (tr == nullptr && L.MT * 4 > sm_count());
+      const Dt2Launch dl = {L.MT, (int64_t)sp->num_layers * L.NT[i], (int64_t)l * L.NT[i], pairs ? 2 : 1};
       if (tr) {
         float* blk = tr->act + (size_t)l * tr->per_layer_act + tr->act_h[i];
         if (i < nh) { g.store_h = blk; g.store_ld = L.sizes[i + 1]; }

@@ -412,6 +412,7 @@ struct Dt2Launch {
   int64_t a_mt;
   int64_t b_tiles;
   int64_t b_tile0;
+  int prefer;  // kernel of this launch when FLOWCUDA_DENSE_TC is unset: 2 = CTA pairs, anything else = single CTAs (dt2_mode)
 };
 
 template <int EPI, bool INV, bool WIDE, int CL>
@@ -468,23 +469,28 @@ static int dt2_launch_w(const DtGemm& g, const Dt2Launch& L, int64_t MT, int NT,
   return FLOWCUDA_OK;
 }
 
-// Which kernel a launch takes.  Default: the single-CTA kernel (dense_tc.cuh) — measured on B200 (profiles/r02/
-// gemm_modes_*.log, ncu_mnist_{1cta,pair}) the D=784 GEMMs were never operand-feed bound (L2 throughput 41 % with the
-// tensor pipe 68 % active; the spline epilogue and the launch-latency chain of the hidden Linears were the limits), and
-// pairing CTAs couples two epilogues to one MMA stream: the pair kernel runs the maf_mnist step in 1.12 ms, the 4-CTA
-// multicast clusters in 1.16 ms, the single-CTA kernel in 1.03 ms.  FLOWCUDA_DENSE_TC = "pair" / "quad" selects the
-// CTA-pair kernels (tests/test_gpu_tc.py runs the parity cases through both).
-static inline int dt2_mode() {
+// Which kernel a launch takes.  FLOWCUDA_DENSE_TC = "pair" / "quad" / "1cta" forces the CTA-pair kernel, the 4-CTA
+// multicast clusters or the single-CTA kernel (dense_tc.cuh) for every launch (tests/test_gpu_tc.py runs the parity cases
+// through all of them); unset, the caller's preference (Dt2Launch::prefer) decides.  Measured on B200 at the end of
+// round 2 (profiles/r02/gemm_modes_final.log), once the single-CTA kernel's issue loop and epilogue had been brought to
+// the MMA rate: the RQS transform Linear [n,512]x[512,9800] reads 64 B per clock and SM as single CTAs — 9.5 KB per
+// clock over the chip, above what the L2 slices deliver — and 43 B as pairs (each CTA stages half of B): pairs for that
+// launch alone run the maf_mnist step in 0.914 instead of 0.940 ms (batch 32768: 6.47 vs 6.92 ms).  The affine output
+// Linear of deep16_nvp is slower as pairs (1.67 vs 1.55 ms: a 784-column output is 4 n tiles, pairs halve the
+// parallelism), the hidden Linears gain as pairs only where the cluster chain kernel does not run (batch 16384 /
+// 32768: +2-3 %), and the MADE Linears (masked K ranges) were slower as pairs all round: those callers prefer 1.
+static inline int dt2_mode(int prefer = 1) {
   // read on every call (a getenv is nothing next to a launch) so that tests can switch kernels in-process
   const char* e = getenv("FLOWCUDA_DENSE_TC");
   if (e && e[0] == 'p') return 2;
   if (e && e[0] == 'q') return 4;
-  return 1;
+  if (e && e[0] == '1') return 1;
+  return prefer == 2 ? 2 : 1;
 }
 
 template <int EPI, bool INV>
 static int dt2_launch_gemm(const DtGemm& g, const Dt2Launch& L, int64_t MT, int NT, cudaStream_t s) {
-  const int mode = dt2_mode();
+  const int mode = dt2_mode(L.prefer);
   if (mode == 1) return dt_launch_gemm<EPI, INV>(g, MT, NT, s);
   const bool quad = mode == 4 && NT >= 2;
   const int64_t MTP = (MT + 1) / 2;

@@ -228,7 +228,7 @@ static int made_log_prob_run(const flowcuda_made_spec* sp, const float* params, 
       g.tiles = 4 * L.tiles; g.made = 1; g.rev = rev ? 1 : 0;
       for (int t = 0; t < L.NT[i] && t < kDtMaxKsTiles; ++t) g.ks_tile[t] = (unsigned char)made_ks_needed(L, i, t, rev);
       int rc;
-      const Dt2Launch dl = {L.MT, (int64_t)sp->num_layers * L.NT[i], (int64_t)l * L.NT[i]};
+      const Dt2Launch dl = {L.MT, (int64_t)sp->num_layers * L.NT[i], (int64_t)l * L.NT[i], 1};  // single CTAs: measured faster here
       if (i < nh) {
         g.out_img = ws + L.off_h[i & 1];
         g.out_KS = L.KS[i + 1];

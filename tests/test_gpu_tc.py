@@ -134,7 +134,8 @@ def test_dense_coupling_bf16x3_parity(case, n):
 @pytest.mark.parametrize("case", ["rqs_d40_uniform", "affine_d300", "rqs_d50_wide"])
 def test_dense_coupling_cta_pair_kernels(case, mode, monkeypatch):
     """The same flows through the CTA-pair GEMM (tcgen05 cta_group::2, tensor-map TMA; `quad`: 4-CTA clusters with the A
-    operand multicast) — csrc/dense_tc2.cuh; FLOWCUDA_DENSE_TC selects it per call."""
+    operand multicast) — csrc/dense_tc2.cuh; FLOWCUDA_DENSE_TC forces one kernel for every launch, unset the driver
+    takes pairs for the RQS transform Linear and for hidden Linears of multi-wave batches."""
     from normalizing_flows_b200 import _lib, ops
 
     monkeypatch.setenv("FLOWCUDA_DENSE_TC", mode)
@@ -151,9 +152,14 @@ def test_dense_coupling_cta_pair_kernels(case, mode, monkeypatch):
     close(lp, O.coupling_flow_log_prob(ospec, params, x.double()).numpy(), tol=2e-4, what="log_prob", nonfinite="equal")
     close(z, zref.numpy(), tol=2e-4, what="z")
     close(ld, ldref.numpy(), tol=2e-4, what="log_det")
-    monkeypatch.delenv("FLOWCUDA_DENSE_TC")
+    xsamp, _ = ops.coupling_sample(spec, G(flat), x.cuda())  # the inverse epilogues of the same kernels
+    close(xsamp, O.coupling_flow_sample(ospec, params, x.double()).numpy(), tol=2e-4, what="sample")
+    monkeypatch.setenv("FLOWCUDA_DENSE_TC", "1cta")
     lp1, _, _ = ops.coupling_log_prob(spec, G(flat), x.cuda())
     assert (lp1 - lp).abs().max().item() <= 1e-5 * max(1.0, lp.abs().max().item())  # same arithmetic, other tiling
+    monkeypatch.delenv("FLOWCUDA_DENSE_TC")  # the default policy: pairs for the RQS transform Linear only at this size
+    lp2, _, _ = ops.coupling_log_prob(spec, G(flat), x.cuda())
+    assert (lp2 - lp).abs().max().item() <= 1e-5 * max(1.0, lp.abs().max().item())
 
 
 def test_hidden_chain_cluster_kernel_matches_per_linear_kernels(monkeypatch):
