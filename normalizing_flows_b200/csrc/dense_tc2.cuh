@@ -115,6 +115,22 @@ __device__ __forceinline__ void mma2_commit_mc(uint64_t* bar, uint16_t mask) {
                "h"(mask)
                : "memory");
 }
+// the same two, executed by the WHOLE converged warp and issued by its elected lane (tc::mma_ss_warp: inside single-thread
+// code every tcgen05.mma is wrapped in an ELECT / BRA.U.ANY loop and its uniform operands are rebuilt)
+__device__ __forceinline__ void mma2_ss_warp(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\telect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void mma2_commit_mc_warp(uint64_t* bar, uint16_t mask) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\telect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n\t}" ::"r"(smem_u32(bar)),
+      "h"(mask)
+      : "memory");
+}
 
 }  // namespace tc
 
@@ -241,7 +257,8 @@ dense_tc2_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       }
     }
   } else if (warp == kMmaWarp) {
-    if (lane == 0 && prank == 0) {  // ===== MMA issuer (pair leader): 3 passes x 2 K steps per stage, M = 256 over the pair
+    if (prank == 0) {  // ===== MMA issuer (pair leader): 3 passes x 2 K steps per stage, M = 256 over the pair; the whole
+                       // warp runs the loop converged, its elected lane issues (as in dense_tc.cuh)
       constexpr uint32_t idesc = tc::make_idesc(tc::kFmtBF16, 256, kDtBN);
       constexpr uint32_t lbo = 16u * 128u;  // both operands are 128-row images in each CTA
       constexpr uint16_t kAll = (uint16_t)((1u << CL) - 1u);
@@ -260,19 +277,20 @@ dense_tc2_gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           tc::mbar_wait(&full[st], ph);
           tc::tc_fence_after();
           const uint32_t sa = tc::smem_u32(stages + st * kDt2StageBytes), sb = sa + kDt2AStage;
+          // one descriptor pair per stage; the six MMAs add their operand offsets (>> 4) to the start-address field
+          const uint64_t da = tc::make_smem_desc(sa, lbo, 128u), db = tc::make_smem_desc(sb, lbo, 128u);
 #pragma unroll
           for (int pass = 0; pass < 3; ++pass) {
-            const uint32_t ab = sa + (pass == 2 ? kDtABytes : 0), bb = sb + (pass == 1 ? kDtABytes : 0);
+            const uint32_t ao = pass == 2 ? (uint32_t)kDtABytes : 0u, bo = pass == 1 ? (uint32_t)kDtABytes : 0u;
 #pragma unroll
             for (int s = 0; s < kDtBK / 16; ++s) {
-              tc::mma2_ss_bf16(dtm, tc::make_smem_desc(ab + s * 2u * lbo, lbo, 128u), tc::make_smem_desc(bb + s * 2u * lbo, lbo, 128u),
-                               idesc, acc);
+              tc::mma2_ss_warp(dtm, da + ((ao + s * 2u * lbo) >> 4), db + ((bo + s * 2u * lbo) >> 4), idesc, acc);
               acc = 1;
             }
           }
-          tc::mma2_commit_mc(&empty[st], kAll);  // the stage is free in every CTA of the cluster once these MMAs are done
+          tc::mma2_commit_mc_warp(&empty[st], kAll);  // the stage is free in every CTA of the cluster once these MMAs are done
         }
-        tc::mma2_commit_mc(&acc_full[slot], kPair);
+        tc::mma2_commit_mc_warp(&acc_full[slot], kPair);
       }
     }
   } else {
